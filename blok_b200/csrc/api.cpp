@@ -1,0 +1,326 @@
+// C-ABI implementation (include/blokb200.h): context, scene upload, frame constants, dispatch, readback.
+// Host C++20; device work lives in kernels.cu. Every CUDA call is checked; nothing here falls back to the CPU.
+#include <cuda_runtime.h>
+
+#include <chrono>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/blokb200.h"
+#include "kernels.h"
+#include "scene_build.h"
+
+using namespace blokb;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define CK(expr)                                                                                          \
+    do {                                                                                                  \
+        cudaError_t e_ = (expr);                                                                          \
+        if (e_ != cudaSuccess) return fail(BLOKB_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+struct blokb_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    // world
+    bool haveWorld = false;
+    DeviceWorld dw{};
+    std::vector<void*> worldAllocs;
+    blokb_world_stats stats{};
+    // frame
+    bool haveFrame = false;
+    FrameDev frame{};
+    blokb_buffers buf{};
+    // scratch for host-ray calls
+    float* dRays = nullptr;
+    blokb_hit* dHits = nullptr;
+    size_t rayCap = 0;
+    unsigned long long* dStats = nullptr;  // 2 counters when stats enabled
+    bool statsOn = false;
+    uint64_t launches = 0;
+};
+
+static void free_world(blokb_ctx* c) {
+    for (void* p : c->worldAllocs) cudaFree(p);
+    c->worldAllocs.clear();
+    c->haveWorld = false;
+}
+static void free_images(blokb_ctx* c) {
+    void* ps[] = {c->buf.hit, c->buf.shadow, c->buf.color, c->buf.worldPos, c->buf.normalRough, c->buf.albedoMetal, c->buf.motion, c->buf.accum};
+    for (void* p : ps) if (p) cudaFree(p);
+    c->buf = blokb_buffers{};
+}
+
+template <class T>
+static int upload_vec(blokb_ctx* c, const std::vector<T>& v, const T** out) {
+    void* d = nullptr;
+    const size_t bytes = std::max<size_t>(v.size() * sizeof(T), 16);
+    CK(cudaMalloc(&d, bytes));
+    c->worldAllocs.push_back(d);
+    if (!v.empty()) CK(cudaMemcpyAsync(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+    *out = static_cast<const T*>(d);
+    return 0;
+}
+
+extern "C" {
+
+const char* blokb_last_error(void) { return g_err.c_str(); }
+
+int blokb_create(int device, blokb_ctx** out) {
+    if (!out) return fail(BLOKB_E_ARG, "out is null");
+    *out = nullptr;
+    int n = 0;
+    CK(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return fail(BLOKB_E_CUDA, "no such CUDA device");
+    CK(cudaSetDevice(device));
+    blokb_ctx* c = new (std::nothrow) blokb_ctx;
+    if (!c) return fail(BLOKB_E_ARG, "out of host memory");
+    c->device = device;
+    cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { delete c; return fail(BLOKB_E_CUDA, cudaGetErrorString(e)); }
+    e = cudaMalloc(&c->dStats, 4 * sizeof(unsigned long long));
+    if (e != cudaSuccess) { cudaStreamDestroy(c->stream); delete c; return fail(BLOKB_E_CUDA, cudaGetErrorString(e)); }
+    cudaMemset(c->dStats, 0, 4 * sizeof(unsigned long long));
+    *out = c;
+    return 0;
+}
+
+void blokb_destroy(blokb_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    free_world(c);
+    free_images(c);
+    if (c->dRays) cudaFree(c->dRays);
+    if (c->dHits) cudaFree(c->dHits);
+    if (c->dStats) cudaFree(c->dStats);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int blokb_upload_world(blokb_ctx* c, const blokb_svo_node* nodes, size_t nNodes, const blokb_subchunk* subs, size_t nSubs,
+                       const blokb_material* materials, size_t nMaterials) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    if ((nNodes && !nodes) || (nSubs && !subs) || (nMaterials && !materials)) return fail(BLOKB_E_ARG, "null array with non-zero count");
+    CK(cudaSetDevice(c->device));
+    const auto t0 = std::chrono::steady_clock::now();
+    HostWorld hw;
+    std::string err;
+    int rc = build_host_world(nodes, nNodes, subs, nSubs, hw, err);
+    if (rc) return fail(rc, err);
+    const auto t1 = std::chrono::steady_clock::now();
+    CK(cudaStreamSynchronize(c->stream));  // updateWorld waits idle before replacing buffers (renderer.hpp:55-71)
+    free_world(c);
+    DeviceWorld& d = c->dw;
+    d = DeviceWorld{};
+    for (int a = 0; a < 3; a++) { d.origin[a] = hw.origin[a]; d.dim[a] = hw.dim[a]; }
+    d.levels = hw.levels;
+    d.matWide = hw.matWide ? 1 : 0;
+    for (int k = 3; k <= hw.levels; k++) {
+        if ((rc = upload_vec(c, hw.dense[k], &d.dense[k]))) return rc;
+        for (int a = 0; a < 3; a++) d.denseDim[k][a] = hw.denseDim[k][a];
+    }
+    if ((rc = upload_vec(c, hw.topGrid, &d.topGrid))) return rc;
+    if ((rc = upload_vec(c, hw.subs, &d.subs))) return rc;
+    if ((rc = upload_vec(c, hw.bricks, &d.bricks))) return rc;
+    if ((rc = upload_vec(c, hw.blockFirstLeaf, &d.blockFirstLeaf))) return rc;
+    if (hw.matWide) { const uint32_t* p; if ((rc = upload_vec(c, hw.mat32, &p))) return rc; d.voxelMat = p; }
+    else { const uint16_t* p; if ((rc = upload_vec(c, hw.mat16, &p))) return rc; d.voxelMat = p; }
+    {
+        // hit.rchit clamps the index to 65535 and reads whatever is there; keep reads in bounds with a default tail entry
+        std::vector<blokb_material> m(materials, materials + nMaterials);
+        if (m.empty()) { blokb_material def{{0.8f, 0.8f, 0.8f}, (127u << 16), {0, 0, 0}, 0.f}; m.push_back(def); }
+        const blokb_material* p;
+        if ((rc = upload_vec(c, m, &p))) return rc;
+        d.materials = reinterpret_cast<const float4*>(p);
+        d.nMaterials = (uint32_t)m.size();
+    }
+    CK(cudaStreamSynchronize(c->stream));
+    const auto t2 = std::chrono::steady_clock::now();
+    blokb_world_stats& s = c->stats;
+    s = blokb_world_stats{};
+    s.nodes = nNodes; s.subChunks = nSubs; s.materials = nMaterials;
+    s.bricks = hw.bricks.size(); s.blocks = hw.blockFirstLeaf.size(); s.voxels = hw.voxels;
+    s.compactBytes = hw.compactBytes();
+    for (int a = 0; a < 3; a++) { s.gridOrigin[a] = hw.origin[a]; s.gridDim[a] = hw.dim[a]; }
+    s.levels = hw.levels;
+    s.buildMs = std::chrono::duration<float, std::milli>(t1 - t0).count();
+    s.uploadMs = std::chrono::duration<float, std::milli>(t2 - t1).count();
+    c->haveWorld = true;
+    return 0;
+}
+
+int blokb_world_stats_get(blokb_ctx* c, blokb_world_stats* out) {
+    if (!c || !out) return fail(BLOKB_E_ARG, "null argument");
+    if (!c->haveWorld) return fail(BLOKB_E_STATE, "no world uploaded");
+    *out = c->stats;
+    return 0;
+}
+
+int blokb_set_frame(blokb_ctx* c, const blokb_frame_ubo* f) {
+    if (!c || !f) return fail(BLOKB_E_ARG, "null argument");
+    if (f->screenWidth == 0 || f->screenHeight == 0 || f->screenWidth > 65536 || f->screenHeight > 65536) return fail(BLOKB_E_ARG, "bad screen size");
+    CK(cudaSetDevice(c->device));
+    if (c->buf.width != f->screenWidth || c->buf.height != f->screenHeight) {
+        CK(cudaStreamSynchronize(c->stream));
+        free_images(c);
+        const size_t n = size_t(f->screenWidth) * f->screenHeight;
+        CK(cudaMalloc((void**)&c->buf.hit, n * sizeof(blokb_hit)));
+        CK(cudaMalloc((void**)&c->buf.shadow, n));
+        CK(cudaMalloc((void**)&c->buf.color, n * 16));
+        CK(cudaMalloc((void**)&c->buf.worldPos, n * 16));
+        CK(cudaMalloc((void**)&c->buf.normalRough, n * 8));
+        CK(cudaMalloc((void**)&c->buf.albedoMetal, n * 4));
+        CK(cudaMalloc((void**)&c->buf.motion, n * 4));
+        CK(cudaMalloc((void**)&c->buf.accum, n * 16));
+        CK(cudaMemsetAsync(c->buf.accum, 0, n * 16, c->stream));
+        c->buf.width = f->screenWidth; c->buf.height = f->screenHeight;
+    }
+    FrameDev& d = c->frame;
+    std::memcpy(d.invView, f->invView, 64);
+    std::memcpy(d.invProj, f->invProj, 64);
+    std::memcpy(d.prevViewProj, f->prevViewProj, 64);
+    std::memcpy(d.camPos, f->camPos, 12);
+    d.frameCount = f->frameCount; d.sampleCount = f->sampleCount; d.width = f->screenWidth; d.height = f->screenHeight;
+    c->haveFrame = true;
+    return 0;
+}
+
+static int ready(blokb_ctx* c, bool needFrame) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    if (!c->haveWorld) return fail(BLOKB_E_STATE, "no world uploaded (blokb_upload_world)");
+    if (needFrame && !c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
+    cudaError_t e = cudaSetDevice(c->device);
+    if (e != cudaSuccess) return fail(BLOKB_E_CUDA, cudaGetErrorString(e));
+    return 0;
+}
+static cudaStream_t pick(blokb_ctx* c, void* s) { return s ? static_cast<cudaStream_t>(s) : c->stream; }
+static unsigned long long* st(blokb_ctx* c) { return c->statsOn ? c->dStats : nullptr; }
+
+int blokb_trace_primary(blokb_ctx* c, void* stream) {
+    if (int rc = ready(c, true)) return rc;
+    CK(launch_primary(c->dw, c->frame, false, c->buf.hit, c->buf.shadow, st(c), pick(c, stream)));
+    c->launches++;
+    return 0;
+}
+int blokb_trace_primary_shadow(blokb_ctx* c, void* stream) {
+    if (int rc = ready(c, true)) return rc;
+    CK(launch_primary(c->dw, c->frame, true, c->buf.hit, c->buf.shadow, st(c), pick(c, stream)));
+    c->launches++;
+    return 0;
+}
+int blokb_render(blokb_ctx* c, void* stream) {
+    if (int rc = ready(c, true)) return rc;
+    if (c->frame.sampleCount == 0) return fail(BLOKB_E_ARG, "frame.sampleCount is 0");
+    CK(launch_render(c->dw, c->frame, c->buf.color, c->buf.worldPos, c->buf.normalRough, c->buf.albedoMetal, c->buf.motion, st(c), pick(c, stream)));
+    c->launches++;
+    return 0;
+}
+int blokb_trace_path(blokb_ctx* c, uint32_t sampleBegin, uint32_t sampleEnd, void* stream) {
+    if (int rc = ready(c, true)) return rc;
+    if (sampleEnd < sampleBegin) return fail(BLOKB_E_ARG, "sampleEnd < sampleBegin");
+    if (sampleEnd == sampleBegin) return 0;
+    CK(launch_path(c->dw, c->frame, sampleBegin, sampleEnd, c->buf.accum, st(c), pick(c, stream)));
+    c->launches++;
+    return 0;
+}
+int blokb_resolve(blokb_ctx* c, void* stream) {
+    if (int rc = ready(c, true)) return rc;
+    CK(launch_resolve(c->buf.accum, c->buf.color, size_t(c->buf.width) * c->buf.height, pick(c, stream)));
+    c->launches++;
+    return 0;
+}
+int blokb_reset_accum(blokb_ctx* c, void* stream) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
+    CK(cudaSetDevice(c->device));
+    CK(cudaMemsetAsync(c->buf.accum, 0, size_t(c->buf.width) * c->buf.height * 16, pick(c, stream)));
+    return 0;
+}
+int blokb_trace_rays(blokb_ctx* c, const float* dRays, size_t n, int /*anyHit*/, blokb_hit* dOut, void* stream) {
+    // The walk is strictly front to back: the first filled voxel answers both closest-hit and any-hit queries.
+    if (int rc = ready(c, false)) return rc;
+    if (n && (!dRays || !dOut)) return fail(BLOKB_E_ARG, "null ray / output pointer");
+    CK(launch_trace_rays(c->dw, dRays, n, dOut, st(c), pick(c, stream)));
+    if (n) c->launches++;
+    return 0;
+}
+int blokb_trace_rays_host(blokb_ctx* c, const float* rays, size_t n, int anyHit, blokb_hit* out) {
+    if (int rc = ready(c, false)) return rc;
+    if (n == 0) return 0;
+    if (!rays || !out) return fail(BLOKB_E_ARG, "null ray / output pointer");
+    if (n > c->rayCap) {
+        CK(cudaStreamSynchronize(c->stream));
+        if (c->dRays) cudaFree(c->dRays);
+        if (c->dHits) cudaFree(c->dHits);
+        c->dRays = nullptr; c->dHits = nullptr; c->rayCap = 0;
+        CK(cudaMalloc((void**)&c->dRays, n * 32));
+        CK(cudaMalloc((void**)&c->dHits, n * sizeof(blokb_hit)));
+        c->rayCap = n;
+    }
+    CK(cudaMemcpyAsync(c->dRays, rays, n * 32, cudaMemcpyHostToDevice, c->stream));
+    if (int rc = blokb_trace_rays(c, c->dRays, n, anyHit, c->dHits, c->stream)) return rc;
+    CK(cudaMemcpyAsync(out, c->dHits, n * sizeof(blokb_hit), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int blokb_get_buffers(blokb_ctx* c, blokb_buffers* out) {
+    if (!c || !out) return fail(BLOKB_E_ARG, "null argument");
+    if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
+    *out = c->buf;
+    return 0;
+}
+int blokb_readback(blokb_ctx* c, int image, void* host, size_t bytes) {
+    if (!c || !host) return fail(BLOKB_E_ARG, "null argument");
+    if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
+    const size_t n = size_t(c->buf.width) * c->buf.height;
+    const void* src = nullptr;
+    size_t sz = 0;
+    switch (image) {
+        case BLOKB_IMG_HIT: src = c->buf.hit; sz = n * 16; break;
+        case BLOKB_IMG_SHADOW: src = c->buf.shadow; sz = n; break;
+        case BLOKB_IMG_COLOR: src = c->buf.color; sz = n * 16; break;
+        case BLOKB_IMG_WORLDPOS: src = c->buf.worldPos; sz = n * 16; break;
+        case BLOKB_IMG_NORMALROUGH: src = c->buf.normalRough; sz = n * 8; break;
+        case BLOKB_IMG_ALBEDOMETAL: src = c->buf.albedoMetal; sz = n * 4; break;
+        case BLOKB_IMG_MOTION: src = c->buf.motion; sz = n * 4; break;
+        case BLOKB_IMG_ACCUM: src = c->buf.accum; sz = n * 16; break;
+        default: return fail(BLOKB_E_ARG, "unknown image id");
+    }
+    if (bytes != sz) return fail(BLOKB_E_ARG, "host buffer size mismatch: expected " + std::to_string(sz));
+    CK(cudaSetDevice(c->device));
+    CK(cudaMemcpyAsync(host, src, sz, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+int blokb_sync(blokb_ctx* c) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+uint64_t blokb_launch_count(blokb_ctx* c) { return c ? c->launches : 0; }
+
+// Profiling aid: when enabled, kernels add {DDA steps, rays} to two device counters.
+int blokb_stats_enable(blokb_ctx* c, int on) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    c->statsOn = on != 0;
+    CK(cudaSetDevice(c->device));
+    CK(cudaMemsetAsync(c->dStats, 0, 4 * sizeof(unsigned long long), c->stream));
+    return 0;
+}
+int blokb_stats_read(blokb_ctx* c, uint64_t* stepsAndRays /*[2]*/) {
+    if (!c || !stepsAndRays) return fail(BLOKB_E_ARG, "null argument");
+    CK(cudaSetDevice(c->device));
+    unsigned long long v[2];
+    CK(cudaMemcpyAsync(v, c->dStats, sizeof v, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    stepsAndRays[0] = v[0]; stepsAndRays[1] = v[1];
+    return 0;
+}
+void* blokb_stream(blokb_ctx* c) { return c ? c->stream : nullptr; }
+}

@@ -1,0 +1,19 @@
+// Qualifier macros so that traverse.cuh / shade.cuh also compile as plain host C++ — used ONLY by
+// tests/host_emul (a CPU build of the very same device functions, to check the DDA's logic against the oracle
+// in a container without a GPU). The product library never runs this path: libblokb200.so contains device code only.
+#pragma once
+#if defined(__CUDACC__)
+#define BLOKB_HD __device__ __forceinline__
+#define BLOKB_D __device__ __forceinline__
+#else
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#define BLOKB_HD inline
+#define BLOKB_D inline
+static inline int __float2int_rd(float v) { return (int)std::floor(v); }
+static inline int __clz(uint32_t v) { return v ? __builtin_clz(v) : 32; }
+static inline int __popcll(unsigned long long v) { return __builtin_popcountll(v); }
+static inline uint32_t __float_as_uint(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
+template <class T> static inline T __ldg(const T* p) { return *p; }
+#endif

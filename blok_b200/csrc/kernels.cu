@@ -1,0 +1,191 @@
+// Kernels of the traversal path. One thread per ray / pixel; a warp covers an 8x4 pixel tile so that its 32
+// rays walk neighbouring cells (coherent mask loads, little divergence). All scene reads are read-only
+// (ld.global.nc) and the compact scene is sized to stay L2-resident.
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include "kernels.h"
+#include "shade.cuh"
+
+namespace blokb {
+
+// pixel of this thread: block = 32x8 pixels, warp = 8x4 tile
+__device__ __forceinline__ bool thread_pixel(uint32_t width, uint32_t height, uint32_t& px, uint32_t& py) {
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    px = blockIdx.x * 32u + (warp & 3u) * 8u + (lane & 7u);
+    py = blockIdx.y * 8u + (warp >> 2) * 4u + (lane >> 3);
+    return px < width && py < height;
+}
+
+__device__ __forceinline__ void store_hit(blokb_hit* dst, bool hit, const HitRec& h) {
+    uint4 v;
+    if (hit) v = make_uint4(h.node, h.material, __float_as_uint(h.t), h.facePrim);
+    else v = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, __float_as_uint(-1.0f), 0xFFFFFFFFu);
+    *reinterpret_cast<uint4*>(dst) = v;
+}
+
+template <bool kStats>
+__global__ void __launch_bounds__(256) k_trace_rays(const __grid_constant__ DeviceWorld W, const float4* __restrict__ rays, size_t n,
+                                                    blokb_hit* __restrict__ out, unsigned long long* stats) {
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 a = __ldg(&rays[2 * i]), b = __ldg(&rays[2 * i + 1]);
+    HitRec h;
+    uint32_t steps = 0;
+    const bool hit = traverse<kStats>(W, a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, h, steps);
+    store_hit(out + i, hit, h);
+    if (kStats) atomicAdd(stats, (unsigned long long)steps);
+}
+
+// Sample-0 primary rays (raygen.rgen:193-229) -> hit records; optionally the sun shadow ray of :280-298.
+template <bool kShadow, bool kStats>
+__global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
+                                                 blokb_hit* __restrict__ out, uint8_t* __restrict__ shadow, unsigned long long* stats) {
+    uint32_t px, py;
+    if (!thread_pixel(F.width, F.height, px, py)) return;
+    const F3 d = primary_dir(F, float(px) + 0.5f, float(py) + 0.5f);
+    HitRec h;
+    uint32_t steps = 0;
+    const bool hit = traverse<kStats>(W, F.camPos[0], F.camPos[1], F.camPos[2], d.x, d.y, d.z, 0.001f, 10000.0f, h, steps);
+    const size_t pi = size_t(py) * F.width + px;
+    store_hit(out + pi, hit, h);
+    if (kShadow) {
+        uint8_t sv = 0;  // 0 = no shadow ray cast, 1 = lit, 2 = shadowed
+        if (hit) {
+            F3 N = face_normal(h.facePrim & 7u);
+            if (dot3(N, d) > 0.0f) N = -N;
+            const F3 sunDir = sun_dir();
+            if (fmaxf(dot3(N, sunDir), 0.0f) > 0.0f) {
+                const F3 o = f3(F.camPos[0], F.camPos[1], F.camPos[2]) + d * h.t + N * 0.001f;
+                HitRec sh;
+                sv = traverse<kStats>(W, o.x, o.y, o.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps) ? 2 : 1;
+            }
+        }
+        shadow[pi] = sv;
+    }
+    if (kStats) atomicAdd(stats, (unsigned long long)steps);
+}
+
+__device__ __forceinline__ uint32_t unorm8(float v) { return __float2uint_rn(__saturatef(v) * 255.0f); }
+
+// Full raygen.rgen: frame.sampleCount samples per pixel, five G-buffer images (raygen.rgen:167-414).
+template <bool kStats>
+__global__ void __launch_bounds__(256) k_render(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F, float4* __restrict__ color,
+                                                float4* __restrict__ worldPos, uint2* __restrict__ normalRough, uint32_t* __restrict__ albedoMetal,
+                                                uint32_t* __restrict__ motion, unsigned long long* stats) {
+    uint32_t px, py;
+    if (!thread_pixel(F.width, F.height, px, py)) return;
+    FirstHit fh;
+    fh.had = false; fh.emissive = false; fh.pos = f3(0.f); fh.N = f3(0.f); fh.albedo = f3(0.f); fh.emission = f3(0.f);
+    fh.roughness = 0.f; fh.metallic = 0.f; fh.depth = 0.f;
+    F3 acc = f3(0.f);
+    uint32_t rays = 0, steps = 0;
+    for (uint32_t s = 0; s < F.sampleCount; s++) acc = acc + path_sample<kStats>(W, F, px, py, s, &fh, rays, steps);
+    F3 c = acc / float(F.sampleCount);
+    const float mv = max3(c);
+    if (mv > 100.0f) c = c * (100.0f / mv);
+    const size_t pi = size_t(py) * F.width + px;
+    color[pi] = make_float4(c.x, c.y, c.z, 1.0f);
+    const F3 cam = f3(F.camPos[0], F.camPos[1], F.camPos[2]);
+    if (!fh.had) {
+        fh.depth = 10000.0f;
+        const F4 fw = mat_mul(F.invView, 0.f, 0.f, -1.f, 0.f);
+        fh.pos = cam + normalize3(f3(fw.x, fw.y, fw.z)) * 10000.0f;
+        fh.N = f3(0.f, 1.f, 0.f);
+        fh.albedo = sky_color(normalize3(fh.pos - cam));
+    }
+    const F3 fa = fh.emissive ? fh.emission : fh.albedo;
+    worldPos[pi] = make_float4(fh.pos.x, fh.pos.y, fh.pos.z, fh.depth);
+    {
+        const __half2 a = __floats2half2_rn(fh.N.x, fh.N.y), b = __floats2half2_rn(fh.N.z, fh.roughness);
+        normalRough[pi] = make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+    }
+    albedoMetal[pi] = unorm8(fa.x) | (unorm8(fa.y) << 8) | (unorm8(fa.z) << 16) | (unorm8(fh.metallic) << 24);
+    float mx = 0.f, my = 0.f;
+    if (fh.had && fh.depth < 9999.0f) {
+        const F4 pc = mat_mul(F.prevViewProj, fh.pos.x, fh.pos.y, fh.pos.z, 1.0f);
+        const float nx = pc.x / pc.w, ny = pc.y / pc.w;
+        mx = (float(px) + 0.5f) / float(F.width) - (nx * 0.5f + 0.5f);
+        my = (float(py) + 0.5f) / float(F.height) - (ny * 0.5f + 0.5f);
+    }
+    {
+        const __half2 m = __floats2half2_rn(mx, my);
+        motion[pi] = *reinterpret_cast<const uint32_t*>(&m);
+    }
+    if (kStats) { atomicAdd(stats, (unsigned long long)steps); atomicAdd(stats + 1, (unsigned long long)rays); }
+}
+
+// Progressive path tracing: samples [sBegin, sEnd) of every pixel added into accum = (sum.rgb, spp)
+// (the reference CUDA tracer's accumulator, cuda_tracer.cu:372-380), with raygen.rgen's per-(pixel, frame,
+// sample) seeding so that any partition of the sample range over launches or GPUs draws the same paths.
+template <bool kStats>
+__global__ void __launch_bounds__(256) k_path(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F, uint32_t sBegin, uint32_t sEnd,
+                                              float4* __restrict__ accum, unsigned long long* stats) {
+    uint32_t px, py;
+    if (!thread_pixel(F.width, F.height, px, py)) return;
+    F3 acc = f3(0.f);
+    uint32_t rays = 0, steps = 0;
+    for (uint32_t s = sBegin; s < sEnd; s++) acc = acc + path_sample<kStats>(W, F, px, py, s, nullptr, rays, steps);
+    const size_t pi = size_t(py) * F.width + px;
+    float4 a = accum[pi];
+    a.x += acc.x; a.y += acc.y; a.z += acc.z; a.w += float(sEnd - sBegin);
+    accum[pi] = a;
+    if (kStats) { atomicAdd(stats, (unsigned long long)steps); atomicAdd(stats + 1, (unsigned long long)rays); }
+}
+
+// color = sum / spp, firefly clamp (raygen.rgen:383-392).
+__global__ void __launch_bounds__(256) k_resolve(const float4* __restrict__ accum, float4* __restrict__ color, size_t n) {
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 a = accum[i];
+    F3 c = f3(a.x, a.y, a.z) / a.w;
+    const float mv = max3(c);
+    if (mv > 100.0f) c = c * (100.0f / mv);
+    color[i] = make_float4(c.x, c.y, c.z, 1.0f);
+}
+
+// ---- launchers ------------------------------------------------------------------------------------
+static inline dim3 pixel_grid(uint32_t w, uint32_t h) { return dim3((w + 31) / 32, (h + 7) / 8); }
+
+cudaError_t launch_trace_rays(const DeviceWorld& W, const float* rays, size_t n, blokb_hit* out, unsigned long long* stats, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    const unsigned blocks = (unsigned)((n + 255) / 256);
+    if (stats) k_trace_rays<true><<<blocks, 256, 0, st>>>(W, reinterpret_cast<const float4*>(rays), n, out, stats);
+    else k_trace_rays<false><<<blocks, 256, 0, st>>>(W, reinterpret_cast<const float4*>(rays), n, out, nullptr);
+    return cudaGetLastError();
+}
+cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow, blokb_hit* out, uint8_t* shadowOut, unsigned long long* stats,
+                           cudaStream_t st) {
+    const dim3 g = pixel_grid(F.width, F.height);
+    if (stats) {
+        if (shadow) k_primary<true, true><<<g, 256, 0, st>>>(W, F, out, shadowOut, stats);
+        else k_primary<false, true><<<g, 256, 0, st>>>(W, F, out, shadowOut, stats);
+    } else {
+        if (shadow) k_primary<true, false><<<g, 256, 0, st>>>(W, F, out, shadowOut, nullptr);
+        else k_primary<false, false><<<g, 256, 0, st>>>(W, F, out, shadowOut, nullptr);
+    }
+    return cudaGetLastError();
+}
+cudaError_t launch_render(const DeviceWorld& W, const FrameDev& F, float* color, float* worldPos, uint16_t* normalRough, uint8_t* albedoMetal,
+                          uint16_t* motion, unsigned long long* stats, cudaStream_t st) {
+    const dim3 g = pixel_grid(F.width, F.height);
+    if (stats)
+        k_render<true><<<g, 256, 0, st>>>(W, F, (float4*)color, (float4*)worldPos, (uint2*)normalRough, (uint32_t*)albedoMetal, (uint32_t*)motion, stats);
+    else
+        k_render<false><<<g, 256, 0, st>>>(W, F, (float4*)color, (float4*)worldPos, (uint2*)normalRough, (uint32_t*)albedoMetal, (uint32_t*)motion, nullptr);
+    return cudaGetLastError();
+}
+cudaError_t launch_path(const DeviceWorld& W, const FrameDev& F, uint32_t sBegin, uint32_t sEnd, float* accum, unsigned long long* stats,
+                        cudaStream_t st) {
+    const dim3 g = pixel_grid(F.width, F.height);
+    if (stats) k_path<true><<<g, 256, 0, st>>>(W, F, sBegin, sEnd, (float4*)accum, stats);
+    else k_path<false><<<g, 256, 0, st>>>(W, F, sBegin, sEnd, (float4*)accum, nullptr);
+    return cudaGetLastError();
+}
+cudaError_t launch_resolve(const float* accum, float* color, size_t n, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    k_resolve<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const float4*)accum, (float4*)color, n);
+    return cudaGetLastError();
+}
+
+}  // namespace blokb

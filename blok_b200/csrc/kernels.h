@@ -1,0 +1,23 @@
+// Launchers implemented in kernels.cu (device code); called from the C-ABI layer in api.cpp.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "../../include/blokb200.h"
+#include "scene.h"
+
+namespace blokb {
+// The fields of FrameUBO that raygen.rgen reads (resources.hpp:103-150).
+struct FrameDev {
+    float invView[16], invProj[16], prevViewProj[16];
+    float camPos[3];
+    uint32_t frameCount, sampleCount, width, height;
+};
+cudaError_t launch_trace_rays(const DeviceWorld& W, const float* rays, size_t n, blokb_hit* out, unsigned long long* stats, cudaStream_t st);
+cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow, blokb_hit* out, uint8_t* shadowOut, unsigned long long* stats,
+                           cudaStream_t st);
+cudaError_t launch_render(const DeviceWorld& W, const FrameDev& F, float* color, float* worldPos, uint16_t* normalRough, uint8_t* albedoMetal,
+                          uint16_t* motion, unsigned long long* stats, cudaStream_t st);
+cudaError_t launch_path(const DeviceWorld& W, const FrameDev& F, uint32_t sBegin, uint32_t sEnd, float* accum, unsigned long long* stats,
+                        cudaStream_t st);
+cudaError_t launch_resolve(const float* accum, float* color, size_t n, cudaStream_t st);
+}  // namespace blokb

@@ -1,0 +1,33 @@
+// Host-side scene upload: reference upload arrays -> compact 64-tree (see scene.h).
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/blokb200.h"
+#include "scene.h"
+
+namespace blokb {
+
+struct HostWorld {
+    int32_t origin[3] = {0, 0, 0}, dim[3] = {0, 0, 0};
+    int32_t levels = 3;
+    bool matWide = false;
+    std::vector<std::vector<uint64_t>> dense;  // [k], k = 0..levels (only 3..levels used)
+    int32_t denseDim[kMaxLevels + 1][3] = {};
+    std::vector<uint32_t> topGrid;
+    std::vector<SubRec> subs;
+    std::vector<Brick> bricks;
+    std::vector<uint32_t> blockFirstLeaf;
+    std::vector<uint16_t> mat16;
+    std::vector<uint32_t> mat32;
+    uint64_t voxels = 0;
+    size_t compactBytes() const;
+};
+
+// Returns 0 or a BLOKB_E_* code with `err` filled.
+int build_host_world(const blokb_svo_node* nodes, size_t nNodes, const blokb_subchunk* subs, size_t nSubs, HostWorld& out,
+                     std::string& err);
+
+}  // namespace blokb

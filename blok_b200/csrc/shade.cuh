@@ -1,0 +1,212 @@
+// Ray generation and shading arithmetic of the reference's raygen.rgen / hit.rchit, as device functions.
+// Operation order follows the shader source statement by statement (and glm's association order where the
+// shader calls a glm-equivalent built-in), and the file is compiled with --fmad=false, so +,-,*,/ and sqrt
+// round exactly like the CPU oracle; sinf/cosf/powf are CUDA's (≤ 2 ulp from glibc's) — radiance parity is
+// therefore a tolerance, hit IDs are exact.
+#pragma once
+#include <cstdint>
+
+#include "kernels.h"
+#include "traverse.cuh"
+
+namespace blokb {
+
+struct F3 { float x, y, z; };
+BLOKB_HD F3 f3(float a, float b, float c) { return {a, b, c}; }
+BLOKB_HD F3 f3(float a) { return {a, a, a}; }
+BLOKB_HD F3 operator+(F3 a, F3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+BLOKB_HD F3 operator-(F3 a, F3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+BLOKB_HD F3 operator*(F3 a, F3 b) { return {a.x * b.x, a.y * b.y, a.z * b.z}; }
+BLOKB_HD F3 operator/(F3 a, F3 b) { return {a.x / b.x, a.y / b.y, a.z / b.z}; }
+BLOKB_HD F3 operator*(F3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
+BLOKB_HD F3 operator/(F3 a, float s) { return {a.x / s, a.y / s, a.z / s}; }
+BLOKB_HD F3 operator-(F3 a) { return {-a.x, -a.y, -a.z}; }
+BLOKB_HD float dot3(F3 a, F3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+BLOKB_HD F3 cross3(F3 a, F3 b) { return {a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y}; }
+BLOKB_HD F3 normalize3(F3 v) { return v * (1.0f / sqrtf(dot3(v, v))); }
+BLOKB_HD F3 mix3(F3 a, F3 b, float t) { return a * (1.0f - t) + b * t; }
+BLOKB_HD F3 reflect3(F3 I, F3 N) { return I - N * dot3(N, I) * 2.0f; }
+BLOKB_HD float max3(F3 a) { return fmaxf(fmaxf(a.x, a.y), a.z); }
+
+struct F4 { float x, y, z, w; };
+BLOKB_HD F4 mat_mul(const float* m, float x, float y, float z, float w) {  // column-major, glm order
+    F4 r;
+    r.x = (m[0] * x + m[4] * y) + (m[8] * z + m[12] * w);
+    r.y = (m[1] * x + m[5] * y) + (m[9] * z + m[13] * w);
+    r.z = (m[2] * x + m[6] * y) + (m[10] * z + m[14] * w);
+    r.w = (m[3] * x + m[7] * y) + (m[11] * z + m[15] * w);
+    return r;
+}
+
+#define BLOKB_PI 3.14159265359f
+#define BLOKB_INV_PI 0.31830988618f
+
+BLOKB_HD uint32_t pcg(uint32_t& s) {  // raygen.rgen:77-82
+    const uint32_t old = s;
+    s = old * 747796405u + 2891336453u;
+    const uint32_t w = ((old >> ((old >> 28u) + 4u)) ^ old) * 277803737u;
+    return (w >> 22u) ^ w;
+}
+BLOKB_HD float random_float(uint32_t& s) { return float(pcg(s)) / 4294967295.0f; }  // :84-86
+BLOKB_HD uint32_t init_rng(uint32_t px, uint32_t py, uint32_t width, uint32_t frame, uint32_t sample) {  // :92-99
+    uint32_t seed = px + py * width;
+    seed ^= frame * 747796405u;
+    seed ^= sample * 1664525u;
+    pcg(seed);
+    pcg(seed);
+    return seed;
+}
+BLOKB_HD void basis(F3 N, F3& T, F3& B) {
+    const F3 up = fabsf(N.z) < 0.999f ? f3(0.f, 0.f, 1.f) : f3(1.f, 0.f, 0.f);
+    T = normalize3(cross3(up, N));
+    B = cross3(N, T);
+}
+BLOKB_HD F3 sample_cosine(float ux, float uy, F3 N) {  // :101-113
+    const float r = sqrtf(ux), phi = 2.0f * BLOKB_PI * uy;
+    const float x = r * cosf(phi), y = r * sinf(phi), z = sqrtf(fmaxf(0.0f, 1.0f - ux));
+    F3 T, B;
+    basis(N, T, B);
+    return normalize3(T * x + B * y + N * z);
+}
+BLOKB_HD F3 sample_ggx(float ux, float uy, F3 N, float rough) {  // :115-130
+    const float a = rough * rough, a2 = a * a, phi = 2.0f * BLOKB_PI * ux;
+    const float ct = sqrtf((1.0f - uy) / (1.0f + (a2 - 1.0f) * uy)), st = sqrtf(fmaxf(0.0f, 1.0f - ct * ct));
+    const F3 H = f3(st * cosf(phi), st * sinf(phi), ct);
+    F3 T, B;
+    basis(N, T, B);
+    return normalize3(T * H.x + B * H.y + N * H.z);
+}
+BLOKB_HD F3 fresnel(float c, F3 F0) { return F0 + (f3(1.0f) - F0) * powf(fmaxf(1.0f - c, 0.0f), 5.0f); }  // :132-134
+BLOKB_HD F3 sun_dir() { return normalize3(f3(0.5f, 0.8f, 0.3f)); }
+BLOKB_HD F3 sky_color(F3 dir) {  // :136-148
+    const float t = 0.5f * (dir.y + 1.0f);
+    const F3 c = mix3(f3(0.8f, 0.85f, 0.95f), f3(0.4f, 0.6f, 0.9f), t);
+    const float sd = fmaxf(dot3(dir, sun_dir()), 0.0f);
+    const F3 sun = f3(1.0f, 0.95f, 0.8f) * powf(sd, 128.0f) * 5.0f, glow = f3(1.0f, 0.9f, 0.7f) * powf(sd, 8.0f) * 0.3f;
+    return c + sun + glow;
+}
+BLOKB_HD bool is_emissive(F3 e) { return dot3(e, f3(1.0f)) > 0.01f; }            // :158-160
+BLOKB_HD float luminance(F3 c) { return dot3(c, f3(0.2126f, 0.7152f, 0.0722f)); }  // :163-165
+
+// Primary ray through pixel-space point (pcx, pcy): raygen.rgen:201-206.
+BLOKB_HD F3 primary_dir(const FrameDev& f, float pcx, float pcy) {
+    const float dx = (pcx / float(f.width)) * 2.0f - 1.0f, dy = (pcy / float(f.height)) * 2.0f - 1.0f;
+    const F4 tg = mat_mul(f.invProj, dx, dy, 1.0f, 1.0f);
+    const F3 tn = normalize3(f3(tg.x, tg.y, tg.z));
+    const F4 wd = mat_mul(f.invView, tn.x, tn.y, tn.z, 0.0f);
+    return normalize3(f3(wd.x, wd.y, wd.z));
+}
+
+BLOKB_HD F3 face_normal(uint32_t face) {  // hit.rchit:46-53
+    const float s = (face & 1u) ? -1.0f : 1.0f;
+    const uint32_t a = face >> 1;
+    return f3(a == 0 ? s : 0.f, a == 1 ? s : 0.f, a == 2 ? s : 0.f);
+}
+
+struct Surface { F3 albedo, emission; float roughness, metallic; };
+BLOKB_HD Surface fetch_surface(const DeviceWorld& W, uint32_t materialId) {  // hit.rchit:62-75
+    const uint32_t id = materialId < 65535u ? materialId : 65535u;
+    const float4 a = __ldg(&W.materials[2 * id]), b = __ldg(&W.materials[2 * id + 1]);
+    const uint32_t flags = __float_as_uint(a.w);
+    Surface s;
+    s.albedo = f3(a.x, a.y, a.z);
+    s.emission = f3(b.x, b.y, b.z);
+    s.metallic = float((flags >> 24) & 0xFFu) / 255.0f;
+    s.roughness = fmaxf(float((flags >> 16) & 0xFFu) / 255.0f, 0.04f);
+    return s;
+}
+
+// One sample of raygen.rgen's path loop (:188-380). Returns the sample's radiance. When `first` is non-null
+// and the primary ray hits, *first receives the G-buffer first-hit data (:253-263).
+struct FirstHit { F3 pos, N, albedo, emission; float roughness, metallic, depth; bool had, emissive; };
+
+template <bool kStats>
+BLOKB_HD F3 path_sample(const DeviceWorld& W, const FrameDev& f, uint32_t px, uint32_t py, uint32_t s,
+                                          FirstHit* first, uint32_t& rays, uint32_t& steps) {
+    uint32_t rng = init_rng(px, py, f.width, f.frameCount, s);
+    float pcx, pcy;
+    if (s == 0u) { pcx = float(px) + 0.5f; pcy = float(py) + 0.5f; }
+    else {
+        const float jx = random_float(rng) - 0.5f;
+        const float jy = random_float(rng) - 0.5f;
+        pcx = float(px) + 0.5f + jx * 0.5f; pcy = float(py) + 0.5f + jy * 0.5f;
+    }
+    F3 rayDir = primary_dir(f, pcx, pcy);
+    F3 rayOrigin = f3(f.camPos[0], f.camPos[1], f.camPos[2]);
+    F3 radiance = f3(0.f), thr = f3(1.f);
+    const F3 sunDir = sun_dir();
+    const F3 sunRad = f3(3.0f, 2.9f, 2.7f);
+    for (uint32_t bounce = 0u; bounce < 2u; bounce++) {
+        HitRec h;
+        rays++;
+        if (!traverse<kStats>(W, rayOrigin.x, rayOrigin.y, rayOrigin.z, rayDir.x, rayDir.y, rayDir.z, 0.001f, 10000.0f, h, steps)) {
+            radiance = radiance + thr * sky_color(rayDir);
+            break;
+        }
+        const Surface m = fetch_surface(W, h.material);
+        F3 N = face_normal(h.facePrim & 7u);
+        const F3 hitPos = rayOrigin + rayDir * h.t;
+        if (dot3(N, rayDir) > 0.0f) N = -N;
+        if (bounce == 0u && first && s == 0u && !first->had) {
+            first->had = true; first->pos = hitPos; first->N = N; first->albedo = m.albedo; first->emission = m.emission;
+            first->roughness = m.roughness; first->metallic = m.metallic; first->depth = h.t; first->emissive = is_emissive(m.emission);
+        }
+        if (is_emissive(m.emission)) {
+            radiance = radiance + thr * m.emission;
+            if (luminance(m.emission) > 5.0f || bounce > 0u) break;
+        }
+        const float NdotL = fmaxf(dot3(N, sunDir), 0.0f);
+        if (NdotL > 0.0f && bounce == 0u) {
+            const F3 so = hitPos + N * 0.001f;
+            HitRec sh;
+            rays++;
+            if (!traverse<kStats>(W, so.x, so.y, so.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps)) {
+                const F3 diffuse = m.albedo * (1.0f - m.metallic);
+                radiance = radiance + thr * diffuse * sunRad * NdotL * BLOKB_INV_PI;
+                if (m.roughness < 0.9f) {
+                    const F3 Hh = normalize3(sunDir - rayDir);
+                    const float NdotH = fmaxf(dot3(N, Hh), 0.0f), VdotH = fmaxf(dot3(-rayDir, Hh), 0.0f);
+                    const float a = m.roughness * m.roughness, a2 = a * a;
+                    const float denom = NdotH * NdotH * (a2 - 1.0f) + 1.0f;
+                    const float D = a2 / (BLOKB_PI * denom * denom);
+                    const F3 F0 = mix3(f3(0.04f), m.albedo, m.metallic);
+                    const F3 F = fresnel(VdotH, F0);
+                    radiance = radiance + thr * F * D * 0.25f * sunRad * NdotL;
+                }
+            }
+        }
+        if (bounce > 0u) {
+            const float p = fminf(max3(thr), 0.95f);
+            if (random_float(rng) > p) break;
+            thr = thr / p;
+        }
+        const float ux = random_float(rng);
+        const float uy = random_float(rng);
+        const F3 F0 = mix3(f3(0.04f), m.albedo, m.metallic);
+        const F3 V = -rayDir;
+        const float NdotV = fmaxf(dot3(N, V), 0.001f);
+        const F3 F = fresnel(NdotV, F0);
+        float sw = (F.x + F.y + F.z) / 3.0f;
+        sw = sw * (1.0f - m.metallic) + 1.0f * m.metallic;
+        if (random_float(rng) < sw) {
+            const F3 Hh = sample_ggx(ux, uy, N, fmaxf(m.roughness, 0.04f));
+            const F3 nd = reflect3(rayDir, Hh);
+            if (dot3(nd, N) <= 0.0f) break;
+            const float HdotV = fmaxf(dot3(Hh, V), 0.0f);
+            const F3 Fh = fresnel(HdotV, F0);
+            thr = thr * (Fh / fmaxf(sw, 0.001f));
+            rayDir = nd;
+        } else {
+            const F3 nd = sample_cosine(ux, uy, N);
+            const F3 diffuse = m.albedo * (1.0f - m.metallic);
+            thr = thr * (diffuse / fmaxf(1.0f - sw, 0.001f));
+            rayDir = nd;
+        }
+        const float mt = max3(thr);
+        if (mt > 10.0f) thr = thr * (10.0f / mt);
+        rayOrigin = hitPos + N * 0.002f;
+    }
+    return radiance;
+}
+
+}  // namespace blokb

@@ -1,0 +1,176 @@
+/* blokb200.h — C-ABI of the B200-native voxel ray-traversal path (drop-in boundary).
+ *
+ * The reference (collinlongoria/blok) has no plugin/FFI interface: its traversal sits behind three C++
+ * seams inside one executable. Each entry point below replaces one of those seams (paths relative to
+ * the reference root; see SURVEY.md §8(b) and INTEGRATION.md for the reference-side binding):
+ *
+ *   scene in      Renderer::addWorld / updateWorld(WorldSvoGpu&)        blok/include/renderer.hpp:40-71
+ *                 uploadSvoBuffers / uploadMaterialBuffer                 blok/src/renderer_upload.cpp:237-312
+ *   frame in      Renderer::render(const Camera&, float dt) -> FrameUBO   blok/include/renderer.hpp:34,
+ *                 Denoiser::fillFrameUBO                                  blok/src/renderer_denoising.cpp:655-704
+ *   dispatch      RayTracing::dispatchRayTracing(cmd, w, h, frame)        blok/src/renderer_raytracing.cpp:666-685
+ *   images out    storage images, bindings 4-8                            assets/shaders/raygen.rgen:55-59
+ *   accumulate    CudaTracer float4(sum.xyz, spp) + resetAccum            blok/src/cuda_tracer.cu:372-380, 478-482
+ *
+ * Conventions: every function returns 0 on success, <0 on error (BLOKB_E_*); blokb_last_error() gives the
+ * thread-local message. No exceptions cross the boundary. A context is single-owner (not thread-safe);
+ * one context per GPU. "Enqueue" calls are asynchronous on the given CUDA stream (a cudaStream_t passed as
+ * void*; NULL = the context's own stream) exactly like recording into the reference's command buffer.
+ * There is no CPU fallback: without a CUDA device every compute entry point fails with BLOKB_E_CUDA.
+ */
+#ifndef BLOKB200_H
+#define BLOKB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BLOKB_E_ARG (-1)         /* bad argument */
+#define BLOKB_E_CUDA (-2)        /* CUDA runtime error / no device */
+#define BLOKB_E_UNSUPPORTED (-3) /* world layout outside what the reference's builder produces */
+#define BLOKB_E_STATE (-4)       /* call order (e.g. trace before upload / set_frame) */
+
+/* blok::SvoNode — blok/include/svo.hpp:23-28 (mirrored in assets/shaders/intersect.rint:11-16). */
+typedef struct blokb_svo_node {
+    uint32_t childMask;  /* bits 0-7: child i present; i = x | y<<1 | z<<2 */
+    uint32_t firstChild; /* chunk-relative index of child 0; 0xFFFFFFFF = none */
+    uint32_t materialId;
+    float occupancy; /* > 0 => filled leaf */
+} blokb_svo_node;
+
+/* blok::SubChunkGpu — blok/include/resources.hpp:170-184 (intersect.rint:18-27). One per non-empty 16^3 region;
+ * its array index is the reference's gl_PrimitiveID. */
+typedef struct blokb_subchunk {
+    uint32_t nodeOffset, rootNodeIndex, nodeCount, startDepth;
+    float worldMin[3];
+    float subChunkSize;
+    float worldMax[3];
+    float pad0;
+} blokb_subchunk;
+
+/* blok::MaterialGpu — blok/include/material.hpp:88-114 (hit.rchit:28-33). */
+typedef struct blokb_material {
+    float albedo[3];
+    uint32_t flags; /* metal8<<24 | rough8<<16 | type4<<12 | alpha4<<8 | spec8 */
+    float emission[3];
+    float ior;
+} blokb_material;
+
+/* blok::FrameUBO — blok/include/resources.hpp:103-150 (raygen.rgen:13-53), std140, 560 bytes, column-major. */
+typedef struct blokb_frame_ubo {
+    float view[16], proj[16], invView[16], invProj[16], prevView[16], prevProj[16], prevViewProj[16];
+    float camPos[3];
+    float deltaTime;
+    float prevCamPos[3];
+    uint32_t depth;
+    uint32_t frameCount, sampleCount, screenWidth, screenHeight;
+    float temporalAlpha, momentAlpha, varianceClipGamma, depthThreshold;
+    float normalThreshold, phiColor, phiNormal, phiDepth;
+    int32_t atrousIteration, stepSize;
+    float varianceBoost;
+    int32_t minHistoryLength;
+    float jitterOffset[2];
+    float _padding[2];
+} blokb_frame_ubo;
+
+/* blok::Camera — blok/include/camera.hpp:15-59. */
+typedef struct blokb_camera {
+    float position[3];
+    float yaw, pitch, fov; /* degrees */
+} blokb_camera;
+
+/* Per-ray result. node = the reference's global SVO node index of the hit leaf (sub.nodeOffset + relative index,
+ * intersect.rint:196), material = that node's materialId, t = the reported hit distance (item.tEntry),
+ * facePrim = face (0..5: +X,-X,+Y,-Y,+Z,-Z; intersect.rint:58-68) | gl_PrimitiveID << 3.
+ * Miss: node = material = facePrim = 0xFFFFFFFF, t = -1. */
+typedef struct blokb_hit {
+    uint32_t node;
+    uint32_t material;
+    float t;
+    uint32_t facePrim;
+} blokb_hit;
+
+/* Device pointers owned by the context (valid until the next set_frame with a different size / destroy). */
+typedef struct blokb_buffers {
+    blokb_hit* hit;        /* w*h       primary-hit records (trace_primary / trace_primary_shadow) */
+    uint8_t* shadow;       /* w*h       0 = no shadow ray cast, 1 = lit, 2 = sun-shadowed (trace_primary_shadow) */
+    float* color;          /* w*h*4 f32 outColor          (binding 4, rgba32f) */
+    float* worldPos;       /* w*h*4 f32 outWorldPosition  (binding 5, rgba32f) */
+    uint16_t* normalRough; /* w*h*4 f16 outNormalRoughness(binding 6, rgba16f) */
+    uint8_t* albedoMetal;  /* w*h*4 u8  outAlbedoMetallic (binding 7, rgba8 unorm) */
+    uint16_t* motion;      /* w*h*2 f16 outMotionVectors  (binding 8, rg16f) */
+    float* accum;          /* w*h*4 f32 (sum.rgb, spp)    (cuda_tracer.cu:372-380) */
+    uint32_t width, height;
+} blokb_buffers;
+
+enum blokb_image {
+    BLOKB_IMG_HIT = 0,
+    BLOKB_IMG_SHADOW = 1,
+    BLOKB_IMG_COLOR = 2,
+    BLOKB_IMG_WORLDPOS = 3,
+    BLOKB_IMG_NORMALROUGH = 4,
+    BLOKB_IMG_ALBEDOMETAL = 5,
+    BLOKB_IMG_MOTION = 6,
+    BLOKB_IMG_ACCUM = 7
+};
+
+/* Sizes of the GPU-resident compact layout built by blokb_upload_world. */
+typedef struct blokb_world_stats {
+    uint64_t nodes, subChunks, materials; /* as uploaded */
+    uint64_t bricks, blocks, voxels;      /* 4^3 bricks, non-empty 2^3 leaf blocks, filled voxels */
+    uint64_t compactBytes;                /* bytes of the traversal structure (masks, bricks, tables) */
+    int32_t gridOrigin[3], gridDim[3];    /* voxel coordinates of the top grid, extent in voxels */
+    int32_t levels;                       /* 4^levels >= max extent */
+    float buildMs, uploadMs;
+} blokb_world_stats;
+
+typedef struct blokb_ctx blokb_ctx;
+
+const char* blokb_last_error(void);
+int blokb_create(int device, blokb_ctx** out);
+void blokb_destroy(blokb_ctx* ctx);
+
+/* Scene in (Renderer::addWorld / updateWorld). Host pointers are borrowed for the call only. Builds the compact
+ * 64-bit-mask hierarchy and copies it (and the materials) to the device. A second call replaces the world. */
+int blokb_upload_world(blokb_ctx* ctx, const blokb_svo_node* nodes, size_t nNodes, const blokb_subchunk* subs, size_t nSubs,
+                       const blokb_material* materials, size_t nMaterials);
+int blokb_world_stats_get(blokb_ctx* ctx, blokb_world_stats* out);
+
+/* Frame in (binding 3). (Re)allocates the output images when the size changes. */
+int blokb_set_frame(blokb_ctx* ctx, const blokb_frame_ubo* frame);
+/* Host helper: Camera::view()/projection() + fillFrameUBO for a first frame without TAA jitter
+ * (camera.hpp:42-59; renderer_draw.cpp:52-89; renderer_denoising.cpp:655-704). Pure host code. */
+int blokb_camera_frame(const blokb_camera* cam, uint32_t width, uint32_t height, uint32_t frameCount, uint32_t sampleCount,
+                       blokb_frame_ubo* out);
+
+/* Dispatch (enqueue only). */
+int blokb_trace_primary(blokb_ctx* ctx, void* stream);        /* sample-0 primary rays -> buffers.hit */
+int blokb_trace_primary_shadow(blokb_ctx* ctx, void* stream); /* + sun shadow ray per lit hit -> buffers.shadow */
+int blokb_render(blokb_ctx* ctx, void* stream);               /* full raygen.rgen: frame.sampleCount spp -> 5 images */
+int blokb_trace_path(blokb_ctx* ctx, uint32_t sampleBegin, uint32_t sampleEnd, void* stream); /* accum += samples */
+int blokb_resolve(blokb_ctx* ctx, void* stream);              /* color = accum.rgb / accum.a, firefly clamp */
+int blokb_reset_accum(blokb_ctx* ctx, void* stream);          /* CudaTracer::resetAccum */
+/* Arbitrary rays (device pointers): rays = n x {ox,oy,oz,dx,dy,dz,tmin,tmax}; anyHit != 0 = shadow-ray rules. */
+int blokb_trace_rays(blokb_ctx* ctx, const float* dRays, size_t n, int anyHit, blokb_hit* dOut, void* stream);
+/* Same with HOST buffers: copies in, traces, copies out, synchronises. */
+int blokb_trace_rays_host(blokb_ctx* ctx, const float* rays, size_t n, int anyHit, blokb_hit* out);
+
+/* Images out. */
+int blokb_get_buffers(blokb_ctx* ctx, blokb_buffers* out);
+int blokb_readback(blokb_ctx* ctx, int image, void* host, size_t bytes); /* stream-ordered copy + sync */
+int blokb_sync(blokb_ctx* ctx);
+/* Number of kernel launches this context has enqueued so far. */
+uint64_t blokb_launch_count(blokb_ctx* ctx);
+/* Profiling aid: while enabled, kernels add {DDA steps, rays traced by render/path kernels} to two device
+ * counters (slower instrumented kernel variants); blokb_stats_read copies them out ([0] steps, [1] rays). */
+int blokb_stats_enable(blokb_ctx* ctx, int on);
+int blokb_stats_read(blokb_ctx* ctx, uint64_t* stepsAndRays);
+/* The context's own CUDA stream (cudaStream_t). */
+void* blokb_stream(blokb_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BLOKB200_H */

@@ -1,0 +1,89 @@
+// TEST INFRASTRUCTURE ONLY — CPU build of the product's device functions (traverse.cuh, shade.cuh, scene_build.cpp)
+// through the BLOKB_HD shim in blok_b200/csrc/hd.h. It exists so that the DDA's logic (not its performance) can be
+// checked against the oracle in a container without a GPU, and so that world-size-2 sharding tests can run on CPU.
+// Nothing in the product loads this library; the product has no CPU path.
+#include <atomic>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../blok_b200/csrc/scene_build.h"
+#include "../../blok_b200/csrc/shade.cuh"
+
+using namespace blokb;
+
+namespace {
+struct Emu {
+    HostWorld hw;
+    DeviceWorld dw{};
+    std::vector<blokb_material> mats;
+};
+template <class F>
+void pfor(size_t n, int nt, F&& fn) {
+    if (nt <= 1) { fn(0, n); return; }
+    std::vector<std::thread> th; std::atomic<size_t> next{0};
+    for (int t = 0; t < nt; t++) th.emplace_back([&] { for (;;) { size_t b = next.fetch_add(4096); if (b >= n) break; fn(b, std::min(n, b + 4096)); } });
+    for (auto& x : th) x.join();
+}
+}  // namespace
+
+extern "C" {
+void* emu_create(const blokb_svo_node* nodes, size_t nNodes, const blokb_subchunk* subs, size_t nSubs, const blokb_material* mats, size_t nMat,
+                 char* errOut, size_t errCap, int* rcOut) {
+    Emu* e = new Emu;
+    std::string err;
+    int rc = build_host_world(nodes, nNodes, subs, nSubs, e->hw, err);
+    if (rcOut) *rcOut = rc;
+    if (rc) { if (errOut && errCap) { std::strncpy(errOut, err.c_str(), errCap - 1); errOut[errCap - 1] = 0; } delete e; return nullptr; }
+    HostWorld& h = e->hw; DeviceWorld& d = e->dw;
+    for (int a = 0; a < 3; a++) { d.origin[a] = h.origin[a]; d.dim[a] = h.dim[a]; }
+    d.levels = h.levels; d.matWide = h.matWide;
+    for (int k = 3; k <= h.levels; k++) { d.dense[k] = h.dense[k].data(); for (int a = 0; a < 3; a++) d.denseDim[k][a] = h.denseDim[k][a]; }
+    d.topGrid = h.topGrid.data(); d.subs = h.subs.data(); d.bricks = h.bricks.data(); d.blockFirstLeaf = h.blockFirstLeaf.data();
+    d.voxelMat = h.matWide ? (const void*)h.mat32.data() : (const void*)h.mat16.data();
+    e->mats.assign(mats, mats + nMat);
+    if (e->mats.empty()) e->mats.push_back(blokb_material{{0.8f, 0.8f, 0.8f}, 127u << 16, {0, 0, 0}, 0.f});
+    d.materials = reinterpret_cast<const float4*>(e->mats.data()); d.nMaterials = (uint32_t)e->mats.size();
+    return e;
+}
+void emu_destroy(void* p) { delete (Emu*)p; }
+void emu_stats(void* p, uint64_t* out /* bricks, blocks, voxels, compactBytes, levels, matWide */) {
+    Emu* e = (Emu*)p;
+    out[0] = e->hw.bricks.size(); out[1] = e->hw.blockFirstLeaf.size(); out[2] = e->hw.voxels; out[3] = e->hw.compactBytes(); out[4] = e->hw.levels; out[5] = e->hw.matWide;
+}
+// rays n x 8 -> blokb_hit n; returns total DDA steps
+uint64_t emu_trace(void* p, const float* rays, size_t n, blokb_hit* out, int nThreads) {
+    Emu* e = (Emu*)p;
+    std::atomic<uint64_t> total{0};
+    pfor(n, nThreads, [&](size_t b, size_t en) {
+        uint64_t st = 0;
+        for (size_t i = b; i < en; i++) {
+            const float* r = rays + 8 * i;
+            HitRec h; uint32_t steps = 0;
+            if (traverse<true>(e->dw, r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7], h, steps)) out[i] = blokb_hit{h.node, h.material, h.t, h.facePrim};
+            else out[i] = blokb_hit{0xFFFFFFFFu, 0xFFFFFFFFu, -1.0f, 0xFFFFFFFFu};
+            st += steps;
+        }
+        total += st;
+    });
+    return total;
+}
+// radiance sum of samples [sBegin, sEnd) per pixel (k_path without the accumulate), out = w*h*4 floats (sum.rgb, count)
+void emu_path(void* p, const blokb_frame_ubo* f, uint32_t sBegin, uint32_t sEnd, float* out, int nThreads) {
+    Emu* e = (Emu*)p;
+    FrameDev F;
+    std::memcpy(F.invView, f->invView, 64); std::memcpy(F.invProj, f->invProj, 64); std::memcpy(F.prevViewProj, f->prevViewProj, 64);
+    std::memcpy(F.camPos, f->camPos, 12);
+    F.frameCount = f->frameCount; F.sampleCount = f->sampleCount; F.width = f->screenWidth; F.height = f->screenHeight;
+    const size_t n = size_t(F.width) * F.height;
+    pfor(n, nThreads, [&](size_t b, size_t en) {
+        for (size_t i = b; i < en; i++) {
+            uint32_t px = uint32_t(i % F.width), py = uint32_t(i / F.width), rays = 0, steps = 0;
+            F3 acc = f3(0.f);
+            for (uint32_t s = sBegin; s < sEnd; s++) acc = acc + path_sample<false>(e->dw, F, px, py, s, nullptr, rays, steps);
+            out[4 * i] = acc.x; out[4 * i + 1] = acc.y; out[4 * i + 2] = acc.z; out[4 * i + 3] = float(sEnd - sBegin);
+        }
+    });
+}
+}
