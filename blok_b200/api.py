@@ -1,0 +1,299 @@
+"""ctypes binding of include/blokb200.h plus a thin host-side mirror of the reference's seams.
+
+Class / method names follow the reference so that callers (and the parity tests) read like code written
+against blok itself:
+
+    Renderer.add_world(world)        <- Renderer::addWorld(WorldSvoGpu&)          blok/include/renderer.hpp:40-54
+    Renderer.update_world(world)     <- Renderer::updateWorld()                    blok/include/renderer.hpp:55-71
+    Renderer.render(camera | ubo)    <- Renderer::render(const Camera&, float dt)  blok/include/renderer.hpp:34
+    Renderer.reset_accum()           <- CudaTracer::resetAccum()                   blok/src/cuda_tracer.cu:478-482
+    WorldSvoGpu(nodes, subs, mats)   <- blok::WorldSvoGpu                          blok/include/resources.hpp:195-210
+    Camera(position, yaw, pitch, fov)<- blok::Camera                               blok/include/camera.hpp:15-59
+
+There is no CPU fallback: if libblokb200.so is missing this module raises at import of the library, and every
+compute call fails loudly (BlokbError) when no CUDA device is present.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libblokb200.so")
+
+NODE_DT = np.dtype([("childMask", "<u4"), ("firstChild", "<u4"), ("materialId", "<u4"), ("occupancy", "<f4")])
+SUB_DT = np.dtype([("nodeOffset", "<u4"), ("rootNodeIndex", "<u4"), ("nodeCount", "<u4"), ("startDepth", "<u4"),
+                   ("worldMin", "<f4", 3), ("subChunkSize", "<f4"), ("worldMax", "<f4", 3), ("pad0", "<f4")])
+MAT_DT = np.dtype([("albedo", "<f4", 3), ("flags", "<u4"), ("emission", "<f4", 3), ("ior", "<f4")])
+HIT_DT = np.dtype([("node", "<u4"), ("material", "<u4"), ("t", "<f4"), ("facePrim", "<u4")])
+assert NODE_DT.itemsize == 16 and SUB_DT.itemsize == 48 and MAT_DT.itemsize == 32 and HIT_DT.itemsize == 16
+
+IMG_HIT, IMG_SHADOW, IMG_COLOR, IMG_WORLDPOS, IMG_NORMALROUGH, IMG_ALBEDOMETAL, IMG_MOTION, IMG_ACCUM = range(8)
+
+_vp = C.c_void_p
+
+
+class BlokbError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"blokb error {code}: {msg}")
+        self.code = code
+
+
+class FrameUBO(C.Structure):
+    """blok::FrameUBO (resources.hpp:103-150), 560 bytes."""
+    _fields_ = [(n, C.c_float * 16) for n in ("view", "proj", "invView", "invProj", "prevView", "prevProj", "prevViewProj")] + [
+        ("camPos", C.c_float * 3), ("deltaTime", C.c_float), ("prevCamPos", C.c_float * 3), ("depth", C.c_uint32),
+        ("frameCount", C.c_uint32), ("sampleCount", C.c_uint32), ("screenWidth", C.c_uint32), ("screenHeight", C.c_uint32),
+        ("temporalAlpha", C.c_float), ("momentAlpha", C.c_float), ("varianceClipGamma", C.c_float), ("depthThreshold", C.c_float),
+        ("normalThreshold", C.c_float), ("phiColor", C.c_float), ("phiNormal", C.c_float), ("phiDepth", C.c_float),
+        ("atrousIteration", C.c_int32), ("stepSize", C.c_int32), ("varianceBoost", C.c_float), ("minHistoryLength", C.c_int32),
+        ("jitterOffset", C.c_float * 2), ("_padding", C.c_float * 2)]
+
+    @staticmethod
+    def from_bytes(b):
+        b = bytes(np.asarray(b, dtype=np.uint8).tobytes()) if not isinstance(b, (bytes, bytearray)) else bytes(b)
+        assert len(b) == 560
+        return FrameUBO.from_buffer_copy(b)
+
+    def to_numpy(self):
+        return np.frombuffer(bytes(self), dtype=np.uint8).copy()
+
+
+assert C.sizeof(FrameUBO) == 560
+
+
+class CameraC(C.Structure):
+    _fields_ = [("position", C.c_float * 3), ("yaw", C.c_float), ("pitch", C.c_float), ("fov", C.c_float)]
+
+
+class Buffers(C.Structure):
+    _fields_ = [("hit", _vp), ("shadow", _vp), ("color", _vp), ("worldPos", _vp), ("normalRough", _vp), ("albedoMetal", _vp),
+                ("motion", _vp), ("accum", _vp), ("width", C.c_uint32), ("height", C.c_uint32)]
+
+
+class WorldStats(C.Structure):
+    _fields_ = [("nodes", C.c_uint64), ("subChunks", C.c_uint64), ("materials", C.c_uint64), ("bricks", C.c_uint64),
+                ("blocks", C.c_uint64), ("voxels", C.c_uint64), ("compactBytes", C.c_uint64), ("gridOrigin", C.c_int32 * 3),
+                ("gridDim", C.c_int32 * 3), ("levels", C.c_int32), ("buildMs", C.c_float), ("uploadMs", C.c_float)]
+
+    def as_dict(self):
+        d = {}
+        for n, _ in self._fields_:
+            v = getattr(self, n)
+            d[n] = list(v) if hasattr(v, "__len__") else v
+        return d
+
+
+# Every symbol include/blokb200.h declares (tests check that the library exports each one).
+EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_world", "blokb_world_stats_get", "blokb_set_frame",
+           "blokb_camera_frame", "blokb_trace_primary", "blokb_trace_primary_shadow", "blokb_render", "blokb_trace_path",
+           "blokb_resolve", "blokb_reset_accum", "blokb_trace_rays", "blokb_trace_rays_host", "blokb_get_buffers",
+           "blokb_readback", "blokb_sync", "blokb_launch_count", "blokb_stats_enable", "blokb_stats_read", "blokb_stream",
+           "blokb_worldgen_pack", "blokb_worldgen_counts", "blokb_worldgen_copy", "blokb_worldgen_nodes", "blokb_worldgen_subs",
+           "blokb_worldgen_free"]
+
+_lib = None
+
+
+def load_library():
+    """Load libblokb200.so (built in-tree by blok_b200/csrc/Makefile). Raises if it is missing: no fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} not built — run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "or `make -C blok_b200/csrc`; blok_b200 has no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    L.blokb_last_error.restype = C.c_char_p
+    L.blokb_create.argtypes = [C.c_int, C.POINTER(_vp)]
+    L.blokb_destroy.argtypes = [_vp]
+    L.blokb_destroy.restype = None
+    L.blokb_upload_world.argtypes = [_vp, _vp, C.c_size_t, _vp, C.c_size_t, _vp, C.c_size_t]
+    L.blokb_world_stats_get.argtypes = [_vp, C.POINTER(WorldStats)]
+    L.blokb_set_frame.argtypes = [_vp, C.POINTER(FrameUBO)]
+    L.blokb_camera_frame.argtypes = [C.POINTER(CameraC), C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(FrameUBO)]
+    for f in ("blokb_trace_primary", "blokb_trace_primary_shadow", "blokb_render", "blokb_resolve", "blokb_reset_accum"):
+        getattr(L, f).argtypes = [_vp, _vp]
+    L.blokb_trace_path.argtypes = [_vp, C.c_uint32, C.c_uint32, _vp]
+    L.blokb_trace_rays.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp, _vp]
+    L.blokb_trace_rays_host.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp]
+    L.blokb_get_buffers.argtypes = [_vp, C.POINTER(Buffers)]
+    L.blokb_readback.argtypes = [_vp, C.c_int, _vp, C.c_size_t]
+    L.blokb_sync.argtypes = [_vp]
+    L.blokb_launch_count.argtypes = [_vp]
+    L.blokb_launch_count.restype = C.c_uint64
+    L.blokb_stats_enable.argtypes = [_vp, C.c_int]
+    L.blokb_stats_read.argtypes = [_vp, _vp]
+    L.blokb_stream.argtypes = [_vp]
+    L.blokb_stream.restype = _vp
+    L.blokb_worldgen_pack.argtypes = [_vp, _vp, C.c_size_t]
+    L.blokb_worldgen_pack.restype = _vp
+    L.blokb_worldgen_counts.argtypes = [_vp, _vp, _vp]
+    L.blokb_worldgen_counts.restype = None
+    L.blokb_worldgen_copy.argtypes = [_vp, _vp, _vp]
+    L.blokb_worldgen_copy.restype = None
+    L.blokb_worldgen_free.argtypes = [_vp]
+    L.blokb_worldgen_free.restype = None
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(_vp)
+
+
+def _ck(rc):
+    if rc != 0:
+        raise BlokbError(rc, load_library().blokb_last_error().decode())
+
+
+class WorldSvoGpu:
+    """blok::WorldSvoGpu (resources.hpp:195-210): the three host arrays the reference uploads."""
+
+    def __init__(self, global_nodes, global_sub_chunks, materials):
+        self.globalNodes = np.ascontiguousarray(global_nodes, dtype=NODE_DT)
+        self.globalSubChunks = np.ascontiguousarray(global_sub_chunks, dtype=SUB_DT)
+        self.materials = np.ascontiguousarray(materials, dtype=MAT_DT)
+
+    @staticmethod
+    def from_voxels(xyz, material_ids, materials):
+        """ChunkManager(128,1).setVoxelMaterial per voxel + rebuildDirtyChunks + packChunksToGpuSvo (host, C++)."""
+        L = load_library()
+        xyz = np.ascontiguousarray(xyz, np.int32).reshape(-1, 3)
+        mid = np.ascontiguousarray(material_ids, np.uint32)
+        assert len(mid) == len(xyz)
+        h = L.blokb_worldgen_pack(_ptr(xyz), _ptr(mid), len(mid))
+        if not h:
+            raise MemoryError("blokb_worldgen_pack")
+        try:
+            n = (C.c_uint64 * 2)()
+            L.blokb_worldgen_counts(h, C.byref(n, 0), C.byref(n, 8))
+            nodes = np.empty(n[0], NODE_DT)
+            subs = np.empty(n[1], SUB_DT)
+            L.blokb_worldgen_copy(h, _ptr(nodes), _ptr(subs))
+        finally:
+            L.blokb_worldgen_free(h)
+        return WorldSvoGpu(nodes, subs, materials)
+
+
+class Camera:
+    """blok::Camera (camera.hpp:15-59)."""
+
+    def __init__(self, position=(0.0, 10.0, -5.0), yaw=0.0, pitch=0.0, fov=60.0):
+        self.position, self.yaw, self.pitch, self.fov = tuple(float(v) for v in position), float(yaw), float(pitch), float(fov)
+
+    def frame(self, width, height, frame_count=0, sample_count=8) -> FrameUBO:
+        """view()/projection() + fillFrameUBO; sample_count defaults to the reference's 8 (renderer_denoising.cpp:683)."""
+        c = CameraC((C.c_float * 3)(*self.position), self.yaw, self.pitch, self.fov)
+        out = FrameUBO()
+        _ck(load_library().blokb_camera_frame(C.byref(c), width, height, frame_count, sample_count, C.byref(out)))
+        return out
+
+
+class Renderer:
+    """Headless stand-in for blok::Renderer's ray-tracing path on one GPU (one context per device)."""
+
+    def __init__(self, width=1280, height=720, device=0):  # app.cpp:95 default size
+        self.L = load_library()
+        self.width, self.height, self.device = width, height, device
+        self._ctx = _vp()
+        _ck(self.L.blokb_create(device, C.byref(self._ctx)))
+        self._frame = None
+
+    def close(self):
+        if self._ctx:
+            self.L.blokb_destroy(self._ctx)
+            self._ctx = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- scene in
+    def add_world(self, world: WorldSvoGpu):
+        _ck(self.L.blokb_upload_world(self._ctx, _ptr(world.globalNodes), len(world.globalNodes), _ptr(world.globalSubChunks),
+                                      len(world.globalSubChunks), _ptr(world.materials), len(world.materials)))
+
+    update_world = add_world
+
+    def world_stats(self) -> dict:
+        s = WorldStats()
+        _ck(self.L.blokb_world_stats_get(self._ctx, C.byref(s)))
+        return s.as_dict()
+
+    # ---- frame in
+    def set_frame(self, frame):
+        if isinstance(frame, Camera):
+            frame = frame.frame(self.width, self.height)
+        elif not isinstance(frame, FrameUBO):
+            frame = FrameUBO.from_bytes(frame)
+        self._frame = frame
+        self.width, self.height = frame.screenWidth, frame.screenHeight
+        _ck(self.L.blokb_set_frame(self._ctx, C.byref(frame)))
+
+    # ---- dispatch (asynchronous; stream = cudaStream_t as int, None = the context's stream)
+    def render(self, frame=None, stream=None):
+        """One frame of raygen.rgen: frame.sampleCount spp -> the five G-buffer images."""
+        if frame is not None:
+            self.set_frame(frame)
+        _ck(self.L.blokb_render(self._ctx, stream))
+
+    def trace_primary(self, frame=None, shadow=False, stream=None):
+        if frame is not None:
+            self.set_frame(frame)
+        _ck((self.L.blokb_trace_primary_shadow if shadow else self.L.blokb_trace_primary)(self._ctx, stream))
+
+    def trace_path(self, sample_begin, sample_end, stream=None):
+        _ck(self.L.blokb_trace_path(self._ctx, sample_begin, sample_end, stream))
+
+    def resolve(self, stream=None):
+        _ck(self.L.blokb_resolve(self._ctx, stream))
+
+    def reset_accum(self, stream=None):
+        _ck(self.L.blokb_reset_accum(self._ctx, stream))
+
+    def trace_rays(self, rays: np.ndarray, any_hit=False) -> np.ndarray:
+        """Host rays (n,8) f32 {o,d,tmin,tmax} -> (n,) HIT_DT, through the host-buffer C-ABI call."""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        out = np.empty(len(rays), HIT_DT)
+        _ck(self.L.blokb_trace_rays_host(self._ctx, _ptr(rays), len(rays), int(any_hit), _ptr(out)))
+        return out
+
+    def trace_rays_device(self, d_rays: int, n: int, d_out: int, any_hit=False, stream=None):
+        _ck(self.L.blokb_trace_rays(self._ctx, d_rays, n, int(any_hit), d_out, stream))
+
+    # ---- images out
+    def buffers(self) -> Buffers:
+        b = Buffers()
+        _ck(self.L.blokb_get_buffers(self._ctx, C.byref(b)))
+        return b
+
+    def readback(self, image: int) -> np.ndarray:
+        h, w = self.height, self.width
+        shape_dt = {IMG_HIT: ((h, w), HIT_DT), IMG_SHADOW: ((h, w), np.uint8), IMG_COLOR: ((h, w, 4), np.float32),
+                    IMG_WORLDPOS: ((h, w, 4), np.float32), IMG_NORMALROUGH: ((h, w, 4), np.float16),
+                    IMG_ALBEDOMETAL: ((h, w, 4), np.uint8), IMG_MOTION: ((h, w, 2), np.float16), IMG_ACCUM: ((h, w, 4), np.float32)}
+        shape, dt = shape_dt[image]
+        out = np.empty(shape, dt)
+        _ck(self.L.blokb_readback(self._ctx, image, _ptr(out), out.nbytes))
+        return out
+
+    def sync(self):
+        _ck(self.L.blokb_sync(self._ctx))
+
+    @property
+    def stream(self) -> int:
+        return self.L.blokb_stream(self._ctx)
+
+    def launch_count(self) -> int:
+        return int(self.L.blokb_launch_count(self._ctx))
+
+    def stats_enable(self, on=True):
+        _ck(self.L.blokb_stats_enable(self._ctx, int(on)))
+
+    def stats_read(self):
+        v = np.zeros(2, np.uint64)
+        _ck(self.L.blokb_stats_read(self._ctx, _ptr(v)))
+        return int(v[0]), int(v[1])

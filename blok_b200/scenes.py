@@ -1,0 +1,111 @@
+"""Deterministic synthetic voxel worlds: integer-hash noise only, no file I/O.
+
+  terrain(N)      heightfield shell h(x,z) = N/4 + N/8*fbm(x/N, z/N; 5 octaves value noise, seed 0xB10C),
+                  filled voxels {h-2 <= y <= h}, 8 materials by height band        (configs 3-5)
+  blob_mesh(N)    a solid "voxelised mesh": union of hash-placed ellipsoids, surface shell + sparse interior
+                  struts, 16 materials                                             (configs 1-2)
+Both return (xyz int32 (n,3), material ids uint32 (n,), materials MAT_DT table); feed them to
+WorldSvoGpu.from_voxels to get the reference's upload arrays.
+"""
+import numpy as np
+
+from .api import MAT_DT
+
+
+def _hash2(ix, iz, seed):
+    h = (ix.astype(np.uint32) * np.uint32(0x9E3779B1)) ^ (iz.astype(np.uint32) * np.uint32(0x85EBCA77)) ^ np.uint32(seed)
+    h ^= h >> np.uint32(15)
+    h *= np.uint32(0x2C1B3C6D)
+    h ^= h >> np.uint32(12)
+    h *= np.uint32(0x297A2D39)
+    h ^= h >> np.uint32(15)
+    return h.astype(np.float64) / 4294967296.0
+
+
+def _value_noise(x, z, seed):
+    ix, iz = np.floor(x).astype(np.int64), np.floor(z).astype(np.int64)
+    fx, fz = x - ix, z - iz
+    sx, sz = fx * fx * (3 - 2 * fx), fz * fz * (3 - 2 * fz)
+    a, b = _hash2(ix, iz, seed), _hash2(ix + 1, iz, seed)
+    c, d = _hash2(ix, iz + 1, seed), _hash2(ix + 1, iz + 1, seed)
+    return (a * (1 - sx) + b * sx) * (1 - sz) + (c * (1 - sx) + d * sx) * sz
+
+
+def fbm(u, v, octaves=5, seed=0xB10C):
+    s, amp, freq, norm = 0.0, 0.5, 4.0, 0.0
+    for o in range(octaves):
+        s = s + amp * _value_noise(u * freq, v * freq, seed + 101 * o)
+        norm += amp
+        amp *= 0.5
+        freq *= 2.0
+    return s / norm  # in [0,1)
+
+
+def default_materials(n=16):
+    """n+1 MaterialGpu records: id 0 = the reference's default grey (material.cpp:19-29), then a fixed palette;
+    one metallic, one dim emissive and one rough entry so every shading branch of raygen.rgen is exercised."""
+    m = np.zeros(n + 1, MAT_DT)
+    def flags(metal, rough, typ=0):
+        return (int(metal * 255) << 24) | (int(rough * 255) << 16) | (typ << 12) | (15 << 8) | int(0.5 * 255)
+    m[0]["albedo"] = (0.8, 0.8, 0.8)
+    m[0]["flags"] = flags(0.0, 0.5)
+    pal = [(0.35, 0.55, 0.25), (0.45, 0.40, 0.30), (0.55, 0.52, 0.50), (0.85, 0.85, 0.90), (0.25, 0.35, 0.65), (0.75, 0.65, 0.40),
+           (0.60, 0.25, 0.20), (0.30, 0.30, 0.32), (0.90, 0.75, 0.30), (0.20, 0.60, 0.55), (0.70, 0.40, 0.65), (0.95, 0.95, 0.95),
+           (0.15, 0.15, 0.18), (0.50, 0.70, 0.30), (0.80, 0.50, 0.25), (0.40, 0.45, 0.75)]
+    for i in range(1, n + 1):
+        m[i]["albedo"] = pal[(i - 1) % len(pal)]
+        m[i]["flags"] = flags(0.0, 0.6 + 0.05 * ((i * 7) % 7))
+    if n >= 8:
+        m[8]["flags"] = flags(1.0, 0.2, 1)              # metal
+        m[4]["flags"] = flags(0.0, 0.1)                 # glossy dielectric
+    if n >= 12:
+        m[12]["emission"] = (0.6, 0.5, 0.3)             # dim emissive (continues the path, raygen.rgen:265-277)
+        m[12]["ior"] = 1.0
+        m[12]["flags"] = flags(0.0, 0.5, 3)
+    return m
+
+
+def terrain(N=2048, seed=0xB10C, thickness=3, origin=(0, 0, 0)):
+    """3-voxel heightfield shell over an N x N footprint."""
+    xs = np.arange(N, dtype=np.float64)
+    X, Z = np.meshgrid(xs, xs, indexing="xy")
+    h = np.floor(N / 4 + N / 8 * fbm(X / N, Z / N, 5, seed)).astype(np.int32)
+    X = X.astype(np.int32).ravel(); Z = Z.astype(np.int32).ravel(); h = h.ravel()
+    xyz = np.empty((thickness, X.size, 3), np.int32)
+    for k in range(thickness):
+        xyz[k, :, 0] = X + origin[0]
+        xyz[k, :, 1] = h - k + origin[1]
+        xyz[k, :, 2] = Z + origin[2]
+    xyz = xyz.reshape(-1, 3)
+    hh = np.tile(h, thickness)
+    band = ((hh - N // 4) * 8 // max(N // 8, 1)).clip(0, 7).astype(np.uint32) + 1
+    return xyz, band, default_materials(16)
+
+
+def blob_mesh(N=512, seed=0x51DE, blobs=24):
+    """Solid union of ellipsoids in an N^3 box, voxelised as a 2-voxel surface shell plus every 8th interior
+    lattice line (keeps dense regions dense without billions of voxels)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    c = rng.uniform(0.2 * N, 0.8 * N, (blobs, 3))
+    r = rng.uniform(0.06 * N, 0.18 * N, (blobs, 3))
+    out_xyz, out_m = [], []
+    ys = np.arange(N, dtype=np.float32)
+    for z0 in range(0, N, 32):
+        zz = np.arange(z0, min(z0 + 32, N), dtype=np.float32)
+        Zg, Yg, Xg = np.meshgrid(zz, ys, ys, indexing="ij")
+        f = np.full(Zg.shape, np.inf, np.float32)
+        which = np.zeros(Zg.shape, np.uint8)
+        for i in range(blobs):
+            d = ((Xg - c[i, 0]) / r[i, 0]) ** 2 + ((Yg - c[i, 1]) / r[i, 1]) ** 2 + ((Zg - c[i, 2]) / r[i, 2]) ** 2
+            upd = d < f
+            f = np.where(upd, d, f)
+            which = np.where(upd, np.uint8(i), which)
+        inside = f < 1.0
+        rmin = r.min(axis=1)[which]
+        shell = inside & (f > (1.0 - 2.5 / rmin) ** 2)
+        xi, yi, zi = Xg.astype(np.int32), Yg.astype(np.int32), Zg.astype(np.int32)
+        struts = inside & ((((xi & 7) == 0) & ((yi & 7) == 0)) | (((yi & 7) == 0) & ((zi & 7) == 0)) | (((xi & 7) == 0) & ((zi & 7) == 0)))
+        keep = shell | struts
+        out_xyz.append(np.stack([xi[keep], yi[keep], zi[keep]], 1))
+        out_m.append((which[keep].astype(np.uint32) % 16) + 1)
+    return np.concatenate(out_xyz).astype(np.int32), np.concatenate(out_m).astype(np.uint32), default_materials(16)

@@ -1,0 +1,64 @@
+"""Partition of one frame across GPUs. Rays are independent and the scene is replicated, so the
+only exchange is the reduce / gather of per-GPU accumulation buffers over torch.distributed (NCCL on GPUs, gloo in
+the CPU tests).
+
+  sample_range(rank, world, spp)  path tracing: GPU g renders sampleIdx in [spp*g/G, spp*(g+1)/G). With raygen.rgen's
+                                  per-(pixel, frame, sample) seeding (raygen.rgen:92-99) the union of samples is exactly
+                                  the single-GPU sample set; only the fp32 summation order differs.
+  row_band(rank, world, height)   primary rays: contiguous 8-row-aligned bands (a kernel block is 32x8 pixels).
+  allreduce_accum(t)              sum of (sum.rgb, spp) buffers; every rank ends with the full frame.
+  reduce_scatter_resolve(...)     reduce-scatter of the accumulation buffer, divide-by-spp + firefly clamp on the owned
+                                  slice, all-gather of the resolved slices (1/G of the all-reduce's resolve work).
+"""
+from typing import Tuple
+
+
+def sample_range(rank: int, world: int, spp: int) -> Tuple[int, int]:
+    if not (0 <= rank < world):
+        raise ValueError("rank out of range")
+    return (spp * rank) // world, (spp * (rank + 1)) // world
+
+
+def row_band(rank: int, world: int, height: int, align: int = 8) -> Tuple[int, int]:
+    if not (0 <= rank < world):
+        raise ValueError("rank out of range")
+    blocks = (height + align - 1) // align
+    b0, b1 = (blocks * rank) // world, (blocks * (rank + 1)) // world
+    return min(b0 * align, height), min(b1 * align, height)
+
+
+def allreduce_accum(accum, group=None):
+    """accum: torch tensor (h, w, 4) float32 on this rank's device; summed in place across ranks."""
+    import torch.distributed as dist
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(accum, op=dist.ReduceOp.SUM, group=group)
+    return accum
+
+
+def resolve(accum):
+    """color = sum.rgb / spp with raygen.rgen's firefly clamp (:383-392), as torch ops (used on the reduced slice)."""
+    import torch
+    c = accum[..., :3] / accum[..., 3:4]
+    mv = c.max(dim=-1, keepdim=True).values
+    c = torch.where(mv > 100.0, c * (100.0 / mv), c)
+    return torch.cat([c, torch.ones_like(c[..., :1])], dim=-1)
+
+
+def reduce_scatter_resolve(accum, group=None):
+    """accum (h, w, 4) f32, h*w divisible by world. Returns the resolved full frame (h, w, 4) on every rank."""
+    import torch
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return resolve(accum)
+    G = dist.get_world_size(group)
+    flat = accum.reshape(-1, 4)
+    n = flat.shape[0]
+    if n % G:
+        dist.all_reduce(accum, op=dist.ReduceOp.SUM, group=group)
+        return resolve(accum)
+    mine = torch.empty((n // G, 4), dtype=flat.dtype, device=flat.device)
+    dist.reduce_scatter_tensor(mine, flat.contiguous(), op=dist.ReduceOp.SUM, group=group)
+    res = resolve(mine)
+    out = torch.empty((n, 4), dtype=flat.dtype, device=flat.device)
+    dist.all_gather_into_tensor(out, res.contiguous(), group=group)
+    return out.reshape(accum.shape)

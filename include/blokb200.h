@@ -170,6 +170,16 @@ int blokb_stats_read(blokb_ctx* ctx, uint64_t* stepsAndRays);
 /* The context's own CUDA stream (cudaStream_t). */
 void* blokb_stream(blokb_ctx* ctx);
 
+/* Host helper (no GPU involved): voxel list -> the reference's upload arrays, restating ChunkManager(128, 1.0f) +
+ * rebuildDirtyChunks + packChunksToGpuSvo (chunk_manager.cpp:106-140, 234-314; svo.cpp:59-101). Chunks are emitted
+ * sorted by (z, y, x); the reference's order is that of a std::unordered_map (unspecified). */
+void* blokb_worldgen_pack(const int32_t* xyz, const uint32_t* materialId, size_t n);
+void blokb_worldgen_counts(void* world, uint64_t* nNodes, uint64_t* nSubs);
+void blokb_worldgen_copy(void* world, blokb_svo_node* nodes, blokb_subchunk* subs);
+const blokb_svo_node* blokb_worldgen_nodes(void* world);
+const blokb_subchunk* blokb_worldgen_subs(void* world);
+void blokb_worldgen_free(void* world);
+
 #ifdef __cplusplus
 }
 #endif
