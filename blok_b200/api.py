@@ -280,6 +280,27 @@ class Renderer:
         _ck(self.L.blokb_readback(self._ctx, image, _ptr(out), out.nbytes))
         return out
 
+    def readback_into(self, image: int, host_ptr: int, nbytes: int):
+        """Stream-ordered copy of one image into caller-owned host memory (pinned for full PCIe speed) + sync."""
+        _ck(self.L.blokb_readback(self._ctx, image, host_ptr, nbytes))
+
+    def device_array(self, image: int):
+        """Zero-copy view of a context-owned device image as an object exposing __cuda_array_interface__ (for
+        torch.as_tensor(..., device="cuda") — used to hand the accumulation buffer to torch.distributed / NCCL)."""
+        b = self.buffers()
+        h, w = int(b.height), int(b.width)
+        table = {IMG_HIT: (b.hit, (h, w, 4), "<u4"), IMG_SHADOW: (b.shadow, (h, w), "|u1"), IMG_COLOR: (b.color, (h, w, 4), "<f4"),
+                 IMG_WORLDPOS: (b.worldPos, (h, w, 4), "<f4"), IMG_NORMALROUGH: (b.normalRough, (h, w, 4), "<f2"),
+                 IMG_ALBEDOMETAL: (b.albedoMetal, (h, w, 4), "|u1"), IMG_MOTION: (b.motion, (h, w, 2), "<f2"),
+                 IMG_ACCUM: (b.accum, (h, w, 4), "<f4")}
+        ptr, shape, typestr = table[image]
+
+        class _View:
+            __cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (int(ptr), False), "version": 2, "strides": None}
+        v = _View()
+        v._owner = self  # keep the context alive as long as the view is
+        return v
+
     def sync(self):
         _ck(self.L.blokb_sync(self._ctx))
 

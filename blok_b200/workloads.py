@@ -1,0 +1,50 @@
+"""Named benchmark workloads = BASELINE.json's configs at full size; all synthetic and deterministic.
+
+  c2  512^3 dense blob "mesh", 1920x1080, primary + sun shadow rays          (BASELINE configs[1])
+  c3  2048^3 heightfield-shell terrain, 3840x2160, primary rays              (configs[2])  <- bench.py headline
+  c4  the c3 scene path traced: 64 spp, <=2 bounces + 1 shadow ray, spp sharded across GPUs   (configs[3])
+  t1  96^3 terrain, 256x144 — CPU-test / smoke scale of the same shapes
+
+Every workload gives {scene generator, N, width, height, camera, kind, spp}. Camera poses follow §8(d): the c3/c4
+camera sits at (N/2, 0.6N, -0.2N) looking along +z, pitched -25 degrees.
+"""
+from . import scenes
+from .api import Camera, WorldSvoGpu
+
+WORKLOADS = {
+    "c2": dict(scene="blob_mesh", N=512, width=1920, height=1080, kind="primary_shadow", spp=1,
+               cam=lambda N: Camera((-0.4 * N, 0.9 * N, -0.4 * N), 45.0, -25.0),
+               desc="512^3 dense voxelized blob mesh, 1920x1080 primary + sun shadow rays"),
+    "c3": dict(scene="terrain", N=2048, width=3840, height=2160, kind="primary", spp=1,
+               cam=lambda N: Camera((N / 2, 0.6 * N, -0.2 * N), 90.0, -25.0),
+               desc="2048^3 SVO terrain shell, 3840x2160 primary rays"),
+    "c4": dict(scene="terrain", N=2048, width=3840, height=2160, kind="path", spp=64,
+               cam=lambda N: Camera((N / 2, 0.6 * N, -0.2 * N), 90.0, -25.0),
+               desc="2048^3 SVO terrain shell, 3840x2160 path traced, 64 spp, 2 bounces + sun shadow ray"),
+    "t1": dict(scene="terrain", N=96, width=256, height=144, kind="primary", spp=1,
+               cam=lambda N: Camera((N / 2, 0.7 * N, -0.3 * N), 90.0, -25.0),
+               desc="96^3 terrain shell, 256x144 primary rays (test scale)"),
+}
+
+
+def build_world(name: str) -> WorldSvoGpu:
+    """Voxel set of the workload -> the reference's upload arrays (host C++ restatement of the reference builder)."""
+    w = WORKLOADS[name]
+    xyz, mid, mats = getattr(scenes, w["scene"])(w["N"])
+    return WorldSvoGpu.from_voxels(xyz, mid, mats)
+
+
+def camera_for(name: str, rank: int = 0) -> Camera:
+    """Rank r's camera: the §8(d) pose, translated along +x by 16 voxels per rank (weak scaling renders one frame per
+    GPU per step — the frames-in-flight of an 8-GPU box — so each rank needs its own view of the same scene)."""
+    w = WORKLOADS[name]
+    c = w["cam"](w["N"])
+    if rank:
+        c.position = (c.position[0] + 16.0 * rank, c.position[1], c.position[2])
+    return c
+
+
+def rays_per_step(name: str) -> int:
+    """Primary rays only (shadow / bounce rays are counted on the device for the kinds that cast them)."""
+    w = WORKLOADS[name]
+    return w["width"] * w["height"]
