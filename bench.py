@@ -245,7 +245,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     import blok_b200
-    from blok_b200 import IMG_ACCUM, IMG_HIT, IMG_SHADOW, workloads
+    from blok_b200 import IMG_ACCUM, IMG_HIT, IMG_SHADOW, sharding, workloads
 
     rank = int(os.environ.get("RANK", "0"))
     world_size = int(os.environ.get("WORLD_SIZE", "1"))
@@ -297,7 +297,7 @@ def run_ours(args):
         cam = workloads.camera_for(name, rank)
         ubo = cam.frame(W, H, 0, spp)
         r.set_frame(ubo)
-        s0, s1 = blok_b200.sharding.sample_range(rank, world_size, spp) if kind == "path" else (0, 1)
+        s0, s1 = sharding.sample_range(rank, world_size, spp) if kind == "path" else (0, 1)
         accum_t = torch.as_tensor(r.device_array(IMG_ACCUM), device=dev) if kind == "path" else None
 
         def step():
