@@ -2,7 +2,9 @@
 // Host C++20; device work lives in kernels.cu. Every CUDA call is checked; nothing here falls back to the CPU.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <chrono>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>

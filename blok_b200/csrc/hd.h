@@ -3,10 +3,13 @@
 // in a container without a GPU). The product library never runs this path: libblokb200.so contains device code only.
 #pragma once
 #if defined(__CUDACC__)
+#define BLOKB_ASSERT(c) ((void)0)
 #define BLOKB_HD __device__ __forceinline__
 #define BLOKB_D __device__ __forceinline__
 #else
+#include <cassert>
 #include <cmath>
+#define BLOKB_ASSERT(c) assert(c)
 #include <cstdint>
 #include <cstring>
 #define BLOKB_HD inline
@@ -15,5 +18,7 @@ static inline int __float2int_rd(float v) { return (int)std::floor(v); }
 static inline int __clz(uint32_t v) { return v ? __builtin_clz(v) : 32; }
 static inline int __popcll(unsigned long long v) { return __builtin_popcountll(v); }
 static inline uint32_t __float_as_uint(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
+static inline float __uint_as_float(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
+static inline float __fmaf_rn(float a, float b, float c) { return std::fmaf(a, b, c); }
 template <class T> static inline T __ldg(const T* p) { return *p; }
 #endif

@@ -1,0 +1,49 @@
+"""Summarise an .ncu-rep (read on the CPU box): key raw metrics + instruction share per source line.
+  python tools/ncu_summary.py gpurun_out/x.ncu-rep [top_n]"""
+import csv
+import io
+import subprocess
+import sys
+
+rep = sys.argv[1]
+top = int(sys.argv[2]) if len(sys.argv) > 2 else 30
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(io.StringIO(raw)))
+KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "lts__t_sector_hit_rate.pct", "l1tex__t_sector_hit_rate.pct", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
+        "l1tex__throughput.avg.pct_of_peak_sustained_active", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+        "smsp__issue_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum", "smsp__thread_inst_executed_per_inst_executed.ratio",
+        "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread", "launch__occupancy_limit_registers",
+        "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+        "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio", "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio", "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio", "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio", "smsp__sass_average_branch_targets_threads_uniform.pct",
+        "sm__cycles_elapsed.max", "smsp__cycles_active.avg"]
+hdr, units = rows[0], rows[1]
+for r in rows[2:]:
+    print("== kernel:", r[hdr.index("Kernel Name")][:90])
+    for k in KEYS:
+        if k in hdr:
+            print(f"  {k:95s} {r[hdr.index(k)]:>16s} {units[hdr.index(k)]}")
+src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
+cur, agg, tot = None, {}, 0
+for r in csv.reader(io.StringIO(src)):
+    if len(r) >= 2 and r[0] == "File Path":
+        cur = r[1].split("/")[-1]
+        continue
+    if len(r) < 8 or r[0] in ("Line No", "Function Name", ""):
+        continue
+    try:
+        n = int(r[7])
+    except ValueError:
+        continue
+    key = (cur, r[0], r[1][:100])
+    a = agg.setdefault(key, [0, 0])
+    a[0] += n
+    a[1] += int(r[4] or 0)
+    tot += n
+print(f"-- warp instructions by source line (total {tot}); share, stall samples")
+for (f, l, s), (n, samp) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+    print(f"{n / tot * 100:5.1f}% {samp:6d}  {f}:{l}  {s}")

@@ -28,11 +28,14 @@ def step():
         r.trace_path(0, min(wl["spp"], 8))
 
 
+ts = []
 for i in range(iters):
     t0 = time.perf_counter()
     step()
     r.sync()
-    print(f"iter {i}: {(time.perf_counter() - t0) * 1e3:.3f} ms")
+    ts.append((time.perf_counter() - t0) * 1e3)
+print(f"mode={os.environ.get('BLOKB_PRIMARY_MODE', '-')} refill={os.environ.get('BLOKB_REFILL', '-')} "
+      f"min {min(ts):.3f} ms  median {sorted(ts)[len(ts) // 2]:.3f} ms over {iters} iters")
 if "--stats" in sys.argv:
     r.stats_enable(True)
     step()
