@@ -121,13 +121,11 @@ int blokb_upload_world(blokb_ctx* c, const blokb_svo_node* nodes, size_t nNodes,
     for (int a = 0; a < 3; a++) { d.origin[a] = hw.origin[a]; d.dim[a] = hw.dim[a]; }
     d.levels = hw.levels;
     d.matWide = hw.matWide ? 1 : 0;
-    for (int k = 3; k <= hw.levels; k++) {
-        if ((rc = upload_vec(c, hw.dense[k], &d.dense[k]))) return rc;
-        for (int a = 0; a < 3; a++) d.denseDim[k][a] = hw.denseDim[k][a];
+    {
+        const Node* p;
+        if ((rc = upload_vec(c, hw.nodes, &p))) return rc;
+        d.nodes = reinterpret_cast<const uint4*>(p);
     }
-    if ((rc = upload_vec(c, hw.topGrid, &d.topGrid))) return rc;
-    if ((rc = upload_vec(c, hw.subs, &d.subs))) return rc;
-    if ((rc = upload_vec(c, hw.bricks, &d.bricks))) return rc;
     if ((rc = upload_vec(c, hw.blockFirstLeaf, &d.blockFirstLeaf))) return rc;
     if (hw.matWide) { const uint32_t* p; if ((rc = upload_vec(c, hw.mat32, &p))) return rc; d.voxelMat = p; }
     else { const uint16_t* p; if ((rc = upload_vec(c, hw.mat16, &p))) return rc; d.voxelMat = p; }

@@ -20,5 +20,9 @@ static inline int __popcll(unsigned long long v) { return __builtin_popcountll(v
 static inline uint32_t __float_as_uint(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
 static inline float __uint_as_float(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
 static inline float __fmaf_rn(float a, float b, float c) { return std::fmaf(a, b, c); }
+#include <vector_types.h>
+#ifndef __VECTOR_FUNCTIONS_H__
+static inline uint4 make_uint4(uint32_t x, uint32_t y, uint32_t z, uint32_t w) { uint4 v; v.x = x; v.y = y; v.z = z; v.w = w; return v; }
+#endif
 template <class T> static inline T __ldg(const T* p) { return *p; }
 #endif

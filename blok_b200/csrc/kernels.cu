@@ -17,6 +17,10 @@ __device__ __forceinline__ bool thread_pixel(uint32_t width, uint32_t height, ui
     return px < width && py < height;
 }
 
+// Shared-memory node stacks: [level][thread] rows of 16 bytes, W.levels rows (launchers pass levels * 256 * 16 bytes).
+extern __shared__ uint4 g_stackMem[];
+__device__ __forceinline__ NodeStack thread_stack() { return NodeStack{g_stackMem + threadIdx.x, blockDim.x}; }
+
 __device__ __forceinline__ void store_hit(blokb_hit* dst, bool hit, const HitRec& h) {
     uint4 v;
     if (hit) v = make_uint4(h.node, h.material, __float_as_uint(h.t), h.facePrim);
@@ -32,7 +36,7 @@ __global__ void __launch_bounds__(256) k_trace_rays(const __grid_constant__ Devi
     const float4 a = __ldg(&rays[2 * i]), b = __ldg(&rays[2 * i + 1]);
     HitRec h;
     uint32_t steps = 0;
-    const bool hit = traverse<kStats>(W, a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, h, steps);
+    const bool hit = traverse<kStats>(W, thread_stack(), a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, h, steps);
     store_hit(out + i, hit, h);
     if (kStats) atomicAdd(stats, (unsigned long long)steps);
 }
@@ -46,7 +50,8 @@ __global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceW
     const F3 d = primary_dir(F, float(px) + 0.5f, float(py) + 0.5f);
     HitRec h;
     uint32_t steps = 0;
-    const bool hit = traverse<kStats>(W, F.camPos[0], F.camPos[1], F.camPos[2], d.x, d.y, d.z, 0.001f, 10000.0f, h, steps);
+    const NodeStack stk = thread_stack();
+    const bool hit = traverse<kStats>(W, stk, F.camPos[0], F.camPos[1], F.camPos[2], d.x, d.y, d.z, 0.001f, 10000.0f, h, steps);
     const size_t pi = size_t(py) * F.width + px;
     store_hit(out + pi, hit, h);
     if (kShadow) {
@@ -58,7 +63,7 @@ __global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceW
             if (fmaxf(dot3(N, sunDir), 0.0f) > 0.0f) {
                 const F3 o = f3(F.camPos[0], F.camPos[1], F.camPos[2]) + d * h.t + N * 0.001f;
                 HitRec sh;
-                sv = traverse<kStats>(W, o.x, o.y, o.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps) ? 2 : 1;
+                sv = traverse<kStats>(W, stk, o.x, o.y, o.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps) ? 2 : 1;
             }
         }
         shadow[pi] = sv;
@@ -80,7 +85,8 @@ __global__ void __launch_bounds__(256) k_render(const __grid_constant__ DeviceWo
     fh.roughness = 0.f; fh.metallic = 0.f; fh.depth = 0.f;
     F3 acc = f3(0.f);
     uint32_t rays = 0, steps = 0;
-    for (uint32_t s = 0; s < F.sampleCount; s++) acc = acc + path_sample<kStats>(W, F, px, py, s, &fh, rays, steps);
+    const NodeStack stk = thread_stack();
+    for (uint32_t s = 0; s < F.sampleCount; s++) acc = acc + path_sample<kStats>(W, stk, F, px, py, s, &fh, rays, steps);
     F3 c = acc / float(F.sampleCount);
     const float mv = max3(c);
     if (mv > 100.0f) c = c * (100.0f / mv);
@@ -125,7 +131,8 @@ __global__ void __launch_bounds__(256) k_path(const __grid_constant__ DeviceWorl
     if (!thread_pixel(F.width, F.height, px, py)) return;
     F3 acc = f3(0.f);
     uint32_t rays = 0, steps = 0;
-    for (uint32_t s = sBegin; s < sEnd; s++) acc = acc + path_sample<kStats>(W, F, px, py, s, nullptr, rays, steps);
+    const NodeStack stk = thread_stack();
+    for (uint32_t s = sBegin; s < sEnd; s++) acc = acc + path_sample<kStats>(W, stk, F, px, py, s, nullptr, rays, steps);
     const size_t pi = size_t(py) * F.width + px;
     float4 a = accum[pi];
     a.x += acc.x; a.y += acc.y; a.z += acc.z; a.w += float(sEnd - sBegin);
@@ -146,23 +153,24 @@ __global__ void __launch_bounds__(256) k_resolve(const float4* __restrict__ accu
 
 // ---- launchers ------------------------------------------------------------------------------------
 static inline dim3 pixel_grid(uint32_t w, uint32_t h) { return dim3((w + 31) / 32, (h + 7) / 8); }
+static inline size_t stack_bytes(const DeviceWorld& W) { return size_t(W.levels) * 256 * sizeof(uint4); }  // <= 48 KB (kMaxLevels = 12)
 
 cudaError_t launch_trace_rays(const DeviceWorld& W, const float* rays, size_t n, blokb_hit* out, unsigned long long* stats, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
     const unsigned blocks = (unsigned)((n + 255) / 256);
-    if (stats) k_trace_rays<true><<<blocks, 256, 0, st>>>(W, reinterpret_cast<const float4*>(rays), n, out, stats);
-    else k_trace_rays<false><<<blocks, 256, 0, st>>>(W, reinterpret_cast<const float4*>(rays), n, out, nullptr);
+    if (stats) k_trace_rays<true><<<blocks, 256, stack_bytes(W), st>>>(W, reinterpret_cast<const float4*>(rays), n, out, stats);
+    else k_trace_rays<false><<<blocks, 256, stack_bytes(W), st>>>(W, reinterpret_cast<const float4*>(rays), n, out, nullptr);
     return cudaGetLastError();
 }
 cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow, blokb_hit* out, uint8_t* shadowOut, unsigned long long* stats,
                            cudaStream_t st) {
     const dim3 g = pixel_grid(F.width, F.height);
     if (stats) {
-        if (shadow) k_primary<true, true><<<g, 256, 0, st>>>(W, F, out, shadowOut, stats);
-        else k_primary<false, true><<<g, 256, 0, st>>>(W, F, out, shadowOut, stats);
+        if (shadow) k_primary<true, true><<<g, 256, stack_bytes(W), st>>>(W, F, out, shadowOut, stats);
+        else k_primary<false, true><<<g, 256, stack_bytes(W), st>>>(W, F, out, shadowOut, stats);
     } else {
-        if (shadow) k_primary<true, false><<<g, 256, 0, st>>>(W, F, out, shadowOut, nullptr);
-        else k_primary<false, false><<<g, 256, 0, st>>>(W, F, out, shadowOut, nullptr);
+        if (shadow) k_primary<true, false><<<g, 256, stack_bytes(W), st>>>(W, F, out, shadowOut, nullptr);
+        else k_primary<false, false><<<g, 256, stack_bytes(W), st>>>(W, F, out, shadowOut, nullptr);
     }
     return cudaGetLastError();
 }
@@ -170,16 +178,16 @@ cudaError_t launch_render(const DeviceWorld& W, const FrameDev& F, float* color,
                           uint16_t* motion, unsigned long long* stats, cudaStream_t st) {
     const dim3 g = pixel_grid(F.width, F.height);
     if (stats)
-        k_render<true><<<g, 256, 0, st>>>(W, F, (float4*)color, (float4*)worldPos, (uint2*)normalRough, (uint32_t*)albedoMetal, (uint32_t*)motion, stats);
+        k_render<true><<<g, 256, stack_bytes(W), st>>>(W, F, (float4*)color, (float4*)worldPos, (uint2*)normalRough, (uint32_t*)albedoMetal, (uint32_t*)motion, stats);
     else
-        k_render<false><<<g, 256, 0, st>>>(W, F, (float4*)color, (float4*)worldPos, (uint2*)normalRough, (uint32_t*)albedoMetal, (uint32_t*)motion, nullptr);
+        k_render<false><<<g, 256, stack_bytes(W), st>>>(W, F, (float4*)color, (float4*)worldPos, (uint2*)normalRough, (uint32_t*)albedoMetal, (uint32_t*)motion, nullptr);
     return cudaGetLastError();
 }
 cudaError_t launch_path(const DeviceWorld& W, const FrameDev& F, uint32_t sBegin, uint32_t sEnd, float* accum, unsigned long long* stats,
                         cudaStream_t st) {
     const dim3 g = pixel_grid(F.width, F.height);
-    if (stats) k_path<true><<<g, 256, 0, st>>>(W, F, sBegin, sEnd, (float4*)accum, stats);
-    else k_path<false><<<g, 256, 0, st>>>(W, F, sBegin, sEnd, (float4*)accum, nullptr);
+    if (stats) k_path<true><<<g, 256, stack_bytes(W), st>>>(W, F, sBegin, sEnd, (float4*)accum, stats);
+    else k_path<false><<<g, 256, stack_bytes(W), st>>>(W, F, sBegin, sEnd, (float4*)accum, nullptr);
     return cudaGetLastError();
 }
 cudaError_t launch_resolve(const float* accum, float* color, size_t n, cudaStream_t st) {

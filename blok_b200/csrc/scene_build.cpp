@@ -13,10 +13,7 @@
 namespace blokb {
 
 size_t HostWorld::compactBytes() const {
-    size_t b = topGrid.size() * 4 + subs.size() * sizeof(SubRec) + bricks.size() * sizeof(Brick) + blockFirstLeaf.size() * 4 +
-               mat16.size() * 2 + mat32.size() * 4;
-    for (auto& d : dense) b += d.size() * 8;
-    return b;
+    return nodes.size() * sizeof(Node) + blockFirstLeaf.size() * 4 + mat16.size() * 2 + mat32.size() * 4;
 }
 
 namespace {
@@ -202,6 +199,48 @@ int build_host_world(const blokb_svo_node* nodes, size_t nNodes, const blokb_sub
                     if (w.dense[k - 1][size_t((z * dc[1] + y) * dc[0] + x)])
                         w.dense[k][size_t(((z >> 2) * dp[1] + (y >> 2)) * dp[0] + (x >> 2))] |= 1ull << ((x & 3) + 4 * (y & 3) + 16 * (z & 3));
     }
+    // ---- the uploaded tree: breadth-first Node array (scene.h). Upper levels from the dense pyramid, then one node per
+    // non-empty sub-chunk (children of a level-3 cell contiguous, in bit order), then the bricks in their existing order.
+    struct Cell { int32_t x, y, z; };
+    std::vector<Cell> cur{{0, 0, 0}}, nxt;
+    w.nodes.clear();
+    w.nodes.push_back(Node{w.dense[w.levels][0], 0u, 0u});
+    size_t levelStart = 0;  // index of the first node of the level being expanded
+    uint64_t nUpper = 1;
+    for (int k = w.levels; k >= 4; k--) {
+        const int32_t* dc = w.denseDim[k - 1];
+        nxt.clear();
+        const size_t childStart = w.nodes.size();
+        for (size_t i = 0; i < cur.size(); i++) {
+            Node& n = w.nodes[levelStart + i];
+            n.base = (uint32_t)(childStart + nxt.size());
+            for (uint64_t m = n.mask; m; m &= m - 1) {
+                const int b = __builtin_ctzll(m);
+                nxt.push_back(Cell{cur[i].x * 4 + (b & 3), cur[i].y * 4 + ((b >> 2) & 3), cur[i].z * 4 + (b >> 4)});
+            }
+        }
+        for (const Cell& c : nxt) w.nodes.push_back(Node{w.dense[k - 1][size_t((int64_t(c.z) * dc[1] + c.y) * dc[0] + c.x)], 0u, 0u});
+        levelStart = childStart;
+        cur.swap(nxt);
+        nUpper = w.nodes.size();
+    }
+    // cur = level-3 cells; their children are sub-chunks
+    uint64_t nSubNodes = 0;
+    for (size_t i = 0; i < cur.size(); i++) nSubNodes += __builtin_popcountll(w.nodes[levelStart + i].mask);
+    const uint64_t brickStart = nUpper + nSubNodes;
+    if (brickStart + w.bricks.size() > 0xFFFFFFF0ull) { err = "world exceeds 32-bit node indices"; return BLOKB_E_UNSUPPORTED; }
+    w.nodes.reserve(size_t(brickStart + w.bricks.size()));
+    for (size_t i = 0; i < cur.size(); i++) {
+        w.nodes[levelStart + i].base = (uint32_t)w.nodes.size();
+        const uint64_t mask = w.nodes[levelStart + i].mask;
+        for (uint64_t m = mask; m; m &= m - 1) {
+            const int b = __builtin_ctzll(m);
+            const int64_t x = cur[i].x * 4 + (b & 3), y = cur[i].y * 4 + ((b >> 2) & 3), z = cur[i].z * 4 + (b >> 4);
+            const uint32_t p = w.topGrid[size_t((z * g[1] + y) * g[0] + x)];
+            w.nodes.push_back(Node{w.subs[p].brickMask, (uint32_t)(brickStart + w.subs[p].brickBase), p});
+        }
+    }
+    for (const Brick& b : w.bricks) w.nodes.push_back(Node{b.voxelMask, b.matBase, b.blockBase});
     return 0;
 }
 

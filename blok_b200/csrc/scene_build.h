@@ -17,6 +17,7 @@ struct HostWorld {
     std::vector<std::vector<uint64_t>> dense;  // [k], k = 0..levels (only 3..levels used)
     int32_t denseDim[kMaxLevels + 1][3] = {};
     std::vector<uint32_t> topGrid;
+    std::vector<Node> nodes;  // the uploaded tree (scene.h); everything above except blockFirstLeaf / mats is an intermediate
     std::vector<SubRec> subs;
     std::vector<Brick> bricks;
     std::vector<uint32_t> blockFirstLeaf;

@@ -121,7 +121,7 @@ BLOKB_HD Surface fetch_surface(const DeviceWorld& W, uint32_t materialId) {  // 
 struct FirstHit { F3 pos, N, albedo, emission; float roughness, metallic, depth; bool had, emissive; };
 
 template <bool kStats>
-BLOKB_HD F3 path_sample(const DeviceWorld& W, const FrameDev& f, uint32_t px, uint32_t py, uint32_t s,
+BLOKB_HD F3 path_sample(const DeviceWorld& W, const NodeStack& stk, const FrameDev& f, uint32_t px, uint32_t py, uint32_t s,
                                           FirstHit* first, uint32_t& rays, uint32_t& steps) {
     uint32_t rng = init_rng(px, py, f.width, f.frameCount, s);
     float pcx, pcy;
@@ -139,7 +139,7 @@ BLOKB_HD F3 path_sample(const DeviceWorld& W, const FrameDev& f, uint32_t px, ui
     for (uint32_t bounce = 0u; bounce < 2u; bounce++) {
         HitRec h;
         rays++;
-        if (!traverse<kStats>(W, rayOrigin.x, rayOrigin.y, rayOrigin.z, rayDir.x, rayDir.y, rayDir.z, 0.001f, 10000.0f, h, steps)) {
+        if (!traverse<kStats>(W, stk, rayOrigin.x, rayOrigin.y, rayOrigin.z, rayDir.x, rayDir.y, rayDir.z, 0.001f, 10000.0f, h, steps)) {
             radiance = radiance + thr * sky_color(rayDir);
             break;
         }
@@ -160,7 +160,7 @@ BLOKB_HD F3 path_sample(const DeviceWorld& W, const FrameDev& f, uint32_t px, ui
             const F3 so = hitPos + N * 0.001f;
             HitRec sh;
             rays++;
-            if (!traverse<kStats>(W, so.x, so.y, so.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps)) {
+            if (!traverse<kStats>(W, stk, so.x, so.y, so.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps)) {
                 const F3 diffuse = m.albedo * (1.0f - m.metallic);
                 radiance = radiance + thr * diffuse * sunRad * NdotL * BLOKB_INV_PI;
                 if (m.roughness < 0.9f) {

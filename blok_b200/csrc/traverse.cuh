@@ -72,28 +72,35 @@ BLOKB_HD void select_child(uint32_t& m, float& w, uint32_t& bit, int axisShift, 
     if (lo) { m += s; bit += 1u << axisShift; }
 }
 
-enum : int { WALK_CONTINUE = 0, WALK_HIT = 1, WALK_MISS = 2 };
+// Per-ray stack of the nodes on the current root-to-cell path, one 16-byte entry per level (entry k-1 = the level-k
+// cell). In kernels it lives in shared memory, laid out [level][thread] so that a warp's accesses are conflict-free
+// 16-byte rows; the host emulation passes a plain array (stride 1). Written when descending, read when the walk
+// leaves a cell and returns to an ancestor.
+struct NodeStack {
+    uint4* base;      // this thread's level-1 entry
+    uint32_t stride;  // entries between consecutive levels
+    BLOKB_HD void put(int level, uint64_t mask, uint32_t b, uint32_t aux) const {
+        base[(level - 1) * stride] = make_uint4(uint32_t(mask), uint32_t(mask >> 32), b, aux);
+    }
+    BLOKB_HD uint4 get(int level) const { return base[(level - 1) * stride]; }
+};
 
-// One ray's walk as an explicit state machine, so that kernels can interleave / refill rays per lane
-// (k_primary's persistent warps) while traverse() below simply runs it to completion.
+// One ray's walk as an explicit state machine: init(), then while the child holding the ray is occupied descend()
+// (or report a hit at voxel level), else step(). traverse() below runs it to completion.
 struct Walker {
-    float ox, oy, oz, dx, dy, dz, ix, iy, iz;  // origin, direction, 1 / substituted direction
-    float gsx, gsy, gsz;                       // +1 / -1: sign of the mirrored frame per axis
-    uint32_t fx, fy, fz;                       // mirrored <-> actual coordinate XOR constants (0 or cap - 1)
+    float ox, oy, oz, ix, iy, iz;  // origin, 1 / substituted direction
+    float gsx, gsy, gsz;           // +1 / -1: sign of the mirrored frame per axis
+    uint32_t flip;                 // mirrored <-> actual child index XOR constant (3 | 12 | 48 per negative axis)
     float t, tEnd;
-    uint32_t mx, my, mz;                       // mirrored corner of the current child cell
-    float wx, wy, wz;                          // float(P) of its near planes
-    int sh;                                    // child cell size = 1 << sh; current cell = 4x that
-    float fs;                                  // float(1 << sh)
-    uint32_t bit;                              // mirrored child index ix + 4 iy + 16 iz inside the current cell
-    uint64_t mask;                             // occupancy of the current cell's 4^3 children (actual orientation)
-    uint64_t subMask;                          // cached sub-chunk record
-    uint32_t subBrickBase, prim;
-    uint32_t blockBase, matBase;               // cached brick record (its voxelMask is `mask` while sh == 0)
+    uint32_t mx, my, mz;           // mirrored corner of the current child cell
+    float wx, wy, wz;              // float(P) of its near planes
+    int sh;                        // child cell size = 1 << sh; current cell = 4x that (level sh / 2 + 1)
+    float fs;                      // float(1 << sh)
+    uint32_t bit;                  // mirrored child index ix + 4 iy + 16 iz inside the current cell
+    uint64_t mask;                 // current cell's node: occupancy of its 4^3 children (actual orientation),
+    uint32_t base, aux;            //   first-child index, level-specific word (scene.h)
 
-    BLOKB_HD uint32_t flip() const { return (fx & 3u) | (fy & 12u) | (fz & 48u); }
-
-    BLOKB_HD void select(const DeviceWorld&) {
+    BLOKB_HD void select() {
         const uint32_t s = 1u << sh;
         const float fs2 = fs + fs;
         bit = 0;
@@ -103,8 +110,8 @@ struct Walker {
     }
 
     // Returns false when the ray misses the grid box altogether.
-    BLOKB_HD bool init(const DeviceWorld& W, float ox_, float oy_, float oz_, float dx_, float dy_, float dz_, float tmin, float tmax) {
-        ox = ox_; oy = oy_; oz = oz_; dx = dx_; dy = dy_; dz = dz_;
+    BLOKB_HD bool init(const DeviceWorld& W, float ox_, float oy_, float oz_, float dx, float dy, float dz, float tmin, float tmax) {
+        ox = ox_; oy = oy_; oz = oz_;
         const float sx = fabsf(dx) < 1e-6f ? 1e-6f : dx, sy = fabsf(dy) < 1e-6f ? 1e-6f : dy, sz = fabsf(dz) < 1e-6f ? 1e-6f : dz;
         ix = 1.0f / sx; iy = 1.0f / sy; iz = 1.0f / sz;
         const bool px = ix > 0.0f, py = iy > 0.0f, pz = iz > 0.0f;
@@ -120,71 +127,38 @@ struct Walker {
             if (!(t < tEnd)) return false;
         }
         const int L = W.levels;
-        const uint32_t cap = 1u << (2 * L);
-        fx = px ? 0u : cap - 1u; fy = py ? 0u : cap - 1u; fz = pz ? 0u : cap - 1u;
+        const int cap = 1 << (2 * L);
+        flip = (px ? 0u : 3u) | (py ? 0u : 12u) | (pz ? 0u : 48u);
         gsx = px ? 1.0f : -1.0f; gsy = py ? 1.0f : -1.0f; gsz = pz ? 1.0f : -1.0f;
         mx = my = mz = 0;
-        wx = float(px ? gx : gx + int(cap)); wy = float(py ? gy : gy + int(cap)); wz = float(pz ? gz : gz + int(cap));
+        wx = float(px ? gx : gx + cap); wy = float(py ? gy : gy + cap); wz = float(pz ? gz : gz + cap);
         sh = 2 * (L - 1);
         fs = pow2f(sh);
-        mask = W.dense[L][0];
-        subMask = 0ull; subBrickBase = 0; prim = 0; blockBase = 0; matBase = 0;
-        select(W);
+        const uint4 r = __ldg(W.nodes);
+        mask = uint64_t(r.x) | (uint64_t(r.y) << 32); base = r.z; aux = r.w;
+        select();
         return true;
     }
 
-    // One iteration: descend into the occupied child holding the ray, or leave the empty one. Every fetch below is
-    // in bounds by construction: the walk only ever selects cells that contain a point of the ray with
-    // t in [grid entry, grid exit) under the plane-compare semantics, i.e. cells that intersect the grid box.
-    template <bool kStats>
-    BLOKB_HD int advance(const DeviceWorld& W, HitRec& out, uint32_t& steps) {
-        const uint32_t abit = bit ^ flip();  // actual-orientation child index: x + 4y + 16z
-        if ((mask >> abit) & 1ull) {
-            // ---- the child holding the ray is occupied: it becomes the current cell
-            if (sh == 0) {
-                // ---- hit: the child is a filled voxel; t is its slab entry (or tmin / grid entry for the first cell)
-                const uint32_t x = mx ^ fx, y = my ^ fy, z = mz ^ fz;
-                const float hx = ox + dx * t, hy = oy + dy * t, hz = oz + dz * t;  // intersect.rint:138
-                const uint32_t face = hit_face(hx, hy, hz, float(W.origin[0] + int(x)) + 0.5f, float(W.origin[1] + int(y)) + 0.5f,
-                                               float(W.origin[2] + int(z)) + 0.5f);
-                const uint64_t vm = mask;
-                const uint32_t b = ((x >> 1) & 1) | (((y >> 1) & 1) << 1) | (((z >> 1) & 1) << 2);
-                uint32_t rank = 0;
-                for (uint32_t j = 0; j < 7; j++) rank += (j < b && (vm & block_bits(j))) ? 1u : 0u;
-                const uint32_t leaf = W.blockFirstLeaf[blockBase + rank] + ((x & 1) | ((y & 1) << 1) | ((z & 1) << 2));
-                const uint32_t mi = matBase + __popcll(vm & ((1ull << abit) - 1ull));
-                const uint32_t mat = W.matWide ? reinterpret_cast<const uint32_t*>(W.voxelMat)[mi]
-                                               : (uint32_t) reinterpret_cast<const uint16_t*>(W.voxelMat)[mi];
-                out.node = leaf; out.material = mat; out.t = t; out.facePrim = face | (prim << 3);
-                return WALK_HIT;
-            }
-            if (sh >= 6) {  // child is a level >= 3 cell: dense mask arrays
-                const int k = sh >> 1;
-                const uint32_t cx = (mx ^ fx) >> sh, cy = (my ^ fy) >> sh, cz = (mz ^ fz) >> sh;
-                BLOKB_ASSERT(cx < (uint32_t)W.denseDim[k][0] && cy < (uint32_t)W.denseDim[k][1] && cz < (uint32_t)W.denseDim[k][2]);
-                mask = W.dense[k][(cz * uint32_t(W.denseDim[k][1]) + cy) * uint32_t(W.denseDim[k][0]) + cx];
-            } else if (sh == 4) {  // child is a 16^3 sub-chunk
-                const uint32_t cx = (mx ^ fx) >> 4, cy = (my ^ fy) >> 4, cz = (mz ^ fz) >> 4;
-                BLOKB_ASSERT(cx < (uint32_t(W.dim[0]) >> 4) && cy < (uint32_t(W.dim[1]) >> 4) && cz < (uint32_t(W.dim[2]) >> 4));
-                prim = W.topGrid[(cz * (uint32_t(W.dim[1]) >> 4) + cy) * (uint32_t(W.dim[0]) >> 4) + cx];
-                const SubRec sr = W.subs[prim];
-                subMask = sr.brickMask; subBrickBase = sr.brickBase;
-                mask = subMask;
-            } else {  // sh == 2: child is a 4^3 brick of the cached sub-chunk
-                const Brick br = W.bricks[subBrickBase + __popcll(subMask & ((1ull << abit) - 1ull))];
-                mask = br.voxelMask; blockBase = br.blockBase; matBase = br.matBase;
-            }
-            sh -= 2;
-            fs = pow2f(sh);
-            select(W);
-            return WALK_CONTINUE;
-        }
-        // ---- the child cell (size 1 << sh) holding the ray is empty: leave it through its nearest exit plane(s)
-        if (kStats) steps++;
+    BLOKB_HD uint32_t abit() const { return bit ^ flip; }  // actual-orientation child index: x + 4y + 16z
+    BLOKB_HD bool occupied() const { return (mask >> abit()) & 1ull; }
+
+    // The occupied child holding the ray becomes the current cell (sh >= 2). Same code at every level.
+    BLOKB_HD void descend(const DeviceWorld& W, const NodeStack& stk) {
+        stk.put((sh >> 1) + 1, mask, base, aux);
+        const uint4 c = __ldg(W.nodes + (base + __popcll(mask & ((1ull << abit()) - 1ull))));
+        mask = uint64_t(c.x) | (uint64_t(c.y) << 32); base = c.z; aux = c.w;
+        sh -= 2;
+        fs = pow2f(sh);
+        select();
+    }
+
+    // Leave the empty child cell (size 1 << sh) through its nearest exit plane(s). Returns false when the ray ends.
+    BLOKB_HD bool step(const DeviceWorld& W, const NodeStack& stk) {
         const float qx = __fmaf_rn(gsx, fs, wx), qy = __fmaf_rn(gsy, fs, wy), qz = __fmaf_rn(gsz, fs, wz);
         const float tx = (qx - ox) * ix, ty = (qy - oy) * iy, tz = (qz - oz) * iz;
         const float te = fminf(fminf(tx, ty), tz);
-        if (!(te < tEnd)) return WALK_MISS;
+        if (!(te < tEnd)) return false;
         const uint32_t s = 1u << sh;
         uint32_t diff = 0;
         if (tx <= te) { diff |= mx ^ (mx + s); mx += s; wx = qx; bit += 1u; }
@@ -204,31 +178,54 @@ struct Walker {
             wx = float(gsx > 0.0f ? W.origin[0] + int(mx) : W.origin[0] + cap - int(mx));
             wy = float(gsy > 0.0f ? W.origin[1] + int(my) : W.origin[1] + cap - int(my));
             wz = float(gsz > 0.0f ? W.origin[2] + int(mz) : W.origin[2] + cap - int(mz));
-            if (sh >= 4) {  // current cell is a level >= 3 cell
-                const int k = (sh >> 1) + 1, s2 = sh + 2;
-                const uint32_t cx = (mx ^ fx) >> s2, cy = (my ^ fy) >> s2, cz = (mz ^ fz) >> s2;
-                BLOKB_ASSERT(cx < (uint32_t)W.denseDim[k][0] && cy < (uint32_t)W.denseDim[k][1] && cz < (uint32_t)W.denseDim[k][2]);
-                mask = W.dense[k][(cz * uint32_t(W.denseDim[k][1]) + cy) * uint32_t(W.denseDim[k][0]) + cx];
-            } else {
-                mask = subMask;  // sh == 2: same sub-chunk, record still cached
-            }
+            const uint4 c = stk.get((sh >> 1) + 1);
+            mask = uint64_t(c.x) | (uint64_t(c.y) << 32); base = c.z; aux = c.w;
             bit = ((mx >> sh) & 3u) | (((my >> sh) & 3u) << 2) | (((mz >> sh) & 3u) << 4);
         }
-        return WALK_CONTINUE;
+        return true;
+    }
+
+    // The child holding the ray is a filled voxel (sh == 0, occupied()): t is its slab entry (or tmin / grid entry
+    // for the first cell). (dx, dy, dz) is the ray's direction as given (intersect.rint:138 uses it unsubstituted).
+    BLOKB_HD void finish_hit(const DeviceWorld& W, const NodeStack& stk, float dx, float dy, float dz, HitRec& out) const {
+        const uint32_t ab = abit();
+        const float hx = ox + dx * t, hy = oy + dy * t, hz = oz + dz * t;
+        // voxel centre = near plane + half a voxel along the ray's sign = float(voxel coordinate) + 0.5 exactly
+        const uint32_t face = hit_face(hx, hy, hz, wx + 0.5f * gsx, wy + 0.5f * gsy, wz + 0.5f * gsz);
+        const uint64_t vm = mask;
+        const uint32_t b = ((ab >> 1) & 1u) | (((ab >> 3) & 1u) << 1) | (((ab >> 5) & 1u) << 2);  // 2^3 block inside the brick
+        uint32_t rank = 0;
+        for (uint32_t j = 0; j < 7; j++) rank += (j < b && (vm & block_bits(j))) ? 1u : 0u;
+        const uint32_t leaf = __ldg(W.blockFirstLeaf + aux + rank) + ((ab & 1u) | (((ab >> 2) & 1u) << 1) | (((ab >> 4) & 1u) << 2));
+        const uint32_t mi = base + __popcll(vm & ((1ull << ab) - 1ull));
+        const uint32_t mat = W.matWide ? __ldg(reinterpret_cast<const uint32_t*>(W.voxelMat) + mi)
+                                       : (uint32_t)__ldg(reinterpret_cast<const uint16_t*>(W.voxelMat) + mi);
+        const uint32_t prim = stk.get(2).w;  // the enclosing sub-chunk's node: aux = gl_PrimitiveID
+        out.node = leaf; out.material = mat; out.t = t; out.facePrim = face | (prim << 3);
     }
 };
 
 // Closest hit of one ray. Because the walk is strictly front to back, the first filled voxel is both the
 // closest-hit and the any-hit (shadow) answer. Returns false on miss. `steps` counts DDA steps (profiling).
+// Loop shape: all lanes of a warp first finish descending, then step together, and the hit record is assembled
+// after the loop — lanes re-converge at every step instead of drifting apart between descend and step phases.
 template <bool kStats>
-BLOKB_HD bool traverse(const DeviceWorld& W, float ox, float oy, float oz, float dx, float dy, float dz,
-                                         float tmin, float tmax, HitRec& out, uint32_t& steps) {
+BLOKB_HD bool traverse(const DeviceWorld& W, const NodeStack& stk, float ox, float oy, float oz, float dx, float dy, float dz,
+                       float tmin, float tmax, HitRec& out, uint32_t& steps) {
     Walker wk;
     if (!wk.init(W, ox, oy, oz, dx, dy, dz, tmin, tmax)) return false;
+    bool hit = false;
     for (;;) {
-        const int r = wk.advance<kStats>(W, out, steps);
-        if (r != WALK_CONTINUE) return r == WALK_HIT;
+        while (wk.occupied()) {
+            if (wk.sh == 0) { hit = true; break; }
+            wk.descend(W, stk);
+        }
+        if (hit) break;
+        if (kStats) steps++;
+        if (!wk.step(W, stk)) return false;
     }
+    wk.finish_hit(W, stk, dx, dy, dz, out);
+    return true;
 }
 
 }  // namespace blokb

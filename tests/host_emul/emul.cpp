@@ -39,8 +39,7 @@ void* emu_create(const blokb_svo_node* nodes, size_t nNodes, const blokb_subchun
     HostWorld& h = e->hw; DeviceWorld& d = e->dw;
     for (int a = 0; a < 3; a++) { d.origin[a] = h.origin[a]; d.dim[a] = h.dim[a]; }
     d.levels = h.levels; d.matWide = h.matWide;
-    for (int k = 3; k <= h.levels; k++) { d.dense[k] = h.dense[k].data(); for (int a = 0; a < 3; a++) d.denseDim[k][a] = h.denseDim[k][a]; }
-    d.topGrid = h.topGrid.data(); d.subs = h.subs.data(); d.bricks = h.bricks.data(); d.blockFirstLeaf = h.blockFirstLeaf.data();
+    d.nodes = reinterpret_cast<const uint4*>(h.nodes.data()); d.blockFirstLeaf = h.blockFirstLeaf.data();
     d.voxelMat = h.matWide ? (const void*)h.mat32.data() : (const void*)h.mat16.data();
     e->mats.assign(mats, mats + nMat);
     if (e->mats.empty()) e->mats.push_back(blokb_material{{0.8f, 0.8f, 0.8f}, 127u << 16, {0, 0, 0}, 0.f});
@@ -60,14 +59,26 @@ uint64_t emu_trace(void* p, const float* rays, size_t n, blokb_hit* out, int nTh
         uint64_t st = 0;
         for (size_t i = b; i < en; i++) {
             const float* r = rays + 8 * i;
-            HitRec h; uint32_t steps = 0;
-            if (traverse<true>(e->dw, r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7], h, steps)) out[i] = blokb_hit{h.node, h.material, h.t, h.facePrim};
+            HitRec h; uint32_t steps = 0; uint4 stackMem[kMaxLevels]; const NodeStack stk{stackMem, 1};
+            if (traverse<true>(e->dw, stk, r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7], h, steps)) out[i] = blokb_hit{h.node, h.material, h.t, h.facePrim};
             else out[i] = blokb_hit{0xFFFFFFFFu, 0xFFFFFFFFu, -1.0f, 0xFFFFFFFFu};
             st += steps;
         }
         total += st;
     });
     return total;
+}
+// per-ray DDA step counts (profiling aid for warp-divergence estimates)
+void emu_trace_steps(void* p, const float* rays, size_t n, uint32_t* stepsOut, int nThreads) {
+    Emu* e = (Emu*)p;
+    pfor(n, nThreads, [&](size_t b, size_t en) {
+        for (size_t i = b; i < en; i++) {
+            const float* r = rays + 8 * i;
+            HitRec h; uint32_t steps = 0; uint4 stackMem[kMaxLevels]; const NodeStack stk{stackMem, 1};
+            traverse<true>(e->dw, stk, r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7], h, steps);
+            stepsOut[i] = steps;
+        }
+    });
 }
 // radiance sum of samples [sBegin, sEnd) per pixel (k_path without the accumulate), out = w*h*4 floats (sum.rgb, count)
 void emu_path(void* p, const blokb_frame_ubo* f, uint32_t sBegin, uint32_t sEnd, float* out, int nThreads) {
@@ -80,8 +91,8 @@ void emu_path(void* p, const blokb_frame_ubo* f, uint32_t sBegin, uint32_t sEnd,
     pfor(n, nThreads, [&](size_t b, size_t en) {
         for (size_t i = b; i < en; i++) {
             uint32_t px = uint32_t(i % F.width), py = uint32_t(i / F.width), rays = 0, steps = 0;
-            F3 acc = f3(0.f);
-            for (uint32_t s = sBegin; s < sEnd; s++) acc = acc + path_sample<false>(e->dw, F, px, py, s, nullptr, rays, steps);
+            F3 acc = f3(0.f); uint4 stackMem[kMaxLevels]; const NodeStack stk{stackMem, 1};
+            for (uint32_t s = sBegin; s < sEnd; s++) acc = acc + path_sample<false>(e->dw, stk, F, px, py, s, nullptr, rays, steps);
             out[4 * i] = acc.x; out[4 * i + 1] = acc.y; out[4 * i + 2] = acc.z; out[4 * i + 3] = float(sEnd - sBegin);
         }
     });
