@@ -17,6 +17,7 @@
 static inline int __float2int_rd(float v) { return (int)std::floor(v); }
 static inline int __clz(uint32_t v) { return v ? __builtin_clz(v) : 32; }
 static inline int __popcll(unsigned long long v) { return __builtin_popcountll(v); }
+static inline int __popc(uint32_t v) { return __builtin_popcount(v); }
 static inline uint32_t __float_as_uint(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
 static inline float __uint_as_float(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
 static inline float __fmaf_rn(float a, float b, float c) { return std::fmaf(a, b, c); }

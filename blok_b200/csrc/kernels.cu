@@ -19,7 +19,9 @@ __device__ __forceinline__ bool thread_pixel(uint32_t width, uint32_t height, ui
 
 // Shared-memory node stacks: [level][thread] rows of 16 bytes, W.levels rows (launchers pass levels * 256 * 16 bytes).
 extern __shared__ uint4 g_stackMem[];
-__device__ __forceinline__ NodeStack thread_stack() { return NodeStack{g_stackMem + threadIdx.x, blockDim.x}; }
+__device__ __forceinline__ NodeStack thread_stack() {
+    return NodeStack{uint32_t(__cvta_generic_to_shared(g_stackMem + threadIdx.x)), uint32_t(blockDim.x * sizeof(uint4))};
+}
 
 __device__ __forceinline__ void store_hit(blokb_hit* dst, bool hit, const HitRec& h) {
     uint4 v;

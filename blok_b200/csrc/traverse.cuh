@@ -74,30 +74,49 @@ BLOKB_HD void select_child(uint32_t& m, float& w, uint32_t& bit, int axisShift, 
 
 // Per-ray stack of the nodes on the current root-to-cell path, one 16-byte entry per level (entry k-1 = the level-k
 // cell). In kernels it lives in shared memory, laid out [level][thread] so that a warp's accesses are conflict-free
-// 16-byte rows; the host emulation passes a plain array (stride 1). Written when descending, read when the walk
-// leaves a cell and returns to an ancestor.
+// 16-byte rows (addressed through a 32-bit shared-window address); the host emulation passes a plain array
+// (stride 16 bytes). Written when descending, read when the walk leaves a cell and returns to an ancestor.
 struct NodeStack {
-    uint4* base;      // this thread's level-1 entry
-    uint32_t stride;  // entries between consecutive levels
-    BLOKB_HD void put(int level, uint64_t mask, uint32_t b, uint32_t aux) const {
-        base[(level - 1) * stride] = make_uint4(uint32_t(mask), uint32_t(mask >> 32), b, aux);
+#if defined(__CUDACC__)
+    uint32_t base;    // shared-window byte address of this thread's level-1 entry
+    uint32_t stride;  // bytes between consecutive levels
+    BLOKB_HD void put(int level, uint32_t mlo, uint32_t mhi, uint32_t b, uint32_t aux) const {
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(base + uint32_t(level - 1) * stride), "r"(mlo), "r"(mhi), "r"(b), "r"(aux) : "memory");
     }
+    BLOKB_HD uint4 get(int level) const {
+        uint4 v;
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(base + uint32_t(level - 1) * stride) : "memory");
+        return v;
+    }
+#else
+    uint4* base;
+    uint32_t stride;  // entries between consecutive levels
+    BLOKB_HD void put(int level, uint32_t mlo, uint32_t mhi, uint32_t b, uint32_t aux) const { base[(level - 1) * stride] = make_uint4(mlo, mhi, b, aux); }
     BLOKB_HD uint4 get(int level) const { return base[(level - 1) * stride]; }
+#endif
 };
 
 // One ray's walk as an explicit state machine: init(), then while the child holding the ray is occupied descend()
 // (or report a hit at voxel level), else step(). traverse() below runs it to completion.
+//
+// Known resolution: (m, w) always describe the smallest cell, of size 1 << rs, that is KNOWN to hold the ray at
+// parameter t. A step at cell size s leaves the position known at granularity s (the crossed axes sit exactly on
+// the entered plane, the others are still inside the same s-slab), so when the walk then climbs to an ancestor and
+// descends again through occupied cells — a ray skimming a surface from brick to brick — the children are read
+// off m's bits; plane tests are spent only when descending BELOW the known resolution, and the float planes are
+// recomputed only when a step is taken at a size ABOVE it.
 struct Walker {
     float ox, oy, oz, ix, iy, iz;  // origin, 1 / substituted direction
     float gsx, gsy, gsz;           // +1 / -1: sign of the mirrored frame per axis
     uint32_t flip;                 // mirrored <-> actual child index XOR constant (3 | 12 | 48 per negative axis)
     float t, tEnd;
-    uint32_t mx, my, mz;           // mirrored corner of the current child cell
+    uint32_t mx, my, mz;           // mirrored corner of the known cell (size 1 << rs)
     float wx, wy, wz;              // float(P) of its near planes
     int sh;                        // child cell size = 1 << sh; current cell = 4x that (level sh / 2 + 1)
+    int rs;                        // known resolution (see above); rs <= sh whenever a child index is needed
     float fs;                      // float(1 << sh)
     uint32_t bit;                  // mirrored child index ix + 4 iy + 16 iz inside the current cell
-    uint64_t mask;                 // current cell's node: occupancy of its 4^3 children (actual orientation),
+    uint32_t mlo, mhi;             // current cell's node: occupancy of its 4^3 children (actual orientation),
     uint32_t base, aux;            //   first-child index, level-specific word (scene.h)
 
     BLOKB_HD void select() {
@@ -107,7 +126,9 @@ struct Walker {
         select_child(mx, wx, bit, 0, s, fs, fs2, gsx, ox, ix, t);
         select_child(my, wy, bit, 2, s, fs, fs2, gsy, oy, iy, t);
         select_child(mz, wz, bit, 4, s, fs, fs2, gsz, oz, iz, t);
+        rs = sh;
     }
+    BLOKB_HD void bit_from_m() { bit = ((mx >> sh) & 3u) | (((my >> sh) & 3u) << 2) | (((mz >> sh) & 3u) << 4); }
 
     // Returns false when the ray misses the grid box altogether.
     BLOKB_HD bool init(const DeviceWorld& W, float ox_, float oy_, float oz_, float dx, float dy, float dz, float tmin, float tmax) {
@@ -135,26 +156,45 @@ struct Walker {
         sh = 2 * (L - 1);
         fs = pow2f(sh);
         const uint4 r = __ldg(W.nodes);
-        mask = uint64_t(r.x) | (uint64_t(r.y) << 32); base = r.z; aux = r.w;
+        mlo = r.x; mhi = r.y; base = r.z; aux = r.w;
         select();
         return true;
     }
 
     BLOKB_HD uint32_t abit() const { return bit ^ flip; }  // actual-orientation child index: x + 4y + 16z
-    BLOKB_HD bool occupied() const { return (mask >> abit()) & 1ull; }
+    BLOKB_HD bool occupied() const {
+        const uint32_t ab = abit();
+        return (((ab & 32u) ? mhi : mlo) >> (ab & 31u)) & 1u;
+    }
+    // number of occupied children before child `ab` = its index among the node's children
+    BLOKB_HD uint32_t child_rank(uint32_t ab) const {
+        const uint32_t below = (1u << (ab & 31u)) - 1u;
+        return (ab & 32u) ? __popc(mlo) + __popc(mhi & below) : __popc(mlo & below);
+    }
 
     // The occupied child holding the ray becomes the current cell (sh >= 2). Same code at every level.
     BLOKB_HD void descend(const DeviceWorld& W, const NodeStack& stk) {
-        stk.put((sh >> 1) + 1, mask, base, aux);
-        const uint4 c = __ldg(W.nodes + (base + __popcll(mask & ((1ull << abit()) - 1ull))));
-        mask = uint64_t(c.x) | (uint64_t(c.y) << 32); base = c.z; aux = c.w;
+        stk.put((sh >> 1) + 1, mlo, mhi, base, aux);
+        const uint4 c = __ldg(W.nodes + (base + child_rank(abit())));
+        mlo = c.x; mhi = c.y; base = c.z; aux = c.w;
         sh -= 2;
-        fs = pow2f(sh);
-        select();
+        fs *= 0.25f;
+        if (sh < rs) select();  // below the known resolution: two plane tests per axis
+        else bit_from_m();      // still inside the known cell: its corner's bits are the child indices
     }
 
     // Leave the empty child cell (size 1 << sh) through its nearest exit plane(s). Returns false when the ray ends.
     BLOKB_HD bool step(const DeviceWorld& W, const NodeStack& stk) {
+        if (sh > rs) {
+            // stepping at a size above the known resolution: widen the known cell to the child cell being left
+            const uint32_t keep = ~((1u << sh) - 1u);
+            mx &= keep; my &= keep; mz &= keep;
+            const int cap = 1 << (2 * W.levels);
+            wx = float(gsx > 0.0f ? W.origin[0] + int(mx) : W.origin[0] + cap - int(mx));
+            wy = float(gsy > 0.0f ? W.origin[1] + int(my) : W.origin[1] + cap - int(my));
+            wz = float(gsz > 0.0f ? W.origin[2] + int(mz) : W.origin[2] + cap - int(mz));
+            rs = sh;
+        }
         const float qx = __fmaf_rn(gsx, fs, wx), qy = __fmaf_rn(gsy, fs, wy), qz = __fmaf_rn(gsz, fs, wz);
         const float tx = (qx - ox) * ix, ty = (qy - oy) * iy, tz = (qz - oz) * iz;
         const float te = fminf(fminf(tx, ty), tz);
@@ -168,36 +208,32 @@ struct Walker {
         const int h = 31 - __clz(diff);
         if (h >= sh + 2) {
             // ---- left the current cell too: the new current cell is the smallest aligned one holding both positions.
-            // (Leaving the root cell is impossible here: its exit planes lie at or beyond the grid's, so tEnd ended the walk.)
+            // (Leaving the root cell is impossible here: its exit planes lie at or beyond the grid's, so tEnd ended the
+            // walk.) The position stays known at the size just stepped: rs is unchanged.
             sh = h & ~1;
             BLOKB_ASSERT(sh < 2 * W.levels);
             fs = pow2f(sh);
-            const uint32_t keep = ~((1u << sh) - 1u);
-            mx &= keep; my &= keep; mz &= keep;
-            const int cap = 1 << (2 * W.levels);
-            wx = float(gsx > 0.0f ? W.origin[0] + int(mx) : W.origin[0] + cap - int(mx));
-            wy = float(gsy > 0.0f ? W.origin[1] + int(my) : W.origin[1] + cap - int(my));
-            wz = float(gsz > 0.0f ? W.origin[2] + int(mz) : W.origin[2] + cap - int(mz));
             const uint4 c = stk.get((sh >> 1) + 1);
-            mask = uint64_t(c.x) | (uint64_t(c.y) << 32); base = c.z; aux = c.w;
-            bit = ((mx >> sh) & 3u) | (((my >> sh) & 3u) << 2) | (((mz >> sh) & 3u) << 4);
+            mlo = c.x; mhi = c.y; base = c.z; aux = c.w;
+            bit_from_m();
         }
         return true;
     }
 
-    // The child holding the ray is a filled voxel (sh == 0, occupied()): t is its slab entry (or tmin / grid entry
-    // for the first cell). (dx, dy, dz) is the ray's direction as given (intersect.rint:138 uses it unsubstituted).
+    // The child holding the ray is a filled voxel (sh == 0, occupied(); then rs == 0 too): t is its slab entry (or
+    // tmin / grid entry for the first cell). (dx, dy, dz) is the ray's direction as given (intersect.rint:138).
     BLOKB_HD void finish_hit(const DeviceWorld& W, const NodeStack& stk, float dx, float dy, float dz, HitRec& out) const {
+        BLOKB_ASSERT(rs == 0 && sh == 0);
         const uint32_t ab = abit();
         const float hx = ox + dx * t, hy = oy + dy * t, hz = oz + dz * t;
         // voxel centre = near plane + half a voxel along the ray's sign = float(voxel coordinate) + 0.5 exactly
         const uint32_t face = hit_face(hx, hy, hz, wx + 0.5f * gsx, wy + 0.5f * gsy, wz + 0.5f * gsz);
-        const uint64_t vm = mask;
+        const uint64_t vm = uint64_t(mlo) | (uint64_t(mhi) << 32);
         const uint32_t b = ((ab >> 1) & 1u) | (((ab >> 3) & 1u) << 1) | (((ab >> 5) & 1u) << 2);  // 2^3 block inside the brick
         uint32_t rank = 0;
         for (uint32_t j = 0; j < 7; j++) rank += (j < b && (vm & block_bits(j))) ? 1u : 0u;
         const uint32_t leaf = __ldg(W.blockFirstLeaf + aux + rank) + ((ab & 1u) | (((ab >> 2) & 1u) << 1) | (((ab >> 4) & 1u) << 2));
-        const uint32_t mi = base + __popcll(vm & ((1ull << ab) - 1ull));
+        const uint32_t mi = base + child_rank(ab);
         const uint32_t mat = W.matWide ? __ldg(reinterpret_cast<const uint32_t*>(W.voxelMat) + mi)
                                        : (uint32_t)__ldg(reinterpret_cast<const uint16_t*>(W.voxelMat) + mi);
         const uint32_t prim = stk.get(2).w;  // the enclosing sub-chunk's node: aux = gl_PrimitiveID

@@ -42,7 +42,7 @@ for r in csv.reader(io.StringIO(src)):
     key = (cur, r[0], r[1][:100])
     a = agg.setdefault(key, [0, 0])
     a[0] += n
-    a[1] += int(r[4] or 0)
+    a[1] += int(r[4]) if r[4].isdigit() else 0
     tot += n
 print(f"-- warp instructions by source line (total {tot}); share, stall samples")
 for (f, l, s), (n, samp) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
