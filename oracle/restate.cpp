@@ -2,7 +2,7 @@
 //
 // Independent CPU restatement of the reference's voxel ray-traversal hot path. It is the checker that
 // travels to the GPU box (where /root/reference does not exist); it is pinned in this container, bit for
-// bit, against oracle/_ref (the reference's own sources compiled in place) by tests/test_oracle_pin.py,
+// bit, against oracle/_ref (the reference's own sources compiled in place) by tests/test_oracle.py::test_restatement_pinned_to_live_reference,
 // and against the committed golden vectors in tests/golden/.
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load it.
 // The product (blok_b200/) never links, imports or calls it.
