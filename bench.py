@@ -237,7 +237,7 @@ def run_reference(args):
                                           "sample": res["sample"]})
         with open(COUNTS_PATH, "w") as f:
             json.dump(allc, f, indent=1, sort_keys=True)
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------ our arm
@@ -294,7 +294,8 @@ def run_ours(args):
         r = blok_b200.Renderer(W, H, local)
         r.add_world(world)
         stats = r.world_stats()
-        cam = workloads.camera_for(name, rank)
+        # weak-scaling kinds render one frame per GPU (own camera); the spp-sharded path frame is ONE frame for all ranks
+        cam = workloads.camera_for(name, 0 if kind == "path" else rank)
         ubo = cam.frame(W, H, 0, spp)
         r.set_frame(ubo)
         s0, s1 = sharding.sample_range(rank, world_size, spp) if kind == "path" else (0, 1)
@@ -403,8 +404,22 @@ def run_ours(args):
     return measure, dict(rank=rank, world_size=world_size, local=local, dev=dev, barrier=barrier, torch=torch, dist=dist)
 
 
+_REAL_STDOUT = None
+
+
+def emit(line: dict):
+    """The one JSON line goes to the real stdout; everything else printed during the run (NCCL's version banner, library
+    chatter) was redirected to stderr by main()."""
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
 def main():
+    global _REAL_STDOUT
     args = parse_args()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
         return
@@ -496,7 +511,7 @@ def main():
                            "timing": "CUDA events on the launching stream around each step, summed; max over ranks",
                            "parallelism": f"{world_size} GPU(s), scene replicated, one frame per GPU per step"},
                 "e2e": e2e, "gpu_launches": m["launches"], "clocks": m["clocks"], "roofline": roof, "cpu_baseline": cpu, "extras": extras}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world_size > 1:
         env["dist"].barrier()
         env["dist"].destroy_process_group()
