@@ -360,28 +360,35 @@ def run_ours(args):
         barrier()
         out["ms_per_step_warm_l2"] = max_over_ranks(a.elapsed_time(b) / steps)
         out["value_warm_l2"] = total_rays / (out["ms_per_step_warm_l2"] * 1e-3) / 1e6
-        if e2e and kind != "path":
-            img = IMG_HIT
+        if e2e and kind == "primary":
+            # frames in flight through the public API: per step the host builds the FrameUBO from the Camera, submits the
+            # frame (trace on the context's stream, hit records copied to pinned host memory on the copy stream) and reads
+            # the previous frame's records; the copy of frame i overlaps the tracing of frame i+1 (depth 2, like the
+            # reference's 2 frames in flight, blok/include/renderer.hpp:185)
             nbytes = W * H * 16
-            host = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
-            e2e_steps = max(3, min(steps, 20))
+            pipe = blok_b200.FramePipeline(r, W, H, depth=2)
+            e2e_steps = max(3, min(steps, 50))
             for i in range(2):
-                r.set_frame(cam.frame(W, H, i, spp))
-                step()
-                r.readback_into(img, host.data_ptr(), nbytes)
+                pipe.result(pipe.submit(cam.frame(W, H, i, spp)))
+            pipe.drain()
             barrier()
             t0 = time.perf_counter()
+            last, seen = None, 0
             for i in range(e2e_steps):
-                r.set_frame(cam.frame(W, H, i, spp))   # host: Camera -> FrameUBO (560 B) -> kernel constants
-                step()
-                stream.synchronize()
-                r.readback_into(img, host.data_ptr(), nbytes)  # device -> pinned host, synchronises
+                tk = pipe.submit(cam.frame(W, H, i, spp))
+                if last is not None:
+                    seen += int(pipe.result(last)["node"][H // 2, W // 2] != 0xFFFFFFFF)
+                last = tk
+            seen += int(pipe.result(last)["node"][H // 2, W // 2] != 0xFFFFFFFF)
+            pipe.drain()
             barrier()
             dt = max_over_ranks(time.perf_counter() - t0)
+            pipe.close()
             out["e2e"] = {"value": total_rays * e2e_steps / dt / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 560,
                           "d2h_bytes_per_step": nbytes, "steps": e2e_steps, "ms_per_step": dt / e2e_steps * 1e3,
-                          "what": "Camera -> FrameUBO on host, blokb_set_frame, blokb_trace_primary, blokb_readback of the "
-                                  "16-B hit records into pinned host memory; scene uploaded once beforehand (Renderer::addWorld)"}
+                          "what": "FramePipeline (blokb_pipeline_*, 2 frames in flight): Camera -> FrameUBO on host, submit = primary pass + "
+                                  "async copy of the 16-B hit records to pinned host memory, result(previous frame) read on the host; "
+                                  "scene uploaded once beforehand (Renderer::addWorld)"}
             r.set_frame(ubo)
         elif e2e:
             nbytes = W * H * 16

@@ -4,5 +4,5 @@ Only what the hot path needs: csrc/ (CUDA kernels + C-ABI, built into libblokb20
 reference's Renderer / Camera / WorldSvoGpu interface), scenes.py (deterministic synthetic worlds for bench and tests),
 sharding.py (tile / sample partition across GPUs).
 """
-from .api import (BlokbError, Camera, FrameUBO, Renderer, WorldSvoGpu, load_library, HIT_DT, MAT_DT, NODE_DT, SUB_DT,  # noqa: F401
+from .api import (BlokbError, Camera, FramePipeline, FrameUBO, Renderer, WorldSvoGpu, load_library, HIT_DT, MAT_DT, NODE_DT, SUB_DT,  # noqa: F401
                   IMG_ACCUM, IMG_ALBEDOMETAL, IMG_COLOR, IMG_HIT, IMG_MOTION, IMG_NORMALROUGH, IMG_SHADOW, IMG_WORLDPOS)

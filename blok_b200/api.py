@@ -90,7 +90,8 @@ EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_wo
            "blokb_resolve", "blokb_reset_accum", "blokb_trace_rays", "blokb_trace_rays_host", "blokb_get_buffers",
            "blokb_readback", "blokb_sync", "blokb_launch_count", "blokb_stats_enable", "blokb_stats_read", "blokb_stream",
            "blokb_worldgen_pack", "blokb_worldgen_counts", "blokb_worldgen_copy", "blokb_worldgen_nodes", "blokb_worldgen_subs",
-           "blokb_worldgen_free"]
+           "blokb_worldgen_free", "blokb_pipeline_create", "blokb_pipeline_submit", "blokb_pipeline_wait", "blokb_pipeline_drain",
+           "blokb_pipeline_destroy", "blokb_host_alloc", "blokb_host_free"]
 
 _lib = None
 
@@ -134,6 +135,16 @@ def load_library():
     L.blokb_worldgen_copy.restype = None
     L.blokb_worldgen_free.argtypes = [_vp]
     L.blokb_worldgen_free.restype = None
+    L.blokb_pipeline_create.argtypes = [_vp, C.c_int, C.c_uint32, C.c_uint32, C.POINTER(_vp)]
+    L.blokb_pipeline_submit.argtypes = [_vp, C.POINTER(FrameUBO), _vp, C.POINTER(C.c_uint64)]
+    L.blokb_pipeline_wait.argtypes = [_vp, C.c_uint64]
+    L.blokb_pipeline_drain.argtypes = [_vp]
+    L.blokb_pipeline_destroy.argtypes = [_vp]
+    L.blokb_pipeline_destroy.restype = None
+    L.blokb_host_alloc.argtypes = [C.c_size_t]
+    L.blokb_host_alloc.restype = _vp
+    L.blokb_host_free.argtypes = [_vp]
+    L.blokb_host_free.restype = None
     _lib = L
     return L
 
@@ -318,3 +329,53 @@ class Renderer:
         v = np.zeros(2, np.uint64)
         _ck(self.L.blokb_stats_read(self._ctx, _ptr(v)))
         return int(v[0]), int(v[1])
+
+
+class FramePipeline:
+    """Frames in flight (the reference keeps 2, blok/include/renderer.hpp:185): submit(frame) enqueues the primary pass
+    and the device->host copy of its hit records into one of `depth` pinned host images; the copy of frame i overlaps
+    the tracing of frame i+1. result(ticket) waits for that frame's copy and returns its (h, w) HIT_DT view (valid until
+    `depth` more frames have been submitted)."""
+
+    def __init__(self, renderer: Renderer, width: int, height: int, depth: int = 2):
+        self.L, self.r, self.width, self.height, self.depth = renderer.L, renderer, width, height, depth
+        self._p = _vp()
+        _ck(self.L.blokb_pipeline_create(renderer._ctx, depth, width, height, C.byref(self._p)))
+        self.nbytes = width * height * HIT_DT.itemsize
+        self._host = []
+        for _ in range(depth):
+            h = self.L.blokb_host_alloc(self.nbytes)
+            if not h:
+                raise MemoryError("blokb_host_alloc")
+            self._host.append(h)
+
+    def submit(self, frame) -> int:
+        if isinstance(frame, Camera):
+            frame = frame.frame(self.width, self.height)
+        t = C.c_uint64()
+        n = getattr(self, "_n", 0)
+        _ck(self.L.blokb_pipeline_submit(self._p, C.byref(frame), self._host[n % self.depth], C.byref(t)))
+        self._n = n + 1
+        return int(t.value)
+
+    def result(self, ticket: int) -> np.ndarray:
+        _ck(self.L.blokb_pipeline_wait(self._p, ticket))
+        buf = (C.c_char * self.nbytes).from_address(self._host[ticket % self.depth])
+        return np.frombuffer(buf, dtype=HIT_DT).reshape(self.height, self.width)
+
+    def drain(self):
+        _ck(self.L.blokb_pipeline_drain(self._p))
+
+    def close(self):
+        if self._p:
+            self.L.blokb_pipeline_destroy(self._p)
+            self._p = _vp()
+            for h in self._host:
+                self.L.blokb_host_free(h)
+            self._host = []
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -323,4 +323,100 @@ int blokb_stats_read(blokb_ctx* c, uint64_t* stepsAndRays /*[2]*/) {
     return 0;
 }
 void* blokb_stream(blokb_ctx* c) { return c ? c->stream : nullptr; }
+
+// ---- frames in flight ---------------------------------------------------------------------------------------
+struct blokb_pipeline {
+    blokb_ctx* ctx = nullptr;
+    int depth = 0;
+    uint32_t width = 0, height = 0;
+    std::vector<blokb_hit*> dHit;
+    std::vector<cudaEvent_t> traced, copied;
+    cudaStream_t copyStream = nullptr;
+    uint64_t submitted = 0;
+};
+
+int blokb_pipeline_create(blokb_ctx* c, int depth, uint32_t width, uint32_t height, blokb_pipeline** out) {
+    if (!c || !out) return fail(BLOKB_E_ARG, "null argument");
+    *out = nullptr;
+    if (depth < 1 || depth > 8 || width == 0 || height == 0 || width > 65536 || height > 65536) return fail(BLOKB_E_ARG, "bad pipeline shape");
+    CK(cudaSetDevice(c->device));
+    blokb_pipeline* p = new (std::nothrow) blokb_pipeline;
+    if (!p) return fail(BLOKB_E_ARG, "out of host memory");
+    p->ctx = c; p->depth = depth; p->width = width; p->height = height;
+    auto bail = [&](cudaError_t e) { blokb_pipeline_destroy(p); return fail(BLOKB_E_CUDA, cudaGetErrorString(e)); };
+    cudaError_t e = cudaStreamCreateWithFlags(&p->copyStream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) return bail(e);
+    for (int i = 0; i < depth; i++) {
+        blokb_hit* d = nullptr;
+        cudaEvent_t a = nullptr, b = nullptr;
+        if ((e = cudaMalloc((void**)&d, size_t(width) * height * sizeof(blokb_hit))) != cudaSuccess) return bail(e);
+        p->dHit.push_back(d);
+        if ((e = cudaEventCreateWithFlags(&a, cudaEventDisableTiming)) != cudaSuccess) return bail(e);
+        p->traced.push_back(a);
+        if ((e = cudaEventCreateWithFlags(&b, cudaEventDisableTiming)) != cudaSuccess) return bail(e);
+        p->copied.push_back(b);
+    }
+    *out = p;
+    return 0;
+}
+
+int blokb_pipeline_submit(blokb_pipeline* p, const blokb_frame_ubo* f, blokb_hit* hostOut, uint64_t* ticket) {
+    if (!p || !f || !hostOut) return fail(BLOKB_E_ARG, "null argument");
+    blokb_ctx* c = p->ctx;
+    if (!c->haveWorld) return fail(BLOKB_E_STATE, "no world uploaded (blokb_upload_world)");
+    if (f->screenWidth != p->width || f->screenHeight != p->height) return fail(BLOKB_E_ARG, "frame size differs from the pipeline's");
+    CK(cudaSetDevice(c->device));
+    const int slot = int(p->submitted % uint64_t(p->depth));
+    FrameDev d{};
+    std::memcpy(d.invView, f->invView, 64);
+    std::memcpy(d.invProj, f->invProj, 64);
+    std::memcpy(d.prevViewProj, f->prevViewProj, 64);
+    std::memcpy(d.camPos, f->camPos, 12);
+    d.frameCount = f->frameCount; d.sampleCount = f->sampleCount; d.width = f->screenWidth; d.height = f->screenHeight;
+    if (p->submitted >= uint64_t(p->depth)) CK(cudaStreamWaitEvent(c->stream, p->copied[slot], 0));  // slot's previous copy must have drained
+    CK(launch_primary(c->dw, d, false, p->dHit[slot], nullptr, st(c), c->stream));
+    c->launches++;
+    CK(cudaEventRecord(p->traced[slot], c->stream));
+    CK(cudaStreamWaitEvent(p->copyStream, p->traced[slot], 0));
+    CK(cudaMemcpyAsync(hostOut, p->dHit[slot], size_t(p->width) * p->height * sizeof(blokb_hit), cudaMemcpyDeviceToHost, p->copyStream));
+    CK(cudaEventRecord(p->copied[slot], p->copyStream));
+    if (ticket) *ticket = p->submitted;
+    p->submitted++;
+    return 0;
+}
+
+int blokb_pipeline_wait(blokb_pipeline* p, uint64_t ticket) {
+    if (!p) return fail(BLOKB_E_ARG, "pipeline is null");
+    if (ticket >= p->submitted || ticket + uint64_t(p->depth) < p->submitted) return fail(BLOKB_E_ARG, "ticket not in flight");
+    CK(cudaSetDevice(p->ctx->device));
+    CK(cudaEventSynchronize(p->copied[ticket % uint64_t(p->depth)]));
+    return 0;
+}
+
+int blokb_pipeline_drain(blokb_pipeline* p) {
+    if (!p) return fail(BLOKB_E_ARG, "pipeline is null");
+    CK(cudaSetDevice(p->ctx->device));
+    CK(cudaStreamSynchronize(p->ctx->stream));
+    CK(cudaStreamSynchronize(p->copyStream));
+    return 0;
+}
+
+void blokb_pipeline_destroy(blokb_pipeline* p) {
+    if (!p) return;
+    cudaSetDevice(p->ctx->device);
+    if (p->copyStream) cudaStreamSynchronize(p->copyStream);
+    cudaStreamSynchronize(p->ctx->stream);
+    for (auto d : p->dHit) cudaFree(d);
+    for (auto e : p->traced) cudaEventDestroy(e);
+    for (auto e : p->copied) cudaEventDestroy(e);
+    if (p->copyStream) cudaStreamDestroy(p->copyStream);
+    delete p;
+}
+
+void* blokb_host_alloc(size_t bytes) {
+    void* h = nullptr;
+    if (cudaHostAlloc(&h, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) { g_err = "cudaHostAlloc failed"; return nullptr; }
+    return h;
+}
+void blokb_host_free(void* h) { if (h) cudaFreeHost(h); }
 }

@@ -170,6 +170,21 @@ int blokb_stats_read(blokb_ctx* ctx, uint64_t* stepsAndRays);
 /* The context's own CUDA stream (cudaStream_t). */
 void* blokb_stream(blokb_ctx* ctx);
 
+/* Frames in flight (the reference keeps 2: blok/include/renderer.hpp:185). A pipeline owns `depth` device hit images, a
+ * copy stream and events: submit() enqueues the primary pass of one frame on the context's stream and the device->host
+ * copy of its hit records into `hostOut` (w*h blokb_hit; pinned memory from blokb_host_alloc for full PCIe speed) on the
+ * copy stream, so the copy of frame i overlaps the tracing of frame i+1. Nothing blocks the host until wait()/drain().
+ * Tickets count submissions from 0; wait(t) is valid for the last `depth` tickets. */
+typedef struct blokb_pipeline blokb_pipeline;
+int blokb_pipeline_create(blokb_ctx* ctx, int depth, uint32_t width, uint32_t height, blokb_pipeline** out);
+int blokb_pipeline_submit(blokb_pipeline* p, const blokb_frame_ubo* frame, blokb_hit* hostOut, uint64_t* ticket);
+int blokb_pipeline_wait(blokb_pipeline* p, uint64_t ticket);
+int blokb_pipeline_drain(blokb_pipeline* p);
+void blokb_pipeline_destroy(blokb_pipeline* p);
+/* Page-locked host memory (cudaHostAlloc / cudaFreeHost). */
+void* blokb_host_alloc(size_t bytes);
+void blokb_host_free(void* p);
+
 /* Host helper (no GPU involved): voxel list -> the reference's upload arrays, restating ChunkManager(128, 1.0f) +
  * rebuildDirtyChunks + packChunksToGpuSvo (chunk_manager.cpp:106-140, 234-314; svo.cpp:59-101). Chunks are emitted
  * sorted by (z, y, x); the reference's order is that of a std::unordered_map (unspecified). */

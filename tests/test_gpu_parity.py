@@ -190,3 +190,28 @@ def test_full_size_properties_terrain(renderer_factory, oracle):
     h, t, cnt = oracle.trace(to_scene(w), rays[idx], threads=8)
     _check_hits(out[idx], h, t)
     assert cnt[2] == 0
+
+
+def test_frame_pipeline_matches_blocking_path(renderer_factory):
+    """Frames in flight: records delivered by the pipeline == trace_primary + readback, frame by frame."""
+    z, w = _gold(GOLD[2])
+    r = renderer_factory(160, 96)
+    r.add_world(w)
+    cams = [Camera((-60 + 3 * i, 40, 30 - 2 * i), 0.0 + 2 * i, -10.0) for i in range(5)]
+    pipe = blok_b200.FramePipeline(r, 160, 96, depth=2)
+    tickets = []
+    got = []
+    for c in cams:
+        tickets.append(pipe.submit(c.frame(160, 96, 0, 1)))
+        if len(tickets) > 1:
+            got.append(pipe.result(tickets[-2]).copy())
+    got.append(pipe.result(tickets[-1]).copy())
+    pipe.drain()
+    with pytest.raises(blok_b200.BlokbError):
+        pipe.result(0)  # no longer in flight
+    pipe.close()
+    for c, g in zip(cams, got):
+        r.trace_primary(c.frame(160, 96, 0, 1))
+        want = r.readback(IMG_HIT)
+        assert np.array_equal(g.view(np.uint32), want.view(np.uint32))
+    assert sum(int((g["node"] != 0xFFFFFFFF).sum()) for g in got) > 1000
