@@ -53,7 +53,7 @@ __global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceW
     HitRec h;
     uint32_t steps = 0;
     const NodeStack stk = thread_stack();
-    const bool hit = traverse<kStats>(W, stk, F.camPos[0], F.camPos[1], F.camPos[2], d.x, d.y, d.z, 0.001f, 10000.0f, h, steps);
+    const bool hit = traverse<kStats>(W, stk, F.camPos[0], F.camPos[1], F.camPos[2], d.x, d.y, d.z, 0.001f, 10000.0f, h, steps, /*locate=*/false);
     const size_t pi = size_t(py) * F.width + px;
     store_hit(out + pi, hit, h);
     if (kShadow) {
@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceW
             if (fmaxf(dot3(N, sunDir), 0.0f) > 0.0f) {
                 const F3 o = f3(F.camPos[0], F.camPos[1], F.camPos[2]) + d * h.t + N * 0.001f;
                 HitRec sh;
-                sv = traverse<kStats>(W, stk, o.x, o.y, o.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps) ? 2 : 1;
+                sv = traverse<kStats>(W, stk, o.x, o.y, o.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps, true) ? 2 : 1;
             }
         }
         shadow[pi] = sv;

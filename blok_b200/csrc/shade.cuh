@@ -139,7 +139,10 @@ BLOKB_HD F3 path_sample(const DeviceWorld& W, const NodeStack& stk, const FrameD
     for (uint32_t bounce = 0u; bounce < 2u; bounce++) {
         HitRec h;
         rays++;
-        if (!traverse<kStats>(W, stk, rayOrigin.x, rayOrigin.y, rayOrigin.z, rayDir.x, rayDir.y, rayDir.z, 0.001f, 10000.0f, h, steps)) {
+        // the camera ray enters the grid from outside, the bounce ray starts on geometry: different start-cell strategies
+        const bool hit = traverse<kStats>(W, stk, rayOrigin.x, rayOrigin.y, rayOrigin.z, rayDir.x, rayDir.y, rayDir.z, 0.001f, 10000.0f, h, steps,
+                                          /*locate=*/bounce > 0u);
+        if (!hit) {
             radiance = radiance + thr * sky_color(rayDir);
             break;
         }
@@ -160,7 +163,7 @@ BLOKB_HD F3 path_sample(const DeviceWorld& W, const NodeStack& stk, const FrameD
             const F3 so = hitPos + N * 0.001f;
             HitRec sh;
             rays++;
-            if (!traverse<kStats>(W, stk, so.x, so.y, so.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps)) {
+            if (!traverse<kStats>(W, stk, so.x, so.y, so.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps, true)) {
                 const F3 diffuse = m.albedo * (1.0f - m.metallic);
                 radiance = radiance + thr * diffuse * sunRad * NdotL * BLOKB_INV_PI;
                 if (m.roughness < 0.9f) {

@@ -72,6 +72,22 @@ BLOKB_HD void select_child(uint32_t& m, float& w, uint32_t& bit, int axisShift, 
     if (lo) { m += s; bit += 1u << axisShift; }
 }
 
+// Mirrored voxel coordinate m (and float(P(m)) of its near plane) of the voxel holding parameter t on one axis:
+// the k with T(k) <= t < T(k + 1). The guess floor(o + d*t) is off by at most a cell or two near planes; the loops
+// settle it with the exact slab values. [lo, hi] = the grid's extent in the mirrored frame (the clip in init()
+// guarantees the answer lies inside it; the bounds only make termination unconditional).
+BLOKB_HD void locate_axis(uint32_t& m, float& w, int g, int dim, int cap, bool pos, float o, float s, float inv, float t) {
+    int x = __float2int_rd(o + s * t) - g;
+    x = x < 0 ? 0 : (x > dim - 1 ? dim - 1 : x);
+    int k = pos ? x : cap - 1 - x;
+    const int lo = pos ? 0 : cap - dim, hi = pos ? dim - 1 : cap - 1;
+    const int base = pos ? g : g + cap, sg = pos ? 1 : -1;  // P(k) = base + sg * k
+    while (k < hi && plane_t(base + sg * (k + 1), o, inv) <= t) k++;
+    while (k > lo && plane_t(base + sg * k, o, inv) > t) k--;
+    m = uint32_t(k);
+    w = float(base + sg * k);
+}
+
 // Per-ray stack of the nodes on the current root-to-cell path, one 16-byte entry per level (entry k-1 = the level-k
 // cell). In kernels it lives in shared memory, laid out [level][thread] so that a warp's accesses are conflict-free
 // 16-byte rows (addressed through a 32-bit shared-window address); the host emulation passes a plain array
@@ -130,8 +146,8 @@ struct Walker {
     }
     BLOKB_HD void bit_from_m() { bit = ((mx >> sh) & 3u) | (((my >> sh) & 3u) << 2) | (((mz >> sh) & 3u) << 4); }
 
-    // Returns false when the ray misses the grid box altogether.
-    BLOKB_HD bool init(const DeviceWorld& W, float ox_, float oy_, float oz_, float dx, float dy, float dz, float tmin, float tmax) {
+    // Returns false when the ray misses the grid box altogether. `locate` picks how the start cell is found (below).
+    BLOKB_HD bool init(const DeviceWorld& W, float ox_, float oy_, float oz_, float dx, float dy, float dz, float tmin, float tmax, bool locate) {
         ox = ox_; oy = oy_; oz = oz_;
         const float sx = fabsf(dx) < 1e-6f ? 1e-6f : dx, sy = fabsf(dy) < 1e-6f ? 1e-6f : dy, sz = fabsf(dz) < 1e-6f ? 1e-6f : dz;
         ix = 1.0f / sx; iy = 1.0f / sy; iz = 1.0f / sz;
@@ -151,13 +167,26 @@ struct Walker {
         const int cap = 1 << (2 * L);
         flip = (px ? 0u : 3u) | (py ? 0u : 12u) | (pz ? 0u : 48u);
         gsx = px ? 1.0f : -1.0f; gsy = py ? 1.0f : -1.0f; gsz = pz ? 1.0f : -1.0f;
-        mx = my = mz = 0;
-        wx = float(px ? gx : gx + cap); wy = float(py ? gy : gy + cap); wz = float(pz ? gz : gz + cap);
         sh = 2 * (L - 1);
         fs = pow2f(sh);
         const uint4 r = __ldg(W.nodes);
         mlo = r.x; mhi = r.y; base = r.z; aux = r.w;
-        select();
+        if (locate) {
+            // Rays that start ON geometry (shadow, bounce): their first descent runs all the way to voxel level, so find
+            // the start voxel per axis once — an arithmetic guess settled with the same plane tests every other decision
+            // uses (T(m) <= t < T(m + 1) in the mirrored frame) — and let the whole descent read child indices off m.
+            locate_axis(mx, wx, gx, W.dim[0], cap, px, ox, sx, ix, t);
+            locate_axis(my, wy, gy, W.dim[1], cap, py, oy, sy, iy, t);
+            locate_axis(mz, wz, gz, W.dim[2], cap, pz, oz, sz, iz, t);
+            rs = 0;
+            bit_from_m();
+        } else {
+            // Rays that enter the grid from outside (primary): the first descent stops at the first empty cell, usually a
+            // coarse one, so refine level by level with plane tests only as deep as it goes.
+            mx = my = mz = 0;
+            wx = float(px ? gx : gx + cap); wy = float(py ? gy : gy + cap); wz = float(pz ? gz : gz + cap);
+            select();
+        }
         return true;
     }
 
@@ -247,9 +276,9 @@ struct Walker {
 // after the loop — lanes re-converge at every step instead of drifting apart between descend and step phases.
 template <bool kStats>
 BLOKB_HD bool traverse(const DeviceWorld& W, const NodeStack& stk, float ox, float oy, float oz, float dx, float dy, float dz,
-                       float tmin, float tmax, HitRec& out, uint32_t& steps) {
+                       float tmin, float tmax, HitRec& out, uint32_t& steps, bool locate = true) {
     Walker wk;
-    if (!wk.init(W, ox, oy, oz, dx, dy, dz, tmin, tmax)) return false;
+    if (!wk.init(W, ox, oy, oz, dx, dy, dz, tmin, tmax, locate)) return false;
     bool hit = false;
     for (;;) {
         while (wk.occupied()) {

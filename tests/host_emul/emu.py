@@ -33,11 +33,12 @@ class Emu:
     def ok(self):
         return bool(self.h)
 
-    def trace(self, rays, threads=8):
+    def trace(self, rays, threads=8, locate=True):
+        """locate: start-cell strategy of Walker::init (True = secondary-ray style, False = primary-ray style)."""
         from blok_b200.api import HIT_DT
         rays = np.ascontiguousarray(rays, np.float32)
         out = np.empty(len(rays), HIT_DT)
-        steps = self.lib.emu_trace(self.h, rays.ctypes.data_as(_vp), len(rays), out.ctypes.data_as(_vp), threads)
+        steps = self.lib.emu_trace(self.h, rays.ctypes.data_as(_vp), len(rays), out.ctypes.data_as(_vp), threads, int(locate))
         return out, steps
 
     def path(self, ubo, s_begin, s_end, threads=8):
@@ -65,7 +66,7 @@ class EmuLib:
         L.emu_create.argtypes = [_vp, C.c_size_t, _vp, C.c_size_t, _vp, C.c_size_t, C.c_char_p, C.c_size_t, _vp]
         L.emu_destroy.argtypes = [_vp]
         L.emu_trace.restype = C.c_uint64
-        L.emu_trace.argtypes = [_vp, _vp, C.c_size_t, _vp, C.c_int]
+        L.emu_trace.argtypes = [_vp, _vp, C.c_size_t, _vp, C.c_int, C.c_int]
         L.emu_path.argtypes = [_vp, _vp, C.c_uint32, C.c_uint32, _vp, C.c_int]
         L.emu_stats.argtypes = [_vp, _vp]
         self.L = L

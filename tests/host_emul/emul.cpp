@@ -52,7 +52,7 @@ void emu_stats(void* p, uint64_t* out /* bricks, blocks, voxels, compactBytes, l
     out[0] = e->hw.bricks.size(); out[1] = e->hw.blockFirstLeaf.size(); out[2] = e->hw.voxels; out[3] = e->hw.compactBytes(); out[4] = e->hw.levels; out[5] = e->hw.matWide;
 }
 // rays n x 8 -> blokb_hit n; returns total DDA steps
-uint64_t emu_trace(void* p, const float* rays, size_t n, blokb_hit* out, int nThreads) {
+uint64_t emu_trace(void* p, const float* rays, size_t n, blokb_hit* out, int nThreads, int locate) {
     Emu* e = (Emu*)p;
     std::atomic<uint64_t> total{0};
     pfor(n, nThreads, [&](size_t b, size_t en) {
@@ -60,7 +60,8 @@ uint64_t emu_trace(void* p, const float* rays, size_t n, blokb_hit* out, int nTh
         for (size_t i = b; i < en; i++) {
             const float* r = rays + 8 * i;
             HitRec h; uint32_t steps = 0; uint4 stackMem[kMaxLevels]; const NodeStack stk{stackMem, 1};
-            if (traverse<true>(e->dw, stk, r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7], h, steps)) out[i] = blokb_hit{h.node, h.material, h.t, h.facePrim};
+            const bool hit = traverse<true>(e->dw, stk, r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7], h, steps, locate != 0);
+            if (hit) out[i] = blokb_hit{h.node, h.material, h.t, h.facePrim};
             else out[i] = blokb_hit{0xFFFFFFFFu, 0xFFFFFFFFu, -1.0f, 0xFFFFFFFFu};
             st += steps;
         }

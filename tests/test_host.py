@@ -86,12 +86,13 @@ def test_dda_logic_matches_reference_goldens(emul, oracle, path):
     e = emul.world(w)
     assert e.ok(), e.err
     rays = oracle.primary_rays(z["ubo_s"])
-    out, _ = e.trace(rays)
     g = z["hits_s"]
     hit = g[:, 0] != 0xFFFFFFFF
-    assert np.array_equal(out["node"], g[:, 1]) and np.array_equal(out["material"], g[:, 2])
-    assert np.array_equal(out["t"].view(np.uint32), g[:, 4])
-    assert np.array_equal(out["facePrim"][hit] & 7, g[hit, 3]) and np.array_equal(out["facePrim"][hit] >> 3, g[hit, 0])
+    for locate in (True, False):  # both start-cell strategies of Walker::init
+        out, _ = e.trace(rays, locate=locate)
+        assert np.array_equal(out["node"], g[:, 1]) and np.array_equal(out["material"], g[:, 2])
+        assert np.array_equal(out["t"].view(np.uint32), g[:, 4])
+        assert np.array_equal(out["facePrim"][hit] & 7, g[hit, 3]) and np.array_equal(out["facePrim"][hit] >> 3, g[hit, 0])
     # 512x512 via the checksum of the reference's records
     rays = oracle.primary_rays(z["ubo_l"])
     out, _ = e.trace(rays)
@@ -107,10 +108,11 @@ def test_dda_logic_random_and_degenerate_rays(emul, oracle):
     w = WorldSvoGpu.from_voxels(xyz, m, mats)
     e = emul.world(w)
     rays = make_rays(rng, 60000, -90, 200)
-    out, _ = e.trace(rays)
     h, t, _ = oracle.trace(to_scene(w), rays, threads=8)
-    assert np.array_equal(out["node"], h[:, 1]) and np.array_equal(out["t"].view(np.uint32), t.view(np.uint32))
-    assert np.array_equal(out["material"], h[:, 2])
+    for locate in (True, False):
+        out, _ = e.trace(rays, locate=locate)
+        assert np.array_equal(out["node"], h[:, 1]) and np.array_equal(out["t"].view(np.uint32), t.view(np.uint32))
+        assert np.array_equal(out["material"], h[:, 2])
 
 
 def test_dda_path_samples_match_oracle(emul, oracle):
