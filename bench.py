@@ -37,7 +37,7 @@ def parse_args():
     p.add_argument("--steps", type=int, default=100)
     p.add_argument("--warmup", type=int, default=5)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    p.add_argument("--workload", default="c3", choices=["c2", "c3", "c4", "t1"])
+    p.add_argument("--workload", default="c3", choices=["c2", "c3", "c4", "c5", "t1"])
     p.add_argument("--no-extras", action="store_true", help="skip the secondary workloads (c2, c4) and warm-L2 numbers")
     p.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (then roofline uses cached V, A)")
     p.add_argument("--write-counts", action="store_true", help="(--impl reference) store V, A in blok_b200/workload_counts.json")

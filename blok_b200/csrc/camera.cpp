@@ -89,8 +89,9 @@ extern "C" int blokb_camera_frame(const blokb_camera* cam, uint32_t width, uint3
     for (int i = 0; i < 3; i++) out->camPos[i] = out->prevCamPos[i] = cam->position[i];
     out->depth = 1;
     out->frameCount = frameCount; out->sampleCount = sampleCount; out->screenWidth = width; out->screenHeight = height;
-    out->temporalAlpha = 0.05f; out->momentAlpha = 0.2f; out->varianceClipGamma = 1.0f; out->depthThreshold = 0.02f;
-    out->normalThreshold = 0.9f; out->phiColor = 4.0f; out->phiNormal = 128.0f; out->phiDepth = 1.0f;
-    out->atrousIteration = 0; out->stepSize = 1; out->varianceBoost = 1.0f; out->minHistoryLength = 4;
+    // Denoiser::Settings defaults (blok/include/renderer_denoising.hpp:57-76), copied in by fillFrameUBO (renderer_denoising.cpp:686-703)
+    out->temporalAlpha = 0.05f; out->momentAlpha = 0.2f; out->varianceClipGamma = 1.5f; out->depthThreshold = 0.1f;
+    out->normalThreshold = 0.95f; out->phiColor = 0.5f; out->phiNormal = 128.0f; out->phiDepth = 0.1f;
+    out->atrousIteration = 0; out->stepSize = 1; out->varianceBoost = 1.5f; out->minHistoryLength = 4;
     return 0;
 }

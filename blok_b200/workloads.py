@@ -3,6 +3,8 @@
   c2  512^3 dense blob "mesh", 1920x1080, primary + sun shadow rays          (BASELINE configs[1])
   c3  2048^3 heightfield-shell terrain, 3840x2160, primary rays              (configs[2])  <- bench.py headline
   c4  the c3 scene path traced: 64 spp, <=2 bounces + 1 shadow ray, spp sharded across GPUs   (configs[3])
+  c5  8192^3 terrain, 7680x4320, 1 spp path (primary + shadow + incoherent bounce)            (configs[4]; ~6 GB of
+      reference-format input, minutes of host-side generation: run by hand, `python tools/prof.py c5`)
   t1  96^3 terrain, 256x144 — CPU-test / smoke scale of the same shapes
 
 Every workload gives {scene generator, N, width, height, camera, kind, spp}. Camera poses follow §8(d): the c3/c4
@@ -21,6 +23,9 @@ WORKLOADS = {
     "c4": dict(scene="terrain", N=2048, width=3840, height=2160, kind="path", spp=64,
                cam=lambda N: Camera((N / 2, 0.6 * N, -0.2 * N), 90.0, -25.0),
                desc="2048^3 SVO terrain shell, 3840x2160 path traced, 64 spp, 2 bounces + sun shadow ray"),
+    "c5": dict(scene="terrain", N=8192, width=7680, height=4320, kind="path", spp=1,
+               cam=lambda N: Camera((N / 2, 0.6 * N, -0.2 * N), 90.0, -25.0),
+               desc="8192^3 procedural terrain shell, 7680x4320, primary + sun shadow + one incoherent bounce ray per pixel"),
     "t1": dict(scene="terrain", N=96, width=256, height=144, kind="primary", spp=1,
                cam=lambda N: Camera((N / 2, 0.7 * N, -0.3 * N), 90.0, -25.0),
                desc="96^3 terrain shell, 256x144 primary rays (test scale)"),

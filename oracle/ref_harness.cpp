@@ -338,9 +338,10 @@ void ref_make_frame(const float* pos, float yaw, float pitch, float fov, uint32_
     u.prevView = view; u.prevProj = proj; u.prevViewProj = proj * view;
     u.camPos = c.position; u.deltaTime = 0.f; u.prevCamPos = c.position; u.depth = 1;
     u.frameCount = frameCount; u.sampleCount = sampleCount; u.screenWidth = w; u.screenHeight = h;
-    u.temporalAlpha = 0.05f; u.momentAlpha = 0.2f; u.varianceClipGamma = 1.0f; u.depthThreshold = 0.02f;
-    u.normalThreshold = 0.9f; u.phiColor = 4.0f; u.phiNormal = 128.0f; u.phiDepth = 1.0f;
-    u.atrousIteration = 0; u.stepSize = 1; u.varianceBoost = 1.0f; u.minHistoryLength = 4;
+    // Denoiser::Settings defaults (blok/include/renderer_denoising.hpp:57-76), copied in by fillFrameUBO (renderer_denoising.cpp:686-703)
+    u.temporalAlpha = 0.05f; u.momentAlpha = 0.2f; u.varianceClipGamma = 1.5f; u.depthThreshold = 0.1f;
+    u.normalThreshold = 0.95f; u.phiColor = 0.5f; u.phiNormal = 128.0f; u.phiDepth = 0.1f;
+    u.atrousIteration = 0; u.stepSize = 1; u.varianceBoost = 1.5f; u.minHistoryLength = 4;
     std::memcpy(outUbo560, &u, 560);
 }
 

@@ -124,6 +124,20 @@ dkey = (q[:, 0] | (q[:, 1] << 2) | (q[:, 2] << 4)).astype(np.uint64)
 key2 = (dkey << np.uint64(58)) | mc
 o3 = np.argsort(key2, kind="stable")
 timed(bounce[o3], "bounce rays, sorted by 4^3 direction cell + Morton")
+for nb in (8, 16):
+    qq = np.clip(((bd + 1) * (nb / 2)).astype(np.int64), 0, nb - 1)
+    dk = (qq[:, 0] + nb * (qq[:, 1] + nb * qq[:, 2])).astype(np.uint64)
+    for shift, lab in ((2, "origin/4"), (4, "origin/16"), (0, "origin/1")):
+        mc2 = morton3((bo[:, 0]).astype(np.int64) >> shift, (bo[:, 1]).astype(np.int64) >> shift, (bo[:, 2]).astype(np.int64) >> shift)
+        oo = np.lexsort((mc2, dk))
+        timed(bounce[oo], f"bounce rays, {nb}^3 direction cell + Morton({lab})")
+# Morton first (spatial blocks of 16^3), direction cell inside
+mc16 = morton3((bo[:, 0]).astype(np.int64) >> 4, (bo[:, 1]).astype(np.int64) >> 4, (bo[:, 2]).astype(np.int64) >> 4)
+oo = np.lexsort((dkey, mc16))
+timed(bounce[oo], "bounce rays, Morton(origin/16) then 4^3 direction cell")
+mc64 = morton3((bo[:, 0]).astype(np.int64) >> 6, (bo[:, 1]).astype(np.int64) >> 6, (bo[:, 2]).astype(np.int64) >> 6)
+oo = np.lexsort((mc, dkey, mc64))
+timed(bounce[oo], "bounce rays, Morton(origin/64), 4^3 dir cell, Morton(origin/4)")
 up_frac = (bd[:, 1] > 0).mean()
 print("bounce rays going up:", up_frac)
 r.close()
