@@ -7,6 +7,10 @@ against blok itself:
     Renderer.update_world(world)     <- Renderer::updateWorld()                    blok/include/renderer.hpp:55-71
     Renderer.render(camera | ubo)    <- Renderer::render(const Camera&, float dt)  blok/include/renderer.hpp:34
     Renderer.reset_accum()           <- CudaTracer::resetAccum()                   blok/src/cuda_tracer.cu:478-482
+    Renderer.denoise(settings)       <- Denoiser::denoise                          blok/src/renderer_denoising.cpp:714-769
+    Renderer.postprocess(settings)   <- PostProcess::process                       blok/src/renderer_postprocess.cpp:505-558
+    Renderer.end_frame()             <- copyCurrentGeometryToHistory + swapHistoryBuffers (renderer_draw.cpp:182, 327-328)
+    PostSettings                     <- Denoiser::Settings::atrousIterations + PostProcess::Settings
     WorldSvoGpu(nodes, subs, mats)   <- blok::WorldSvoGpu                          blok/include/resources.hpp:195-210
     Camera(position, yaw, pitch, fov)<- blok::Camera                               blok/include/camera.hpp:15-59
 
@@ -29,6 +33,8 @@ HIT_DT = np.dtype([("node", "<u4"), ("material", "<u4"), ("t", "<f4"), ("facePri
 assert NODE_DT.itemsize == 16 and SUB_DT.itemsize == 48 and MAT_DT.itemsize == 32 and HIT_DT.itemsize == 16
 
 IMG_HIT, IMG_SHADOW, IMG_COLOR, IMG_WORLDPOS, IMG_NORMALROUGH, IMG_ALBEDOMETAL, IMG_MOTION, IMG_ACCUM = range(8)
+(IMG_HISTORY_COLOR, IMG_MOMENTS, IMG_HISTORY_LENGTH, IMG_VARIANCE, IMG_DENOISED, IMG_TAA_HISTORY, IMG_TAA_OUTPUT, IMG_TONEMAPPED,
+ IMG_FINAL) = range(8, 17)
 
 _vp = C.c_void_p
 
@@ -62,6 +68,20 @@ class FrameUBO(C.Structure):
 assert C.sizeof(FrameUBO) == 560
 
 
+class PostSettings(C.Structure):
+    """blokb_post_settings: Denoiser::Settings::atrousIterations (renderer_denoising.hpp:71) + PostProcess::Settings
+    (renderer_postprocess.hpp:102-119); defaults are the reference's."""
+    _fields_ = [("atrousIterations", C.c_int32), ("enableTAA", C.c_int32), ("feedbackMin", C.c_float), ("feedbackMax", C.c_float),
+                ("enableTonemapping", C.c_int32), ("exposure", C.c_float), ("saturationBoost", C.c_float), ("tonemapOperator", C.c_int32),
+                ("whitePoint", C.c_float), ("enableSharpening", C.c_int32), ("sharpenStrength", C.c_float)]
+
+    def __init__(self, **kw):
+        super().__init__(4, 1, 0.93, 0.98, 1, 1.0, 1.15, 1, 0.0, 1, 0.5)
+        for k, v in kw.items():
+            assert k in dict(self._fields_), k
+            setattr(self, k, v)
+
+
 class CameraC(C.Structure):
     _fields_ = [("position", C.c_float * 3), ("yaw", C.c_float), ("pitch", C.c_float), ("fov", C.c_float)]
 
@@ -86,12 +106,13 @@ class WorldStats(C.Structure):
 
 # Every symbol include/blokb200.h declares (tests check that the library exports each one).
 EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_world", "blokb_world_stats_get", "blokb_set_frame",
-           "blokb_camera_frame", "blokb_trace_primary", "blokb_trace_primary_shadow", "blokb_render", "blokb_trace_path",
+           "blokb_camera_frame", "blokb_camera_frame_seq", "blokb_trace_primary", "blokb_trace_primary_shadow", "blokb_render", "blokb_trace_path",
            "blokb_resolve", "blokb_reset_accum", "blokb_trace_rays", "blokb_trace_rays_host", "blokb_get_buffers",
            "blokb_readback", "blokb_sync", "blokb_launch_count", "blokb_stats_enable", "blokb_stats_read", "blokb_stream",
            "blokb_worldgen_pack", "blokb_worldgen_counts", "blokb_worldgen_copy", "blokb_worldgen_nodes", "blokb_worldgen_subs",
            "blokb_worldgen_free", "blokb_pipeline_create", "blokb_pipeline_submit", "blokb_pipeline_wait", "blokb_pipeline_drain",
-           "blokb_pipeline_destroy", "blokb_host_alloc", "blokb_host_free"]
+           "blokb_pipeline_destroy", "blokb_host_alloc", "blokb_host_free", "blokb_post_settings_default", "blokb_denoise",
+           "blokb_postprocess", "blokb_end_frame", "blokb_reset_history", "blokb_write_image"]
 
 _lib = None
 
@@ -113,6 +134,8 @@ def load_library():
     L.blokb_world_stats_get.argtypes = [_vp, C.POINTER(WorldStats)]
     L.blokb_set_frame.argtypes = [_vp, C.POINTER(FrameUBO)]
     L.blokb_camera_frame.argtypes = [C.POINTER(CameraC), C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(FrameUBO)]
+    L.blokb_camera_frame_seq.argtypes = [C.POINTER(CameraC), C.POINTER(CameraC), C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int32,
+                                         C.POINTER(FrameUBO)]
     for f in ("blokb_trace_primary", "blokb_trace_primary_shadow", "blokb_render", "blokb_resolve", "blokb_reset_accum"):
         getattr(L, f).argtypes = [_vp, _vp]
     L.blokb_trace_path.argtypes = [_vp, C.c_uint32, C.c_uint32, _vp]
@@ -121,6 +144,13 @@ def load_library():
     L.blokb_get_buffers.argtypes = [_vp, C.POINTER(Buffers)]
     L.blokb_readback.argtypes = [_vp, C.c_int, _vp, C.c_size_t]
     L.blokb_sync.argtypes = [_vp]
+    L.blokb_post_settings_default.argtypes = [C.POINTER(PostSettings)]
+    L.blokb_post_settings_default.restype = None
+    L.blokb_denoise.argtypes = [_vp, C.POINTER(PostSettings), _vp]
+    L.blokb_postprocess.argtypes = [_vp, C.POINTER(PostSettings), _vp]
+    L.blokb_end_frame.argtypes = [_vp, _vp]
+    L.blokb_reset_history.argtypes = [_vp, _vp]
+    L.blokb_write_image.argtypes = [_vp, C.c_int, _vp, C.c_size_t]
     L.blokb_launch_count.argtypes = [_vp]
     L.blokb_launch_count.restype = C.c_uint64
     L.blokb_stats_enable.argtypes = [_vp, C.c_int]
@@ -193,11 +223,20 @@ class Camera:
     def __init__(self, position=(0.0, 10.0, -5.0), yaw=0.0, pitch=0.0, fov=60.0):
         self.position, self.yaw, self.pitch, self.fov = tuple(float(v) for v in position), float(yaw), float(pitch), float(fov)
 
-    def frame(self, width, height, frame_count=0, sample_count=8) -> FrameUBO:
-        """view()/projection() + fillFrameUBO; sample_count defaults to the reference's 8 (renderer_denoising.cpp:683)."""
-        c = CameraC((C.c_float * 3)(*self.position), self.yaw, self.pitch, self.fov)
+    def _c(self):
+        return CameraC((C.c_float * 3)(*self.position), self.yaw, self.pitch, self.fov)
+
+    def frame(self, width, height, frame_count=0, sample_count=8, prev: "Camera" = None, jitter_index=-1) -> FrameUBO:
+        """view()/projection() + fillFrameUBO; sample_count defaults to the reference's 8 (renderer_denoising.cpp:683).
+        prev = the previous frame's camera (prev* matrices for reprojection), jitter_index >= 0 = TAA Halton jitter."""
+        c = self._c()
         out = FrameUBO()
-        _ck(load_library().blokb_camera_frame(C.byref(c), width, height, frame_count, sample_count, C.byref(out)))
+        if prev is None and jitter_index < 0:
+            _ck(load_library().blokb_camera_frame(C.byref(c), width, height, frame_count, sample_count, C.byref(out)))
+        else:
+            pc = prev._c() if prev is not None else None
+            _ck(load_library().blokb_camera_frame_seq(C.byref(c), C.byref(pc) if pc is not None else None, width, height, frame_count,
+                                                      sample_count, jitter_index, C.byref(out)))
         return out
 
 
@@ -265,6 +304,28 @@ class Renderer:
     def reset_accum(self, stream=None):
         _ck(self.L.blokb_reset_accum(self._ctx, stream))
 
+    # ---- denoiser + post-process (enqueue only)
+    def denoise(self, settings: "PostSettings" = None, stream=None):
+        """Denoiser::denoise on the current G-buffer -> IMG_DENOISED (+ history / moments / variance)."""
+        self._post = settings or getattr(self, "_post", None) or PostSettings()
+        _ck(self.L.blokb_denoise(self._ctx, C.byref(self._post), stream))
+
+    def postprocess(self, settings: "PostSettings" = None, stream=None):
+        """PostProcess::process on the denoised image -> IMG_FINAL."""
+        self._post = settings or getattr(self, "_post", None) or PostSettings()
+        _ck(self.L.blokb_postprocess(self._ctx, C.byref(self._post), stream))
+
+    def end_frame(self, stream=None):
+        _ck(self.L.blokb_end_frame(self._ctx, stream))
+
+    def reset_history(self, stream=None):
+        _ck(self.L.blokb_reset_history(self._ctx, stream))
+
+    def write_image(self, image: int, data: np.ndarray):
+        """Host -> device copy into one of the G-buffer images (feeds denoise / postprocess from a G-buffer made elsewhere)."""
+        a = np.ascontiguousarray(data)
+        _ck(self.L.blokb_write_image(self._ctx, image, _ptr(a), a.nbytes))
+
     def trace_rays(self, rays: np.ndarray, any_hit=False) -> np.ndarray:
         """Host rays (n,8) f32 {o,d,tmin,tmax} -> (n,) HIT_DT, through the host-buffer C-ABI call."""
         rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
@@ -285,8 +346,13 @@ class Renderer:
         h, w = self.height, self.width
         shape_dt = {IMG_HIT: ((h, w), HIT_DT), IMG_SHADOW: ((h, w), np.uint8), IMG_COLOR: ((h, w, 4), np.float32),
                     IMG_WORLDPOS: ((h, w, 4), np.float32), IMG_NORMALROUGH: ((h, w, 4), np.float16),
-                    IMG_ALBEDOMETAL: ((h, w, 4), np.uint8), IMG_MOTION: ((h, w, 2), np.float16), IMG_ACCUM: ((h, w, 4), np.float32)}
+                    IMG_ALBEDOMETAL: ((h, w, 4), np.uint8), IMG_MOTION: ((h, w, 2), np.float16), IMG_ACCUM: ((h, w, 4), np.float32),
+                    IMG_HISTORY_COLOR: ((h, w, 4), np.float32), IMG_MOMENTS: ((h, w, 2), np.float32), IMG_HISTORY_LENGTH: ((h, w), np.float16),
+                    IMG_VARIANCE: ((h, w), np.float32), IMG_DENOISED: ((h, w, 4), np.float32), IMG_TAA_HISTORY: ((h, w, 4), np.float32),
+                    IMG_TAA_OUTPUT: ((h, w, 4), np.float32), IMG_TONEMAPPED: ((h, w, 4), np.uint8), IMG_FINAL: ((h, w, 4), np.uint8)}
         shape, dt = shape_dt[image]
+        if image == IMG_FINAL and getattr(self, "_post", None) is not None and not self._post.enableTonemapping:
+            dt = np.float32
         out = np.empty(shape, dt)
         _ck(self.L.blokb_readback(self._ctx, image, _ptr(out), out.nbytes))
         return out

@@ -12,6 +12,7 @@
 
 #include "../../include/blokb200.h"
 #include "kernels.h"
+#include "post.h"
 #include "scene_build.h"
 
 using namespace blokb;
@@ -36,6 +37,27 @@ struct blokb_ctx {
     bool haveFrame = false;
     FrameDev frame{};
     blokb_buffers buf{};
+    // denoiser / post-process images (allocated by the first blokb_denoise / blokb_postprocess at this size)
+    blokb_frame_ubo ubo{};
+    struct Post {
+        bool alloc = false;
+        float* histColor[2] = {nullptr, nullptr};     // gbuffer.historyColor[2]      rgba32f
+        float* histMoments[2] = {nullptr, nullptr};   // gbuffer.historyMoments[2]    rg32f
+        uint16_t* histLen[2] = {nullptr, nullptr};    // gbuffer.historyLength[2]     r16f
+        float* prevWorldPos = nullptr;                // previousWorldPosition()  — the other half of the double-buffered
+        uint16_t* prevNormalRough = nullptr;          // previousNormalRoughness()  G-buffer geometry; roles flip in end_frame
+        float* variance = nullptr;                    // gbuffer.variance             r32f
+        float* ping = nullptr;                        // gbuffer.filterPing / filterPong rgba32f
+        float* pong = nullptr;
+        float* taaHist[2] = {nullptr, nullptr};       // PostProcessBuffers::taaHistory[2] rgba32f
+        float* taaOut = nullptr;                      // taaOutput (only when tonemapping is off)
+        uint8_t* tonemapOut = nullptr;                // tonemapOutput rgba8
+        uint8_t* sharpenOut = nullptr;                // sharpenOutput rgba8
+        int i = 0, j = 0;                             // DenoiserGBuffer::historyIndex, PostProcessBuffers::historyIndex
+        const float* denoised = nullptr;              // Denoiser::getOutputImage() of the current frame
+        const void* final = nullptr;                  // PostProcess::getOutputImage() of the current frame
+        size_t finalBytesPerPixel = 0;
+    } post;
     // scratch for host-ray calls
     float* dRays = nullptr;
     blokb_hit* dHits = nullptr;
@@ -54,6 +76,11 @@ static void free_images(blokb_ctx* c) {
     void* ps[] = {c->buf.hit, c->buf.shadow, c->buf.color, c->buf.worldPos, c->buf.normalRough, c->buf.albedoMetal, c->buf.motion, c->buf.accum};
     for (void* p : ps) if (p) cudaFree(p);
     c->buf = blokb_buffers{};
+    auto& P = c->post;
+    void* qs[] = {P.histColor[0], P.histColor[1], P.histMoments[0], P.histMoments[1], P.histLen[0], P.histLen[1], P.prevWorldPos, P.prevNormalRough,
+                  P.variance, P.ping, P.pong, P.taaHist[0], P.taaHist[1], P.taaOut, P.tonemapOut, P.sharpenOut};
+    for (void* p : qs) if (p) cudaFree(p);
+    P = blokb_ctx::Post{};
 }
 
 template <class T>
@@ -185,6 +212,7 @@ int blokb_set_frame(blokb_ctx* c, const blokb_frame_ubo* f) {
     std::memcpy(d.prevViewProj, f->prevViewProj, 64);
     std::memcpy(d.camPos, f->camPos, 12);
     d.frameCount = f->frameCount; d.sampleCount = f->sampleCount; d.width = f->screenWidth; d.height = f->screenHeight;
+    c->ubo = *f;
     c->haveFrame = true;
     return 0;
 }
@@ -268,6 +296,118 @@ int blokb_trace_rays_host(blokb_ctx* c, const float* rays, size_t n, int anyHit,
     return 0;
 }
 
+// ---- denoiser + post-process ------------------------------------------------------
+void blokb_post_settings_default(blokb_post_settings* s) {
+    if (!s) return;
+    // Denoiser::Settings (renderer_denoising.hpp:57-76), PostProcess::Settings (renderer_postprocess.hpp:102-119)
+    *s = blokb_post_settings{4, 1, 0.93f, 0.98f, 1, 1.0f, 1.15f, 1, 0.0f, 1, 0.5f};
+}
+static int post_zero(blokb_ctx* c, cudaStream_t s) {
+    auto& P = c->post;
+    const size_t n = size_t(c->buf.width) * c->buf.height;
+    for (int k = 0; k < 2; k++) {
+        CK(cudaMemsetAsync(P.histColor[k], 0, n * 16, s));
+        CK(cudaMemsetAsync(P.histMoments[k], 0, n * 8, s));
+        CK(cudaMemsetAsync(P.histLen[k], 0, n * 2, s));
+        CK(cudaMemsetAsync(P.taaHist[k], 0, n * 16, s));
+    }
+    CK(cudaMemsetAsync(P.prevWorldPos, 0, n * 16, s));
+    CK(cudaMemsetAsync(P.prevNormalRough, 0, n * 8, s));
+    P.i = P.j = 0;
+    P.denoised = nullptr; P.final = nullptr;
+    return 0;
+}
+static int post_ready(blokb_ctx* c, const blokb_post_settings* s, cudaStream_t stream) {
+    if (!c || !s) return fail(BLOKB_E_ARG, "null argument");
+    if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
+    CK(cudaSetDevice(c->device));
+    auto& P = c->post;
+    if (P.alloc) return 0;
+    const size_t n = size_t(c->buf.width) * c->buf.height;
+    for (int k = 0; k < 2; k++) {
+        CK(cudaMalloc((void**)&P.histColor[k], n * 16));
+        CK(cudaMalloc((void**)&P.histMoments[k], n * 8));
+        CK(cudaMalloc((void**)&P.histLen[k], n * 2));
+        CK(cudaMalloc((void**)&P.taaHist[k], n * 16));
+    }
+    CK(cudaMalloc((void**)&P.prevWorldPos, n * 16));
+    CK(cudaMalloc((void**)&P.prevNormalRough, n * 8));
+    CK(cudaMalloc((void**)&P.variance, n * 4));
+    CK(cudaMalloc((void**)&P.ping, n * 16));
+    CK(cudaMalloc((void**)&P.pong, n * 16));
+    CK(cudaMalloc((void**)&P.tonemapOut, n * 4));
+    CK(cudaMalloc((void**)&P.sharpenOut, n * 4));
+    P.alloc = true;
+    return post_zero(c, stream);
+}
+int blokb_denoise(blokb_ctx* c, const blokb_post_settings* s, void* stream) {
+    cudaStream_t q = c ? pick(c, stream) : nullptr;
+    if (int rc = post_ready(c, s, q)) return rc;
+    if (s->atrousIterations < 1 || s->atrousIterations > 5) return fail(BLOKB_E_ARG, "atrousIterations must be 1..5 (MAX_ATROUS_ITERATIONS)");
+    auto& P = c->post;
+    const post::PostFrame F = post::make_post_frame(c->ubo, *s);
+    const int i = P.i, p = 1 - P.i;
+    // image-to-binding wiring of Denoiser::updateDescriptorSets (renderer_denoising.cpp:432-556)
+    post::TemporalIO io{c->buf.color, c->buf.worldPos, c->buf.normalRough, c->buf.motion, P.histColor[p], P.histMoments[p], P.histLen[p],
+                        P.prevWorldPos, P.prevNormalRough, P.histColor[i], P.histMoments[i], P.histLen[i], P.variance};
+    CK(post::launch_temporal_variance(F, io, q));
+    c->launches++;
+    const float* src = P.histColor[i];
+    for (int it = 0; it < s->atrousIterations; it++) {
+        float* dst = (it % 2 == 0) ? P.ping : P.pong;
+        CK(post::launch_atrous(F, 1 << it, src, P.variance, c->buf.worldPos, c->buf.normalRough, dst, q));
+        c->launches++;
+        src = dst;
+    }
+    P.denoised = src;
+    return 0;
+}
+int blokb_postprocess(blokb_ctx* c, const blokb_post_settings* s, void* stream) {
+    cudaStream_t q = c ? pick(c, stream) : nullptr;
+    if (int rc = post_ready(c, s, q)) return rc;
+    auto& P = c->post;
+    if (!P.denoised) return fail(BLOKB_E_STATE, "blokb_postprocess needs this frame's blokb_denoise output");
+    if (!s->enableTAA && !s->enableTonemapping) return fail(BLOKB_E_UNSUPPORTED, "neither TAA nor tonemapping enabled (the reference has no passthrough either)");
+    const post::PostFrame F = post::make_post_frame(c->ubo, *s);
+    const size_t n = size_t(c->buf.width) * c->buf.height;
+    if (!s->enableTonemapping && !P.taaOut) CK(cudaMalloc((void**)&P.taaOut, n * 16));
+    const int j = P.j, pj = 1 - P.j;
+    CK(post::launch_taa_tonemap(F, s->enableTAA != 0, s->enableTonemapping != 0, P.denoised, P.taaHist[pj], c->buf.motion, P.taaHist[j], P.taaOut,
+                                reinterpret_cast<uint32_t*>(P.tonemapOut), q));
+    c->launches++;
+    if (s->enableTonemapping) {
+        P.final = P.tonemapOut; P.finalBytesPerPixel = 4;
+        if (s->enableSharpening) {
+            CK(post::launch_sharpen(F, P.tonemapOut, reinterpret_cast<uint32_t*>(P.sharpenOut), q));
+            c->launches++;
+            P.final = P.sharpenOut;
+        }
+    } else {
+        P.final = P.taaOut; P.finalBytesPerPixel = 16;
+    }
+    return 0;
+}
+int blokb_end_frame(blokb_ctx* c, void* /*stream*/) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
+    auto& P = c->post;
+    if (!P.alloc) return 0;
+    // copyCurrentGeometryToHistory without the copy: this frame's geometry images become "previous", the old
+    // previous ones receive the next frame. Everything is stream-ordered, so no synchronisation is needed.
+    std::swap(c->buf.worldPos, P.prevWorldPos);
+    std::swap(c->buf.normalRough, P.prevNormalRough);
+    P.i = 1 - P.i;
+    P.j = 1 - P.j;
+    P.denoised = nullptr; P.final = nullptr;
+    return 0;
+}
+int blokb_reset_history(blokb_ctx* c, void* stream) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    if (!c->post.alloc) return 0;
+    CK(cudaSetDevice(c->device));
+    return post_zero(c, pick(c, stream));
+}
+
 int blokb_get_buffers(blokb_ctx* c, blokb_buffers* out) {
     if (!c || !out) return fail(BLOKB_E_ARG, "null argument");
     if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
@@ -289,11 +429,42 @@ int blokb_readback(blokb_ctx* c, int image, void* host, size_t bytes) {
         case BLOKB_IMG_ALBEDOMETAL: src = c->buf.albedoMetal; sz = n * 4; break;
         case BLOKB_IMG_MOTION: src = c->buf.motion; sz = n * 4; break;
         case BLOKB_IMG_ACCUM: src = c->buf.accum; sz = n * 16; break;
+        case BLOKB_IMG_HISTORY_COLOR: src = c->post.histColor[c->post.i]; sz = n * 16; break;
+        case BLOKB_IMG_MOMENTS: src = c->post.histMoments[c->post.i]; sz = n * 8; break;
+        case BLOKB_IMG_HISTORY_LENGTH: src = c->post.histLen[c->post.i]; sz = n * 2; break;
+        case BLOKB_IMG_VARIANCE: src = c->post.variance; sz = n * 4; break;
+        case BLOKB_IMG_DENOISED: src = c->post.denoised; sz = n * 16; break;
+        case BLOKB_IMG_TAA_HISTORY: src = c->post.taaHist[c->post.j]; sz = n * 16; break;
+        case BLOKB_IMG_TAA_OUTPUT: src = c->post.taaOut; sz = n * 16; break;
+        case BLOKB_IMG_TONEMAPPED: src = c->post.tonemapOut; sz = n * 4; break;
+        case BLOKB_IMG_FINAL: src = c->post.final; sz = n * c->post.finalBytesPerPixel; break;
         default: return fail(BLOKB_E_ARG, "unknown image id");
     }
+    if (!src) return fail(BLOKB_E_STATE, "image not produced yet (blokb_denoise / blokb_postprocess of the current frame)");
     if (bytes != sz) return fail(BLOKB_E_ARG, "host buffer size mismatch: expected " + std::to_string(sz));
     CK(cudaSetDevice(c->device));
     CK(cudaMemcpyAsync(host, src, sz, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+int blokb_write_image(blokb_ctx* c, int image, const void* host, size_t bytes) {
+    if (!c || !host) return fail(BLOKB_E_ARG, "null argument");
+    if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
+    const size_t n = size_t(c->buf.width) * c->buf.height;
+    void* dst = nullptr;
+    size_t sz = 0;
+    switch (image) {
+        case BLOKB_IMG_COLOR: dst = c->buf.color; sz = n * 16; break;
+        case BLOKB_IMG_WORLDPOS: dst = c->buf.worldPos; sz = n * 16; break;
+        case BLOKB_IMG_NORMALROUGH: dst = c->buf.normalRough; sz = n * 8; break;
+        case BLOKB_IMG_ALBEDOMETAL: dst = c->buf.albedoMetal; sz = n * 4; break;
+        case BLOKB_IMG_MOTION: dst = c->buf.motion; sz = n * 4; break;
+        case BLOKB_IMG_ACCUM: dst = c->buf.accum; sz = n * 16; break;
+        default: return fail(BLOKB_E_ARG, "image is not writable");
+    }
+    if (bytes != sz) return fail(BLOKB_E_ARG, "host buffer size mismatch: expected " + std::to_string(sz));
+    CK(cudaSetDevice(c->device));
+    CK(cudaMemcpyAsync(dst, host, sz, cudaMemcpyHostToDevice, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     return 0;
 }

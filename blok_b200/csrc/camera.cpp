@@ -54,13 +54,12 @@ void mat_inverse(const float* m, float* out) {
 }
 }  // namespace
 
-extern "C" int blokb_camera_frame(const blokb_camera* cam, uint32_t width, uint32_t height, uint32_t frameCount, uint32_t sampleCount,
-                                  blokb_frame_ubo* out) {
-    if (!cam || !out || width == 0 || height == 0) return BLOKB_E_ARG;
-    std::memset(out, 0, sizeof *out);
+namespace {
+void camera_matrices(const blokb_camera* cam, uint32_t width, uint32_t height, float* view, float* proj) {
     const float yaw = radians(cam->yaw), pitch = radians(cam->pitch);
-    V3 dir = {std::cos(yaw) * std::cos(pitch), std::sin(pitch), std::sin(yaw) * std::cos(pitch)};
-    const V3 fwd = normalize(dir);                                  // camera.hpp:25-31
+    // camera.hpp:25-31 calls the unqualified C `cos` / `sin`, i.e. the double overloads: products in double, one rounding to float
+    V3 dir = {float(std::cos(double(yaw)) * std::cos(double(pitch))), float(std::sin(double(pitch))), float(std::sin(double(yaw)) * std::cos(double(pitch)))};
+    const V3 fwd = normalize(dir);
     const V3 right = normalize(cross(fwd, V3{0.f, 1.f, 0.f}));      // :34-36
     const V3 up = normalize(cross(right, fwd));                     // :39-41
     const V3 eye = {cam->position[0], cam->position[1], cam->position[2]};
@@ -68,25 +67,61 @@ extern "C" int blokb_camera_frame(const blokb_camera* cam, uint32_t width, uint3
     const V3 f = normalize(sub(add(eye, fwd), eye));
     const V3 s = normalize(cross(f, up));
     const V3 u = cross(s, f);
-    float view[16] = {s.x, u.x, -f.x, 0.f, s.y, u.y, -f.y, 0.f, s.z, u.z, -f.z, 0.f, -dot(s, eye), -dot(u, eye), dot(f, eye), 1.f};
+    const float v[16] = {s.x, u.x, -f.x, 0.f, s.y, u.y, -f.y, 0.f, s.z, u.z, -f.z, 0.f, -dot(s, eye), -dot(u, eye), dot(f, eye), 1.f};
+    std::memcpy(view, v, 64);
     // glm::perspectiveRH_NO(radians(fov), aspect, 0.1, 10000); [1][1] *= -1   (camera.hpp:55-59)
     const float aspect = static_cast<float>(width) / static_cast<float>(height), zn = 0.1f, zf = 10000.0f;
     const float thf = std::tan(radians(cam->fov) / 2.0f);
-    float proj[16] = {};
+    std::memset(proj, 0, 64);
     proj[0] = 1.0f / (aspect * thf);
     proj[5] = 1.0f / thf;
     proj[10] = -(zf + zn) / (zf - zn);
     proj[11] = -1.0f;
     proj[14] = -(2.0f * zf * zn) / (zf - zn);
     proj[5] *= -1.0f;
+}
+float halton(int index, int base) {  // PostProcess::halton (renderer_postprocess.cpp:216-228)
+    float result = 0.0f, f = 1.0f / static_cast<float>(base);
+    for (int i = index; i > 0; i = i / base) {
+        result += f * static_cast<float>(i % base);
+        f = f / static_cast<float>(base);
+    }
+    return result;
+}
+}  // namespace
+
+extern "C" int blokb_camera_frame_seq(const blokb_camera* cam, const blokb_camera* prevCam, uint32_t width, uint32_t height, uint32_t frameCount,
+                                      uint32_t sampleCount, int32_t jitterIndex, blokb_frame_ubo* out) {
+    if (!cam || !out || width == 0 || height == 0) return BLOKB_E_ARG;
+    std::memset(out, 0, sizeof *out);
+    float view[16], base[16], proj[16];
+    camera_matrices(cam, width, height, view, base);
+    std::memcpy(proj, base, 64);
+    if (jitterIndex >= 0) {  // PostProcess::getJitteredProjection (renderer_postprocess.cpp:254-268), sequence :208-214
+        const int k = jitterIndex % 16;
+        const float jx = halton(k + 1, 2) - 0.5f, jy = halton(k + 1, 3) - 0.5f;
+        proj[8] += (2.0f * jx) / static_cast<float>(width);
+        proj[9] += (2.0f * jy) / static_cast<float>(height);
+        out->jitterOffset[0] = jx; out->jitterOffset[1] = jy;
+    }
     std::memcpy(out->view, view, 64);
     std::memcpy(out->proj, proj, 64);
     mat_inverse(view, out->invView);
     mat_inverse(proj, out->invProj);
-    std::memcpy(out->prevView, view, 64);
-    std::memcpy(out->prevProj, proj, 64);
-    mat_mul(proj, view, out->prevViewProj);
-    for (int i = 0; i < 3; i++) out->camPos[i] = out->prevCamPos[i] = cam->position[i];
+    if (prevCam) {  // Denoiser::updatePreviousFrameData(view, baseProj, position) of the previous frame (renderer_draw.cpp:314-318)
+        float pv[16], pp[16];
+        camera_matrices(prevCam, width, height, pv, pp);
+        std::memcpy(out->prevView, pv, 64);
+        std::memcpy(out->prevProj, pp, 64);
+        mat_mul(pp, pv, out->prevViewProj);
+        for (int i = 0; i < 3; i++) out->prevCamPos[i] = prevCam->position[i];
+    } else {  // hasPreviousFrame == false: prev* = this frame's (jittered) matrices (renderer_denoising.cpp:672-680)
+        std::memcpy(out->prevView, view, 64);
+        std::memcpy(out->prevProj, proj, 64);
+        mat_mul(proj, view, out->prevViewProj);
+        for (int i = 0; i < 3; i++) out->prevCamPos[i] = cam->position[i];
+    }
+    for (int i = 0; i < 3; i++) out->camPos[i] = cam->position[i];
     out->depth = 1;
     out->frameCount = frameCount; out->sampleCount = sampleCount; out->screenWidth = width; out->screenHeight = height;
     // Denoiser::Settings defaults (blok/include/renderer_denoising.hpp:57-76), copied in by fillFrameUBO (renderer_denoising.cpp:686-703)
@@ -94,4 +129,9 @@ extern "C" int blokb_camera_frame(const blokb_camera* cam, uint32_t width, uint3
     out->normalThreshold = 0.95f; out->phiColor = 0.5f; out->phiNormal = 128.0f; out->phiDepth = 0.1f;
     out->atrousIteration = 0; out->stepSize = 1; out->varianceBoost = 1.5f; out->minHistoryLength = 4;
     return 0;
+}
+
+extern "C" int blokb_camera_frame(const blokb_camera* cam, uint32_t width, uint32_t height, uint32_t frameCount, uint32_t sampleCount,
+                                  blokb_frame_ubo* out) {
+    return blokb_camera_frame_seq(cam, nullptr, width, height, frameCount, sampleCount, -1, out);
 }

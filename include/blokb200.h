@@ -105,6 +105,21 @@ typedef struct blokb_buffers {
     uint32_t width, height;
 } blokb_buffers;
 
+/* Denoiser::Settings::atrousIterations (blok/include/renderer_denoising.hpp:71) + PostProcess::Settings
+ * (blok/include/renderer_postprocess.hpp:102-119). The remaining Denoiser settings travel in the FrameUBO, exactly as
+ * Denoiser::fillFrameUBO puts them there (renderer_denoising.cpp:686-703). */
+typedef struct blokb_post_settings {
+    int32_t atrousIterations; /* 1..5 (DenoiserPipeline::MAX_ATROUS_ITERATIONS) */
+    int32_t enableTAA;
+    float feedbackMin, feedbackMax;
+    int32_t enableTonemapping;
+    float exposure, saturationBoost;
+    int32_t tonemapOperator; /* 0 = soft clip, 1 = Khronos PBR neutral */
+    float whitePoint;
+    int32_t enableSharpening;
+    float sharpenStrength;
+} blokb_post_settings;
+
 enum blokb_image {
     BLOKB_IMG_HIT = 0,
     BLOKB_IMG_SHADOW = 1,
@@ -113,7 +128,17 @@ enum blokb_image {
     BLOKB_IMG_NORMALROUGH = 4,
     BLOKB_IMG_ALBEDOMETAL = 5,
     BLOKB_IMG_MOTION = 6,
-    BLOKB_IMG_ACCUM = 7
+    BLOKB_IMG_ACCUM = 7,
+    /* denoiser / post-process images (valid after blokb_denoise / blokb_postprocess of the current frame) */
+    BLOKB_IMG_HISTORY_COLOR = 8,  /* currentHistory()        rgba32f  temporal accumulation output */
+    BLOKB_IMG_MOMENTS = 9,        /* currentMoments()        rg32f */
+    BLOKB_IMG_HISTORY_LENGTH = 10, /* currentHistoryLength() r16f */
+    BLOKB_IMG_VARIANCE = 11,      /* gbuffer.variance        r32f */
+    BLOKB_IMG_DENOISED = 12,      /* Denoiser::getOutputImage() rgba32f (last a-trous iteration) */
+    BLOKB_IMG_TAA_HISTORY = 13,   /* PostProcess currentHistory() rgba32f */
+    BLOKB_IMG_TAA_OUTPUT = 14,    /* taaOutput rgba32f — only materialised when tonemapping is disabled */
+    BLOKB_IMG_TONEMAPPED = 15,    /* tonemapOutput rgba8 */
+    BLOKB_IMG_FINAL = 16          /* PostProcess::getOutputImage(): sharpenOutput / tonemapOutput rgba8 (or taaOutput rgba32f) */
 };
 
 /* Sizes of the GPU-resident compact layout built by blokb_upload_world. */
@@ -145,6 +170,13 @@ int blokb_set_frame(blokb_ctx* ctx, const blokb_frame_ubo* frame);
 int blokb_camera_frame(const blokb_camera* cam, uint32_t width, uint32_t height, uint32_t frameCount, uint32_t sampleCount,
                        blokb_frame_ubo* out);
 
+/* The same for frame n of a sequence: prevCam = the previous frame's camera (NULL on the first frame) fills
+ * prevView / prevProj / prevViewProj / prevCamPos as Denoiser::updatePreviousFrameData left them (non-jittered,
+ * renderer_draw.cpp:314-318); jitterIndex >= 0 applies PostProcess::getJitteredProjection with Halton(2,3) sample
+ * jitterIndex % 16 (renderer_postprocess.cpp:208-268), < 0 = TAA jitter off. */
+int blokb_camera_frame_seq(const blokb_camera* cam, const blokb_camera* prevCam, uint32_t width, uint32_t height, uint32_t frameCount,
+                           uint32_t sampleCount, int32_t jitterIndex, blokb_frame_ubo* out);
+
 /* Dispatch (enqueue only). */
 int blokb_trace_primary(blokb_ctx* ctx, void* stream);        /* sample-0 primary rays -> buffers.hit */
 int blokb_trace_primary_shadow(blokb_ctx* ctx, void* stream); /* + sun shadow ray per lit hit -> buffers.shadow */
@@ -152,6 +184,22 @@ int blokb_render(blokb_ctx* ctx, void* stream);               /* full raygen.rge
 int blokb_trace_path(blokb_ctx* ctx, uint32_t sampleBegin, uint32_t sampleEnd, void* stream); /* accum += samples */
 int blokb_resolve(blokb_ctx* ctx, void* stream);              /* color = accum.rgb / accum.a, firefly clamp */
 int blokb_reset_accum(blokb_ctx* ctx, void* stream);          /* CudaTracer::resetAccum */
+/* Denoiser + post-process, enqueue only. Frame order as in Renderer::render
+ * (blok/src/renderer_draw.cpp:141-213, 314-328): blokb_set_frame, blokb_render, blokb_denoise, blokb_postprocess,
+ * blokb_end_frame. History images start zero-filled; frameCount == 0 in the FrameUBO disables both reprojections.
+ *   blokb_denoise      Denoiser::denoise (renderer_denoising.cpp:714-769): temporal accumulation + variance (one fused
+ *                      kernel) and settings->atrousIterations a-trous passes -> BLOKB_IMG_DENOISED
+ *   blokb_postprocess  PostProcess::process (renderer_postprocess.cpp:505-558): TAA + tonemap (one fused kernel) and
+ *                      sharpen -> BLOKB_IMG_FINAL
+ *   blokb_end_frame    copyCurrentGeometryToHistory + both swapHistoryBuffers (renderer_denoising.cpp:833-865): the
+ *                      G-buffer's worldPos / normalRough images are double-buffered and the roles flip (no copy), so
+ *                      blokb_get_buffers must be called again after it
+ *   blokb_reset_history zero-fills every history image and restarts the ping-pong */
+void blokb_post_settings_default(blokb_post_settings* out);
+int blokb_denoise(blokb_ctx* ctx, const blokb_post_settings* settings, void* stream);
+int blokb_postprocess(blokb_ctx* ctx, const blokb_post_settings* settings, void* stream);
+int blokb_end_frame(blokb_ctx* ctx, void* stream);
+int blokb_reset_history(blokb_ctx* ctx, void* stream);
 /* Arbitrary rays (device pointers): rays = n x {ox,oy,oz,dx,dy,dz,tmin,tmax}; anyHit != 0 = shadow-ray rules. */
 int blokb_trace_rays(blokb_ctx* ctx, const float* dRays, size_t n, int anyHit, blokb_hit* dOut, void* stream);
 /* Same with HOST buffers: copies in, traces, copies out, synchronises. */
@@ -160,6 +208,9 @@ int blokb_trace_rays_host(blokb_ctx* ctx, const float* rays, size_t n, int anyHi
 /* Images out. */
 int blokb_get_buffers(blokb_ctx* ctx, blokb_buffers* out);
 int blokb_readback(blokb_ctx* ctx, int image, void* host, size_t bytes); /* stream-ordered copy + sync */
+/* Inverse of blokb_readback for the G-buffer images (COLOR, WORLDPOS, NORMALROUGH, ALBEDOMETAL, MOTION, ACCUM): lets a
+ * caller that produced the G-buffer elsewhere (or a test) feed blokb_denoise / blokb_postprocess. Copy + sync. */
+int blokb_write_image(blokb_ctx* ctx, int image, const void* host, size_t bytes);
 int blokb_sync(blokb_ctx* ctx);
 /* Number of kernel launches this context has enqueued so far. */
 uint64_t blokb_launch_count(blokb_ctx* ctx);

@@ -28,7 +28,7 @@ def _array_ctor(src: str) -> str:
     # `T[]( a, b, c )` -> `{ a, b, c }` (balanced parentheses)
     out = []
     i = 0
-    pat = re.compile(r"\b\w+\[\]\(")
+    pat = re.compile(r"\b\w+\[\d*\]\(")
     while True:
         m = pat.search(src, i)
         if not m:
@@ -46,7 +46,40 @@ def _array_ctor(src: str) -> str:
     return "".join(out)
 
 
+def rewrite_comp(src: str) -> str:
+    """Compute shaders (temporal_reproject / variance / atrous / taa / tonemap / sharpen .comp): same mechanical rules,
+    plus storage images with format qualifiers, combined image samplers, push constants and `out` parameters.
+    Appends `bind_image(binding, image)` so the harness can attach buffers by the shader's own binding numbers."""
+    src = re.sub(r"^\s*#(version|extension).*$", "", src, flags=re.M)
+    src = re.sub(r"layout\(local_size_x[^)]*\)\s*in\s*;", "", src)
+    binds = []
+
+    def img(m):
+        binds.append((int(m.group(1)), m.group(3), m.group(2)))
+        return f"static {m.group(2)} {m.group(3)};"
+    src = re.sub(r"layout\(\s*binding\s*=\s*(\d+)[^)]*\)\s*uniform\s+(?:readonly\s+|writeonly\s+)?(image2D|sampler2D)\s+(\w+)\s*;", img, src)
+    src = re.sub(r"layout\([^)]*\)\s*uniform\s+FrameUBO\s*\{", "struct FrameUBO_t {", src)
+    src = re.sub(r"\}\s*(frame|ubo)\s*;", r"};\nstatic FrameUBO_t \1;", src)
+    src = re.sub(r"layout\(push_constant\)\s*uniform\s+PushConstants\s*\{", "struct PushConstants_t {", src)
+    src = re.sub(r"\}\s*pc\s*;", "};\nstatic PushConstants_t pc;", src)
+    src = re.sub(r"\binout\s+(\w+)\s+(\w+)", r"\1& \2", src)
+    src = re.sub(r"\bout\s+(\w+)\s+(\w+)", r"\1& \2", src)
+    src = re.sub(r"\bvoid\s+main\s*\(\s*\)", "void shader_main()", src)
+    src = re.sub(r"(?<![\w.])((?:\d+\.\d*|\.\d+)(?:[eE][+-]?\d+)?|\d+[eE][+-]?\d+)(?![\w.])", r"\1f", src)
+    src = re.sub(r"\.(xyz|xy|rgb|rg)\b(?!\s*\()", r".\1()", src)
+    src = _array_ctor(src)
+    if not binds or "shader_main" not in src:
+        raise SystemExit("glsl2cpp: compute shader anchors not found")
+    src += "\nstatic bool bind_image(int binding, const image2D& im) {\n    switch (binding) {\n"
+    for b, name, ty in sorted(binds):
+        src += f"        case {b}: {name}{'.img' if ty == 'sampler2D' else ''} = im; return true;\n"
+    src += "    }\n    return false;\n}\n"
+    return src
+
+
 def rewrite(src: str, kind: str) -> str:
+    if kind == "comp":
+        return rewrite_comp(src)
     src = re.sub(r"^\s*#(version|extension).*$", "", src, flags=re.M)
     # storage buffers
     src = re.sub(r"layout\([^)]*\)\s*readonly\s+buffer\s+\w+\s*\{\s*(\w+)\s+(\w+)\[\];\s*\};",

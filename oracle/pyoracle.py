@@ -125,6 +125,8 @@ class RefLib(_TraceMixin):
         lib.ref_scene_free.argtypes = [_vp]
         lib.ref_make_frame.argtypes = [_vp, C.c_float, C.c_float, C.c_float, C.c_uint32, C.c_uint32, C.c_uint32,
                                        C.c_uint32, _vp]
+        lib.ref_make_frame_seq.argtypes = [_vp, C.c_float, C.c_float, C.c_float, _vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
+                                           C.c_int32, _vp]
         lib.ref_hardware_threads.restype = C.c_int
         lib.ref_primary_rays.argtypes = [_vp, _vp]
         self._setup_trace("ref")
@@ -171,6 +173,16 @@ class RefLib(_TraceMixin):
         return out
 
 
+    def make_frame_seq(self, cam, prev_cam, w, h, frame_count, sample_count=8, jitter_index=-1):
+        """cam / prev_cam: (pos3, yaw, pitch[, fov]); prev_cam None on the first frame. Renderer::render's FrameUBO for frame n."""
+        def flat(c):
+            return np.array([*c[0], c[1], c[2], c[3] if len(c) > 3 else 60.0], np.float32)
+        a = flat(cam)
+        b = None if prev_cam is None else flat(prev_cam)
+        out = np.zeros(560, np.uint8)
+        self.lib.ref_make_frame_seq(_ptr(a), float(a[3]), float(a[4]), float(a[5]), _ptr(b), w, h, frame_count, sample_count, jitter_index, _ptr(out))
+        return out
+
     def primary_rays(self, ubo):
         u32 = np.frombuffer(ubo.tobytes(), dtype="<u4")
         w, h = int(u32[488 // 4]), int(u32[492 // 4])
@@ -205,3 +217,124 @@ class OracleLib(_TraceMixin):
 
     def threads(self):
         return self.lib.orc_hardware_threads()
+
+
+# ------------------------------------------------------------------------------------------------------------
+# Denoiser + post-process chain on the CPU checker's compute-shader entry point.
+# ------------------------------------------------------------------------------------------------------------
+FMT_RGBA32F, FMT_RG32F, FMT_R32F, FMT_RGBA16F, FMT_RG16F, FMT_R16F, FMT_RGBA8 = range(7)
+_FMT_NP = {FMT_RGBA32F: (np.float32, 4), FMT_RG32F: (np.float32, 2), FMT_R32F: (np.float32, 1),
+           FMT_RGBA16F: (np.uint16, 4), FMT_RG16F: (np.uint16, 2), FMT_R16F: (np.uint16, 1), FMT_RGBA8: (np.uint8, 4)}
+
+
+class _ImageDesc(C.Structure):
+    _fields_ = [("data", _vp), ("width", C.c_int32), ("height", C.c_int32), ("fmt", C.c_int32), ("binding", C.c_int32)]
+
+
+class PostSettings:
+    """Denoiser::Settings::atrousIterations (renderer_denoising.hpp:71) + PostProcess::Settings (renderer_postprocess.hpp:102-119).
+    The other Denoiser settings travel inside the FrameUBO (fillFrameUBO, renderer_denoising.cpp:686-703)."""
+
+    def __init__(self, **kw):
+        self.atrousIterations = 4
+        self.enableTAA, self.feedbackMin, self.feedbackMax = True, 0.93, 0.98
+        self.enableTonemapping, self.exposure, self.saturationBoost, self.tonemapOperator, self.whitePoint = True, 1.0, 1.15, 1, 0.0
+        self.enableSharpening, self.sharpenStrength = True, 0.5
+        self.jitter = (0.0, 0.0)  # TAAPushConstants.jitterX/Y (unused by taa.comp's arithmetic)
+        for k, v in kw.items():
+            assert hasattr(self, k), k
+            setattr(self, k, v)
+
+
+class PostChain:
+    """Runs the reference's per-frame pass sequence — Denoiser::denoise (renderer_denoising.cpp:714-769),
+    copyCurrentGeometryToHistory (:833-861), PostProcess::process (renderer_postprocess.cpp:505-558), the two
+    swapHistoryBuffers (renderer_draw.cpp:327-328) — with the image-to-binding wiring of the two updateDescriptorSets
+    (renderer_denoising.cpp:432-556, renderer_postprocess.cpp:330-405). History images start zero-filled (Vulkan leaves
+    them undefined; frame 0 never lets them through: frameCount == 0 disables both reprojections)."""
+
+    def __init__(self, lib, prefix, w, h, threads=1, settings=None):
+        self.run = getattr(lib, prefix + "_comp_run")
+        self.run.argtypes = [C.c_char_p, _vp, C.c_size_t, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int]
+        self.run.restype = C.c_int
+        self.w, self.h, self.threads = w, h, threads
+        self.s = settings or PostSettings()
+        z = self._img
+        self.histColor = [z(FMT_RGBA32F), z(FMT_RGBA32F)]
+        self.histMoments = [z(FMT_RG32F), z(FMT_RG32F)]
+        self.histLen = [z(FMT_R16F), z(FMT_R16F)]
+        self.histWorldPos = [z(FMT_RGBA32F), z(FMT_RGBA32F)]
+        self.histNormal = [z(FMT_RGBA16F), z(FMT_RGBA16F)]
+        self.variance, self.ping, self.pong = z(FMT_R32F), z(FMT_RGBA32F), z(FMT_RGBA32F)
+        self.taaHist = [z(FMT_RGBA32F), z(FMT_RGBA32F)]
+        self.taaOut, self.tonemapOut, self.sharpenOut = z(FMT_RGBA32F), z(FMT_RGBA8), z(FMT_RGBA8)
+        self.i = 0  # DenoiserGBuffer::historyIndex
+        self.j = 0  # PostProcessBuffers::historyIndex
+
+    def _img(self, fmt):
+        dt, n = _FMT_NP[fmt]
+        a = np.zeros((self.h, self.w, n), dt)
+        return (a, fmt)
+
+    def _dispatch(self, shader, ubo, pc, binds):
+        arr = (_ImageDesc * len(binds))()
+        for k, (b, (a, fmt)) in enumerate(binds.items()):
+            assert a.flags["C_CONTIGUOUS"] and a.shape[:2] == (self.h, self.w)
+            arr[k] = _ImageDesc(a.ctypes.data, self.w, self.h, fmt, b)
+        pcb = None if pc is None else np.frombuffer(pc, np.uint8).copy()
+        rc = self.run(shader.encode(), _ptr(ubo), ubo.nbytes, _ptr(pcb), C.cast(arr, _vp), len(binds), self.w, self.h, self.threads)
+        assert rc == 0, (shader, rc)
+
+    def frame(self, ubo, color, worldPos, normalRough16, motion16):
+        """color/worldPos (h,w,4) f32, normalRough16 (h,w,4) u16 (binary16 bits), motion16 (h,w,2) u16. Returns the images a
+        frame produces (views of internal buffers; copy them to keep across frames)."""
+        import struct
+        s = self.s
+        assert s.atrousIterations >= 1
+        ubo = np.ascontiguousarray(ubo, np.uint8)
+        fl = np.frombuffer(ubo.tobytes(), "<f4")
+        gc = (np.ascontiguousarray(color, np.float32), FMT_RGBA32F)
+        gw = (np.ascontiguousarray(worldPos, np.float32), FMT_RGBA32F)
+        gn = (np.ascontiguousarray(normalRough16, np.uint16), FMT_RGBA16F)
+        gm = (np.ascontiguousarray(motion16, np.uint16), FMT_RG16F)
+        i, p = self.i, 1 - self.i
+        self._dispatch("temporal", ubo, None, {0: gc, 1: gw, 2: gn, 3: gm, 4: self.histColor[p], 5: self.histMoments[p],
+                                               6: self.histLen[p], 7: self.histWorldPos[p], 8: self.histNormal[p],
+                                               9: self.histColor[i], 10: self.histMoments[i], 11: self.histLen[i]})
+        self._dispatch("variance", ubo, None, {0: gc, 1: self.histMoments[i], 2: self.histLen[i], 3: self.variance, 5: gw, 6: gn})
+        phiColor, phiNormal, phiDepth = float(fl[516 // 4]), float(fl[520 // 4]), float(fl[524 // 4])
+        src = self.histColor[i]
+        for it in range(s.atrousIterations):
+            dst = self.ping if it % 2 == 0 else self.pong
+            self._dispatch("atrous", ubo, struct.pack("<ifff", 1 << it, phiColor, phiNormal, phiDepth),
+                           {0: src, 1: self.variance, 2: gw, 3: gn, 4: dst})
+            src = dst
+        denoised = src
+        self.histWorldPos[i][0][...] = gw[0]
+        self.histNormal[i][0][...] = gn[0]
+        j, q = self.j, 1 - self.j
+        final = denoised
+        if s.enableTAA:
+            self._dispatch("taa", ubo, struct.pack("<ffff", s.jitter[0], s.jitter[1], s.feedbackMin, s.feedbackMax),
+                           {0: denoised, 1: self.taaHist[q], 2: gm, 3: gw, 4: self.taaOut, 5: self.taaHist[j]})
+            final = self.taaOut
+        if s.enableTonemapping:
+            self._dispatch("tonemap", ubo, struct.pack("<ffif", s.exposure, s.saturationBoost, s.tonemapOperator, s.whitePoint),
+                           {0: final, 1: self.tonemapOut})
+            final = self.tonemapOut
+            if s.enableSharpening:
+                self._dispatch("sharpen", ubo, struct.pack("<ffff", s.sharpenStrength, 0.0, 0.0, 0.0), {0: self.tonemapOut, 1: self.sharpenOut})
+                final = self.sharpenOut
+        out = {"historyColor": self.histColor[i][0], "moments": self.histMoments[i][0], "historyLength": self.histLen[i][0],
+               "variance": self.variance[0], "denoised": denoised[0], "taaHistory": self.taaHist[j][0], "taaOutput": self.taaOut[0],
+               "tonemapped": self.tonemapOut[0], "final": final[0]}
+        self.i, self.j = p, q
+        return out
+
+
+def float_to_half_bits(lib, a):
+    a = np.ascontiguousarray(a, np.float32)
+    out = np.empty(a.shape, np.uint16)
+    lib.ref_float_to_half.argtypes = [_vp, _vp, C.c_size_t]
+    lib.ref_float_to_half(_ptr(a), _ptr(out), a.size)
+    return out

@@ -345,6 +345,47 @@ void ref_make_frame(const float* pos, float yaw, float pitch, float fov, uint32_
     std::memcpy(outUbo560, &u, 560);
 }
 
+// Frame n of a sequence, as Renderer::render builds it (renderer_draw.cpp:52-89, 314-328): jittered projection from
+// PostProcess::getJitteredProjection (renderer_postprocess.cpp:254-268; the Halton table of :208-228 is restated here
+// because PostProcess itself needs Vulkan), prev* from the previous frame's camera with the non-jittered projection.
+static float ref_halton(int index, int base) {
+    float result = 0.0f, f = 1.0f / static_cast<float>(base);
+    int i = index;
+    while (i > 0) { result += f * static_cast<float>(i % base); i = i / base; f = f / static_cast<float>(base); }
+    return result;
+}
+void ref_make_frame_seq(const float* pos, float yaw, float pitch, float fov, const float* prevCam6 /* pos,yaw,pitch,fov or null */, uint32_t w,
+                        uint32_t h, uint32_t frameCount, uint32_t sampleCount, int32_t jitterIndex, void* outUbo560) {
+    blok::Camera c;
+    c.position = glm::vec3(pos[0], pos[1], pos[2]); c.yaw = yaw; c.pitch = pitch; c.fov = fov;
+    const float aspect = static_cast<float>(w) / static_cast<float>(h);
+    glm::mat4 view = c.view(), baseProj = c.projection(aspect, 0.1f, 10000.0f), proj = baseProj;
+    glm::vec2 jitter(0.0f);
+    if (jitterIndex >= 0) {
+        const int k = jitterIndex % 16;
+        jitter = glm::vec2(ref_halton(k + 1, 2) - 0.5f, ref_halton(k + 1, 3) - 0.5f);
+        glm::vec2 clip((2.0f * jitter.x) / static_cast<float>(w), (2.0f * jitter.y) / static_cast<float>(h));
+        proj[2][0] += clip.x; proj[2][1] += clip.y;
+    }
+    glslenv::rgen::FrameUBO_t u{};
+    u.view = view; u.proj = proj; u.invView = glm::inverse(view); u.invProj = glm::inverse(proj);
+    if (prevCam6) {
+        blok::Camera p;
+        p.position = glm::vec3(prevCam6[0], prevCam6[1], prevCam6[2]); p.yaw = prevCam6[3]; p.pitch = prevCam6[4]; p.fov = prevCam6[5];
+        glm::mat4 pv = p.view(), pp = p.projection(aspect, 0.1f, 10000.0f);
+        u.prevView = pv; u.prevProj = pp; u.prevViewProj = pp * pv; u.prevCamPos = p.position;
+    } else {
+        u.prevView = view; u.prevProj = proj; u.prevViewProj = proj * view; u.prevCamPos = c.position;
+    }
+    u.camPos = c.position; u.deltaTime = 0.f; u.depth = 1;
+    u.frameCount = frameCount; u.sampleCount = sampleCount; u.screenWidth = w; u.screenHeight = h;
+    u.temporalAlpha = 0.05f; u.momentAlpha = 0.2f; u.varianceClipGamma = 1.5f; u.depthThreshold = 0.1f;
+    u.normalThreshold = 0.95f; u.phiColor = 0.5f; u.phiNormal = 128.0f; u.phiDepth = 0.1f;
+    u.atrousIteration = 0; u.stepSize = 1; u.varianceBoost = 1.5f; u.minHistoryLength = 4;
+    std::memcpy(outUbo560, &u, 560);
+    std::memcpy((char*)outUbo560 + 544, &jitter, 8);
+}
+
 static void bind_world(World& w, const void* nodes, size_t nNodes, const void* subs, size_t nSub, const void* mats,
                        size_t nMat) {
     w.nodes = (const SvoNode*)nodes; w.nNodes = nNodes; w.subs = (const SubChunkGpu*)subs; w.nSub = nSub;

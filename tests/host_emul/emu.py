@@ -13,7 +13,7 @@ _vp = C.c_void_p
 
 def build():
     srcs = [os.path.join(HERE, "emul.cpp"), os.path.join(ROOT, "blok_b200", "csrc", "scene_build.cpp")]
-    deps = srcs + [os.path.join(ROOT, "blok_b200", "csrc", f) for f in ("traverse.cuh", "shade.cuh", "scene.h", "hd.h", "scene_build.h", "kernels.h")]
+    deps = srcs + [os.path.join(ROOT, "blok_b200", "csrc", f) for f in ("traverse.cuh", "shade.cuh", "post.cuh", "post.h", "scene.h", "hd.h", "scene_build.h", "kernels.h")]
     if os.path.exists(SO) and all(os.path.getmtime(SO) >= os.path.getmtime(d) for d in deps):
         return
     cuda_inc = "/usr/local/cuda/include"
@@ -77,3 +77,67 @@ class EmuLib:
 
 def load():
     return EmuLib()
+
+
+class _TemporalIO(C.Structure):
+    _fields_ = [(n, _vp) for n in ("color", "worldPos", "normalRough", "motion", "prevHistory", "prevMoments", "prevLength", "prevWorldPos",
+                                   "prevNormal", "outHistory", "outMoments", "outLength", "outVariance")]
+
+
+class EmuPostChain:
+    """The product's denoise / postprocess / end_frame sequence (blok_b200/csrc/api.cpp) with the kernels replaced by host
+    loops over the same per-pixel functions (post.cuh). CPU-only logic check against the reference's compute shaders."""
+
+    def __init__(self, lib, w, h, settings=None, threads=8):
+        from blok_b200.api import PostSettings
+        lib = getattr(lib, "L", lib)
+        self.lib, self.w, self.h, self.threads = lib, w, h, threads
+        self.s = settings or PostSettings()
+        lib.emu_post_frame_size.restype = C.c_size_t
+        lib.emu_post_frame.argtypes = [_vp, _vp, _vp]
+        lib.emu_post_temporal_variance.argtypes = [_vp, _vp, C.c_int]
+        lib.emu_post_atrous.argtypes = [_vp, C.c_int, _vp, _vp, _vp, _vp, _vp, C.c_int]
+        lib.emu_post_taa_tonemap.argtypes = [_vp, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int]
+        lib.emu_post_sharpen.argtypes = [_vp, _vp, _vp, C.c_int]
+        z = lambda n, dt: np.zeros((h, w, n), dt)
+        self.histColor = [z(4, np.float32), z(4, np.float32)]
+        self.histMoments = [z(2, np.float32), z(2, np.float32)]
+        self.histLen = [z(1, np.uint16), z(1, np.uint16)]
+        self.prevWorldPos, self.prevNormal = z(4, np.float32), z(4, np.uint16)
+        self.variance, self.ping, self.pong = z(1, np.float32), z(4, np.float32), z(4, np.float32)
+        self.taaHist = [z(4, np.float32), z(4, np.float32)]
+        self.taaOut, self.tonemapOut, self.sharpenOut = z(4, np.float32), z(4, np.uint8), z(4, np.uint8)
+        self.i = self.j = 0
+
+    def frame(self, ubo, color, worldPos, normalRough16, motion16):
+        from blok_b200.api import FrameUBO
+        L, s, nt = self.lib, self.s, self.threads
+        f = ubo if isinstance(ubo, FrameUBO) else FrameUBO.from_bytes(ubo)
+        P = C.create_string_buffer(L.emu_post_frame_size())
+        L.emu_post_frame(C.byref(f), C.byref(s), P)
+        p = lambda a: a.ctypes.data_as(_vp)
+        gc, gw = np.ascontiguousarray(color, np.float32), np.ascontiguousarray(worldPos, np.float32)
+        gn, gm = np.ascontiguousarray(normalRough16, np.uint16), np.ascontiguousarray(motion16, np.uint16)
+        i, q = self.i, 1 - self.i
+        io = _TemporalIO(p(gc), p(gw), p(gn), p(gm), p(self.histColor[q]), p(self.histMoments[q]), p(self.histLen[q]), p(self.prevWorldPos),
+                         p(self.prevNormal), p(self.histColor[i]), p(self.histMoments[i]), p(self.histLen[i]), p(self.variance))
+        L.emu_post_temporal_variance(P, C.byref(io), nt)
+        src = self.histColor[i]
+        for it in range(s.atrousIterations):
+            dst = self.ping if it % 2 == 0 else self.pong
+            L.emu_post_atrous(P, 1 << it, p(src), p(self.variance), p(gw), p(gn), p(dst), nt)
+            src = dst
+        denoised = src
+        j, r = self.j, 1 - self.j
+        L.emu_post_taa_tonemap(P, int(s.enableTAA), int(s.enableTonemapping), p(denoised), p(self.taaHist[r]), p(gm), p(self.taaHist[j]),
+                               p(self.taaOut), p(self.tonemapOut), nt)
+        final = self.tonemapOut if s.enableTonemapping else self.taaOut
+        if s.enableTonemapping and s.enableSharpening:
+            L.emu_post_sharpen(P, p(self.tonemapOut), p(self.sharpenOut), nt)
+            final = self.sharpenOut
+        out = {"historyColor": self.histColor[i], "moments": self.histMoments[i], "historyLength": self.histLen[i][..., 0],
+               "variance": self.variance[..., 0], "denoised": denoised, "taaHistory": self.taaHist[j], "tonemapped": self.tonemapOut, "final": final}
+        # end_frame: geometry images change roles (the product swaps pointers; here the caller owns gw/gn, so keep references)
+        self.prevWorldPos, self.prevNormal = gw, gn
+        self.i, self.j = q, r
+        return out

@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "../../blok_b200/csrc/scene_build.h"
+#include "../../blok_b200/csrc/post.cuh"
 #include "../../blok_b200/csrc/shade.cuh"
 
 using namespace blokb;
@@ -96,6 +97,36 @@ void emu_path(void* p, const blokb_frame_ubo* f, uint32_t sBegin, uint32_t sEnd,
             for (uint32_t s = sBegin; s < sEnd; s++) acc = acc + path_sample<false>(e->dw, stk, F, px, py, s, nullptr, rays, steps);
             out[4 * i] = acc.x; out[4 * i + 1] = acc.y; out[4 * i + 2] = acc.z; out[4 * i + 3] = float(sEnd - sBegin);
         }
+    });
+}
+
+// ---- denoiser / post-process pixel functions (post.cuh), looped over the image on the host --------------------
+void emu_post_frame(const blokb_frame_ubo* u, const blokb_post_settings* s, post::PostFrame* out) { *out = post::make_post_frame(*u, *s); }
+size_t emu_post_frame_size() { return sizeof(post::PostFrame); }
+void emu_post_temporal_variance(const post::PostFrame* P, const post::TemporalIO* io, int nThreads) {
+    pfor(size_t(P->width) * P->height, nThreads, [&](size_t b, size_t e) {
+        for (size_t i = b; i < e; i++) post::temporal_variance_pixel(*P, *io, int(i % P->width), int(i / P->width));
+    });
+}
+void emu_post_atrous(const post::PostFrame* P, int step, const float* in, const float* var, const float* wp, const uint16_t* nr, float* out, int nThreads) {
+    pfor(size_t(P->width) * P->height, nThreads, [&](size_t b, size_t e) {
+        for (size_t i = b; i < e; i++) post::atrous_pixel(*P, step, in, var, wp, nr, out, int(i % P->width), int(i / P->width));
+    });
+}
+void emu_post_taa_tonemap(const post::PostFrame* P, int taa, int tonemap, const float* cur, const float* prevHist, const uint16_t* motion, float* outHist,
+                          float* outColor, uint32_t* outLdr, int nThreads) {
+    pfor(size_t(P->width) * P->height, nThreads, [&](size_t b, size_t e) {
+        for (size_t i = b; i < e; i++) {
+            const int x = int(i % P->width), y = int(i / P->width);
+            if (taa && tonemap) post::taa_tonemap_pixel<true, true>(*P, cur, prevHist, motion, outHist, outColor, outLdr, x, y);
+            else if (taa) post::taa_tonemap_pixel<true, false>(*P, cur, prevHist, motion, outHist, outColor, outLdr, x, y);
+            else post::taa_tonemap_pixel<false, true>(*P, cur, prevHist, motion, outHist, outColor, outLdr, x, y);
+        }
+    });
+}
+void emu_post_sharpen(const post::PostFrame* P, const uint8_t* in, uint32_t* out, int nThreads) {
+    pfor(size_t(P->width) * P->height, nThreads, [&](size_t b, size_t e) {
+        for (size_t i = b; i < e; i++) post::sharpen_pixel(*P, in, out, int(i % P->width), int(i / P->width));
     });
 }
 }
