@@ -7,14 +7,15 @@ namespace blokb {
 namespace post {
 namespace {
 constexpr int kBX = 32, kBY = 8;
+static_assert(kBX * kBY == 256, "k_sharpen fills its 256-entry unorm8 table with one entry per thread");
 inline dim3 grid_for(const PostFrame& P) { return dim3((P.width + kBX - 1) / kBX, (P.height + kBY - 1) / kBY); }
 
-__global__ void __launch_bounds__(kBX* kBY) k_temporal_variance(const __grid_constant__ PostFrame P, const __grid_constant__ TemporalIO io) {
+__global__ void __launch_bounds__(kBX* kBY, 4) k_temporal_variance(const __grid_constant__ PostFrame P, const __grid_constant__ TemporalIO io) {
     const int x = blockIdx.x * kBX + threadIdx.x, y = blockIdx.y * kBY + threadIdx.y;
     if (x >= (int)P.width || y >= (int)P.height) return;
     temporal_variance_pixel(P, io, x, y);
 }
-__global__ void __launch_bounds__(kBX* kBY) k_atrous(const __grid_constant__ PostFrame P, int stepSize, const float* __restrict__ in,
+__global__ void __launch_bounds__(kBX* kBY, 4) k_atrous(const __grid_constant__ PostFrame P, int stepSize, const float* __restrict__ in,
                                                      const float* __restrict__ variance, const float* __restrict__ worldPos,
                                                      const uint16_t* __restrict__ normalRough, float* __restrict__ out) {
     const int x = blockIdx.x * kBX + threadIdx.x, y = blockIdx.y * kBY + threadIdx.y;
@@ -30,9 +31,12 @@ __global__ void __launch_bounds__(kBX* kBY) k_taa_tonemap(const __grid_constant_
     taa_tonemap_pixel<TAA, TONEMAP>(P, current, prevHistory, motion, outHistory, outColor, outLdr, x, y);
 }
 __global__ void __launch_bounds__(kBX* kBY) k_sharpen(const __grid_constant__ PostFrame P, const uint8_t* __restrict__ in, uint32_t* __restrict__ out) {
+    __shared__ float lut255[256];
+    lut255[threadIdx.y * kBX + threadIdx.x] = float(threadIdx.y * kBX + threadIdx.x) / 255.0f;
+    __syncthreads();
     const int x = blockIdx.x * kBX + threadIdx.x, y = blockIdx.y * kBY + threadIdx.y;
     if (x >= (int)P.width || y >= (int)P.height) return;
-    sharpen_pixel(P, in, out, x, y);
+    sharpen_pixel(P, lut255, in, out, x, y);
 }
 }  // namespace
 

@@ -69,15 +69,15 @@ BLOKB_HD F3 ycocg_to_rgb(F3 c) { return {c.x + c.y - c.z, c.x + c.z, c.x - c.y -
 // ---- image access ------------------------------------------------------------------------------------------
 BLOKB_HD int iclamp(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 BLOKB_HD F4 ld_rgba32f(const float* img, int W, int x, int y) {
-    const float4 v = __ldg(reinterpret_cast<const float4*>(img) + (size_t(y) * W + x));
+    const float4 v = __ldg(reinterpret_cast<const float4*>(img) + (unsigned(y) * unsigned(W) + unsigned(x)));
     return {v.x, v.y, v.z, v.w};
 }
 BLOKB_HD F4 ld_rgba16f(const uint16_t* img, int W, int x, int y) {
-    const uint2 v = __ldg(reinterpret_cast<const uint2*>(img) + (size_t(y) * W + x));
+    const uint2 v = __ldg(reinterpret_cast<const uint2*>(img) + (unsigned(y) * unsigned(W) + unsigned(x)));
     return {h2f(v.x & 0xFFFFu), h2f(v.x >> 16), h2f(v.y & 0xFFFFu), h2f(v.y >> 16)};
 }
 BLOKB_HD F4 ld_rgba8(const uint8_t* img, int W, int x, int y) {
-    const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(img) + (size_t(y) * W + x));
+    const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(img) + (unsigned(y) * unsigned(W) + unsigned(x)));
     return {float(v & 255u) / 255.0f, float((v >> 8) & 255u) / 255.0f, float((v >> 16) & 255u) / 255.0f, float(v >> 24) / 255.0f};
 }
 BLOKB_HD uint32_t pack_unorm8(float v) {
@@ -110,6 +110,23 @@ template <bool UNORM8> BLOKB_HD F4 tex_linear(const void* img, int W, int H, flo
     return ((t00 * w00 + t10 * w10) + t01 * w01) + t11 * w11;
 }
 
+// Texel a pixel-centre fetch `texture(img, (vec2(s) + 0.5) / N)` lands on under the pinned sampler, for one axis.
+// `exact` is cleared when the quantised weight is not 0 or 1 (then the caller must take the generic bilinear path);
+// it never is at real frame sizes (tests/test_post_cpu.py::test_texel_centre_fetches_are_exact).
+BLOKB_HD int centre_texel(int s, int N, bool& exact) {
+    const float b = ((float(s) + 0.5f) / float(N)) * float(N) - 0.5f;
+    const float f = floorf(b);
+    const int q = int((b - f) * 256.0f + 0.5f);
+    exact = exact && (q == 0 || q == 256);
+    const float t = q ? f + 1.0f : f;
+    return !(t >= 0.0f) ? 0 : (t > float(N - 1) ? N - 1 : int(t));
+}
+// normalize() of a G-buffer normal. Voxel faces give exactly unit axis vectors: dot == 1 -> v * (1 / sqrt(1)) == v bit for bit.
+BLOKB_HD F3 normalize_gbuf(F3 v) {
+    const float d = dot3(v, v);
+    return d == 1.0f ? v : v * (1.0f / sqrtf(d));
+}
+
 // temporal_reproject.comp main() + variance.comp main() for pixel (x, y).
 BLOKB_HD void temporal_variance_pixel(const PostFrame& P, const TemporalIO& io, int x, int y) {
     const int W = (int)P.width, H = (int)P.height;
@@ -120,7 +137,7 @@ BLOKB_HD void temporal_variance_pixel(const PostFrame& P, const TemporalIO& io, 
     const F4 nrd = ld_rgba16f(io.normalRough, W, x, y);
     const F3 worldPos = f3(wpd.x, wpd.y, wpd.z);
     const float depth = wpd.w;
-    const F3 normal = normalize3(f3(nrd.x, nrd.y, nrd.z));
+    const F3 normal = normalize_gbuf(f3(nrd.x, nrd.y, nrd.z));
     const uint32_t mvb = __ldg(reinterpret_cast<const uint32_t*>(io.motion) + idx);
     const float mvx = h2f(mvb & 0xFFFFu), mvy = h2f(mvb >> 16);
 
@@ -152,7 +169,7 @@ BLOKB_HD void temporal_variance_pixel(const PostFrame& P, const TemporalIO& io, 
                 }
             }
             {   // spatial variance: normalised sample normal, Gaussian depth weight
-                const float normalDot = dot3(normal, normalize3(f3(snd.x, snd.y, snd.z)));
+                const float normalDot = dot3(normal, normalize_gbuf(f3(snd.x, snd.y, snd.z)));
                 const float depthWeight = expf(-depthDiff * depthDiff / (0.5f * 0.5f));
                 const float normalWeight = normalDot > 0.9f ? 1.0f : 0.0f;
                 const float weight = depthWeight * normalWeight;
@@ -188,7 +205,7 @@ BLOKB_HD void temporal_variance_pixel(const PostFrame& P, const TemporalIO& io, 
         const F4 pwd = ld_rgba32f(io.prevWorldPos, W, pcx, pcy);
         const F4 pnd = ld_rgba16f(io.prevNormal, W, pcx, pcy);
         const float prevDepth = pwd.w;
-        const F3 prevNormal = normalize3(f3(pnd.x, pnd.y, pnd.z));
+        const F3 prevNormal = normalize_gbuf(f3(pnd.x, pnd.y, pnd.z));
         const float absoluteDepthThreshold = P.depthThreshold * depth + 0.5f;
         const bool depthValid = fabsf(depth - prevDepth) < absoluteDepthThreshold;
         const bool normalValid = dot3(normal, prevNormal) > P.normalThreshold;
@@ -262,6 +279,10 @@ BLOKB_HD void temporal_variance_pixel(const PostFrame& P, const TemporalIO& io, 
 }
 
 // atrous.comp main() for pixel (x, y): in -> out with step `stepSize`.
+// Same results as the shader for every input; the work is ordered so that the common voxel case is cheap: the 5 + 5
+// distinct tap columns / rows are resolved to texels once (instead of 25 sampler evaluations), a tap is dropped as soon
+// as one factor of its weight is known to be zero (weight < 0.001 discards it in the shader too), and unit normals
+// skip normalisation and the normal-weight division ((1 - 0.9) / (1 - 0.9) == 1).
 BLOKB_HD void atrous_pixel(const PostFrame& P, int stepSize, const float* inColor, const float* variance, const float* worldPosImg,
                            const uint16_t* normalRough, float* outColor, int x, int y) {
     const int W = (int)P.width, H = (int)P.height;
@@ -277,50 +298,74 @@ BLOKB_HD void atrous_pixel(const PostFrame& P, int stepSize, const float* inColo
     const F4 cn4 = ld_rgba16f(normalRough, W, x, y);
     const float centerVariance = __ldg(variance + idx);
     const F3 centerWorldPos = f3(cw.x, cw.y, cw.z);
-    const F3 centerNormal = normalize3(f3(cn4.x, cn4.y, cn4.z));
+    const F3 centerNormal = normalize_gbuf(f3(cn4.x, cn4.y, cn4.z));
     // computeColorWeight's sigma depends on the centre only (:85-94)
     const float csigma = 0.01f + P.phiColor * sqrtf(gmax(centerVariance, 0.0f));
     const float cden = 2.0f * csigma * csigma + 1e-6f;
     const float dsigma = P.phiDepth * float(stepSize) + 0.1f;  // (:131)
     const float dden = dsigma * dsigma + 1e-6f;
-    const float kern[3] = {1.0f, 2.0f / 3.0f, 1.0f / 6.0f};
+    const float dcut = dsigma * 2.0f;
+    auto kern_w = [](int o) { return o == 0 ? 1.0f : ((o == 1 || o == -1) ? 2.0f / 3.0f : 1.0f / 6.0f); };  // kernel[abs(o)] (:58)
+    int sxs[5], txs[5];
+    bool exact = true;
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+        sxs[k] = iclamp(x + (k - 2) * stepSize, 0, W - 1);
+        txs[k] = centre_texel(sxs[k], W, exact);
+        centre_texel(iclamp(y + (k - 2) * stepSize, 0, H - 1), H, exact);
+    }
     F3 sumColor = f3(0.0f);
     float sumWeight = 0.0f;
-#pragma unroll
-    for (int oy = -2; oy <= 2; oy++)
-#pragma unroll
-        for (int ox = -2; ox <= 2; ox++) {
-            const int sx = iclamp(x + ox * stepSize, 0, W - 1), sy = iclamp(y + oy * stepSize, 0, H - 1);
-            const F4 sw = ld_rgba32f(worldPosImg, W, sx, sy);
-            if (sw.w > 9000.0f) continue;
-            const F4 s4 = tex_linear<false>(inColor, W, H, (float(sx) + 0.5f) / float(P.width), (float(sy) + 0.5f) / float(P.height));
-            const F3 sampleColor = f3(s4.x, s4.y, s4.z);
-            const F4 sn4 = ld_rgba16f(normalRough, W, sx, sy);
-            const F3 sampleNormal = normalize3(f3(sn4.x, sn4.y, sn4.z));
-            const float kernelWeight = kern[ox < 0 ? -ox : ox] * kern[oy < 0 ? -oy : oy];
-            const F3 diff = centerColor - sampleColor;
-            const float colorWeight = 1.0f / (1.0f + dot3(diff, diff) / cden);
-            float normalWeight;
-            {
-                const float dp = gmax(dot3(centerNormal, sampleNormal), 0.0f);
-                if (dp < 0.9f) normalWeight = 0.0f;
-                else {
-                    const float t = (dp - 0.9f) / (1.0f - 0.9f);
-                    normalWeight = t * t;
-                }
+    auto tap = [&](int ox, int oy, int sx, int sy, int txl, int tyl, bool fast) {
+        const F4 sw = ld_rgba32f(worldPosImg, W, sx, sy);
+        if (sw.w > 9000.0f) return;
+        const uint2 nb = __ldg(reinterpret_cast<const uint2*>(normalRough) + (unsigned(sy) * unsigned(W) + unsigned(sx)));
+        const F3 sampleNormal = normalize_gbuf(f3(h2f(nb.x & 0xFFFFu), h2f(nb.x >> 16), h2f(nb.y & 0xFFFFu)));
+        float normalWeight;
+        {
+            const float dp = gmax(dot3(centerNormal, sampleNormal), 0.0f);
+            if (dp < 0.9f) normalWeight = 0.0f;
+            else if (dp == 1.0f) normalWeight = 1.0f;
+            else {
+                const float t = (dp - 0.9f) / (1.0f - 0.9f);
+                normalWeight = t * t;
             }
-            float depthWeight;
-            {
-                const float depthDiff = fabsf(centerDepth - sw.w);
-                const float planeDistance = fabsf(dot3(f3(sw.x, sw.y, sw.z) - centerWorldPos, centerNormal));
-                const float eff = gmax(depthDiff * 0.1f, planeDistance);
-                depthWeight = eff > dsigma * 2.0f ? 0.0f : 1.0f / (1.0f + eff * eff / dden);
-            }
-            const float weight = kernelWeight * colorWeight * normalWeight * depthWeight;
-            if (weight < 0.001f) continue;
-            sumColor = sumColor + sampleColor * weight;
-            sumWeight += weight;
         }
+        const float depthDiff = fabsf(centerDepth - sw.w);
+        const float planeDistance = fabsf(dot3(f3(sw.x, sw.y, sw.z) - centerWorldPos, centerNormal));
+        const float eff = gmax(depthDiff * 0.1f, planeDistance);
+        const bool depthCut = eff > dcut;
+        const F4 s4 = fast ? ld_rgba32f(inColor, W, txl, tyl)
+                           : tex_linear<false>(inColor, W, H, (float(sx) + 0.5f) / float(P.width), (float(sy) + 0.5f) / float(P.height));
+        const F3 sampleColor = f3(s4.x, s4.y, s4.z);
+        const F3 diff = centerColor - sampleColor;
+        const float cq = dot3(diff, diff) / cden;
+        // a zero factor with finite partners makes the product (+)0 < 0.001: the shader `continue`s. (cq is NaN only for a NaN colour.)
+        if ((normalWeight == 0.0f || depthCut) && cq == cq) return;
+        const float colorWeight = 1.0f / (1.0f + cq);
+        const float depthWeight = depthCut ? 0.0f : 1.0f / (1.0f + eff * eff / dden);
+        const float kernelWeight = kern_w(ox) * kern_w(oy);
+        const float weight = kernelWeight * colorWeight * normalWeight * depthWeight;
+        if (weight < 0.001f) return;
+        sumColor = sumColor + sampleColor * weight;
+        sumWeight += weight;
+    };
+    if (exact) {
+#pragma unroll 1
+        for (int oy = -2; oy <= 2; oy++) {  // rows stay a loop (instruction-cache footprint), the five columns are unrolled
+            const int sy = iclamp(y + oy * stepSize, 0, H - 1);
+            bool e2 = true;
+            const int ty = centre_texel(sy, H, e2);
+#pragma unroll
+            for (int ox = -2; ox <= 2; ox++) tap(ox, oy, sxs[ox + 2], sy, txs[ox + 2], ty, true);
+        }
+    } else {
+#pragma unroll 1
+        for (int i = 0; i < 25; i++) {
+            const int ox = i % 5 - 2, oy = i / 5 - 2;
+            tap(ox, oy, iclamp(x + ox * stepSize, 0, W - 1), iclamp(y + oy * stepSize, 0, H - 1), 0, 0, false);
+        }
+    }
     F3 o = sumWeight > 0.01f ? sumColor / sumWeight : centerColor;
     o = gmax3(o, f3(0.0f));
     reinterpret_cast<float4*>(outColor)[idx] = make_float4(o.x, o.y, o.z, 1.0f);
@@ -425,20 +470,40 @@ BLOKB_HD void taa_tonemap_pixel(const PostFrame& P, const float* currentColor, c
     else reinterpret_cast<float4*>(outColor)[idx] = make_float4(outputResult.x, outputResult.y, outputResult.z, cs.w);
 }
 
-// sharpen.comp main() for pixel (x, y).
-BLOKB_HD void sharpen_pixel(const PostFrame& P, const uint8_t* in, uint32_t* out, int x, int y) {
+// One axis of the pinned sampler for an arbitrary coordinate (sharpen.comp's uv +- texelSize taps).
+BLOKB_HD int axis_texel(float u, int N, bool& exact) {
+    const float b = u * float(N) - 0.5f;
+    const float f = floorf(b);
+    const int q = int((b - f) * 256.0f + 0.5f);
+    exact = exact && (q == 0 || q == 256);
+    const float t = q ? f + 1.0f : f;
+    return !(t >= 0.0f) ? 0 : (t > float(N - 1) ? N - 1 : int(t));
+}
+
+// sharpen.comp main() for pixel (x, y). lut255[i] = float(i) / 255.0f (the unorm8 decode, computed once per block with
+// the same IEEE division); the 3 + 3 tap columns / rows are resolved to texels once.
+BLOKB_HD void sharpen_pixel(const PostFrame& P, const float* lut255, const uint8_t* in, uint32_t* out, int x, int y) {
     const int W = (int)P.width, H = (int)P.height;
     const float tx = 1.0f / float(W), ty = 1.0f / float(H);
     const float u = (float(x) + 0.5f) / float(W), v = (float(y) + 0.5f) / float(H);
-    auto tap = [&](float ox, float oy) {
-        const F4 t = tex_linear<true>(in, W, H, u + tx * ox, v + ty * oy);
+    bool exact = true;
+    int cx[3], cy[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        cx[k] = axis_texel(u + tx * float(k - 1), W, exact);
+        cy[k] = axis_texel(v + ty * float(k - 1), H, exact);
+    }
+    auto tap = [&](int ox, int oy) {
+        if (exact) {
+            const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(in) + (size_t(cy[oy + 1]) * W + cx[ox + 1]));
+            return f3(lut255[w & 255u], lut255[(w >> 8) & 255u], lut255[(w >> 16) & 255u]);
+        }
+        const F4 t = tex_linear<true>(in, W, H, u + tx * float(ox), v + ty * float(oy));
         return f3(t.x, t.y, t.z);
     };
-    const F3 a = tap(-1.f, -1.f), b = tap(0.f, -1.f), c = tap(1.f, -1.f);
-    const F3 d = tap(-1.f, 0.f), f = tap(1.f, 0.f);
-    const F4 e4 = tex_linear<true>(in, W, H, u, v);
-    const F3 e = f3(e4.x, e4.y, e4.z);
-    const F3 g = tap(-1.f, 1.f), h = tap(0.f, 1.f), i = tap(1.f, 1.f);
+    const F3 a = tap(-1, -1), b = tap(0, -1), c = tap(1, -1);
+    const F3 d = tap(-1, 0), e = tap(0, 0), f = tap(1, 0);
+    const F3 g = tap(-1, 1), h = tap(0, 1), i = tap(1, 1);
     const F3 blur = (1.0f * (a + c + g + i) + 2.0f * (b + d + f + h) + 4.0f * e) / 16.0f;
     const F3 detail = e - blur;
     const float intensity = P.sharpenStrength * 3.0f;

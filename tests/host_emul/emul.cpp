@@ -125,8 +125,10 @@ void emu_post_taa_tonemap(const post::PostFrame* P, int taa, int tonemap, const 
     });
 }
 void emu_post_sharpen(const post::PostFrame* P, const uint8_t* in, uint32_t* out, int nThreads) {
+    float lut255[256];
+    for (int i = 0; i < 256; i++) lut255[i] = float(i) / 255.0f;
     pfor(size_t(P->width) * P->height, nThreads, [&](size_t b, size_t e) {
-        for (size_t i = b; i < e; i++) post::sharpen_pixel(*P, in, out, int(i % P->width), int(i / P->width));
+        for (size_t i = b; i < e; i++) post::sharpen_pixel(*P, lut255, in, out, int(i % P->width), int(i / P->width));
     });
 }
 }

@@ -70,3 +70,36 @@ def test_pixel_functions_match_reference_shaders(reflib, emul, settings):
     # the sequence exercised the interesting paths
     hl = np.squeeze(a["historyLength"]).view(np.float16).astype(np.float32)
     assert hl.max() >= 1.0
+
+
+GOLD_POST = sorted(__import__("glob").glob(os.path.join(os.path.dirname(__file__), "golden", "post", "*.npz")))
+
+
+@pytest.mark.parametrize("path", GOLD_POST, ids=lambda p: os.path.basename(p)[:-4])
+def test_pixel_functions_match_golden_fixtures(emul, path):
+    """The committed fixtures (reference shaders, run by tests/golden/make_golden_post.py) — usable without /root/reference."""
+    from tests.host_emul.emu import EmuPostChain
+    z = np.load(path)
+    flt = ("exposure", "saturationBoost", "feedbackMin", "feedbackMax", "sharpenStrength", "whitePoint")
+    st = PostSettings(**{k: (float(v) if k in flt else int(v)) for k, v in zip(z["settings_keys"], z["settings_vals"])})
+    h, w = z["f0_color"].shape[:2]
+    ours = EmuPostChain(emul, w, h, st)
+    for k in range(int(z["frames"][0])):
+        b = ours.frame(z[f"f{k}_ubo"], z[f"f{k}_color"], z[f"f{k}_worldPos"], z[f"f{k}_normalRough"], z[f"f{k}_motion"])
+        for key in KEYS:
+            x, y = z[f"f{k}_{key}"], np.squeeze(b[key])
+            assert x.shape == y.shape and x.dtype == y.dtype, (k, key)
+            assert np.array_equal(np.ascontiguousarray(x).view(np.uint8), np.ascontiguousarray(y).view(np.uint8)), (k, key)
+
+
+def test_texel_centre_fetches_are_exact():
+    """The fast path of the pinned sampler: (x + 0.5) / W * W - 0.5 quantises to an integer texel for every x at the sizes
+    the bench uses (so a-trous / tonemap / sharpen taps read single texels, as the shader comments intend)."""
+    for W in (64, 173, 1920, 2160, 3840, 7680):
+        x = np.arange(W, dtype=np.float32)
+        for off in (-1.0, 0.0, 1.0):
+            u = (x + np.float32(0.5)) / np.float32(W) + np.float32(off) * (np.float32(1.0) / np.float32(W))
+            xb = u * np.float32(W) - np.float32(0.5)
+            q = ((xb - np.floor(xb)) * np.float32(256.0) + np.float32(0.5)).astype(np.int32)
+            texel = np.floor(xb).astype(np.int64) + (q == 256)
+            assert np.all((q == 0) | (q == 256)) and np.array_equal(texel, np.arange(W) + int(off)), (W, off)
