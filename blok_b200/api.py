@@ -36,6 +36,9 @@ IMG_HIT, IMG_SHADOW, IMG_COLOR, IMG_WORLDPOS, IMG_NORMALROUGH, IMG_ALBEDOMETAL, 
 (IMG_HISTORY_COLOR, IMG_MOMENTS, IMG_HISTORY_LENGTH, IMG_VARIANCE, IMG_DENOISED, IMG_TAA_HISTORY, IMG_TAA_OUTPUT, IMG_TONEMAPPED,
  IMG_FINAL) = range(8, 17)
 
+WORLD_NODES, WORLD_BLOCKFIRSTLEAF, WORLD_VOXELMAT, WORLD_SUBCHUNKS = range(4)
+CNODE_DT = np.dtype([("mask", "<u8"), ("base", "<u4"), ("aux", "<u4")])  # blok_b200/csrc/scene.h Node
+
 _vp = C.c_void_p
 
 
@@ -112,7 +115,7 @@ EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_wo
            "blokb_worldgen_pack", "blokb_worldgen_counts", "blokb_worldgen_copy", "blokb_worldgen_nodes", "blokb_worldgen_subs",
            "blokb_worldgen_free", "blokb_pipeline_create", "blokb_pipeline_submit", "blokb_pipeline_wait", "blokb_pipeline_drain",
            "blokb_pipeline_destroy", "blokb_host_alloc", "blokb_host_free", "blokb_post_settings_default", "blokb_denoise",
-           "blokb_postprocess", "blokb_end_frame", "blokb_reset_history", "blokb_write_image"]
+           "blokb_postprocess", "blokb_end_frame", "blokb_reset_history", "blokb_write_image", "blokb_upload_voxels", "blokb_world_export"]
 
 _lib = None
 
@@ -133,6 +136,8 @@ def load_library():
     L.blokb_upload_world.argtypes = [_vp, _vp, C.c_size_t, _vp, C.c_size_t, _vp, C.c_size_t]
     L.blokb_world_stats_get.argtypes = [_vp, C.POINTER(WorldStats)]
     L.blokb_set_frame.argtypes = [_vp, C.POINTER(FrameUBO)]
+    L.blokb_upload_voxels.argtypes = [_vp, _vp, _vp, C.c_size_t, _vp, C.c_size_t]
+    L.blokb_world_export.argtypes = [_vp, C.c_int, _vp, C.c_size_t, C.POINTER(C.c_size_t)]
     L.blokb_camera_frame.argtypes = [C.POINTER(CameraC), C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(FrameUBO)]
     L.blokb_camera_frame_seq.argtypes = [C.POINTER(CameraC), C.POINTER(CameraC), C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int32,
                                          C.POINTER(FrameUBO)]
@@ -267,6 +272,25 @@ class Renderer:
                                       len(world.globalSubChunks), _ptr(world.materials), len(world.materials)))
 
     update_world = add_world
+
+    def add_voxels(self, xyz, material_ids, materials):
+        """Scene in, built on the GPU: the voxel list (what ChunkManager::setVoxelMaterial would be fed) goes to the device as
+        is; equivalent to WorldSvoGpu.from_voxels(...) + add_world(...) with the same node numbering."""
+        xyz = np.ascontiguousarray(xyz, np.int32).reshape(-1, 3)
+        mid = np.ascontiguousarray(material_ids, np.uint32)
+        mats = np.ascontiguousarray(materials, dtype=MAT_DT)
+        assert len(mid) == len(xyz)
+        _ck(self.L.blokb_upload_voxels(self._ctx, _ptr(xyz), _ptr(mid), len(mid), _ptr(mats), len(mats)))
+
+    def world_export(self, which: int) -> np.ndarray:
+        """Device-resident world array -> numpy (WORLD_NODES: (n,) {mask,base,aux}; WORLD_BLOCKFIRSTLEAF: u32; WORLD_VOXELMAT: raw
+        bytes as u8; WORLD_SUBCHUNKS: SUB_DT)."""
+        n = C.c_size_t()
+        _ck(self.L.blokb_world_export(self._ctx, which, None, 0, C.byref(n)))
+        dt = {WORLD_NODES: CNODE_DT, WORLD_BLOCKFIRSTLEAF: np.dtype("<u4"), WORLD_VOXELMAT: np.dtype("u1"), WORLD_SUBCHUNKS: SUB_DT}[which]
+        out = np.empty(n.value // dt.itemsize, dt)
+        _ck(self.L.blokb_world_export(self._ctx, which, _ptr(out), out.nbytes, None))
+        return out
 
     def world_stats(self) -> dict:
         s = WorldStats()

@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "../../include/blokb200.h"
+#include "build.h"
 #include "kernels.h"
 #include "post.h"
 #include "scene_build.h"
@@ -33,6 +34,10 @@ struct blokb_ctx {
     DeviceWorld dw{};
     std::vector<void*> worldAllocs;
     blokb_world_stats stats{};
+    // sizes of the device-resident compact arrays (blokb_world_export) and, for device-built worlds, the SubChunkGpu records
+    size_t nNodesCompact = 0, nBlocks = 0, nVoxels = 0;
+    const blokb_subchunk* dSubs = nullptr;
+    size_t nSubsDev = 0;
     // frame
     bool haveFrame = false;
     FrameDev frame{};
@@ -71,6 +76,8 @@ static void free_world(blokb_ctx* c) {
     for (void* p : c->worldAllocs) cudaFree(p);
     c->worldAllocs.clear();
     c->haveWorld = false;
+    c->nNodesCompact = c->nBlocks = c->nVoxels = c->nSubsDev = 0;
+    c->dSubs = nullptr;
 }
 static void free_images(blokb_ctx* c) {
     void* ps[] = {c->buf.hit, c->buf.shadow, c->buf.color, c->buf.worldPos, c->buf.normalRough, c->buf.albedoMetal, c->buf.motion, c->buf.accum};
@@ -176,7 +183,99 @@ int blokb_upload_world(blokb_ctx* c, const blokb_svo_node* nodes, size_t nNodes,
     s.levels = hw.levels;
     s.buildMs = std::chrono::duration<float, std::milli>(t1 - t0).count();
     s.uploadMs = std::chrono::duration<float, std::milli>(t2 - t1).count();
+    c->nNodesCompact = hw.nodes.size(); c->nBlocks = hw.blockFirstLeaf.size(); c->nVoxels = hw.voxels;
     c->haveWorld = true;
+    return 0;
+}
+
+// Scene in, built on the device: ChunkManager::setVoxelMaterial per voxel + rebuildDirtyChunks +
+// packChunksToGpuSvo + uploadSvoBuffers in one call, without the reference-format node arrays ever existing.
+int blokb_upload_voxels(blokb_ctx* c, const int32_t* xyz, const uint32_t* materialId, size_t n, const blokb_material* materials, size_t nMaterials) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    if ((n && (!xyz || !materialId)) || (nMaterials && !materials)) return fail(BLOKB_E_ARG, "null array with non-zero count");
+    CK(cudaSetDevice(c->device));
+    const auto t0 = std::chrono::steady_clock::now();
+    CK(cudaStreamSynchronize(c->stream));
+    build::DeviceBuild B;
+    std::string err;
+    int rc = build::from_voxels(xyz, materialId, n, c->stream, B, err);
+    if (rc) return fail(rc, err);
+    HostWorld hw;
+    hw.subs = B.recs;
+    uint64_t brickStart = 0;
+    rc = build_top(B.subs.data(), B.subs.size(), B.nBricks, hw, brickStart, err);
+    if (rc) { build::release(B); return fail(rc, err); }
+    const auto t1 = std::chrono::steady_clock::now();
+    free_world(c);
+    DeviceWorld& d = c->dw;
+    d = DeviceWorld{};
+    for (int a = 0; a < 3; a++) { d.origin[a] = hw.origin[a]; d.dim[a] = hw.dim[a]; }
+    d.levels = hw.levels;
+    d.matWide = B.matWide ? 1 : 0;
+    // take ownership of the device arrays first so that any failure below frees them with the world
+    for (void* p : {(void*)B.bricks, (void*)B.blockFirstLeaf, B.voxelMat, (void*)B.dSubs}) if (p) c->worldAllocs.push_back(p);
+    Node* dBricks = B.bricks;
+    d.blockFirstLeaf = B.blockFirstLeaf; d.voxelMat = B.voxelMat; c->dSubs = B.dSubs; c->nSubsDev = B.nSubs;
+    B.bricks = nullptr; B.blockFirstLeaf = nullptr; B.voxelMat = nullptr; B.dSubs = nullptr;
+    if (!d.blockFirstLeaf) { const std::vector<uint32_t> e; if ((rc = upload_vec(c, e, &d.blockFirstLeaf))) return rc; }
+    if (!d.voxelMat) { const std::vector<uint16_t> e; const uint16_t* p; if ((rc = upload_vec(c, e, &p))) return rc; d.voxelMat = p; }
+    {
+        // nodes[] = host-built top (root ... sub-chunk nodes) followed by the device-built brick nodes
+        void* dn = nullptr;
+        const size_t total = size_t(brickStart + B.nBricks);
+        if (hw.nodes.size() != brickStart) return fail(BLOKB_E_CUDA, "internal: top-of-tree size mismatch");
+        CK(cudaMalloc(&dn, std::max<size_t>(total * sizeof(Node), 16)));
+        c->worldAllocs.push_back(dn);
+        CK(cudaMemcpyAsync(dn, hw.nodes.data(), hw.nodes.size() * sizeof(Node), cudaMemcpyHostToDevice, c->stream));
+        if (B.nBricks) CK(cudaMemcpyAsync(static_cast<Node*>(dn) + brickStart, dBricks, B.nBricks * sizeof(Node), cudaMemcpyDeviceToDevice, c->stream));
+        d.nodes = reinterpret_cast<const uint4*>(dn);
+        c->nNodesCompact = total;
+    }
+    {
+        std::vector<blokb_material> m(materials, materials + nMaterials);
+        if (m.empty()) { blokb_material def{{0.8f, 0.8f, 0.8f}, (127u << 16), {0, 0, 0}, 0.f}; m.push_back(def); }
+        const blokb_material* p;
+        if ((rc = upload_vec(c, m, &p))) return rc;
+        d.materials = reinterpret_cast<const float4*>(p);
+        d.nMaterials = (uint32_t)m.size();
+    }
+    CK(cudaStreamSynchronize(c->stream));
+    const auto t2 = std::chrono::steady_clock::now();
+    blokb_world_stats& s = c->stats;
+    s = blokb_world_stats{};
+    s.nodes = B.refNodes; s.subChunks = B.nSubs; s.materials = nMaterials;
+    s.bricks = B.nBricks; s.blocks = B.nBlocks; s.voxels = B.nVox;
+    s.compactBytes = c->nNodesCompact * sizeof(Node) + B.nBlocks * 4 + B.nVox * (B.matWide ? 4 : 2);
+    for (int a = 0; a < 3; a++) { s.gridOrigin[a] = hw.origin[a]; s.gridDim[a] = hw.dim[a]; }
+    s.levels = hw.levels;
+    s.buildMs = std::chrono::duration<float, std::milli>(t1 - t0).count();  // H2D of the voxel list + device build + top of tree
+    s.uploadMs = std::chrono::duration<float, std::milli>(t2 - t1).count();
+    c->nBlocks = B.nBlocks; c->nVoxels = B.nVox;
+    c->haveWorld = true;
+    return 0;
+}
+
+// Copies one of the device-resident world arrays to the host (parity checks, tools). bytes must match exactly; pass
+// host == NULL to query the size through *bytesOut.
+int blokb_world_export(blokb_ctx* c, int which, void* host, size_t bytes, size_t* bytesOut) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    if (!c->haveWorld) return fail(BLOKB_E_STATE, "no world uploaded");
+    const void* src = nullptr;
+    size_t sz = 0;
+    switch (which) {
+        case BLOKB_WORLD_NODES: src = c->dw.nodes; sz = c->nNodesCompact * sizeof(Node); break;
+        case BLOKB_WORLD_BLOCKFIRSTLEAF: src = c->dw.blockFirstLeaf; sz = c->nBlocks * 4; break;
+        case BLOKB_WORLD_VOXELMAT: src = c->dw.voxelMat; sz = c->nVoxels * (c->dw.matWide ? 4 : 2); break;
+        case BLOKB_WORLD_SUBCHUNKS: src = c->dSubs; sz = c->nSubsDev * sizeof(blokb_subchunk); break;
+        default: return fail(BLOKB_E_ARG, "unknown world array id");
+    }
+    if (bytesOut) *bytesOut = sz;
+    if (!host) return 0;
+    if (which == BLOKB_WORLD_SUBCHUNKS && !src && sz == 0 && c->stats.subChunks) return fail(BLOKB_E_STATE, "sub-chunk records are kept on the device only for worlds built by blokb_upload_voxels");
+    if (bytes != sz) return fail(BLOKB_E_ARG, "host buffer size mismatch: expected " + std::to_string(sz));
+    CK(cudaSetDevice(c->device));
+    if (sz) CK(cudaMemcpyAsync(host, src, sz, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
     return 0;
 }
 

@@ -1,0 +1,36 @@
+// Device scene build (build.cu): voxel list -> brick nodes, blockFirstLeaf, voxelMat and the sub-chunk records on the GPU.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/blokb200.h"
+#include "scene.h"
+
+namespace blokb {
+namespace build {
+
+struct DeviceBuild {
+    // device arrays, owned by the caller after a successful build (cudaFree)
+    Node* bricks = nullptr;            // nBricks level-1 nodes, in sub-chunk order then brick-bit order
+    uint32_t* blockFirstLeaf = nullptr;  // nBlocks reference node indices
+    void* voxelMat = nullptr;          // nVox material ids (u16, or u32 when matWide)
+    blokb_subchunk* dSubs = nullptr;   // nSubs SubChunkGpu records (reference format)
+    uint64_t nBricks = 0, nBlocks = 0, nVox = 0, nSubs = 0, nChunks = 0;
+    uint64_t refNodes = 0;             // nodes the reference's packed array would hold: sum over chunks of 1 + 8 * interior
+    bool matWide = false;
+    // host copies for the top of the tree (build_top)
+    std::vector<blokb_subchunk> subs;
+    std::vector<SubRec> recs;
+    float sortMs = 0.f, buildMs = 0.f;
+};
+
+// xyz: n x int32[3] world voxel coordinates, mat: n x u32 (host pointers; a voxel listed twice keeps the last material,
+// like ChunkManager::setVoxelMaterial). Returns 0 or BLOKB_E_*; on failure nothing is left allocated.
+int from_voxels(const int32_t* xyz, const uint32_t* mat, size_t n, cudaStream_t st, DeviceBuild& out, std::string& err);
+void release(DeviceBuild& b);
+
+}  // namespace build
+}  // namespace blokb

@@ -78,10 +78,13 @@ static void decode_sub(const blokb_svo_node* nodes, size_t nNodes, const blokb_s
 static inline uint64_t block_bits(uint32_t b) { return 0x0000000000330033ull << (2 * (b & 1) + 8 * (b >> 1 & 1) + 32 * (b >> 2 & 1)); }
 }  // namespace
 
-int build_host_world(const blokb_svo_node* nodes, size_t nNodes, const blokb_subchunk* subs, size_t nSubs, HostWorld& w,
-                     std::string& err) {
-    w = HostWorld();
+// Bounding box, level count, top grid, mask pyramid and the breadth-first upper part of the tree (root ... sub-chunk
+// nodes) from the sub-chunk records alone: w.subs[i] = {brickMask, brickBase} must be filled. Brick nodes are NOT appended;
+// they start at index `brickStart` (returned) in sub-chunk order. Shared by the host builder below and the device
+// builder (build.cu), which produces the per-sub-chunk records and the brick nodes on the GPU.
+int build_top(const blokb_subchunk* subs, size_t nSubs, uint64_t nBricks, HostWorld& w, uint64_t& brickStart, std::string& err) {
     if (nSubs == 0) {  // empty world: a single empty 16^3 grid
+        w.origin[0] = w.origin[1] = w.origin[2] = 0;
         w.dim[0] = w.dim[1] = w.dim[2] = 16;
     } else {
         int64_t lo[3] = {INT64_MAX, INT64_MAX, INT64_MAX}, hi[3] = {INT64_MIN, INT64_MIN, INT64_MIN};
@@ -104,8 +107,85 @@ int build_host_world(const blokb_svo_node* nodes, size_t nNodes, const blokb_sub
     w.levels = 3;
     while ((int64_t(1) << (2 * w.levels)) < maxDim) w.levels++;
     if (w.levels > kMaxLevels) { err = "world too large"; return BLOKB_E_UNSUPPORTED; }
-
     w.topGrid.assign(size_t(g[0] * g[1] * g[2]), 0xFFFFFFFFu);
+    // top grid; later sub-chunks at the same cell do not occur in reference output (one entry per region)
+    for (size_t i = 0; i < nSubs; i++) {
+        int64_t c[3];
+        for (int a = 0; a < 3; a++) c[a] = ((int64_t)subs[i].worldMin[a] - w.origin[a]) / 16;
+        uint32_t& cell = w.topGrid[size_t((c[2] * g[1] + c[1]) * g[0] + c[0])];
+        if (cell != 0xFFFFFFFFu) { err = "two sub-chunks cover the same 16^3 region"; return BLOKB_E_UNSUPPORTED; }
+        cell = (uint32_t)i;
+    }
+    // dense mask pyramid, levels 3..levels. Level-3 bit = sub-chunk present *and* non-empty.
+    w.dense.assign(w.levels + 1, {});
+    for (int k = 3; k <= w.levels; k++) {
+        const int64_t cs = int64_t(1) << (2 * k);
+        for (int a = 0; a < 3; a++) w.denseDim[k][a] = (int32_t)((w.dim[a] + cs - 1) / cs);
+        w.dense[k].assign(size_t(w.denseDim[k][0]) * w.denseDim[k][1] * w.denseDim[k][2], 0ull);
+    }
+    for (int64_t z = 0; z < g[2]; z++)
+        for (int64_t y = 0; y < g[1]; y++)
+            for (int64_t x = 0; x < g[0]; x++) {
+                uint32_t p = w.topGrid[size_t((z * g[1] + y) * g[0] + x)];
+                if (p == 0xFFFFFFFFu || w.subs[p].brickMask == 0) continue;
+                const int32_t* d = w.denseDim[3];
+                w.dense[3][size_t(((z >> 2) * d[1] + (y >> 2)) * d[0] + (x >> 2))] |= 1ull << ((x & 3) + 4 * (y & 3) + 16 * (z & 3));
+            }
+    for (int k = 4; k <= w.levels; k++) {
+        const int32_t* dc = w.denseDim[k - 1]; const int32_t* dp = w.denseDim[k];
+        for (int64_t z = 0; z < dc[2]; z++)
+            for (int64_t y = 0; y < dc[1]; y++)
+                for (int64_t x = 0; x < dc[0]; x++)
+                    if (w.dense[k - 1][size_t((z * dc[1] + y) * dc[0] + x)])
+                        w.dense[k][size_t(((z >> 2) * dp[1] + (y >> 2)) * dp[0] + (x >> 2))] |= 1ull << ((x & 3) + 4 * (y & 3) + 16 * (z & 3));
+    }
+    // ---- the uploaded tree: breadth-first Node array (scene.h). Upper levels from the dense pyramid, then one node per
+    // non-empty sub-chunk (children of a level-3 cell contiguous, in bit order), then the bricks in their existing order.
+    struct Cell { int32_t x, y, z; };
+    std::vector<Cell> cur{{0, 0, 0}}, nxt;
+    w.nodes.clear();
+    w.nodes.push_back(Node{w.dense[w.levels][0], 0u, 0u});
+    size_t levelStart = 0;  // index of the first node of the level being expanded
+    uint64_t nUpper = 1;
+    for (int k = w.levels; k >= 4; k--) {
+        const int32_t* dc = w.denseDim[k - 1];
+        nxt.clear();
+        const size_t childStart = w.nodes.size();
+        for (size_t i = 0; i < cur.size(); i++) {
+            Node& n = w.nodes[levelStart + i];
+            n.base = (uint32_t)(childStart + nxt.size());
+            for (uint64_t m = n.mask; m; m &= m - 1) {
+                const int b = __builtin_ctzll(m);
+                nxt.push_back(Cell{cur[i].x * 4 + (b & 3), cur[i].y * 4 + ((b >> 2) & 3), cur[i].z * 4 + (b >> 4)});
+            }
+        }
+        for (const Cell& c : nxt) w.nodes.push_back(Node{w.dense[k - 1][size_t((int64_t(c.z) * dc[1] + c.y) * dc[0] + c.x)], 0u, 0u});
+        levelStart = childStart;
+        cur.swap(nxt);
+        nUpper = w.nodes.size();
+    }
+    // cur = level-3 cells; their children are sub-chunks
+    uint64_t nSubNodes = 0;
+    for (size_t i = 0; i < cur.size(); i++) nSubNodes += __builtin_popcountll(w.nodes[levelStart + i].mask);
+    brickStart = nUpper + nSubNodes;
+    if (brickStart + nBricks > 0xFFFFFFF0ull) { err = "world exceeds 32-bit node indices"; return BLOKB_E_UNSUPPORTED; }
+    w.nodes.reserve(size_t(brickStart + nBricks));
+    for (size_t i = 0; i < cur.size(); i++) {
+        w.nodes[levelStart + i].base = (uint32_t)w.nodes.size();
+        const uint64_t mask = w.nodes[levelStart + i].mask;
+        for (uint64_t m = mask; m; m &= m - 1) {
+            const int b = __builtin_ctzll(m);
+            const int64_t x = cur[i].x * 4 + (b & 3), y = cur[i].y * 4 + ((b >> 2) & 3), z = cur[i].z * 4 + (b >> 4);
+            const uint32_t p = w.topGrid[size_t((z * g[1] + y) * g[0] + x)];
+            w.nodes.push_back(Node{w.subs[p].brickMask, (uint32_t)(brickStart + w.subs[p].brickBase), p});
+        }
+    }
+    return 0;
+}
+
+int build_host_world(const blokb_svo_node* nodes, size_t nNodes, const blokb_subchunk* subs, size_t nSubs, HostWorld& w,
+                     std::string& err) {
+    w = HostWorld();
     w.subs.resize(nSubs);
     // pass 1 (parallel): decode each sub-chunk
     unsigned nt = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
@@ -168,78 +248,8 @@ int build_host_world(const blokb_svo_node* nodes, size_t nNodes, const blokb_sub
         delete o;
     };
     run(fill_range);
-    // top grid; later sub-chunks at the same cell do not occur in reference output (one entry per region)
-    for (size_t i = 0; i < nSubs; i++) {
-        int64_t c[3];
-        for (int a = 0; a < 3; a++) c[a] = ((int64_t)subs[i].worldMin[a] - w.origin[a]) / 16;
-        uint32_t& cell = w.topGrid[size_t((c[2] * g[1] + c[1]) * g[0] + c[0])];
-        if (cell != 0xFFFFFFFFu) { err = "two sub-chunks cover the same 16^3 region"; return BLOKB_E_UNSUPPORTED; }
-        cell = (uint32_t)i;
-    }
-    // dense mask pyramid, levels 3..levels. Level-3 bit = sub-chunk present *and* non-empty.
-    w.dense.assign(w.levels + 1, {});
-    for (int k = 3; k <= w.levels; k++) {
-        const int64_t cs = int64_t(1) << (2 * k);
-        for (int a = 0; a < 3; a++) w.denseDim[k][a] = (int32_t)((w.dim[a] + cs - 1) / cs);
-        w.dense[k].assign(size_t(w.denseDim[k][0]) * w.denseDim[k][1] * w.denseDim[k][2], 0ull);
-    }
-    for (int64_t z = 0; z < g[2]; z++)
-        for (int64_t y = 0; y < g[1]; y++)
-            for (int64_t x = 0; x < g[0]; x++) {
-                uint32_t p = w.topGrid[size_t((z * g[1] + y) * g[0] + x)];
-                if (p == 0xFFFFFFFFu || w.subs[p].brickMask == 0) continue;
-                const int32_t* d = w.denseDim[3];
-                w.dense[3][size_t(((z >> 2) * d[1] + (y >> 2)) * d[0] + (x >> 2))] |= 1ull << ((x & 3) + 4 * (y & 3) + 16 * (z & 3));
-            }
-    for (int k = 4; k <= w.levels; k++) {
-        const int32_t* dc = w.denseDim[k - 1]; const int32_t* dp = w.denseDim[k];
-        for (int64_t z = 0; z < dc[2]; z++)
-            for (int64_t y = 0; y < dc[1]; y++)
-                for (int64_t x = 0; x < dc[0]; x++)
-                    if (w.dense[k - 1][size_t((z * dc[1] + y) * dc[0] + x)])
-                        w.dense[k][size_t(((z >> 2) * dp[1] + (y >> 2)) * dp[0] + (x >> 2))] |= 1ull << ((x & 3) + 4 * (y & 3) + 16 * (z & 3));
-    }
-    // ---- the uploaded tree: breadth-first Node array (scene.h). Upper levels from the dense pyramid, then one node per
-    // non-empty sub-chunk (children of a level-3 cell contiguous, in bit order), then the bricks in their existing order.
-    struct Cell { int32_t x, y, z; };
-    std::vector<Cell> cur{{0, 0, 0}}, nxt;
-    w.nodes.clear();
-    w.nodes.push_back(Node{w.dense[w.levels][0], 0u, 0u});
-    size_t levelStart = 0;  // index of the first node of the level being expanded
-    uint64_t nUpper = 1;
-    for (int k = w.levels; k >= 4; k--) {
-        const int32_t* dc = w.denseDim[k - 1];
-        nxt.clear();
-        const size_t childStart = w.nodes.size();
-        for (size_t i = 0; i < cur.size(); i++) {
-            Node& n = w.nodes[levelStart + i];
-            n.base = (uint32_t)(childStart + nxt.size());
-            for (uint64_t m = n.mask; m; m &= m - 1) {
-                const int b = __builtin_ctzll(m);
-                nxt.push_back(Cell{cur[i].x * 4 + (b & 3), cur[i].y * 4 + ((b >> 2) & 3), cur[i].z * 4 + (b >> 4)});
-            }
-        }
-        for (const Cell& c : nxt) w.nodes.push_back(Node{w.dense[k - 1][size_t((int64_t(c.z) * dc[1] + c.y) * dc[0] + c.x)], 0u, 0u});
-        levelStart = childStart;
-        cur.swap(nxt);
-        nUpper = w.nodes.size();
-    }
-    // cur = level-3 cells; their children are sub-chunks
-    uint64_t nSubNodes = 0;
-    for (size_t i = 0; i < cur.size(); i++) nSubNodes += __builtin_popcountll(w.nodes[levelStart + i].mask);
-    const uint64_t brickStart = nUpper + nSubNodes;
-    if (brickStart + w.bricks.size() > 0xFFFFFFF0ull) { err = "world exceeds 32-bit node indices"; return BLOKB_E_UNSUPPORTED; }
-    w.nodes.reserve(size_t(brickStart + w.bricks.size()));
-    for (size_t i = 0; i < cur.size(); i++) {
-        w.nodes[levelStart + i].base = (uint32_t)w.nodes.size();
-        const uint64_t mask = w.nodes[levelStart + i].mask;
-        for (uint64_t m = mask; m; m &= m - 1) {
-            const int b = __builtin_ctzll(m);
-            const int64_t x = cur[i].x * 4 + (b & 3), y = cur[i].y * 4 + ((b >> 2) & 3), z = cur[i].z * 4 + (b >> 4);
-            const uint32_t p = w.topGrid[size_t((z * g[1] + y) * g[0] + x)];
-            w.nodes.push_back(Node{w.subs[p].brickMask, (uint32_t)(brickStart + w.subs[p].brickBase), p});
-        }
-    }
+    uint64_t brickStart = 0;
+    if (int rc = build_top(subs, nSubs, w.bricks.size(), w, brickStart, err)) return rc;
     for (const Brick& b : w.bricks) w.nodes.push_back(Node{b.voxelMask, b.matBase, b.blockBase});
     return 0;
 }

@@ -31,4 +31,6 @@ struct HostWorld {
 int build_host_world(const blokb_svo_node* nodes, size_t nNodes, const blokb_subchunk* subs, size_t nSubs, HostWorld& out,
                      std::string& err);
 
+int build_top(const blokb_subchunk* subs, size_t nSubs, uint64_t nBricks, HostWorld& out, uint64_t& brickStart, std::string& err);
+
 }  // namespace blokb

@@ -162,6 +162,23 @@ void blokb_destroy(blokb_ctx* ctx);
 int blokb_upload_world(blokb_ctx* ctx, const blokb_svo_node* nodes, size_t nNodes, const blokb_subchunk* subs, size_t nSubs,
                        const blokb_material* materials, size_t nMaterials);
 int blokb_world_stats_get(blokb_ctx* ctx, blokb_world_stats* out);
+/* Scene in, built on the GPU. Equivalent to ChunkManager(128, 1.0f)::setVoxelMaterial(p, id, 1.0f) for
+ * every listed voxel (a voxel listed twice keeps the last id), rebuildDirtyChunks (blok/src/chunk_manager.cpp:106-140;
+ * SvoTree::insertVoxel, svo.cpp:59-101), packChunksToGpuSvo (:234-314) and blokb_upload_world — but the voxel list goes
+ * to the device as is and the compact hierarchy is built there; the reference's 16-byte node arrays are never
+ * materialised, only their numbering (hit records carry the same global node indices as after blokb_upload_world of the
+ * reference's arrays; chunks are ordered by (z, y, x) like blokb_worldgen_pack). xyz: n x int32[3] world voxel
+ * coordinates (|coordinate| < 2^20), materialId: n x uint32; host pointers, borrowed for the call. */
+int blokb_upload_voxels(blokb_ctx* ctx, const int32_t* xyz, const uint32_t* materialId, size_t n, const blokb_material* materials,
+                        size_t nMaterials);
+/* Device-resident world arrays -> host (parity checks, tools). host == NULL: only *bytesOut is set. */
+enum blokb_world_array {
+    BLOKB_WORLD_NODES = 0,          /* 16-byte {u64 mask, u32 base, u32 aux} records of the compact 64-tree */
+    BLOKB_WORLD_BLOCKFIRSTLEAF = 1, /* u32 reference node index of leaf 0 of every non-empty 2^3 block */
+    BLOKB_WORLD_VOXELMAT = 2,       /* u16 (u32 if any id > 65535) material id per filled voxel */
+    BLOKB_WORLD_SUBCHUNKS = 3       /* blokb_subchunk records (worlds built by blokb_upload_voxels) */
+};
+int blokb_world_export(blokb_ctx* ctx, int which, void* host, size_t bytes, size_t* bytesOut);
 
 /* Frame in (binding 3). (Re)allocates the output images when the size changes. */
 int blokb_set_frame(blokb_ctx* ctx, const blokb_frame_ubo* frame);

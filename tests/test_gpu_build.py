@@ -1,0 +1,128 @@
+"""GPU: the device scene builder (blokb_upload_voxels) against the reference's own builder.
+
+The reference builds a chunk by replaying SvoTree::insertVoxel over the dense grid and packs chunks with
+packChunksToGpuSvo; its node numbering is part of the contract because hit records carry node indices. The device
+builder never materialises those arrays, so parity is checked on everything that depends on them:
+  * the compact world (nodes, blockFirstLeaf = reference node index of every leaf block, voxelMat) is byte-identical to
+    the one blokb_upload_world builds from the reference-format arrays;
+  * the SubChunkGpu records (nodeOffset, rootNodeIndex, nodeCount, bounds) are byte-identical to the reference's;
+  * hit records traced through either world are identical.
+Reference-format arrays come from oracle/_ref (the reference's ChunkManager + packChunksToGpuSvo, single-chunk worlds:
+its multi-chunk order is that of a std::unordered_map) and from blokb_worldgen_pack (the host restatement, chunks in
+(z, y, x) order, itself checked against the reference in tests/test_host.py)."""
+import numpy as np
+import pytest
+
+import blok_b200
+from blok_b200 import IMG_HIT, WORLD_BLOCKFIRSTLEAF, WORLD_NODES, WORLD_SUBCHUNKS, WORLD_VOXELMAT, BlokbError, Camera, WorldSvoGpu, scenes
+from tests.conftest import make_rays
+
+pytestmark = pytest.mark.gpu
+
+
+def _cloud(rng, n, lo, hi):
+    xyz = rng.integers(lo, hi, (n, 3)).astype(np.int32)
+    return xyz, rng.integers(1, 9, n).astype(np.uint32)
+
+
+def _cases():
+    rng = np.random.default_rng(7)
+    mats = scenes.default_materials(16)
+    out = {}
+    out["terrain96"] = scenes.terrain(96)
+    out["blob64"] = scenes.blob_mesh(64)
+    out["terrain320_multi_chunk"] = scenes.terrain(320)
+    xyz, m = _cloud(rng, 5000, -300, 300)
+    out["sparse_cloud_negative"] = (xyz, m, mats)
+    xyz, m = _cloud(rng, 40000, 0, 40)
+    out["dense_cloud_duplicates"] = (xyz, m, mats)  # 64 000 cells, 40 000 draws: many repeated voxels, last write wins
+    out["single_voxel"] = (np.array([[5, 6, 7]], np.int32), np.array([3], np.uint32), mats)
+    out["single_voxel_negative"] = (np.array([[-1, -1, -1]], np.int32), np.array([2], np.uint32), mats)
+    g = np.stack(np.meshgrid(np.arange(120, 136), np.arange(120, 136), np.arange(-8, 8), indexing="ij"), -1).reshape(-1, 3).astype(np.int32)
+    out["cube_across_8_chunks"] = (g, (1 + (g.sum(1) % 7)).astype(np.uint32), mats)
+    xyz, m = _cloud(rng, 3000, 0, 128)
+    out["wide_material_ids"] = (xyz, (m + 70000).astype(np.uint32), mats)
+    full = np.stack(np.meshgrid(np.arange(16), np.arange(16), np.arange(16), indexing="ij"), -1).reshape(-1, 3).astype(np.int32)
+    out["full_subchunk"] = (full + 32, np.ones(len(full), np.uint32), mats)
+    return out
+
+
+CASES = _cases()
+
+
+def _export(r):
+    return {k: r.world_export(k) for k in (WORLD_NODES, WORLD_BLOCKFIRSTLEAF, WORLD_VOXELMAT)}
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_device_build_equals_reference_numbering(renderer_factory, name):
+    xyz, mid, mats = CASES[name]
+    world = WorldSvoGpu.from_voxels(xyz, mid, mats)  # reference-format arrays (host restatement of the reference builder)
+    a = renderer_factory(64, 64)
+    a.add_world(world)
+    b = renderer_factory(64, 64)
+    b.add_voxels(xyz, mid, mats)
+    ea, eb = _export(a), _export(b)
+    for k in ea:
+        assert ea[k].shape == eb[k].shape, (name, k, ea[k].shape, eb[k].shape)
+        assert np.array_equal(ea[k].view(np.uint8), eb[k].view(np.uint8)), (name, k)
+    subs = b.world_export(WORLD_SUBCHUNKS)
+    assert np.array_equal(subs.view(np.uint8), world.globalSubChunks.view(np.uint8)), name
+    sa, sb = a.world_stats(), b.world_stats()
+    for key in ("nodes", "subChunks", "bricks", "blocks", "voxels", "compactBytes", "gridOrigin", "gridDim", "levels"):
+        assert sa[key] == sb[key], (name, key, sa[key], sb[key])
+    assert sb["nodes"] == len(world.globalNodes)
+    # and the traversal sees the same world
+    lo = xyz.min(0).astype(np.float32) - 20
+    hi = xyz.max(0).astype(np.float32) + 20
+    rays = make_rays(np.random.default_rng(1), 4000, lo, hi)
+    ha, hb = a.trace_rays(rays), b.trace_rays(rays)
+    assert np.array_equal(ha.view(np.uint8), hb.view(np.uint8)), name
+
+
+@pytest.mark.parametrize("name", ["terrain96", "blob64", "dense_cloud_duplicates", "single_voxel", "full_subchunk"])
+def test_device_build_equals_the_reference_builder(renderer_factory, reflib, name):
+    """Single-chunk worlds through the reference's own ChunkManager + packChunksToGpuSvo (oracle/_ref)."""
+    xyz, mid, mats = CASES[name]
+    assert xyz.min() >= 0 and xyz.max() < 128
+    # the reference keeps the last write too (setVoxelMaterial overwrites the dense cell)
+    sc = reflib.scene_from_voxels(xyz, mid, mats)
+    a = renderer_factory(64, 64)
+    a.add_world(WorldSvoGpu(sc.nodes, sc.subs, sc.mats))
+    b = renderer_factory(64, 64)
+    b.add_voxels(xyz, mid, mats)
+    ea, eb = _export(a), _export(b)
+    for k in ea:
+        assert np.array_equal(ea[k].view(np.uint8), eb[k].view(np.uint8)), (name, k)
+    assert np.array_equal(b.world_export(WORLD_SUBCHUNKS).view(np.uint8), sc.subs.view(np.uint8))
+    assert b.world_stats()["nodes"] == len(sc.nodes)
+
+
+def test_empty_and_bad_input(renderer_factory):
+    r = renderer_factory(32, 32)
+    mats = scenes.default_materials(4)
+    r.add_voxels(np.zeros((0, 3), np.int32), np.zeros(0, np.uint32), mats)
+    st = r.world_stats()
+    assert st["voxels"] == 0 and st["subChunks"] == 0
+    r.trace_primary(Camera((0, 0, -10), 90.0, 0.0).frame(32, 32, 0, 1))
+    assert np.all(r.readback(IMG_HIT)["node"] == 0xFFFFFFFF)
+    with pytest.raises(BlokbError) as e:
+        r.add_voxels(np.array([[1 << 21, 0, 0]], np.int32), np.array([1], np.uint32), mats)
+    assert e.value.code == -3
+    # a failed build leaves the previous world in place
+    assert r.world_stats()["voxels"] == 0
+    r.add_voxels(np.array([[3, 3, 3]], np.int32), np.array([1], np.uint32), mats)  # update_world: replaces it
+    assert r.world_stats()["voxels"] == 1
+
+
+def test_rendered_frame_identical(renderer_factory):
+    xyz, mid, mats = CASES["terrain96"]
+    a = renderer_factory(96, 64)
+    a.add_world(WorldSvoGpu.from_voxels(xyz, mid, mats))
+    b = renderer_factory(96, 64)
+    b.add_voxels(xyz, mid, mats)
+    f = Camera((48, 60, -20), 90.0, -25.0).frame(96, 64, 2, 2)
+    for r in (a, b):
+        r.render(f)
+    for img in (blok_b200.IMG_COLOR, blok_b200.IMG_WORLDPOS, blok_b200.IMG_NORMALROUGH, blok_b200.IMG_ALBEDOMETAL):
+        assert np.array_equal(a.readback(img).view(np.uint8), b.readback(img).view(np.uint8))
