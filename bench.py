@@ -411,6 +411,68 @@ def run_ours(args):
     return measure, dict(rank=rank, world_size=world_size, local=local, dev=dev, barrier=barrier, torch=torch, dist=dist)
 
 
+def extra_device_build(name, r, env):
+    """Scene upload on the device (blokb_upload_voxels) beside the host path the headline used, and the
+    full-size parity property: both leave byte-identical compact arrays (incl. the reference node index of every leaf block)."""
+    import hashlib
+    import blok_b200
+    from blok_b200 import WORLD_BLOCKFIRSTLEAF, WORLD_NODES, WORLD_VOXELMAT, workloads
+    xyz, mid, mats = workloads.voxels(name)
+    b = blok_b200.Renderer(64, 64, env["local"])
+    b.add_voxels(xyz[:4096], mid[:4096], mats)
+    ts = []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        b.add_voxels(xyz, mid, mats)
+        ts.append(time.perf_counter() - t0)
+    same = all(hashlib.sha256(r.world_export(k).tobytes()).digest() == hashlib.sha256(b.world_export(k).tobytes()).digest()
+               for k in (WORLD_NODES, WORLD_BLOCKFIRSTLEAF, WORLD_VOXELMAT))
+    st = b.world_stats()
+    b.close()
+    return {"what": "blokb_upload_voxels: voxel list H2D (pageable) + sort/dedupe + compact 64-tree + reference node numbering on the GPU",
+            "voxels": int(len(mid)), "wall_ms": min(ts) * 1e3, "input_bytes": int(xyz.nbytes + mid.nbytes),
+            "identical_to_host_path": bool(same), "nodes_reference_format": int(st["nodes"])}
+
+
+def extra_full_frame(name, r, env):
+    """The reference's whole frame (Renderer::render, blok/src/renderer_draw.cpp): raygen at the reference's 8 spp, Denoiser::denoise,
+    PostProcess::process, over a slow dolly so that both temporal passes are live. Per stage, CUDA events on the launching stream."""
+    import blok_b200
+    from blok_b200 import Camera, PostSettings, workloads
+    torch = env["torch"]
+    wl = workloads.WORKLOADS[name]
+    W, H = wl["width"], wl["height"]
+    base = workloads.camera_for(name)
+    frames = 8
+    cams = [Camera((base.position[0] + 0.5 * k, base.position[1], base.position[2] + 0.25 * k), base.yaw + 0.02 * k, base.pitch) for k in range(frames)]
+    st = PostSettings()
+    stream = torch.cuda.Stream()
+    sp = stream.cuda_stream
+    names = ("raygen_8spp", "denoise", "postprocess")
+    times = {n: [] for n in names}
+    l0 = r.launch_count()
+    for k, cam in enumerate(cams):
+        r.set_frame(cam.frame(W, H, k, 8, prev=cams[k - 1] if k else None, jitter_index=k))
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        ev[0].record(stream)
+        r.render(stream=sp)
+        ev[1].record(stream)
+        r.denoise(st, stream=sp)
+        ev[2].record(stream)
+        r.postprocess(st, stream=sp)
+        ev[3].record(stream)
+        stream.synchronize()
+        r.end_frame()
+        if k >= 2:
+            for i, n in enumerate(names):
+                times[n].append(ev[i].elapsed_time(ev[i + 1]))
+    out = {n + "_ms": float(np.median(times[n])) for n in names}
+    out["frame_ms"] = sum(out.values())
+    out["launches_per_frame"] = (r.launch_count() - l0) // frames
+    out["what"] = f"{W}x{H}, 8 spp raygen + temporal/variance + 4 a-trous + TAA/tonemap + sharpen (reference defaults)"
+    return out
+
+
 _REAL_STDOUT = None
 
 
@@ -494,6 +556,12 @@ def main():
     if parity:
         extras["parity"] = parity
     e2e = m.get("e2e")
+    if rank == 0 and world_size == 1 and not args.no_extras:
+        for key, fn in (("device_build", extra_device_build), ("frame", extra_full_frame)):
+            try:
+                extras[key] = fn(name, r, env)
+            except Exception as ex:  # an extra must never cost the headline line
+                extras[key] = {"error": repr(ex)}
     r.close()
     if not args.no_extras:
         for other, st, wu in (("c2", 20, 3), ("c4", 2, 1)):

@@ -32,10 +32,15 @@ WORKLOADS = {
 }
 
 
+def voxels(name: str):
+    """(xyz, material ids, materials) of the workload's voxel set — what ChunkManager::setVoxelMaterial would be fed."""
+    w = WORKLOADS[name]
+    return getattr(scenes, w["scene"])(w["N"])
+
+
 def build_world(name: str) -> WorldSvoGpu:
     """Voxel set of the workload -> the reference's upload arrays (host C++ restatement of the reference builder)."""
-    w = WORKLOADS[name]
-    xyz, mid, mats = getattr(scenes, w["scene"])(w["N"])
+    xyz, mid, mats = voxels(name)
     return WorldSvoGpu.from_voxels(xyz, mid, mats)
 
 
