@@ -115,7 +115,8 @@ EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_wo
            "blokb_worldgen_pack", "blokb_worldgen_counts", "blokb_worldgen_copy", "blokb_worldgen_nodes", "blokb_worldgen_subs",
            "blokb_worldgen_free", "blokb_pipeline_create", "blokb_pipeline_submit", "blokb_pipeline_wait", "blokb_pipeline_drain",
            "blokb_pipeline_destroy", "blokb_host_alloc", "blokb_host_free", "blokb_post_settings_default", "blokb_denoise",
-           "blokb_postprocess", "blokb_end_frame", "blokb_reset_history", "blokb_write_image", "blokb_upload_voxels", "blokb_world_export"]
+           "blokb_postprocess", "blokb_end_frame", "blokb_reset_history", "blokb_write_image", "blokb_upload_voxels", "blokb_world_export", "blokb_vox_load", "blokb_vox_parse",
+           "blokb_vox_counts", "blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free", "blokb_vox_last_error", "blokb_upload_vox"]
 
 _lib = None
 
@@ -138,6 +139,16 @@ def load_library():
     L.blokb_set_frame.argtypes = [_vp, C.POINTER(FrameUBO)]
     L.blokb_upload_voxels.argtypes = [_vp, _vp, _vp, C.c_size_t, _vp, C.c_size_t]
     L.blokb_world_export.argtypes = [_vp, C.c_int, _vp, C.c_size_t, C.POINTER(C.c_size_t)]
+    L.blokb_vox_load.argtypes = [C.c_char_p, C.c_uint32, _vp, C.POINTER(_vp)]
+    L.blokb_vox_parse.argtypes = [_vp, C.c_size_t, C.c_uint32, _vp, C.POINTER(_vp)]
+    L.blokb_vox_counts.argtypes = [_vp, _vp, _vp, _vp, _vp]
+    L.blokb_vox_counts.restype = None
+    for f, t in (("blokb_vox_xyz", _vp), ("blokb_vox_material_ids", _vp), ("blokb_vox_materials", _vp), ("blokb_vox_last_error", C.c_char_p)):
+        getattr(L, f).restype = t
+    for f in ("blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free"):
+        getattr(L, f).argtypes = [_vp]
+    L.blokb_vox_free.restype = None
+    L.blokb_upload_vox.argtypes = [_vp, C.c_char_p, C.c_uint32, _vp]
     L.blokb_camera_frame.argtypes = [C.POINTER(CameraC), C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(FrameUBO)]
     L.blokb_camera_frame_seq.argtypes = [C.POINTER(CameraC), C.POINTER(CameraC), C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int32,
                                          C.POINTER(FrameUBO)]
@@ -222,6 +233,31 @@ class WorldSvoGpu:
         return WorldSvoGpu(nodes, subs, materials)
 
 
+def load_vox(source, model_index=0, offset=(0.0, 0.0, 0.0)):
+    """loadVoxFile + importVoxMaterials + importVoxToChunks (blok/src/vox_loader.cpp) as data: returns (xyz (n,3) i32, material ids
+    (n,) u32, materials (256,) MAT_DT, info dict). source: a path or the file's bytes. Host only."""
+    L = load_library()
+    off = (C.c_float * 3)(*[float(v) for v in offset])
+    h = _vp()
+    if isinstance(source, (bytes, bytearray)):
+        buf = (C.c_char * len(source)).from_buffer_copy(bytes(source))
+        rc = L.blokb_vox_parse(buf, len(source), model_index, off, C.byref(h))
+    else:
+        rc = L.blokb_vox_load(str(source).encode(), model_index, off, C.byref(h))
+    if rc != 0:
+        raise BlokbError(rc, L.blokb_vox_last_error().decode())
+    try:
+        n, nm = C.c_uint64(), C.c_uint64()
+        nmod, size = C.c_uint32(), (C.c_uint32 * 3)()
+        L.blokb_vox_counts(h, C.byref(n), C.byref(nm), C.byref(nmod), size)
+        xyz = np.ctypeslib.as_array(C.cast(L.blokb_vox_xyz(h), C.POINTER(C.c_int32)), (n.value, 3)).copy() if n.value else np.zeros((0, 3), np.int32)
+        ids = np.ctypeslib.as_array(C.cast(L.blokb_vox_material_ids(h), C.POINTER(C.c_uint32)), (n.value,)).copy() if n.value else np.zeros(0, np.uint32)
+        mats = np.frombuffer(C.string_at(L.blokb_vox_materials(h), nm.value * 32), dtype=MAT_DT).copy()
+    finally:
+        L.blokb_vox_free(h)
+    return xyz, ids, mats, {"models": int(nmod.value), "size": tuple(int(v) for v in size)}
+
+
 class Camera:
     """blok::Camera (camera.hpp:15-59)."""
 
@@ -281,6 +317,11 @@ class Renderer:
         mats = np.ascontiguousarray(materials, dtype=MAT_DT)
         assert len(mid) == len(xyz)
         _ck(self.L.blokb_upload_voxels(self._ctx, _ptr(xyz), _ptr(mid), len(mid), _ptr(mats), len(mats)))
+
+    def add_vox(self, path, model_index=0, offset=(0.0, 0.0, 0.0)):
+        """loadAndImportVox + rebuild + pack + addWorld (blok/src/app.cpp:100-126): the file's voxels go straight to the device builder."""
+        off = (C.c_float * 3)(*[float(v) for v in offset])
+        _ck(self.L.blokb_upload_vox(self._ctx, str(path).encode(), model_index, off))
 
     def world_export(self, which: int) -> np.ndarray:
         """Device-resident world array -> numpy (WORLD_NODES: (n,) {mask,base,aux}; WORLD_BLOCKFIRSTLEAF: u32; WORLD_VOXELMAT: raw

@@ -255,6 +255,17 @@ int blokb_upload_voxels(blokb_ctx* c, const int32_t* xyz, const uint32_t* materi
     return 0;
 }
 
+int blokb_upload_vox(blokb_ctx* c, const char* path, uint32_t modelIndex, const float* offset3) {
+    if (!c || !path) return fail(BLOKB_E_ARG, "null argument");
+    blokb_vox* v = nullptr;
+    if (int rc = blokb_vox_load(path, modelIndex, offset3, &v)) return fail(rc, blokb_vox_last_error());
+    uint64_t n = 0, nm = 0;
+    blokb_vox_counts(v, &n, &nm, nullptr, nullptr);
+    const int rc = blokb_upload_voxels(c, blokb_vox_xyz(v), blokb_vox_material_ids(v), (size_t)n, blokb_vox_materials(v), (size_t)nm);
+    blokb_vox_free(v);
+    return rc;
+}
+
 // Copies one of the device-resident world arrays to the host (parity checks, tools). bytes must match exactly; pass
 // host == NULL to query the size through *bytesOut.
 int blokb_world_export(blokb_ctx* c, int which, void* host, size_t bytes, size_t* bytesOut) {

@@ -171,6 +171,23 @@ int blokb_world_stats_get(blokb_ctx* ctx, blokb_world_stats* out);
  * coordinates (|coordinate| < 2^20), materialId: n x uint32; host pointers, borrowed for the call. */
 int blokb_upload_voxels(blokb_ctx* ctx, const int32_t* xyz, const uint32_t* materialId, size_t n, const blokb_material* materials,
                         size_t nMaterials);
+/* MagicaVoxel .vox import: loadVoxFile + importVoxMaterials + importVoxToChunks of the reference
+ * (blok/src/vox_loader.cpp:151-430) restated as "file -> voxel list + material table", the inputs of blokb_upload_voxels.
+ * Material id i = palette entry i (1..255) and id 0 = the library's default grey, as in a fresh MaterialLibrary
+ * (material.cpp:19-29; MaterialGpu::pack, material.hpp:95-111); world voxel = floor(offset + (x, z, y)) (VOX z is up).
+ * Host only. offset may be NULL (= 0,0,0). Errors: code < 0 and blokb_vox_last_error(). */
+typedef struct blokb_vox blokb_vox;
+int blokb_vox_load(const char* path, uint32_t modelIndex, const float* offset3, blokb_vox** out);
+int blokb_vox_parse(const void* fileBytes, size_t n, uint32_t modelIndex, const float* offset3, blokb_vox** out);
+void blokb_vox_counts(const blokb_vox* v, uint64_t* nVoxels, uint64_t* nMaterials, uint32_t* nModels, uint32_t* modelSize3);
+const int32_t* blokb_vox_xyz(const blokb_vox* v);               /* nVoxels x int32[3] */
+const uint32_t* blokb_vox_material_ids(const blokb_vox* v);     /* nVoxels */
+const blokb_material* blokb_vox_materials(const blokb_vox* v);  /* 256 entries */
+void blokb_vox_free(blokb_vox* v);
+const char* blokb_vox_last_error(void);
+/* loadAndImportVox + rebuildDirtyChunks + packChunksToGpuSvo + addWorld (blok/src/app.cpp:100-126) in one call: the file's voxels
+ * go straight to the device builder. */
+int blokb_upload_vox(blokb_ctx* ctx, const char* path, uint32_t modelIndex, const float* offset3);
 /* Device-resident world arrays -> host (parity checks, tools). host == NULL: only *bytesOut is set. */
 enum blokb_world_array {
     BLOKB_WORLD_NODES = 0,          /* 16-byte {u64 mask, u32 base, u32 aux} records of the compact 64-tree */

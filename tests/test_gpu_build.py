@@ -126,3 +126,27 @@ def test_rendered_frame_identical(renderer_factory):
         r.render(f)
     for img in (blok_b200.IMG_COLOR, blok_b200.IMG_WORLDPOS, blok_b200.IMG_NORMALROUGH, blok_b200.IMG_ALBEDOMETAL):
         assert np.array_equal(a.readback(img).view(np.uint8), b.readback(img).view(np.uint8))
+
+
+def test_vox_file_straight_to_the_device(renderer_factory):
+    """blokb_upload_vox on the committed synthetic file == blokb_upload_world of what the reference's loader + builder made of it
+    (tests/golden/vox/synth_ref.npz, from oracle/_ref), for both models, incl. a world offset."""
+    import os
+    here = os.path.dirname(os.path.abspath(__file__))
+    z = np.load(os.path.join(here, "golden", "vox", "synth_ref.npz"))
+    for tag, model in (("m0", 0), ("m1", 1)):
+        a = renderer_factory(64, 64)
+        a.add_world(WorldSvoGpu(z[tag + "_nodes"], z[tag + "_subs"], z[tag + "_mats"]))
+        b = renderer_factory(64, 64)
+        b.add_vox(os.path.join(here, "golden", "vox", "synth.vox"), model, tuple(z[tag + "_offset"]))
+        ea, eb = _export(a), _export(b)
+        for k in ea:
+            assert np.array_equal(ea[k].view(np.uint8), eb[k].view(np.uint8)), (tag, k)
+        assert np.array_equal(b.world_export(WORLD_SUBCHUNKS).view(np.uint8), z[tag + "_subs"].view(np.uint8))
+        f = Camera((-30, 40, -30), 45.0, -25.0).frame(64, 64, 1, 2)
+        for r in (a, b):
+            r.render(f)
+        for img in (blok_b200.IMG_COLOR, blok_b200.IMG_ALBEDOMETAL):  # materials (MATL: metal / glass / emissive) reach the shading
+            assert np.array_equal(a.readback(img).view(np.uint8), b.readback(img).view(np.uint8)), (tag, img)
+    with pytest.raises(BlokbError):
+        b.add_vox(os.path.join(here, "golden", "vox", "missing.vox"))
