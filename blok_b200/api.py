@@ -85,6 +85,11 @@ class PostSettings(C.Structure):
             setattr(self, k, v)
 
 
+class DenseChunkC(C.Structure):
+    """blokb_dense_chunk: one blok::Chunk (chunk.hpp:33-42) — index + its density / materialIds arrays (128^3 each)."""
+    _fields_ = [("cx", C.c_int32), ("cy", C.c_int32), ("cz", C.c_int32), ("density", _vp), ("materialIds", _vp)]
+
+
 class CameraC(C.Structure):
     _fields_ = [("position", C.c_float * 3), ("yaw", C.c_float), ("pitch", C.c_float), ("fov", C.c_float)]
 
@@ -115,7 +120,7 @@ EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_wo
            "blokb_worldgen_pack", "blokb_worldgen_counts", "blokb_worldgen_copy", "blokb_worldgen_nodes", "blokb_worldgen_subs",
            "blokb_worldgen_free", "blokb_pipeline_create", "blokb_pipeline_submit", "blokb_pipeline_wait", "blokb_pipeline_drain",
            "blokb_pipeline_destroy", "blokb_host_alloc", "blokb_host_free", "blokb_post_settings_default", "blokb_denoise",
-           "blokb_postprocess", "blokb_end_frame", "blokb_reset_history", "blokb_write_image", "blokb_upload_voxels", "blokb_world_export", "blokb_vox_load", "blokb_vox_parse",
+           "blokb_postprocess", "blokb_end_frame", "blokb_reset_history", "blokb_write_image", "blokb_upload_voxels", "blokb_upload_dense", "blokb_world_export", "blokb_vox_load", "blokb_vox_parse",
            "blokb_vox_counts", "blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free", "blokb_vox_last_error", "blokb_upload_vox"]
 
 _lib = None
@@ -139,6 +144,7 @@ def load_library():
     L.blokb_set_frame.argtypes = [_vp, C.POINTER(FrameUBO)]
     L.blokb_upload_voxels.argtypes = [_vp, _vp, _vp, C.c_size_t, _vp, C.c_size_t]
     L.blokb_world_export.argtypes = [_vp, C.c_int, _vp, C.c_size_t, C.POINTER(C.c_size_t)]
+    L.blokb_upload_dense.argtypes = [_vp, _vp, C.c_size_t, _vp, C.c_size_t]
     L.blokb_vox_load.argtypes = [C.c_char_p, C.c_uint32, _vp, C.POINTER(_vp)]
     L.blokb_vox_parse.argtypes = [_vp, C.c_size_t, C.c_uint32, _vp, C.POINTER(_vp)]
     L.blokb_vox_counts.argtypes = [_vp, _vp, _vp, _vp, _vp]
@@ -317,6 +323,20 @@ class Renderer:
         mats = np.ascontiguousarray(materials, dtype=MAT_DT)
         assert len(mid) == len(xyz)
         _ck(self.L.blokb_upload_voxels(self._ctx, _ptr(xyz), _ptr(mid), len(mid), _ptr(mats), len(mats)))
+
+    def add_dense(self, chunks, materials):
+        """chunks: {(cx, cy, cz): (density f32[128^3], materialIds u32[128^3])} — ChunkManager::chunks as the reference holds them
+        (index x + 128 y + 16384 z). rebuildDirtyChunks + packChunksToGpuSvo + addWorld, on the device."""
+        keep = []
+        arr = (DenseChunkC * len(chunks))()
+        for k, ((cx, cy, cz), (den, ids)) in enumerate(chunks.items()):
+            den = np.ascontiguousarray(den, np.float32).reshape(-1)
+            ids = np.ascontiguousarray(ids, np.uint32).reshape(-1)
+            assert den.size == 128 ** 3 and ids.size == 128 ** 3
+            keep += [den, ids]
+            arr[k] = DenseChunkC(cx, cy, cz, den.ctypes.data, ids.ctypes.data)
+        mats = np.ascontiguousarray(materials, dtype=MAT_DT)
+        _ck(self.L.blokb_upload_dense(self._ctx, C.cast(arr, _vp), len(chunks), _ptr(mats), len(mats)))
 
     def add_vox(self, path, model_index=0, offset=(0.0, 0.0, 0.0)):
         """loadAndImportVox + rebuild + pack + addWorld (blok/src/app.cpp:100-126): the file's voxels go straight to the device builder."""

@@ -190,6 +190,9 @@ int blokb_upload_world(blokb_ctx* c, const blokb_svo_node* nodes, size_t nNodes,
 
 // Scene in, built on the device: ChunkManager::setVoxelMaterial per voxel + rebuildDirtyChunks +
 // packChunksToGpuSvo + uploadSvoBuffers in one call, without the reference-format node arrays ever existing.
+static int finish_device_build(blokb_ctx* c, build::DeviceBuild& B, const blokb_material* materials, size_t nMaterials,
+                               std::chrono::steady_clock::time_point t0);
+
 int blokb_upload_voxels(blokb_ctx* c, const int32_t* xyz, const uint32_t* materialId, size_t n, const blokb_material* materials, size_t nMaterials) {
     if (!c) return fail(BLOKB_E_ARG, "ctx is null");
     if ((n && (!xyz || !materialId)) || (nMaterials && !materials)) return fail(BLOKB_E_ARG, "null array with non-zero count");
@@ -200,6 +203,26 @@ int blokb_upload_voxels(blokb_ctx* c, const int32_t* xyz, const uint32_t* materi
     std::string err;
     int rc = build::from_voxels(xyz, materialId, n, c->stream, B, err);
     if (rc) return fail(rc, err);
+    return finish_device_build(c, B, materials, nMaterials, t0);
+}
+
+int blokb_upload_dense(blokb_ctx* c, const blokb_dense_chunk* chunks, size_t nChunks, const blokb_material* materials, size_t nMaterials) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    if ((nChunks && !chunks) || (nMaterials && !materials)) return fail(BLOKB_E_ARG, "null array with non-zero count");
+    CK(cudaSetDevice(c->device));
+    const auto t0 = std::chrono::steady_clock::now();
+    CK(cudaStreamSynchronize(c->stream));
+    build::DeviceBuild B;
+    std::string err;
+    int rc = build::from_dense(chunks, nChunks, c->stream, B, err);
+    if (rc) return fail(rc, err);
+    return finish_device_build(c, B, materials, nMaterials, t0);
+}
+
+static int finish_device_build(blokb_ctx* c, build::DeviceBuild& B, const blokb_material* materials, size_t nMaterials,
+                               std::chrono::steady_clock::time_point t0) {
+    std::string err;
+    int rc = 0;
     HostWorld hw;
     hw.subs = B.recs;
     uint64_t brickStart = 0;

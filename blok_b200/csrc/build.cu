@@ -227,13 +227,14 @@ __global__ void k_row_counts(const unsigned long long* __restrict__ brickMask, c
 // rowBase = exclusive scan of rowCnt over all chunks' rows (global). Block ranks -> blockFirstLeaf, brick ranks, levels 0..4.
 __global__ void k_ranks(const unsigned long long* __restrict__ brickMask, const uint32_t* __restrict__ first, uint32_t nRows,
                         const uint32_t* __restrict__ rowBase, const uint32_t* __restrict__ brickIdx, const Node* __restrict__ bricks,
-                        uint32_t* __restrict__ blockFirstLeaf, uint32_t* __restrict__ rankSmall) {
+                        uint32_t* __restrict__ blockFirstLeaf, uint32_t* __restrict__ rankSmall, const uint32_t* __restrict__ extra) {
     const uint32_t g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (g >= nRows) return;
     const uint32_t c = g >> 12, bz = (g >> 6) & 63u, by = g & 63u;
     const uint32_t chunkBase = rowBase[size_t(c) * 16384];  // interior nodes of all earlier chunks
-    const uint32_t nodeOffset = c + 8u * chunkBase;          // sum over earlier chunks of (1 + 8 * interior)
+    // sum over earlier chunks of (1 + 8 * interior); extra[c] = all-empty chunks (1 root node each) the reference packs before c
+    const uint32_t nodeOffset = c + (extra ? extra[c] : 0u) + 8u * chunkBase;
     BlockInfo b[2];
     uint64_t packed = 0;  // four 16-bit per-class counters
 #pragma unroll
@@ -271,7 +272,7 @@ __global__ void k_ranks(const unsigned long long* __restrict__ brickMask, const 
 // SubChunkGpu records (chunk_manager.cpp:255-303) for the non-empty 16^3 regions, in (chunk, sz, sy, sx) order.
 __global__ void k_sub_records(uint32_t nSubDense, const uint32_t* __restrict__ flag, const uint32_t* __restrict__ primIdx,
                               const uint64_t* __restrict__ chunkKey, const uint32_t* __restrict__ rowBase, const uint32_t* __restrict__ rankSmall,
-                              uint32_t nChunks, uint32_t totalInterior, blokb_subchunk* __restrict__ subs) {
+                              uint32_t nChunks, uint32_t totalInterior, blokb_subchunk* __restrict__ subs, const uint32_t* __restrict__ extra) {
     const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= nSubDense || !flag[g]) return;
     const uint32_t c = g >> 9, s = g & 511u, sx = s & 7u, sy = (s >> 3) & 7u, sz = s >> 6;
@@ -281,7 +282,7 @@ __global__ void k_sub_records(uint32_t nSubDense, const uint32_t* __restrict__ f
     const uint64_t ck = chunkKey[c];
     const int cx = int(ck & 16383u) - kBias, cy = int((ck >> 14) & 16383u) - kBias, cz = int((ck >> 28) & 16383u) - kBias;
     blokb_subchunk o;
-    o.nodeOffset = c + 8u * chunkBase;
+    o.nodeOffset = c + (extra ? extra[c] : 0u) + 8u * chunkBase;
     o.rootNodeIndex = 1u + 8u * parent + ((sx & 1) | (sy & 1) << 1 | (sz & 1) << 2);
     o.nodeCount = 1u + 8u * (nextBase - chunkBase);
     o.startDepth = 3u;
@@ -326,7 +327,8 @@ void release(DeviceBuild& b) {
 #define BNULL(p) \
     if (!(p)) { err = std::string("cudaMalloc: ") + cudaGetErrorString(A.last); release(out); return BLOKB_E_CUDA; }
 
-int from_voxels(const int32_t* hXyz, const uint32_t* hMat, size_t n, cudaStream_t st, DeviceBuild& out, std::string& err) {
+int from_device_voxels(const int32_t* dXyz, const uint32_t* dMat, size_t n, cudaStream_t st, DeviceBuild& out, std::string& err,
+                       const std::vector<uint64_t>* emptyChunkKeys) {
     out = DeviceBuild{};
     if (n == 0) return 0;
     if (n > 0xFFFFFFF0ull) { err = "too many voxels"; return BLOKB_E_UNSUPPORTED; }
@@ -337,8 +339,6 @@ int from_voxels(const int32_t* hXyz, const uint32_t* hMat, size_t n, cudaStream_
     constexpr unsigned BS = 256;
 
     // ---- keys, stable sort, last-write-wins dedupe -----------------------------------------------------------------
-    int32_t* dXyz = A.get<int32_t>(3 * n); BNULL(dXyz)
-    uint32_t* dMat = A.get<uint32_t>(n); BNULL(dMat)
     uint64_t* keysA = A.get<uint64_t>(n); BNULL(keysA)
     uint64_t* keysB = A.get<uint64_t>(n); BNULL(keysB)
     uint32_t* idxA = A.get<uint32_t>(n); BNULL(idxA)
@@ -346,8 +346,6 @@ int from_voxels(const int32_t* hXyz, const uint32_t* hMat, size_t n, cudaStream_
     uint8_t* keep = A.get<uint8_t>(n); BNULL(keep)
     int* dScalars = A.get<int>(8); BNULL(dScalars)  // [0] range error, [1] max material, [2] unique count
     BCK(cudaMemsetAsync(dScalars, 0, 8 * sizeof(int), st));
-    BCK(cudaMemcpyAsync(dXyz, hXyz, 3 * n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
-    BCK(cudaMemcpyAsync(dMat, hMat, n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
     BCK(cudaEventRecord(ev[0], st));
     k_make_keys<<<blocks_for(n, BS), BS, 0, st>>>(dXyz, n, keysA, idxA, dScalars);
     size_t tmpBytes = 0, t2 = 0;
@@ -437,11 +435,24 @@ int from_voxels(const int32_t* hXyz, const uint32_t* hMat, size_t n, cudaStream_
     BCK(cudaMemcpyAsync(&lastRowBase, rowBase + (nRows - 1), 4, cudaMemcpyDeviceToHost, st));
     BCK(cudaStreamSynchronize(st));
     const uint64_t totalInterior = uint64_t(lastRowCnt) + lastRowBase;
-    out.refNodes = uint64_t(nChunks) + 8ull * totalInterior;
+    uint32_t* dExtra = nullptr;
+    const size_t nEmpty = emptyChunkKeys ? emptyChunkKeys->size() : 0;
+    if (nEmpty) {  // the reference packs an all-empty chunk as a single root node: later chunks' node offsets move up by one each
+        std::vector<uint64_t> ck(nChunks);
+        BCK(cudaMemcpyAsync(ck.data(), chunkKey, size_t(nChunks) * 8, cudaMemcpyDeviceToHost, st));
+        BCK(cudaStreamSynchronize(st));
+        std::vector<uint32_t> extra(nChunks);
+        for (uint32_t c = 0; c < nChunks; c++)
+            extra[c] = uint32_t(std::lower_bound(emptyChunkKeys->begin(), emptyChunkKeys->end(), ck[c]) - emptyChunkKeys->begin());
+        dExtra = A.get<uint32_t>(nChunks); BNULL(dExtra)
+        BCK(cudaMemcpyAsync(dExtra, extra.data(), size_t(nChunks) * 4, cudaMemcpyHostToDevice, st));
+        BCK(cudaStreamSynchronize(st));
+    }
+    out.refNodes = uint64_t(nChunks) + nEmpty + 8ull * totalInterior;
     if (out.refNodes > 0xFFFFFFF0ull) { err = "world exceeds the reference's 32-bit node indices"; release(out); return BLOKB_E_UNSUPPORTED; }
-    k_ranks<<<blocks_for(nRowsW * 32, BS), BS, 0, st>>>(brickMask, first, (uint32_t)nRowsW, rowBase, brickIdx, out.bricks, out.blockFirstLeaf, rankSmall);
+    k_ranks<<<blocks_for(nRowsW * 32, BS), BS, 0, st>>>(brickMask, first, (uint32_t)nRowsW, rowBase, brickIdx, out.bricks, out.blockFirstLeaf, rankSmall, dExtra);
     k_sub_records<<<blocks_for(nSubDense, BS), BS, 0, st>>>((uint32_t)nSubDense, flag, primIdx, chunkKey, rowBase, rankSmall, nChunks,
-                                                            (uint32_t)totalInterior, out.dSubs);
+                                                            (uint32_t)totalInterior, out.dSubs, dExtra);
     BCK(cudaEventRecord(ev[2], st));
     out.subs.resize(out.nSubs);
     out.recs.resize(out.nSubs);
@@ -454,6 +465,76 @@ int from_voxels(const int32_t* hXyz, const uint32_t* hMat, size_t n, cudaStream_
     cudaEventElapsedTime(&out.sortMs, ev[0], ev[1]);
     cudaEventElapsedTime(&out.buildMs, ev[1], ev[2]);
     return 0;
+}
+
+int from_voxels(const int32_t* hXyz, const uint32_t* hMat, size_t n, cudaStream_t st, DeviceBuild& out, std::string& err) {
+    out = DeviceBuild{};
+    if (n == 0) return 0;
+    Arena A;
+    int32_t* dXyz = A.get<int32_t>(3 * n); BNULL(dXyz)
+    uint32_t* dMat = A.get<uint32_t>(n); BNULL(dMat)
+    BCK(cudaMemcpyAsync(dXyz, hXyz, 3 * n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    BCK(cudaMemcpyAsync(dMat, hMat, n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    return from_device_voxels(dXyz, dMat, n, st, out, err, nullptr);  // synchronises the stream before it returns
+}
+
+namespace {
+// Dense chunk (Chunk::density / materialIds, x + y*C + z*C*C, chunk.hpp:33-42) -> voxel list entries for density > 0
+// (buildSvoFromDensity's test, chunk_manager.cpp:112-116). Order is irrelevant: the builder sorts.
+__global__ void k_dense_emit(const float* __restrict__ density, const uint32_t* __restrict__ ids, int cx, int cy, int cz, int32_t* __restrict__ xyz,
+                             uint32_t* __restrict__ mat, unsigned long long* __restrict__ counter) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;  // 128^3 cells
+    const bool filled = density[t] > 0.0f;
+    const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, filled);
+    if (!ballot) return;
+    const int lane = threadIdx.x & 31;
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(counter, (unsigned long long)__popc(ballot));
+    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+    if (filled) {
+        const size_t o = size_t(base) + __popc(ballot & ((1u << lane) - 1u));
+        xyz[3 * o] = cx * 128 + int(t & 127u); xyz[3 * o + 1] = cy * 128 + int((t >> 7) & 127u); xyz[3 * o + 2] = cz * 128 + int(t >> 14);
+        mat[o] = ids[t];
+    }
+}
+}  // namespace
+
+int from_dense(const blokb_dense_chunk* chunks, size_t nChunks, cudaStream_t st, DeviceBuild& out, std::string& err) {
+    out = DeviceBuild{};
+    constexpr size_t kCells = size_t(128) * 128 * 128;
+    size_t n = 0;
+    std::vector<uint64_t> emptyKeys;
+    for (size_t c = 0; c < nChunks; c++) {
+        if (!chunks[c].density || !chunks[c].materialIds) { err = "dense chunk " + std::to_string(c) + ": null array"; return BLOKB_E_ARG; }
+        for (size_t d = 0; d < c; d++)
+            if (chunks[d].cx == chunks[c].cx && chunks[d].cy == chunks[c].cy && chunks[d].cz == chunks[c].cz) { err = "dense chunk listed twice"; return BLOKB_E_ARG; }
+        const float* dn = chunks[c].density;
+        size_t k = 0;
+        for (size_t i = 0; i < kCells; i++) k += dn[i] > 0.0f;
+        n += k;
+        const int cx = chunks[c].cx, cy = chunks[c].cy, cz = chunks[c].cz;
+        if (cx < -kBias || cx >= kBias || cy < -kBias || cy >= kBias || cz < -kBias || cz >= kBias) { err = "chunk index outside [-8192, 8191]"; return BLOKB_E_UNSUPPORTED; }
+        if (k == 0) emptyKeys.push_back(uint64_t(cz + kBias) << 28 | uint64_t(cy + kBias) << 14 | uint64_t(cx + kBias));
+    }
+    std::sort(emptyKeys.begin(), emptyKeys.end());
+    if (n == 0) { out.refNodes = emptyKeys.size(); return 0; }
+    Arena A;
+    int32_t* dXyz = A.get<int32_t>(3 * n); BNULL(dXyz)
+    uint32_t* dMat = A.get<uint32_t>(n); BNULL(dMat)
+    float* dDen = A.get<float>(kCells); BNULL(dDen)
+    uint32_t* dIds = A.get<uint32_t>(kCells); BNULL(dIds)
+    unsigned long long* dCount = A.get<unsigned long long>(1); BNULL(dCount)
+    BCK(cudaMemsetAsync(dCount, 0, 8, st));
+    for (size_t c = 0; c < nChunks; c++) {
+        BCK(cudaMemcpyAsync(dDen, chunks[c].density, kCells * 4, cudaMemcpyHostToDevice, st));
+        BCK(cudaMemcpyAsync(dIds, chunks[c].materialIds, kCells * 4, cudaMemcpyHostToDevice, st));
+        k_dense_emit<<<(unsigned)(kCells / 256), 256, 0, st>>>(dDen, dIds, chunks[c].cx, chunks[c].cy, chunks[c].cz, dXyz, dMat, dCount);
+    }
+    unsigned long long got = 0;
+    BCK(cudaMemcpyAsync(&got, dCount, 8, cudaMemcpyDeviceToHost, st));
+    BCK(cudaStreamSynchronize(st));
+    if (got != n) { err = "dense chunk arrays changed during the upload"; return BLOKB_E_ARG; }
+    return from_device_voxels(dXyz, dMat, n, st, out, err, &emptyKeys);
 }
 
 }  // namespace build

@@ -30,6 +30,12 @@ struct DeviceBuild {
 // xyz: n x int32[3] world voxel coordinates, mat: n x u32 (host pointers; a voxel listed twice keeps the last material,
 // like ChunkManager::setVoxelMaterial). Returns 0 or BLOKB_E_*; on failure nothing is left allocated.
 int from_voxels(const int32_t* xyz, const uint32_t* mat, size_t n, cudaStream_t st, DeviceBuild& out, std::string& err);
+// The same from device-resident arrays (borrowed; the call synchronises the stream before returning).
+// emptyChunkKeys (sorted, optional): chunks the reference would pack as a lone root node; they shift later chunks' node offsets.
+int from_device_voxels(const int32_t* dXyz, const uint32_t* dMat, size_t n, cudaStream_t st, DeviceBuild& out, std::string& err,
+                       const std::vector<uint64_t>* emptyChunkKeys = nullptr);
+// Dense 128^3 chunks in the reference's Chunk layout (host pointers): cells with density > 0 are filled.
+int from_dense(const blokb_dense_chunk* chunks, size_t nChunks, cudaStream_t st, DeviceBuild& out, std::string& err);
 void release(DeviceBuild& b);
 
 }  // namespace build

@@ -171,6 +171,16 @@ int blokb_world_stats_get(blokb_ctx* ctx, blokb_world_stats* out);
  * coordinates (|coordinate| < 2^20), materialId: n x uint32; host pointers, borrowed for the call. */
 int blokb_upload_voxels(blokb_ctx* ctx, const int32_t* xyz, const uint32_t* materialId, size_t n, const blokb_material* materials,
                         size_t nMaterials);
+/* The same from the reference's dense representation: one entry per Chunk (blok/include/chunk.hpp:33-42), density and
+ * materialIds being its two 128^3 arrays (index x + 128 y + 16384 z); a cell is filled iff density > 0
+ * (buildSvoFromDensity, chunk_manager.cpp:106-119). Replaces rebuildDirtyChunks + packChunksToGpuSvo + addWorld for a
+ * ChunkManager(128, 1.0f): pass every chunk of mgr.chunks. Chunks are ordered by (z, y, x); listing one twice is an error. */
+typedef struct blokb_dense_chunk {
+    int32_t cx, cy, cz; /* Chunk::cx, cy, cz */
+    const float* density;
+    const uint32_t* materialIds;
+} blokb_dense_chunk;
+int blokb_upload_dense(blokb_ctx* ctx, const blokb_dense_chunk* chunks, size_t nChunks, const blokb_material* materials, size_t nMaterials);
 /* MagicaVoxel .vox import: loadVoxFile + importVoxMaterials + importVoxToChunks of the reference
  * (blok/src/vox_loader.cpp:151-430) restated as "file -> voxel list + material table", the inputs of blokb_upload_voxels.
  * Material id i = palette entry i (1..255) and id 0 = the library's default grey, as in a fresh MaterialLibrary

@@ -118,6 +118,8 @@ class RefLib(_TraceMixin):
         lib.ref_scene_from_vox.restype = _vp
         lib.ref_scene_from_voxels.argtypes = [_vp, _vp, C.c_size_t, _vp, C.c_size_t]
         lib.ref_scene_from_voxels.restype = _vp
+        lib.ref_scene_from_voxels_d.argtypes = [_vp, _vp, _vp, C.c_size_t, _vp, C.c_size_t]
+        lib.ref_scene_from_voxels_d.restype = _vp
         lib.ref_scene_counts.argtypes = [_vp, _vp, _vp, _vp]
         lib.ref_scene_copy.argtypes = [_vp, _vp, _vp, _vp]
         lib.ref_scene_voxel_material.argtypes = [_vp, C.c_int32, C.c_int32, C.c_int32]
@@ -161,6 +163,17 @@ class RefLib(_TraceMixin):
             s.handle = h
         else:
             self.lib.ref_scene_free(h)
+        return s
+
+    def scene_from_writes(self, xyz, mat, density, mats):
+        """ChunkManager::setVoxelMaterial(p, mat, density) per entry, in order (density 0 erases), then rebuild + pack."""
+        xyz = np.ascontiguousarray(xyz, np.int32)
+        mat = np.ascontiguousarray(mat, np.uint32)
+        density = np.ascontiguousarray(density, np.float32)
+        mats = np.ascontiguousarray(mats, MAT_DT)
+        h = self.lib.ref_scene_from_voxels_d(_ptr(xyz), _ptr(mat), _ptr(density), len(mat), _ptr(mats), len(mats))
+        s = self._take(h)
+        self.lib.ref_scene_free(h)
         return s
 
     def voxel_material(self, scene, x, y, z):

@@ -309,6 +309,21 @@ void* ref_scene_from_voxels(const int32_t* xyz, const uint32_t* mat, size_t n, c
     return s;
 }
 
+// The same with a density per write (0 erases: the chunk stays in ChunkManager::chunks and is packed as a lone root node).
+void* ref_scene_from_voxels_d(const int32_t* xyz, const uint32_t* mat, const float* density, size_t n, const void* materials, size_t nMat) {
+    auto* s = new RefScene;
+    s->lib = new blok::MaterialLibrary;
+    s->mgr = new blok::ChunkManager(128, 1.0f);
+    s->mgr->setMaterialLibrary(s->lib);
+    for (size_t i = 0; i < n; i++)
+        s->mgr->setVoxelMaterial(glm::vec3((float)xyz[3 * i], (float)xyz[3 * i + 1], (float)xyz[3 * i + 2]), mat[i], density[i]);
+    blok::rebuildDirtyChunks(*s->mgr, 1 << 30);
+    blok::packChunksToGpuSvo(*s->mgr, s->world);
+    s->mats.resize(nMat);
+    if (nMat) std::memcpy(s->mats.data(), materials, nMat * sizeof(blok::MaterialGpu));
+    return s;
+}
+
 void ref_scene_counts(void* h, uint64_t* nNodes, uint64_t* nSub, uint64_t* nMat) {
     auto* s = (RefScene*)h;
     *nNodes = s->world.globalNodes.size(); *nSub = s->world.globalSubChunks.size(); *nMat = s->mats.size();

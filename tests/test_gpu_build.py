@@ -150,3 +150,71 @@ def test_vox_file_straight_to_the_device(renderer_factory):
             assert np.array_equal(a.readback(img).view(np.uint8), b.readback(img).view(np.uint8)), (tag, img)
     with pytest.raises(BlokbError):
         b.add_vox(os.path.join(here, "golden", "vox", "missing.vox"))
+
+
+def _dense_from_voxels(xyz, mid, density=None):
+    """Voxel writes -> {chunk: (density, materialIds)} exactly as ChunkManager::setVoxel fills its dense arrays."""
+    chunks = {}
+    den = np.ones(len(mid), np.float32) if density is None else density
+    c = np.floor_divide(xyz, 128)
+    l = xyz - c * 128
+    for i in range(len(mid)):
+        key = (int(c[i, 0]), int(c[i, 1]), int(c[i, 2]))
+        if key not in chunks:
+            chunks[key] = (np.zeros(128 ** 3, np.float32), np.zeros(128 ** 3, np.uint32))
+        t = int(l[i, 0]) + 128 * int(l[i, 1]) + 16384 * int(l[i, 2])
+        chunks[key][0][t] = den[i]
+        chunks[key][1][t] = mid[i]
+    return chunks
+
+
+@pytest.mark.parametrize("name", ["terrain96", "sparse_cloud_negative", "cube_across_8_chunks"])
+def test_dense_chunks_equal_voxel_list(renderer_factory, name):
+    """blokb_upload_dense (the reference's Chunk arrays) == blokb_upload_voxels == the host path."""
+    xyz, mid, mats = CASES[name]
+    if name == "sparse_cloud_negative":
+        xyz, mid = xyz[:600], mid[:600]  # keeps the number of 16 MiB dense chunks small
+    a = renderer_factory(64, 64)
+    a.add_world(WorldSvoGpu.from_voxels(xyz, mid, mats))
+    b = renderer_factory(64, 64)
+    b.add_dense(_dense_from_voxels(xyz, mid), mats)
+    ea, eb = _export(a), _export(b)
+    for k in ea:
+        assert np.array_equal(ea[k].view(np.uint8), eb[k].view(np.uint8)), (name, k)
+    assert a.world_stats()["nodes"] == b.world_stats()["nodes"]
+
+
+def test_dense_density_and_empty_chunk_follow_the_reference(renderer_factory, reflib):
+    """Fractional densities fill (> 0), zero / negative ones do not, and a chunk whose only voxel was erased is still packed by
+    the reference as a lone root node — every later node index moves up by one. Checked against the reference's own
+    ChunkManager; its chunk order is a hash map's, so the erased voxel is placed where both orders put that chunk first."""
+    xyz, mid, mats = CASES["blob64"]
+    rng = np.random.default_rng(3)
+    den = rng.choice(np.array([1.0, 0.25, 0.0, -1.0], np.float32), len(mid), p=[0.6, 0.2, 0.1, 0.1])
+    found = False
+    for ghost in ([-5, 3, 3], [3, -5, 3], [3, 3, -5], [-5, -5, -5], [-200, 3, 3]):
+        # written last: libstdc++'s unordered_map iterates the most recently created chunk first
+        wx = np.concatenate([xyz, np.array([ghost], np.int32)])
+        wm = np.concatenate([mid, np.array([9], np.uint32)])
+        wd = np.concatenate([den, np.array([0.0], np.float32)])
+        sc = reflib.scene_from_writes(wx, wm, wd, mats)
+        if len(sc.subs) and sc.subs["nodeOffset"][0] == 1:  # the reference packed the empty chunk first, like our (z, y, x) order
+            found = True
+            break
+    assert found, "no ghost position where the reference's unordered_map puts the empty chunk first"
+    a = renderer_factory(64, 64)
+    a.add_world(WorldSvoGpu(sc.nodes, sc.subs, sc.mats))
+    b = renderer_factory(64, 64)
+    b.add_dense(_dense_from_voxels(wx, wm, wd), mats)
+    ea, eb = _export(a), _export(b)
+    for k in ea:
+        assert np.array_equal(ea[k].view(np.uint8), eb[k].view(np.uint8)), k
+    assert np.array_equal(b.world_export(WORLD_SUBCHUNKS).view(np.uint8), sc.subs.view(np.uint8))
+    assert b.world_stats()["nodes"] == len(sc.nodes)
+    with pytest.raises(BlokbError):
+        z = (np.zeros(128 ** 3, np.float32), np.zeros(128 ** 3, np.uint32))
+        b.L.blokb_upload_dense  # same chunk twice is rejected
+        import ctypes as C
+        from blok_b200.api import DenseChunkC, _ck
+        arr = (DenseChunkC * 2)(DenseChunkC(0, 0, 0, z[0].ctypes.data, z[1].ctypes.data), DenseChunkC(0, 0, 0, z[0].ctypes.data, z[1].ctypes.data))
+        _ck(b.L.blokb_upload_dense(b._ctx, C.cast(arr, C.c_void_p), 2, None, 0))
