@@ -121,7 +121,7 @@ EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_wo
            "blokb_worldgen_free", "blokb_pipeline_create", "blokb_pipeline_submit", "blokb_pipeline_wait", "blokb_pipeline_drain",
            "blokb_pipeline_destroy", "blokb_host_alloc", "blokb_host_free", "blokb_post_settings_default", "blokb_denoise",
            "blokb_postprocess", "blokb_end_frame", "blokb_reset_history", "blokb_write_image", "blokb_upload_voxels", "blokb_upload_dense", "blokb_world_export", "blokb_vox_load", "blokb_vox_parse",
-           "blokb_vox_counts", "blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free", "blokb_vox_last_error", "blokb_upload_vox"]
+           "blokb_vox_counts", "blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free", "blokb_vox_last_error", "blokb_upload_vox", "blokb_set_strips"]
 
 _lib = None
 
@@ -161,6 +161,7 @@ def load_library():
     for f in ("blokb_trace_primary", "blokb_trace_primary_shadow", "blokb_render", "blokb_resolve", "blokb_reset_accum"):
         getattr(L, f).argtypes = [_vp, _vp]
     L.blokb_trace_path.argtypes = [_vp, C.c_uint32, C.c_uint32, _vp]
+    L.blokb_set_strips.argtypes = [_vp, C.c_uint32, C.c_uint32]
     L.blokb_trace_rays.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp, _vp]
     L.blokb_trace_rays_host.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp]
     L.blokb_get_buffers.argtypes = [_vp, C.POINTER(Buffers)]
@@ -375,6 +376,11 @@ class Renderer:
             self.set_frame(frame)
         _ck(self.L.blokb_render(self._ctx, stream))
 
+    def set_strips(self, first=0, stride=1):
+        """Tile scheduler: later dispatches render the frame's 8-row strips first, first + stride, ... only (this GPU's
+        share of ONE frame, sharding.strip_set); (0, 1) = the whole frame."""
+        _ck(self.L.blokb_set_strips(self._ctx, first, stride))
+
     def trace_primary(self, frame=None, shadow=False, stream=None):
         if frame is not None:
             self.set_frame(frame)
@@ -448,10 +454,11 @@ class Renderer:
 
     def device_array(self, image: int):
         """Zero-copy view of a context-owned device image as an object exposing __cuda_array_interface__ (for
-        torch.as_tensor(..., device="cuda") — used to hand the accumulation buffer to torch.distributed / NCCL)."""
+        torch.as_tensor(..., device="cuda") — used to hand the accumulation buffer to torch.distributed / NCCL). The 16-B
+        hit records are exposed as (h, w, 4) int32 words (NCCL and torch index ops have no uint32)."""
         b = self.buffers()
         h, w = int(b.height), int(b.width)
-        table = {IMG_HIT: (b.hit, (h, w, 4), "<u4"), IMG_SHADOW: (b.shadow, (h, w), "|u1"), IMG_COLOR: (b.color, (h, w, 4), "<f4"),
+        table = {IMG_HIT: (b.hit, (h, w, 4), "<i4"), IMG_SHADOW: (b.shadow, (h, w), "|u1"), IMG_COLOR: (b.color, (h, w, 4), "<f4"),
                  IMG_WORLDPOS: (b.worldPos, (h, w, 4), "<f4"), IMG_NORMALROUGH: (b.normalRough, (h, w, 4), "<f2"),
                  IMG_ALBEDOMETAL: (b.albedoMetal, (h, w, 4), "|u1"), IMG_MOTION: (b.motion, (h, w, 2), "<f2"),
                  IMG_ACCUM: (b.accum, (h, w, 4), "<f4")}

@@ -361,6 +361,12 @@ static int ready(blokb_ctx* c, bool needFrame) {
 static cudaStream_t pick(blokb_ctx* c, void* s) { return s ? static_cast<cudaStream_t>(s) : c->stream; }
 static unsigned long long* st(blokb_ctx* c) { return c->statsOn ? c->dStats : nullptr; }
 
+int blokb_set_strips(blokb_ctx* c, uint32_t first, uint32_t stride) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    if (stride == 0) return fail(BLOKB_E_ARG, "strip stride is 0");
+    c->frame.stripFirst = first; c->frame.stripStride = stride;
+    return 0;
+}
 int blokb_trace_primary(blokb_ctx* c, void* stream) {
     if (int rc = ready(c, true)) return rc;
     CK(launch_primary(c->dw, c->frame, false, c->buf.hit, c->buf.shadow, st(c), pick(c, stream)));
@@ -593,6 +599,8 @@ int blokb_write_image(blokb_ctx* c, int image, const void* host, size_t bytes) {
         case BLOKB_IMG_ALBEDOMETAL: dst = c->buf.albedoMetal; sz = n * 4; break;
         case BLOKB_IMG_MOTION: dst = c->buf.motion; sz = n * 4; break;
         case BLOKB_IMG_ACCUM: dst = c->buf.accum; sz = n * 16; break;
+        case BLOKB_IMG_HIT: dst = c->buf.hit; sz = n * sizeof(blokb_hit); break;
+        case BLOKB_IMG_SHADOW: dst = c->buf.shadow; sz = n; break;
         default: return fail(BLOKB_E_ARG, "image is not writable");
     }
     if (bytes != sz) return fail(BLOKB_E_ARG, "host buffer size mismatch: expected " + std::to_string(sz));

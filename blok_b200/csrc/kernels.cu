@@ -10,11 +10,13 @@
 namespace blokb {
 
 // pixel of this thread: block = 32x8 pixels, warp = 8x4 tile
-__device__ __forceinline__ bool thread_pixel(uint32_t width, uint32_t height, uint32_t& px, uint32_t& py) {
+// blockIdx.y counts the strips THIS launch renders (FrameDev::stripFirst / stripStride): pixel coordinates, seeds and
+// output addresses are those of the full frame, so any partition of the strips over launches or GPUs writes the same bytes.
+__device__ __forceinline__ bool thread_pixel(const FrameDev& F, uint32_t& px, uint32_t& py) {
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     px = blockIdx.x * 32u + (warp & 3u) * 8u + (lane & 7u);
-    py = blockIdx.y * 8u + (warp >> 2) * 4u + (lane >> 3);
-    return px < width && py < height;
+    py = (F.stripFirst + blockIdx.y * F.stripStride) * 8u + (warp >> 2) * 4u + (lane >> 3);
+    return px < F.width && py < F.height;
 }
 
 // Shared-memory node stacks: [level][thread] rows of 16 bytes, W.levels rows (launchers pass levels * 256 * 16 bytes).
@@ -48,7 +50,7 @@ template <bool kShadow, bool kStats>
 __global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
                                                  blokb_hit* __restrict__ out, uint8_t* __restrict__ shadow, unsigned long long* stats) {
     uint32_t px, py;
-    if (!thread_pixel(F.width, F.height, px, py)) return;
+    if (!thread_pixel(F, px, py)) return;
     const F3 d = primary_dir(F, float(px) + 0.5f, float(py) + 0.5f);
     HitRec h;
     uint32_t steps = 0;
@@ -81,7 +83,7 @@ __global__ void __launch_bounds__(256) k_render(const __grid_constant__ DeviceWo
                                                 float4* __restrict__ worldPos, uint2* __restrict__ normalRough, uint32_t* __restrict__ albedoMetal,
                                                 uint32_t* __restrict__ motion, unsigned long long* stats) {
     uint32_t px, py;
-    if (!thread_pixel(F.width, F.height, px, py)) return;
+    if (!thread_pixel(F, px, py)) return;
     FirstHit fh;
     fh.had = false; fh.emissive = false; fh.pos = f3(0.f); fh.N = f3(0.f); fh.albedo = f3(0.f); fh.emission = f3(0.f);
     fh.roughness = 0.f; fh.metallic = 0.f; fh.depth = 0.f;
@@ -130,7 +132,7 @@ template <bool kStats>
 __global__ void __launch_bounds__(256) k_path(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F, uint32_t sBegin, uint32_t sEnd,
                                               float4* __restrict__ accum, unsigned long long* stats) {
     uint32_t px, py;
-    if (!thread_pixel(F.width, F.height, px, py)) return;
+    if (!thread_pixel(F, px, py)) return;
     F3 acc = f3(0.f);
     uint32_t rays = 0, steps = 0;
     const NodeStack stk = thread_stack();
@@ -154,7 +156,11 @@ __global__ void __launch_bounds__(256) k_resolve(const float4* __restrict__ accu
 }
 
 // ---- launchers ------------------------------------------------------------------------------------
-static inline dim3 pixel_grid(uint32_t w, uint32_t h) { return dim3((w + 31) / 32, (h + 7) / 8); }
+static inline dim3 pixel_grid(const FrameDev& F) {
+    const uint32_t strips = (F.height + 7) / 8;
+    const uint32_t mine = F.stripFirst < strips ? (strips - F.stripFirst + F.stripStride - 1) / F.stripStride : 0;
+    return dim3((F.width + 31) / 32, mine);
+}
 static inline size_t stack_bytes(const DeviceWorld& W) { return size_t(W.levels) * 256 * sizeof(uint4); }  // <= 48 KB (kMaxLevels = 12)
 
 cudaError_t launch_trace_rays(const DeviceWorld& W, const float* rays, size_t n, blokb_hit* out, unsigned long long* stats, cudaStream_t st) {
@@ -166,7 +172,8 @@ cudaError_t launch_trace_rays(const DeviceWorld& W, const float* rays, size_t n,
 }
 cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow, blokb_hit* out, uint8_t* shadowOut, unsigned long long* stats,
                            cudaStream_t st) {
-    const dim3 g = pixel_grid(F.width, F.height);
+    const dim3 g = pixel_grid(F);
+    if (g.y == 0) return cudaSuccess;
     if (stats) {
         if (shadow) k_primary<true, true><<<g, 256, stack_bytes(W), st>>>(W, F, out, shadowOut, stats);
         else k_primary<false, true><<<g, 256, stack_bytes(W), st>>>(W, F, out, shadowOut, stats);
@@ -178,7 +185,8 @@ cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow,
 }
 cudaError_t launch_render(const DeviceWorld& W, const FrameDev& F, float* color, float* worldPos, uint16_t* normalRough, uint8_t* albedoMetal,
                           uint16_t* motion, unsigned long long* stats, cudaStream_t st) {
-    const dim3 g = pixel_grid(F.width, F.height);
+    const dim3 g = pixel_grid(F);
+    if (g.y == 0) return cudaSuccess;
     if (stats)
         k_render<true><<<g, 256, stack_bytes(W), st>>>(W, F, (float4*)color, (float4*)worldPos, (uint2*)normalRough, (uint32_t*)albedoMetal, (uint32_t*)motion, stats);
     else
@@ -187,7 +195,8 @@ cudaError_t launch_render(const DeviceWorld& W, const FrameDev& F, float* color,
 }
 cudaError_t launch_path(const DeviceWorld& W, const FrameDev& F, uint32_t sBegin, uint32_t sEnd, float* accum, unsigned long long* stats,
                         cudaStream_t st) {
-    const dim3 g = pixel_grid(F.width, F.height);
+    const dim3 g = pixel_grid(F);
+    if (g.y == 0) return cudaSuccess;
     if (stats) k_path<true><<<g, 256, stack_bytes(W), st>>>(W, F, sBegin, sEnd, (float4*)accum, stats);
     else k_path<false><<<g, 256, stack_bytes(W), st>>>(W, F, sBegin, sEnd, (float4*)accum, nullptr);
     return cudaGetLastError();

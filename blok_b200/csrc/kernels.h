@@ -11,6 +11,9 @@ struct FrameDev {
     float invView[16], invProj[16], prevViewProj[16];
     float camPos[3];
     uint32_t frameCount, sampleCount, width, height;
+    // tile scheduler: of the frame's 8-row strips (one row of 32x8-pixel blocks each) this launch renders strips
+    // stripFirst, stripFirst + stripStride, ... — the whole frame by default (blokb_set_strips)
+    uint32_t stripFirst = 0, stripStride = 1;
 };
 cudaError_t launch_trace_rays(const DeviceWorld& W, const float* rays, size_t n, blokb_hit* out, unsigned long long* stats, cudaStream_t st);
 cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow, blokb_hit* out, uint8_t* shadowOut, unsigned long long* stats,

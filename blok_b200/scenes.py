@@ -65,21 +65,40 @@ def default_materials(n=16):
     return m
 
 
-def terrain(N=2048, seed=0xB10C, thickness=3, origin=(0, 0, 0)):
-    """3-voxel heightfield shell over an N x N footprint."""
+def terrain_heights(N=2048, seed=0xB10C, rows=512):
+    """h[z, x] of the heightfield, int32 (N, N); evaluated in bands of `rows` z-rows so N = 8192 stays within a few GB."""
     xs = np.arange(N, dtype=np.float64)
-    X, Z = np.meshgrid(xs, xs, indexing="xy")
-    h = np.floor(N / 4 + N / 8 * fbm(X / N, Z / N, 5, seed)).astype(np.int32)
-    X = X.astype(np.int32).ravel(); Z = Z.astype(np.int32).ravel(); h = h.ravel()
-    xyz = np.empty((thickness, X.size, 3), np.int32)
+    h = np.empty((N, N), np.int32)
+
+    def band(z0):
+        X, Z = np.meshgrid(xs, xs[z0:z0 + rows], indexing="xy")
+        h[z0:z0 + rows] = np.floor(N / 4 + N / 8 * fbm(X / N, Z / N, 5, seed)).astype(np.int32)
+
+    starts = list(range(0, N, rows))
+    if len(starts) > 1:  # numpy releases the GIL inside its loops: bands in parallel (elementwise, so identical values)
+        from concurrent.futures import ThreadPoolExecutor
+        import os
+        with ThreadPoolExecutor(min(len(starts), os.cpu_count() or 1, 16)) as ex:
+            list(ex.map(band, starts))
+    else:
+        band(0)
+    return h
+
+
+def terrain(N=2048, seed=0xB10C, thickness=3, origin=(0, 0, 0)):
+    """3-voxel heightfield shell over an N x N footprint: filled voxels {h - 2 <= y <= h}."""
+    h = terrain_heights(N, seed).ravel()
+    n = h.size
+    X = np.tile(np.arange(N, dtype=np.int32), N)
+    Z = np.repeat(np.arange(N, dtype=np.int32), N)
+    xyz = np.empty((thickness, n, 3), np.int32)
     for k in range(thickness):
         xyz[k, :, 0] = X + origin[0]
         xyz[k, :, 1] = h - k + origin[1]
         xyz[k, :, 2] = Z + origin[2]
     xyz = xyz.reshape(-1, 3)
-    hh = np.tile(h, thickness)
-    band = ((hh - N // 4) * 8 // max(N // 8, 1)).clip(0, 7).astype(np.uint32) + 1
-    return xyz, band, default_materials(16)
+    band = ((h - N // 4) * 8 // max(N // 8, 1)).clip(0, 7).astype(np.uint32) + 1
+    return xyz, np.tile(band, thickness), default_materials(16)
 
 
 def blob_mesh(N=512, seed=0x51DE, blobs=24):

@@ -6,6 +6,9 @@ the CPU tests).
                                   per-(pixel, frame, sample) seeding (raygen.rgen:92-99) the union of samples is exactly
                                   the single-GPU sample set; only the fp32 summation order differs.
   row_band(rank, world, height)   primary rays: contiguous 8-row-aligned bands (a kernel block is 32x8 pixels).
+  strip_set(rank, world)          primary / G-buffer passes of ONE frame: GPU g renders the 8-row strips g, g + G, ... of
+                                  the full frame (Renderer.set_strips) — interleaved so sky and ground rows are shared
+                                  evenly; gather_strips all-gathers the strips so every rank ends with the full image.
   allreduce_accum(t)              sum of (sum.rgb, spp) buffers; every rank ends with the full frame.
   reduce_scatter_resolve(...)     reduce-scatter of the accumulation buffer, divide-by-spp + firefly clamp on the owned
                                   slice, all-gather of the resolved slices (1/G of the all-reduce's resolve work).
@@ -25,6 +28,48 @@ def row_band(rank: int, world: int, height: int, align: int = 8) -> Tuple[int, i
     blocks = (height + align - 1) // align
     b0, b1 = (blocks * rank) // world, (blocks * (rank + 1)) // world
     return min(b0 * align, height), min(b1 * align, height)
+
+
+STRIP_ROWS = 8  # one row of 32x8-pixel kernel blocks (csrc/kernels.cu)
+
+
+def strip_set(rank: int, world: int) -> Tuple[int, int]:
+    """(first, stride) for Renderer.set_strips: rank g of G owns strips g, g + G, g + 2G, ..."""
+    if not (0 <= rank < world):
+        raise ValueError("rank out of range")
+    return rank, world
+
+
+def strips_owned(rank: int, world: int, height: int) -> int:
+    strips = (height + STRIP_ROWS - 1) // STRIP_ROWS
+    return (strips - rank + world - 1) // world if rank < strips else 0
+
+
+def gather_strips(image, group=None):
+    """image: torch tensor (h, w, ...) holding this rank's strips at their full-frame positions (what the kernels wrote
+    after set_strips(rank, world)). All-gathers the strips; returns the full (h, w, ...) image, on every rank.
+    One exchange step: pack own strips (1/G of the image) -> all_gather_into_tensor -> un-interleave."""
+    import torch
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return image
+    G, g = dist.get_world_size(group), dist.get_rank(group)
+    h = image.shape[0]
+    strips = (h + STRIP_ROWS - 1) // STRIP_ROWS
+    per = (strips + G - 1) // G                      # strips per rank, padded
+    hp = per * G * STRIP_ROWS                        # padded height
+    rest = tuple(image.shape[1:])
+    if hp != h:
+        padded = torch.zeros((hp,) + rest, dtype=image.dtype, device=image.device)
+        padded[:h] = image
+    else:
+        padded = image
+    v = padded.reshape((per, G, STRIP_ROWS) + rest)  # strip s = per-index s // G, owner s % G
+    mine = v[:, g].contiguous()
+    out = torch.empty((G,) + tuple(mine.shape), dtype=image.dtype, device=image.device)
+    dist.all_gather_into_tensor(out.view(-1), mine.view(-1), group=group)
+    full = out.transpose(0, 1).reshape((hp,) + rest)[:h]
+    return full.contiguous()
 
 
 def allreduce_accum(accum, group=None):

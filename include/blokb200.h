@@ -221,6 +221,14 @@ int blokb_camera_frame(const blokb_camera* cam, uint32_t width, uint32_t height,
 int blokb_camera_frame_seq(const blokb_camera* cam, const blokb_camera* prevCam, uint32_t width, uint32_t height, uint32_t frameCount,
                            uint32_t sampleCount, int32_t jitterIndex, blokb_frame_ubo* out);
 
+/* Tile scheduler. The reference dispatches the whole image in one traceRaysKHR(width, height, 1)
+ * (renderer_raytracing.cpp:666-685); to split ONE frame over launches or GPUs the frame is cut into 8-row strips
+ * (strip s = rows [8s, 8s + 8)) and the dispatch calls below render strips first, first + stride, first + 2*stride, ...
+ * only. Pixel coordinates, RNG seeds (raygen.rgen:92-99) and output addresses stay those of the full frame, so the union
+ * of the strip sets {(g, G) : g < G} writes exactly the bytes of the undivided dispatch; interleaving (stride = G)
+ * balances sky and ground rows across GPUs. Default (0, 1) = the whole frame. stride == 0 is BLOKB_E_ARG. */
+int blokb_set_strips(blokb_ctx* ctx, uint32_t first, uint32_t stride);
+
 /* Dispatch (enqueue only). */
 int blokb_trace_primary(blokb_ctx* ctx, void* stream);        /* sample-0 primary rays -> buffers.hit */
 int blokb_trace_primary_shadow(blokb_ctx* ctx, void* stream); /* + sun shadow ray per lit hit -> buffers.shadow */

@@ -1,0 +1,90 @@
+"""GPU: the tile scheduler (blokb_set_strips). Any partition of a frame's 8-row strips over dispatches — the way one frame
+is split across GPUs (SURVEY.md 8(e), configs[4]) — writes exactly the bytes of the undivided dispatch."""
+import os
+
+import numpy as np
+import pytest
+
+import blok_b200
+from blok_b200 import (IMG_ACCUM, IMG_ALBEDOMETAL, IMG_COLOR, IMG_HIT, IMG_MOTION, IMG_NORMALROUGH, IMG_SHADOW, IMG_WORLDPOS,
+                       WorldSvoGpu, sharding)
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "castle.npz")
+
+
+def _setup(renderer_factory):
+    z = np.load(GOLD)
+    r = renderer_factory()
+    r.add_world(WorldSvoGpu(z["nodes"], z["subs"], z["mats"]))
+    return z, r
+
+
+@pytest.mark.parametrize("G", [2, 3, 8])
+def test_primary_and_shadow_strips_compose_to_the_full_frame(renderer_factory, G):
+    z, r = _setup(renderer_factory)
+    r.set_frame(z["ubo_s"])
+    r.trace_primary(shadow=True)
+    full_hit, full_sh = r.readback(IMG_HIT).copy(), r.readback(IMG_SHADOW).copy()
+    h = full_hit.shape[0]
+    acc_hit, acc_sh = np.zeros_like(full_hit), np.zeros_like(full_sh)
+    owner = (np.arange(h) // sharding.STRIP_ROWS) % G
+    for g in range(G):
+        r.set_strips(*sharding.strip_set(g, G))
+        r.trace_primary(shadow=True)
+        hit, sh = r.readback(IMG_HIT), r.readback(IMG_SHADOW)
+        acc_hit[owner == g] = hit[owner == g]
+        acc_sh[owner == g] = sh[owner == g]
+        assert sharding.strips_owned(g, G, h) == len(np.unique(np.arange(h)[owner == g] // sharding.STRIP_ROWS))
+    r.set_strips(0, 1)
+    assert acc_hit.tobytes() == full_hit.tobytes()
+    assert acc_sh.tobytes() == full_sh.tobytes()
+
+
+def test_strip_dispatch_touches_only_its_rows(renderer_factory):
+    z, r = _setup(renderer_factory)
+    r.set_frame(z["ubo_s"])
+    r.trace_primary()
+    full = r.readback(IMG_HIT).copy()
+    marker = np.zeros_like(full)
+    marker["node"] = 0x12345678
+    r.write_image(IMG_HIT, marker)
+    r.set_strips(1, 3)
+    r.trace_primary()
+    got = r.readback(IMG_HIT)
+    mine = ((np.arange(full.shape[0]) // sharding.STRIP_ROWS) % 3) == 1
+    assert got[mine].tobytes() == full[mine].tobytes()
+    assert np.all(got[~mine]["node"] == 0x12345678)
+    # a strip set beyond the frame is an empty dispatch, not an error
+    r.set_strips(10_000, 3)
+    r.trace_primary()
+    r.sync()
+    with pytest.raises(blok_b200.BlokbError):
+        r.set_strips(0, 0)
+
+
+def test_render_and_path_strips_compose(renderer_factory):
+    z, r = _setup(renderer_factory)
+    r.set_frame(z["ubo_r"])
+    ids = (IMG_COLOR, IMG_WORLDPOS, IMG_NORMALROUGH, IMG_ALBEDOMETAL, IMG_MOTION)
+    r.render()
+    full = {i: r.readback(i).copy() for i in ids}
+    r.reset_accum()
+    r.trace_path(0, 3)
+    full_acc = r.readback(IMG_ACCUM).copy()
+    G = 4
+    h = full_acc.shape[0]
+    owner = (np.arange(h) // sharding.STRIP_ROWS) % G
+    parts = {i: np.zeros_like(full[i]) for i in ids}
+    acc = np.zeros_like(full_acc)
+    r.reset_accum()
+    for g in range(G):
+        r.set_strips(g, G)
+        r.render()
+        for i in ids:
+            parts[i][owner == g] = r.readback(i)[owner == g]
+        r.trace_path(0, 3)
+    acc = r.readback(IMG_ACCUM)  # each strip accumulated exactly once over the G dispatches
+    for i in ids:
+        assert parts[i].tobytes() == full[i].tobytes()
+    assert acc.tobytes() == full_acc.tobytes()

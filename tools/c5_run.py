@@ -1,0 +1,205 @@
+"""BASELINE configs[4] at full size: 8192^3 procedural terrain shell (201 M voxels), 7680x4320, primary + sun shadow +
+incoherent bounce rays, ONE frame tiled across the GPUs of the box.
+
+  python tools/c5_run.py [--N 8192 --width 7680 --height 4320 --steps 5 --warmup 3 --check 20000 --out gpurun_out/c5.json]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 tools/c5_run.py ...
+
+Scene: the voxel list goes straight to the device builder (blokb_upload_voxels) — no 6 GB reference-format detour.
+Tiling: rank g of G renders the 8-row strips g, g + G, ... (blokb_set_strips) and the strips are all-gathered over NCCL
+(sharding.gather_strips), so every rank ends with the full hit image / accumulation buffer; time = max over ranks of the
+CUDA-event time around dispatch + gather. Full-size parity: the size-independent heightfield properties of
+tests/heightfield.py on --check sampled pixels (hit voxel filled + right material, nothing filled in front, misses clear).
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def primary_rays_np(ubo, px, py):
+    """raygen.rgen:201-206 in fp32 numpy for pixels (px, py) (unfused, same association as shade.cuh:primary_dir)."""
+    f = np.float32
+    W, H = f(ubo.screenWidth), f(ubo.screenHeight)
+    ip, iv = np.array(ubo.invProj, f), np.array(ubo.invView, f)
+    dx = ((px.astype(f) + f(0.5)) / W) * f(2) - f(1)
+    dy = ((py.astype(f) + f(0.5)) / H) * f(2) - f(1)
+
+    def mul(m, x, y, z, w):
+        return [(m[i] * x + m[4 + i] * y) + (m[8 + i] * z + m[12 + i] * w) for i in range(3)]
+
+    def norm(v):
+        s = f(1) / np.sqrt((v[0] * v[0] + v[1] * v[1]) + v[2] * v[2], dtype=f)
+        return [c * s for c in v]
+    one, zero = np.ones_like(dx), np.zeros_like(dx)
+    tn = norm(mul(ip, dx, dy, one, one))
+    wd = norm(mul(iv, tn[0], tn[1], tn[2], zero))
+    n = len(px)
+    rays = np.empty((n, 8), f)
+    rays[:, 0:3] = np.array(ubo.camPos, f)[None, :]
+    for i in range(3):
+        rays[:, 3 + i] = wd[i]
+    rays[:, 6], rays[:, 7] = 0.001, 10000.0
+    return rays
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--N", type=int, default=8192)
+    ap.add_argument("--width", type=int, default=7680)
+    ap.add_argument("--height", type=int, default=4320)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--check", type=int, default=20000)
+    ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "c5.json"))
+    a = ap.parse_args()
+
+    import torch
+    import torch.distributed as dist
+    import blok_b200
+    from blok_b200 import IMG_ACCUM, IMG_HIT, IMG_SHADOW, Camera, scenes, sharding
+
+    rank, G, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if G > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if G > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def allmax(x):
+        if G == 1:
+            return float(x)
+        t = torch.tensor([float(x)], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(x):
+        if G == 1:
+            return float(x)
+        t = torch.tensor([float(x)], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    N, W, H = a.N, a.width, a.height
+    t0 = time.perf_counter()
+    xyz, mid, mats = scenes.terrain(N)
+    t_gen = time.perf_counter() - t0
+    r = blok_b200.Renderer(W, H, local)
+    t0 = time.perf_counter()
+    r.add_voxels(xyz, mid, mats)
+    r.sync()
+    t_build = time.perf_counter() - t0
+    nvox = len(mid)
+    del xyz, mid
+    stats = r.world_stats()
+    cam = Camera((N / 2, 0.6 * N, -0.2 * N), 90.0, -25.0)
+    ubo = cam.frame(W, H, 0, 1)
+    r.set_frame(ubo)
+    r.set_strips(*sharding.strip_set(rank, G))
+    stream = torch.cuda.Stream(device=dev)
+    sp = stream.cuda_stream
+    hit_t = torch.as_tensor(r.device_array(IMG_HIT), device=dev)
+    sh_t = torch.as_tensor(r.device_array(IMG_SHADOW), device=dev)
+    acc_t = torch.as_tensor(r.device_array(IMG_ACCUM), device=dev)
+    gathered = {}
+
+    def p_primary():
+        r.trace_primary(stream=sp)
+        if G > 1:
+            with torch.cuda.stream(stream):
+                gathered["hit"] = sharding.gather_strips(hit_t)
+
+    def p_shadow():
+        r.trace_primary(shadow=True, stream=sp)
+        if G > 1:
+            with torch.cuda.stream(stream):
+                gathered["hit"] = sharding.gather_strips(hit_t)
+                gathered["shadow"] = sharding.gather_strips(sh_t)
+
+    def p_path():
+        r.reset_accum(stream=sp)
+        r.trace_path(0, 1, stream=sp)
+        if G > 1:
+            with torch.cuda.stream(stream):
+                full = sharding.gather_strips(acc_t)
+                acc_t.copy_(full)
+        r.resolve(stream=sp)
+
+    def timed(fn):
+        for _ in range(a.warmup):
+            fn()
+        barrier()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
+        for s, e in ev:
+            s.record(stream)
+            fn()
+            e.record(stream)
+        barrier()
+        return allmax(sum(s.elapsed_time(e) for s, e in ev) / a.steps)
+
+    res = {"workload": f"c5: {N}^3 terrain shell ({nvox} voxels), {W}x{H}, one frame tiled over {G} GPU(s) in interleaved 8-row strips",
+           "n_gpus": G, "steps": a.steps, "warmup": a.warmup, "scene_gen_s": t_gen, "device_build_wall_s": t_build,
+           "world": {k: stats[k] for k in ("nodes", "subChunks", "voxels", "bricks", "compactBytes", "levels", "buildMs", "uploadMs")},
+           "l2": f"per-step output {W * H * 16 / 1e6:.0f} MB of hit records exceeds the 126 MB L2", "passes": {}}
+
+    ms = timed(p_primary)
+    res["passes"]["primary"] = {"ms": ms, "rays": W * H, "Mrays_s": W * H / ms / 1e3}
+    ms = timed(p_shadow)
+    barrier()
+    nshadow = int(torch.count_nonzero(gathered["shadow"] if G > 1 else sh_t).item())
+    res["passes"]["primary_shadow"] = {"ms": ms, "rays": W * H + nshadow, "Mrays_s": (W * H + nshadow) / ms / 1e3}
+    r.stats_enable(True)
+    r.reset_accum(stream=sp)
+    r.trace_path(0, 1, stream=sp)
+    torch.cuda.synchronize()
+    rays_path = allsum(r.stats_read()[1])
+    r.stats_enable(False)
+    ms = timed(p_path)
+    res["passes"]["path_1spp"] = {"ms": ms, "rays": rays_path, "Mrays_s": rays_path / ms / 1e3,
+                                  "what": "primary + sun shadow + up to 2 bounce rays (incoherent) per pixel, accumulate + resolve"}
+
+    # ---- full-size parity through the heightfield properties (rank 0)
+    p_primary()
+    barrier()
+    if rank == 0 and a.check > 0:
+        from tests import heightfield
+        full = np.ascontiguousarray((gathered["hit"] if G > 1 else hit_t).cpu().numpy()).view(blok_b200.HIT_DT).reshape(H, W)
+        rng = np.random.default_rng(7)
+        px, py = rng.integers(0, W, a.check), rng.integers(0, H, a.check)
+        rays = primary_rays_np(ubo, px, py)
+        r.set_strips(0, 1)
+        rec = r.trace_rays(rays)                     # the same rays through the ray-list entry point
+        img = full[py, px]
+        same = float(np.mean((img["node"] == rec["node"]) & (img["material"] == rec["material"])))
+        hgt = scenes.terrain_heights(N)
+        t0 = time.perf_counter()
+        chk = heightfield.check_hits(hgt, 3, rays, rec["node"], rec["material"], rec["t"], rec["facePrim"] & 7, eps=2e-2)
+        chk["seconds"] = time.perf_counter() - t0
+        chk["passed"] = heightfield.passed(chk)
+        chk["frame_vs_raylist_same_voxel"] = same    # the frame's own rays differ from the numpy ones by <= 1 ulp of direction
+        # the frame's records under the same properties (rays reconstructed in numpy: a looser eps absorbs the ulp)
+        chk2 = heightfield.check_hits(hgt, 3, rays, img["node"], img["material"], img["t"], img["facePrim"] & 7, eps=5e-2)
+        chk["frame_records"] = {k: chk2[k] for k in ("bad_hit_voxel", "bad_material", "filled_before_hit", "filled_on_missed_ray", "unfinished")}
+        res["parity"] = chk
+    if rank == 0:
+        os.makedirs(os.path.dirname(a.out), exist_ok=True)
+        with open(a.out, "w") as f:
+            json.dump(res, f, indent=1)
+        print(json.dumps(res))
+    r.close()
+    if G > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
