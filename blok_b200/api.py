@@ -121,7 +121,7 @@ EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_wo
            "blokb_worldgen_free", "blokb_pipeline_create", "blokb_pipeline_submit", "blokb_pipeline_wait", "blokb_pipeline_drain",
            "blokb_pipeline_destroy", "blokb_host_alloc", "blokb_host_free", "blokb_post_settings_default", "blokb_denoise",
            "blokb_postprocess", "blokb_end_frame", "blokb_reset_history", "blokb_write_image", "blokb_upload_voxels", "blokb_upload_dense", "blokb_world_export", "blokb_vox_load", "blokb_vox_parse",
-           "blokb_vox_counts", "blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free", "blokb_vox_last_error", "blokb_upload_vox", "blokb_set_strips"]
+           "blokb_vox_counts", "blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free", "blokb_vox_last_error", "blokb_upload_vox", "blokb_set_strips", "blokb_ipc_export", "blokb_set_peers"]
 
 _lib = None
 
@@ -162,6 +162,8 @@ def load_library():
         getattr(L, f).argtypes = [_vp, _vp]
     L.blokb_trace_path.argtypes = [_vp, C.c_uint32, C.c_uint32, _vp]
     L.blokb_set_strips.argtypes = [_vp, C.c_uint32, C.c_uint32]
+    L.blokb_ipc_export.argtypes = [_vp, C.c_int, _vp]
+    L.blokb_set_peers.argtypes = [_vp, C.c_int, _vp, C.c_uint32, C.c_uint32]
     L.blokb_trace_rays.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp, _vp]
     L.blokb_trace_rays_host.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp]
     L.blokb_get_buffers.argtypes = [_vp, C.POINTER(Buffers)]
@@ -380,6 +382,22 @@ class Renderer:
         """Tile scheduler: later dispatches render the frame's 8-row strips first, first + stride, ... only (this GPU's
         share of ONE frame, sharding.strip_set); (0, 1) = the whole frame."""
         _ck(self.L.blokb_set_strips(self._ctx, first, stride))
+
+    def ipc_export(self, image: int) -> bytes:
+        """64-byte CUDA IPC handle of one of this context's exchangeable images (IMG_HIT, IMG_SHADOW, IMG_ACCUM)."""
+        h = C.create_string_buffer(64)
+        _ck(self.L.blokb_ipc_export(self._ctx, image, h))
+        return h.raw
+
+    def set_peers(self, image: int, handles, self_index: int):
+        """handles: the ranks' ipc_export(image) results in rank order (this rank's own entry is ignored). Later dispatches
+        store `image` into every rank's buffer (fused exchange); handles=None unmaps."""
+        if not handles:
+            _ck(self.L.blokb_set_peers(self._ctx, image, None, 0, 0))
+            return
+        blob = b"".join(handles)
+        assert len(blob) == 64 * len(handles)
+        _ck(self.L.blokb_set_peers(self._ctx, image, blob, len(handles), self_index))
 
     def trace_primary(self, frame=None, shadow=False, stream=None):
         if frame is not None:

@@ -63,6 +63,11 @@ struct blokb_ctx {
         const void* final = nullptr;                  // PostProcess::getOutputImage() of the current frame
         size_t finalBytesPerPixel = 0;
     } post;
+    // peer mappings of the exchanged images (blokb_set_peers): slot 0 hit, 1 shadow, 2 accum
+    struct Peers {
+        void* mapped[kMaxPeers] = {};   // cudaIpcOpenMemHandle results, nullptr at `self`
+        uint32_t n = 0, self = 0;
+    } peers[3];
     // scratch for host-ray calls
     float* dRays = nullptr;
     blokb_hit* dHits = nullptr;
@@ -79,7 +84,33 @@ static void free_world(blokb_ctx* c) {
     c->nNodesCompact = c->nBlocks = c->nVoxels = c->nSubsDev = 0;
     c->dSubs = nullptr;
 }
+static int peer_slot(int image) {
+    return image == BLOKB_IMG_HIT ? 0 : image == BLOKB_IMG_SHADOW ? 1 : image == BLOKB_IMG_ACCUM ? 2 : -1;
+}
+static void close_peers(blokb_ctx* c, int slot) {
+    auto& P = c->peers[slot];
+    for (uint32_t k = 0; k < P.n; k++)
+        if (P.mapped[k]) cudaIpcCloseMemHandle(P.mapped[k]);
+    P = blokb_ctx::Peers{};
+}
+// own buffer first, then the peers' mappings of the same image
+static PeerOut out_for(blokb_ctx* c, int slot, void* own) {
+    PeerOut o;
+    o.dst[0] = own;
+    o.n = 1;
+    const auto& P = c->peers[slot];
+    for (uint32_t k = 0; k < P.n; k++)
+        if (k != P.self) o.dst[o.n++] = P.mapped[k];
+    return o;
+}
+static PeerOut own_only(void* own) {
+    PeerOut o;
+    o.dst[0] = own;
+    return o;
+}
+
 static void free_images(blokb_ctx* c) {
+    for (int sl = 0; sl < 3; sl++) close_peers(c, sl);
     void* ps[] = {c->buf.hit, c->buf.shadow, c->buf.color, c->buf.worldPos, c->buf.normalRough, c->buf.albedoMetal, c->buf.motion, c->buf.accum};
     for (void* p : ps) if (p) cudaFree(p);
     c->buf = blokb_buffers{};
@@ -367,15 +398,53 @@ int blokb_set_strips(blokb_ctx* c, uint32_t first, uint32_t stride) {
     c->frame.stripFirst = first; c->frame.stripStride = stride;
     return 0;
 }
+int blokb_ipc_export(blokb_ctx* c, int image, void* handle64) {
+    if (!c || !handle64) return fail(BLOKB_E_ARG, "null argument");
+    if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame allocates the images)");
+    void* p = image == BLOKB_IMG_HIT ? (void*)c->buf.hit : image == BLOKB_IMG_SHADOW ? (void*)c->buf.shadow : image == BLOKB_IMG_ACCUM ? (void*)c->buf.accum : nullptr;
+    if (!p) return fail(BLOKB_E_ARG, "image is not exchangeable (hit, shadow, accum)");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    CK(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, p));
+    std::memcpy(handle64, &h, 64);
+    return 0;
+}
+int blokb_set_peers(blokb_ctx* c, int image, const void* handles, uint32_t n, uint32_t self) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    const int slot = peer_slot(image);
+    if (slot < 0) return fail(BLOKB_E_ARG, "image is not exchangeable (hit, shadow, accum)");
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    close_peers(c, slot);
+    if (n == 0) return 0;
+    if (!handles) return fail(BLOKB_E_ARG, "handles is null");
+    if (n > kMaxPeers) return fail(BLOKB_E_ARG, "more than 8 peers");
+    if (self >= n) return fail(BLOKB_E_ARG, "self >= n");
+    auto& P = c->peers[slot];
+    P.n = n; P.self = self;
+    for (uint32_t k = 0; k < n; k++) {
+        if (k == self) continue;
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, static_cast<const char*>(handles) + 64 * size_t(k), 64);
+        cudaError_t e = cudaIpcOpenMemHandle(&P.mapped[k], h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            P.mapped[k] = nullptr;
+            close_peers(c, slot);
+            return fail(BLOKB_E_CUDA, std::string("cudaIpcOpenMemHandle(peer ") + std::to_string(k) + "): " + cudaGetErrorString(e));
+        }
+    }
+    return 0;
+}
 int blokb_trace_primary(blokb_ctx* c, void* stream) {
     if (int rc = ready(c, true)) return rc;
-    CK(launch_primary(c->dw, c->frame, false, c->buf.hit, c->buf.shadow, st(c), pick(c, stream)));
+    CK(launch_primary(c->dw, c->frame, false, out_for(c, 0, c->buf.hit), own_only(c->buf.shadow), st(c), pick(c, stream)));
     c->launches++;
     return 0;
 }
 int blokb_trace_primary_shadow(blokb_ctx* c, void* stream) {
     if (int rc = ready(c, true)) return rc;
-    CK(launch_primary(c->dw, c->frame, true, c->buf.hit, c->buf.shadow, st(c), pick(c, stream)));
+    CK(launch_primary(c->dw, c->frame, true, out_for(c, 0, c->buf.hit), out_for(c, 1, c->buf.shadow), st(c), pick(c, stream)));
     c->launches++;
     return 0;
 }
@@ -390,7 +459,7 @@ int blokb_trace_path(blokb_ctx* c, uint32_t sampleBegin, uint32_t sampleEnd, voi
     if (int rc = ready(c, true)) return rc;
     if (sampleEnd < sampleBegin) return fail(BLOKB_E_ARG, "sampleEnd < sampleBegin");
     if (sampleEnd == sampleBegin) return 0;
-    CK(launch_path(c->dw, c->frame, sampleBegin, sampleEnd, c->buf.accum, st(c), pick(c, stream)));
+    CK(launch_path(c->dw, c->frame, sampleBegin, sampleEnd, out_for(c, 2, c->buf.accum), st(c), pick(c, stream)));
     c->launches++;
     return 0;
 }
@@ -686,7 +755,7 @@ int blokb_pipeline_submit(blokb_pipeline* p, const blokb_frame_ubo* f, blokb_hit
     std::memcpy(d.camPos, f->camPos, 12);
     d.frameCount = f->frameCount; d.sampleCount = f->sampleCount; d.width = f->screenWidth; d.height = f->screenHeight;
     if (p->submitted >= uint64_t(p->depth)) CK(cudaStreamWaitEvent(c->stream, p->copied[slot], 0));  // slot's previous copy must have drained
-    CK(launch_primary(c->dw, d, false, p->dHit[slot], nullptr, st(c), c->stream));
+    CK(launch_primary(c->dw, d, false, own_only(p->dHit[slot]), own_only(nullptr), st(c), c->stream));
     c->launches++;
     CK(cudaEventRecord(p->traced[slot], c->stream));
     CK(cudaStreamWaitEvent(p->copyStream, p->traced[slot], 0));

@@ -32,6 +32,17 @@ __device__ __forceinline__ void store_hit(blokb_hit* dst, bool hit, const HitRec
     *reinterpret_cast<uint4*>(dst) = v;
 }
 
+// One 16-byte record to every destination of the image (own buffer + peers over NVLink); n is launch-uniform.
+__device__ __forceinline__ void store16_all(const PeerOut& o, size_t index, uint4 v) {
+#pragma unroll
+    for (uint32_t k = 0; k < kMaxPeers; k++)
+        if (k < o.n) reinterpret_cast<uint4*>(o.dst[k])[index] = v;
+}
+__device__ __forceinline__ void store_hit_all(const PeerOut& o, size_t index, bool hit, const HitRec& h) {
+    store16_all(o, index, hit ? make_uint4(h.node, h.material, __float_as_uint(h.t), h.facePrim)
+                              : make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, __float_as_uint(-1.0f), 0xFFFFFFFFu));
+}
+
 template <bool kStats>
 __global__ void __launch_bounds__(256) k_trace_rays(const __grid_constant__ DeviceWorld W, const float4* __restrict__ rays, size_t n,
                                                     blokb_hit* __restrict__ out, unsigned long long* stats) {
@@ -48,7 +59,8 @@ __global__ void __launch_bounds__(256) k_trace_rays(const __grid_constant__ Devi
 // Sample-0 primary rays (raygen.rgen:193-229) -> hit records; optionally the sun shadow ray of :280-298.
 template <bool kShadow, bool kStats>
 __global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
-                                                 blokb_hit* __restrict__ out, uint8_t* __restrict__ shadow, unsigned long long* stats) {
+                                                 const __grid_constant__ PeerOut out, const __grid_constant__ PeerOut shadow,
+                                                 unsigned long long* stats) {
     uint32_t px, py;
     if (!thread_pixel(F, px, py)) return;
     const F3 d = primary_dir(F, float(px) + 0.5f, float(py) + 0.5f);
@@ -57,7 +69,7 @@ __global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceW
     const NodeStack stk = thread_stack();
     const bool hit = traverse<kStats>(W, stk, F.camPos[0], F.camPos[1], F.camPos[2], d.x, d.y, d.z, 0.001f, 10000.0f, h, steps, /*locate=*/false);
     const size_t pi = size_t(py) * F.width + px;
-    store_hit(out + pi, hit, h);
+    store_hit_all(out, pi, hit, h);
     if (kShadow) {
         uint8_t sv = 0;  // 0 = no shadow ray cast, 1 = lit, 2 = shadowed
         if (hit) {
@@ -70,7 +82,9 @@ __global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceW
                 sv = traverse<kStats>(W, stk, o.x, o.y, o.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps, true) ? 2 : 1;
             }
         }
-        shadow[pi] = sv;
+#pragma unroll
+        for (uint32_t k = 0; k < kMaxPeers; k++)
+            if (k < shadow.n) static_cast<uint8_t*>(shadow.dst[k])[pi] = sv;
     }
     if (kStats) atomicAdd(stats, (unsigned long long)steps);
 }
@@ -130,7 +144,7 @@ __global__ void __launch_bounds__(256) k_render(const __grid_constant__ DeviceWo
 // sample) seeding so that any partition of the sample range over launches or GPUs draws the same paths.
 template <bool kStats>
 __global__ void __launch_bounds__(256) k_path(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F, uint32_t sBegin, uint32_t sEnd,
-                                              float4* __restrict__ accum, unsigned long long* stats) {
+                                              const __grid_constant__ PeerOut accum, unsigned long long* stats) {
     uint32_t px, py;
     if (!thread_pixel(F, px, py)) return;
     F3 acc = f3(0.f);
@@ -138,9 +152,9 @@ __global__ void __launch_bounds__(256) k_path(const __grid_constant__ DeviceWorl
     const NodeStack stk = thread_stack();
     for (uint32_t s = sBegin; s < sEnd; s++) acc = acc + path_sample<kStats>(W, stk, F, px, py, s, nullptr, rays, steps);
     const size_t pi = size_t(py) * F.width + px;
-    float4 a = accum[pi];
+    float4 a = static_cast<const float4*>(accum.dst[0])[pi];  // the pixel's owner accumulates locally, then replicates
     a.x += acc.x; a.y += acc.y; a.z += acc.z; a.w += float(sEnd - sBegin);
-    accum[pi] = a;
+    store16_all(accum, pi, make_uint4(__float_as_uint(a.x), __float_as_uint(a.y), __float_as_uint(a.z), __float_as_uint(a.w)));
     if (kStats) { atomicAdd(stats, (unsigned long long)steps); atomicAdd(stats + 1, (unsigned long long)rays); }
 }
 
@@ -170,8 +184,8 @@ cudaError_t launch_trace_rays(const DeviceWorld& W, const float* rays, size_t n,
     else k_trace_rays<false><<<blocks, 256, stack_bytes(W), st>>>(W, reinterpret_cast<const float4*>(rays), n, out, nullptr);
     return cudaGetLastError();
 }
-cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow, blokb_hit* out, uint8_t* shadowOut, unsigned long long* stats,
-                           cudaStream_t st) {
+cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow, const PeerOut& out, const PeerOut& shadowOut,
+                           unsigned long long* stats, cudaStream_t st) {
     const dim3 g = pixel_grid(F);
     if (g.y == 0) return cudaSuccess;
     if (stats) {
@@ -193,12 +207,12 @@ cudaError_t launch_render(const DeviceWorld& W, const FrameDev& F, float* color,
         k_render<false><<<g, 256, stack_bytes(W), st>>>(W, F, (float4*)color, (float4*)worldPos, (uint2*)normalRough, (uint32_t*)albedoMetal, (uint32_t*)motion, nullptr);
     return cudaGetLastError();
 }
-cudaError_t launch_path(const DeviceWorld& W, const FrameDev& F, uint32_t sBegin, uint32_t sEnd, float* accum, unsigned long long* stats,
+cudaError_t launch_path(const DeviceWorld& W, const FrameDev& F, uint32_t sBegin, uint32_t sEnd, const PeerOut& accum, unsigned long long* stats,
                         cudaStream_t st) {
     const dim3 g = pixel_grid(F);
     if (g.y == 0) return cudaSuccess;
-    if (stats) k_path<true><<<g, 256, stack_bytes(W), st>>>(W, F, sBegin, sEnd, (float4*)accum, stats);
-    else k_path<false><<<g, 256, stack_bytes(W), st>>>(W, F, sBegin, sEnd, (float4*)accum, nullptr);
+    if (stats) k_path<true><<<g, 256, stack_bytes(W), st>>>(W, F, sBegin, sEnd, accum, stats);
+    else k_path<false><<<g, 256, stack_bytes(W), st>>>(W, F, sBegin, sEnd, accum, nullptr);
     return cudaGetLastError();
 }
 cudaError_t launch_resolve(const float* accum, float* color, size_t n, cudaStream_t st) {

@@ -15,12 +15,20 @@ struct FrameDev {
     // stripFirst, stripFirst + stripStride, ... — the whole frame by default (blokb_set_strips)
     uint32_t stripFirst = 0, stripStride = 1;
 };
+// Destinations of one output image: dst[0] is this GPU's own buffer; dst[1..n) are the same image in peer GPUs' memory
+// (CUDA IPC mappings, blokb_set_peers). A tiled frame's kernels store every record to all of them, so the exchange of
+// strips rides NVLink under the traversal instead of following it as a separate all-gather.
+constexpr uint32_t kMaxPeers = 8;
+struct PeerOut {
+    void* dst[kMaxPeers] = {};
+    uint32_t n = 1;
+};
 cudaError_t launch_trace_rays(const DeviceWorld& W, const float* rays, size_t n, blokb_hit* out, unsigned long long* stats, cudaStream_t st);
-cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow, blokb_hit* out, uint8_t* shadowOut, unsigned long long* stats,
+cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow, const PeerOut& out, const PeerOut& shadowOut, unsigned long long* stats,
                            cudaStream_t st);
 cudaError_t launch_render(const DeviceWorld& W, const FrameDev& F, float* color, float* worldPos, uint16_t* normalRough, uint8_t* albedoMetal,
                           uint16_t* motion, unsigned long long* stats, cudaStream_t st);
-cudaError_t launch_path(const DeviceWorld& W, const FrameDev& F, uint32_t sBegin, uint32_t sEnd, float* accum, unsigned long long* stats,
+cudaError_t launch_path(const DeviceWorld& W, const FrameDev& F, uint32_t sBegin, uint32_t sEnd, const PeerOut& accum, unsigned long long* stats,
                         cudaStream_t st);
 cudaError_t launch_resolve(const float* accum, float* color, size_t n, cudaStream_t st);
 }  // namespace blokb

@@ -9,6 +9,10 @@ the CPU tests).
   strip_set(rank, world)          primary / G-buffer passes of ONE frame: GPU g renders the 8-row strips g, g + G, ... of
                                   the full frame (Renderer.set_strips) — interleaved so sky and ground rows are shared
                                   evenly; gather_strips all-gathers the strips so every rank ends with the full image.
+  connect_peers(renderer, images) the fused form of that exchange: ranks swap CUDA IPC handles of their hit / shadow / accum
+                                  images and map each other's buffers (Renderer.set_peers); the traversal kernels then store
+                                  every record into all ranks' images over NVLink, and frame_barrier() — one tiny all-reduce
+                                  on the dispatch stream — is the only collective left in the frame.
   allreduce_accum(t)              sum of (sum.rgb, spp) buffers; every rank ends with the full frame.
   reduce_scatter_resolve(...)     reduce-scatter of the accumulation buffer, divide-by-spp + firefly clamp on the owned
                                   slice, all-gather of the resolved slices (1/G of the all-reduce's resolve work).
@@ -70,6 +74,40 @@ def gather_strips(image, group=None):
     dist.all_gather_into_tensor(out.view(-1), mine.view(-1), group=group)
     full = out.transpose(0, 1).reshape((hp,) + rest)[:h]
     return full.contiguous()
+
+
+def connect_peers(renderer, images, group=None):
+    """Map every rank's `images` (IMG_HIT / IMG_SHADOW / IMG_ACCUM) into this rank's renderer. Call after set_frame (the
+    images exist) on every rank; the renderers must keep their resolution while connected."""
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return
+    G, g = dist.get_world_size(group), dist.get_rank(group)
+    for img in images:
+        handles = [None] * G
+        dist.all_gather_object(handles, renderer.ipc_export(img), group=group)
+        renderer.set_peers(img, handles, g)
+    dist.barrier(group=group)
+
+
+def disconnect_peers(renderer, images, group=None):
+    import torch.distributed as dist
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.barrier(group=group)     # nobody may still be writing into a buffer that is about to be unmapped / freed
+    for img in images:
+        renderer.set_peers(img, None, 0)
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.barrier(group=group)
+
+
+def frame_barrier(token, group=None):
+    """After a fused-exchange dispatch: `token` is a small tensor on the dispatching device, all-reduced on the CURRENT
+    torch stream — when it completes, every rank's kernel has finished, so every rank's image is complete. Also the
+    fence before the next frame may overwrite the images."""
+    import torch.distributed as dist
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(token, group=group)
+    return token
 
 
 def allreduce_accum(accum, group=None):

@@ -229,6 +229,17 @@ int blokb_camera_frame_seq(const blokb_camera* cam, const blokb_camera* prevCam,
  * balances sky and ground rows across GPUs. Default (0, 1) = the whole frame. stride == 0 is BLOKB_E_ARG. */
 int blokb_set_strips(blokb_ctx* ctx, uint32_t first, uint32_t stride);
 
+/* Fused exchange for a frame tiled over the GPUs of one box (one process per GPU). Each rank exports its hit / shadow /
+ * accumulation image as a CUDA IPC handle (64 bytes), the ranks swap handles by any means (torch.distributed
+ * all_gather in the Python layer), and blokb_set_peers(image, handles[n], n, self) maps the peers' images. From then on
+ * every dispatch that writes that image stores each record into ALL n images — its own and, over NVLink, the peers' —
+ * at the full-frame address, so when every rank's kernel has finished (one barrier) every rank holds the complete image:
+ * the all-gather of the strips is fused into the traversal kernel instead of following it (the one
+ * exchange step of the pixel-partitioned path). n <= 8; n == 0 unmaps. Images must keep their size while mapped
+ * (blokb_set_frame with another resolution unmaps this side). The reference has no multi-GPU path. */
+int blokb_ipc_export(blokb_ctx* ctx, int image, void* handle64);
+int blokb_set_peers(blokb_ctx* ctx, int image, const void* handles, uint32_t n, uint32_t self);
+
 /* Dispatch (enqueue only). */
 int blokb_trace_primary(blokb_ctx* ctx, void* stream);        /* sample-0 primary rays -> buffers.hit */
 int blokb_trace_primary_shadow(blokb_ctx* ctx, void* stream); /* + sun shadow ray per lit hit -> buffers.shadow */

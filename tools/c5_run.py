@@ -56,6 +56,8 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--check", type=int, default=20000)
+    ap.add_argument("--exchange", default="fused", choices=["fused", "gather"],
+                    help="fused: kernels store into every rank's image over NVLink (blokb_set_peers); gather: NCCL all-gather of strips")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "c5.json"))
     a = ap.parse_args()
 
@@ -111,24 +113,44 @@ def main():
     sh_t = torch.as_tensor(r.device_array(IMG_SHADOW), device=dev)
     acc_t = torch.as_tensor(r.device_array(IMG_ACCUM), device=dev)
     gathered = {}
+    fused = G > 1 and a.exchange == "fused"
+    token = torch.zeros(1, device=dev)
+    if fused:
+        sharding.connect_peers(r, (IMG_HIT, IMG_SHADOW, IMG_ACCUM))
+
+    def fence():
+        with torch.cuda.stream(stream):
+            sharding.frame_barrier(token)
 
     def p_primary():
         r.trace_primary(stream=sp)
-        if G > 1:
+        if fused:
+            fence()
+            gathered["hit"] = hit_t
+        elif G > 1:
             with torch.cuda.stream(stream):
                 gathered["hit"] = sharding.gather_strips(hit_t)
 
     def p_shadow():
         r.trace_primary(shadow=True, stream=sp)
-        if G > 1:
+        if fused:
+            fence()
+            gathered["hit"], gathered["shadow"] = hit_t, sh_t
+        elif G > 1:
             with torch.cuda.stream(stream):
                 gathered["hit"] = sharding.gather_strips(hit_t)
                 gathered["shadow"] = sharding.gather_strips(sh_t)
 
     def p_path():
+        if fused:
+            fence()                       # nobody may still be reading / writing last frame's accum when it is cleared
         r.reset_accum(stream=sp)
+        if fused:
+            fence()                       # every rank's clear has landed before peers store into it
         r.trace_path(0, 1, stream=sp)
-        if G > 1:
+        if fused:
+            fence()
+        elif G > 1:
             with torch.cuda.stream(stream):
                 full = sharding.gather_strips(acc_t)
                 acc_t.copy_(full)
@@ -147,7 +169,7 @@ def main():
         return allmax(sum(s.elapsed_time(e) for s, e in ev) / a.steps)
 
     res = {"workload": f"c5: {N}^3 terrain shell ({nvox} voxels), {W}x{H}, one frame tiled over {G} GPU(s) in interleaved 8-row strips",
-           "n_gpus": G, "steps": a.steps, "warmup": a.warmup, "scene_gen_s": t_gen, "device_build_wall_s": t_build,
+           "n_gpus": G, "exchange": ("fused: kernels store strips into every rank's image over NVLink (CUDA IPC), one 4-byte all-reduce as the frame fence" if fused else "NCCL all-gather of strips after the kernel" if G > 1 else "none"), "steps": a.steps, "warmup": a.warmup, "scene_gen_s": t_gen, "device_build_wall_s": t_build,
            "world": {k: stats[k] for k in ("nodes", "subChunks", "voxels", "bricks", "compactBytes", "levels", "buildMs", "uploadMs")},
            "l2": f"per-step output {W * H * 16 / 1e6:.0f} MB of hit records exceeds the 126 MB L2", "passes": {}}
 
@@ -195,6 +217,8 @@ def main():
         with open(a.out, "w") as f:
             json.dump(res, f, indent=1)
         print(json.dumps(res))
+    if fused:
+        sharding.disconnect_peers(r, (IMG_HIT, IMG_SHADOW, IMG_ACCUM))
     r.close()
     if G > 1:
         dist.barrier()
