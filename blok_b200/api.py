@@ -121,7 +121,7 @@ EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_wo
            "blokb_worldgen_free", "blokb_pipeline_create", "blokb_pipeline_submit", "blokb_pipeline_wait", "blokb_pipeline_drain",
            "blokb_pipeline_destroy", "blokb_host_alloc", "blokb_host_free", "blokb_post_settings_default", "blokb_denoise",
            "blokb_postprocess", "blokb_end_frame", "blokb_reset_history", "blokb_write_image", "blokb_upload_voxels", "blokb_upload_dense", "blokb_world_export", "blokb_vox_load", "blokb_vox_parse",
-           "blokb_vox_counts", "blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free", "blokb_vox_last_error", "blokb_upload_vox", "blokb_set_strips", "blokb_ipc_export", "blokb_set_peers"]
+           "blokb_vox_counts", "blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free", "blokb_vox_last_error", "blokb_upload_vox", "blokb_set_strips", "blokb_ipc_export", "blokb_set_peers", "blokb_bind_image"]
 
 _lib = None
 
@@ -163,6 +163,7 @@ def load_library():
     L.blokb_trace_path.argtypes = [_vp, C.c_uint32, C.c_uint32, _vp]
     L.blokb_set_strips.argtypes = [_vp, C.c_uint32, C.c_uint32]
     L.blokb_ipc_export.argtypes = [_vp, C.c_int, _vp]
+    L.blokb_bind_image.argtypes = [_vp, C.c_int, _vp, _vp]
     L.blokb_set_peers.argtypes = [_vp, C.c_int, _vp, C.c_uint32, C.c_uint32]
     L.blokb_trace_rays.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp, _vp]
     L.blokb_trace_rays_host.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp]
@@ -382,6 +383,11 @@ class Renderer:
         """Tile scheduler: later dispatches render the frame's 8-row strips first, first + stride, ... only (this GPU's
         share of ONE frame, sharding.strip_set); (0, 1) = the whole frame."""
         _ck(self.L.blokb_set_strips(self._ctx, first, stride))
+
+    def bind_image(self, image: int, local_ptr=None, multicast_ptr=None):
+        """Place IMG_HIT / IMG_SHADOW / IMG_ACCUM in caller-owned (symmetric) memory; with multicast_ptr the kernels store each
+        record once to the NVLink multicast address (sharding.connect_multicast). bind_image(image) restores the own buffer."""
+        _ck(self.L.blokb_bind_image(self._ctx, image, local_ptr or None, multicast_ptr or None))
 
     def ipc_export(self, image: int) -> bytes:
         """64-byte CUDA IPC handle of one of this context's exchangeable images (IMG_HIT, IMG_SHADOW, IMG_ACCUM)."""

@@ -68,6 +68,12 @@ struct blokb_ctx {
         void* mapped[kMaxPeers] = {};   // cudaIpcOpenMemHandle results, nullptr at `self`
         uint32_t n = 0, self = 0;
     } peers[3];
+    // externally owned symmetric memory standing in for an image (blokb_bind_image); own = the context's allocation, kept aside
+    struct Bound {
+        void* own = nullptr;
+        void* mc = nullptr;
+        bool on = false;
+    } bound[3];
     // scratch for host-ray calls
     float* dRays = nullptr;
     blokb_hit* dHits = nullptr;
@@ -98,10 +104,22 @@ static PeerOut out_for(blokb_ctx* c, int slot, void* own) {
     PeerOut o;
     o.dst[0] = own;
     o.n = 1;
+    if (c->bound[slot].on && c->bound[slot].mc) {
+        o.mc = c->bound[slot].mc;
+        return o;
+    }
     const auto& P = c->peers[slot];
     for (uint32_t k = 0; k < P.n; k++)
         if (k != P.self) o.dst[o.n++] = P.mapped[k];
     return o;
+}
+static void** image_slot_ptr(blokb_ctx* c, int slot) {
+    return slot == 0 ? reinterpret_cast<void**>(&c->buf.hit) : slot == 1 ? reinterpret_cast<void**>(&c->buf.shadow) : reinterpret_cast<void**>(&c->buf.accum);
+}
+static void unbind(blokb_ctx* c, int slot) {
+    auto& B = c->bound[slot];
+    if (B.on) *image_slot_ptr(c, slot) = B.own;
+    B = blokb_ctx::Bound{};
 }
 static PeerOut own_only(void* own) {
     PeerOut o;
@@ -110,7 +128,7 @@ static PeerOut own_only(void* own) {
 }
 
 static void free_images(blokb_ctx* c) {
-    for (int sl = 0; sl < 3; sl++) close_peers(c, sl);
+    for (int sl = 0; sl < 3; sl++) { close_peers(c, sl); unbind(c, sl); }
     void* ps[] = {c->buf.hit, c->buf.shadow, c->buf.color, c->buf.worldPos, c->buf.normalRough, c->buf.albedoMetal, c->buf.motion, c->buf.accum};
     for (void* p : ps) if (p) cudaFree(p);
     c->buf = blokb_buffers{};
@@ -434,6 +452,26 @@ int blokb_set_peers(blokb_ctx* c, int image, const void* handles, uint32_t n, ui
             return fail(BLOKB_E_CUDA, std::string("cudaIpcOpenMemHandle(peer ") + std::to_string(k) + "): " + cudaGetErrorString(e));
         }
     }
+    return 0;
+}
+int blokb_bind_image(blokb_ctx* c, int image, void* local, void* multicast) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    const int slot = peer_slot(image);
+    if (slot < 0) return fail(BLOKB_E_ARG, "image is not exchangeable (hit, shadow, accum)");
+    if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame allocates the images)");
+    if (!local && multicast) return fail(BLOKB_E_ARG, "a multicast address needs the local address of the same memory");
+    if (multicast && image == BLOKB_IMG_SHADOW && (c->buf.width & 3u)) return fail(BLOKB_E_ARG, "multicast shadow image needs width % 4 == 0");
+    if ((reinterpret_cast<uintptr_t>(local) | reinterpret_cast<uintptr_t>(multicast)) & 15u) return fail(BLOKB_E_ARG, "addresses must be 16-byte aligned");
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    close_peers(c, slot);
+    unbind(c, slot);
+    if (!local) return 0;
+    auto& B = c->bound[slot];
+    B.own = *image_slot_ptr(c, slot);
+    B.mc = multicast;
+    B.on = true;
+    *image_slot_ptr(c, slot) = local;
     return 0;
 }
 int blokb_trace_primary(blokb_ctx* c, void* stream) {

@@ -33,10 +33,33 @@ __device__ __forceinline__ void store_hit(blokb_hit* dst, bool hit, const HitRec
 }
 
 // One 16-byte record to every destination of the image (own buffer + peers over NVLink); n is launch-uniform.
+// With a multicast binding (o.mc) ONE multimem.st reaches every GPU's copy through the NVSwitch.
 __device__ __forceinline__ void store16_all(const PeerOut& o, size_t index, uint4 v) {
+    if (o.mc) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(static_cast<uint4*>(o.mc) + index),
+                     "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+                     : "memory");
+        return;
+    }
 #pragma unroll
     for (uint32_t k = 0; k < kMaxPeers; k++)
         if (k < o.n) reinterpret_cast<uint4*>(o.dst[k])[index] = v;
+}
+// One byte per pixel. multimem.st has no byte form: with a multicast binding the four pixels of a lane quad (x = 4q..4q+3
+// of one row; whole quads are in or out of the frame because blokb_bind_image requires width % 4 == 0) travel as one word.
+__device__ __forceinline__ void store8_all(const PeerOut& o, size_t index, uint8_t b) {
+    if (o.mc) {
+        const uint32_t lane = threadIdx.x & 31u, quad = 0xFu << (lane & 28u);
+        uint32_t w = b;
+        w |= __shfl_down_sync(quad, w, 1) << 8;
+        w |= __shfl_down_sync(quad, w, 2) << 16;
+        if ((lane & 3u) == 0u)
+            asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(static_cast<uint8_t*>(o.mc) + index), "r"(w) : "memory");
+        return;
+    }
+#pragma unroll
+    for (uint32_t k = 0; k < kMaxPeers; k++)
+        if (k < o.n) static_cast<uint8_t*>(o.dst[k])[index] = b;
 }
 __device__ __forceinline__ void store_hit_all(const PeerOut& o, size_t index, bool hit, const HitRec& h) {
     store16_all(o, index, hit ? make_uint4(h.node, h.material, __float_as_uint(h.t), h.facePrim)
@@ -82,9 +105,7 @@ __global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceW
                 sv = traverse<kStats>(W, stk, o.x, o.y, o.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps, true) ? 2 : 1;
             }
         }
-#pragma unroll
-        for (uint32_t k = 0; k < kMaxPeers; k++)
-            if (k < shadow.n) static_cast<uint8_t*>(shadow.dst[k])[pi] = sv;
+        store8_all(shadow, pi, sv);
     }
     if (kStats) atomicAdd(stats, (unsigned long long)steps);
 }

@@ -18,10 +18,14 @@ struct FrameDev {
 // Destinations of one output image: dst[0] is this GPU's own buffer; dst[1..n) are the same image in peer GPUs' memory
 // (CUDA IPC mappings, blokb_set_peers). A tiled frame's kernels store every record to all of them, so the exchange of
 // strips rides NVLink under the traversal instead of following it as a separate all-gather.
+// mc != nullptr: the image lives in symmetric memory bound to an NVLink multicast object (blokb_bind_image); ONE
+// multimem.st to mc is replicated by the NVSwitch into every GPU's copy (this GPU's included), so the sender's egress is
+// 1x the strip instead of (G-1)x. dst[0] then only serves reads of the local copy (accumulate).
 constexpr uint32_t kMaxPeers = 8;
 struct PeerOut {
     void* dst[kMaxPeers] = {};
     uint32_t n = 1;
+    void* mc = nullptr;
 };
 cudaError_t launch_trace_rays(const DeviceWorld& W, const float* rays, size_t n, blokb_hit* out, unsigned long long* stats, cudaStream_t st);
 cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow, const PeerOut& out, const PeerOut& shadowOut, unsigned long long* stats,

@@ -90,6 +90,54 @@ def connect_peers(renderer, images, group=None):
     dist.barrier(group=group)
 
 
+def connect_multicast(renderer, images, group=None):
+    """The fused exchange through NVLink multicast: each of `images` is re-homed in torch symmetric memory bound to a
+    multicast object (Renderer.bind_image); kernels then store every record once and the NVSwitch replicates it into all
+    ranks' copies. Returns the keep-alive list [(image, tensor, handle)] (pass it to disconnect_multicast), or None when
+    the platform has no multicast support — callers fall back to connect_peers."""
+    import torch
+    import torch.distributed as dist
+    import torch.distributed._symmetric_memory as symm_mem
+    from .api import IMG_ACCUM, IMG_HIT, IMG_SHADOW
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return None
+    b = renderer.buffers()
+    n = int(b.width) * int(b.height)
+    per_pixel = {IMG_HIT: 16, IMG_SHADOW: 1, IMG_ACCUM: 16}
+    pg = group if group is not None else dist.group.WORLD
+    name = pg.group_name if hasattr(pg, "group_name") else pg
+    dev = torch.device("cuda", torch.cuda.current_device())
+    keep = []
+    for img in images:
+        nbytes = (n * per_pixel[img] + 15) // 16 * 16
+        t = symm_mem.empty(nbytes, dtype=torch.uint8, device=dev)
+        h = symm_mem.rendezvous(t, name)
+        if not int(h.multicast_ptr):
+            for im, _, _ in keep:
+                renderer.bind_image(im)
+            return None
+        t.zero_()
+        keep.append((img, t, h))
+    torch.cuda.synchronize()
+    dist.barrier(group=group)
+    for img, t, h in keep:
+        renderer.bind_image(img, t.data_ptr(), int(h.multicast_ptr))
+    dist.barrier(group=group)
+    return keep
+
+
+def disconnect_multicast(renderer, keep, group=None):
+    import torch
+    import torch.distributed as dist
+    torch.cuda.synchronize()
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.barrier(group=group)
+    for img, _, _ in keep or []:
+        renderer.bind_image(img)
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.barrier(group=group)
+
+
 def disconnect_peers(renderer, images, group=None):
     import torch.distributed as dist
     if dist.is_initialized() and dist.get_world_size(group) > 1:

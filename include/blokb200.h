@@ -237,6 +237,14 @@ int blokb_set_strips(blokb_ctx* ctx, uint32_t first, uint32_t stride);
  * the all-gather of the strips is fused into the traversal kernel instead of following it (the one
  * exchange step of the pixel-partitioned path). n <= 8; n == 0 unmaps. Images must keep their size while mapped
  * (blokb_set_frame with another resolution unmaps this side). The reference has no multi-GPU path. */
+/* The same exchange through NVLink multicast (NVLS): the image is placed in caller-owned symmetric memory — `local` is this
+ * GPU's address of it, `multicast` the address of the multicast object all ranks' copies are bound to (both e.g. from
+ * torch.distributed._symmetric_memory: tensor.data_ptr() and rendezvous(...).multicast_ptr). The context then uses
+ * `local` as the image (readback, get_buffers, resolve ...) and its kernels store each record ONCE, with multimem.st to
+ * `multicast`; the NVSwitch replicates it into every GPU's copy, so a rank's NVLink egress is its own strips, not
+ * (G-1) copies of them. multicast == NULL just substitutes the memory; local == NULL restores the context's own
+ * allocation. The memory must hold the whole image and outlive the binding. */
+int blokb_bind_image(blokb_ctx* ctx, int image, void* local, void* multicast);
 int blokb_ipc_export(blokb_ctx* ctx, int image, void* handle64);
 int blokb_set_peers(blokb_ctx* ctx, int image, const void* handles, uint32_t n, uint32_t self);
 

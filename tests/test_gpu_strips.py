@@ -132,3 +132,79 @@ def test_fused_exchange_between_two_processes(tmp_path):
     port = 33500 + (os.getpid() % 2000)
     mp.spawn(_peer_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     assert (tmp_path / "ok_0").read_text() == "1" and (tmp_path / "ok_1").read_text() == "1"
+
+
+def test_bind_image_substitutes_external_memory(renderer_factory):
+    """blokb_bind_image without a multicast address: the kernels write into caller-owned memory, readback follows it, and
+    unbinding restores the context's own buffer."""
+    import torch
+    z, r = _setup(renderer_factory)
+    r.set_frame(z["ubo_s"])
+    r.trace_primary()
+    full = r.readback(IMG_HIT).copy()
+    ext = torch.zeros(full.nbytes, dtype=torch.uint8, device="cuda:0")
+    r.bind_image(IMG_HIT, ext.data_ptr(), None)
+    r.trace_primary()
+    r.sync()
+    assert ext.cpu().numpy().tobytes() == full.tobytes()
+    assert r.readback(IMG_HIT).tobytes() == full.tobytes()
+    r.bind_image(IMG_HIT)
+    ext.zero_()
+    r.trace_primary()
+    assert r.readback(IMG_HIT).tobytes() == full.tobytes() and int(ext.sum()) == 0
+    with pytest.raises(blok_b200.BlokbError):
+        r.bind_image(IMG_HIT, ext.data_ptr() + 4, None)   # misaligned
+    with pytest.raises(blok_b200.BlokbError):
+        r.bind_image(IMG_COLOR, ext.data_ptr(), None)     # not an exchangeable image
+
+
+def _mc_worker(rank, world, port, out_dir):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    z = np.load(GOLD)
+    r = blok_b200.Renderer(64, 64, rank)
+    r.add_world(WorldSvoGpu(z["nodes"], z["subs"], z["mats"]))
+    r.set_frame(z["ubo_r"])
+    images = (IMG_HIT, IMG_SHADOW, IMG_ACCUM)
+    r.trace_primary(shadow=True)
+    r.reset_accum()
+    r.trace_path(0, 2)
+    full = {i: r.readback(i).copy() for i in images}
+    keep = sharding.connect_multicast(r, images)
+    status = "nomc"
+    if keep is not None:
+        r.set_strips(*sharding.strip_set(rank, world))
+        r.trace_primary(shadow=True)
+        r.trace_path(0, 2)           # the symmetric images start zeroed
+        r.sync()
+        dist.barrier()
+        status = "1" if all(r.readback(i).tobytes() == full[i].tobytes() for i in images) else "0"
+        sharding.disconnect_multicast(r, keep)
+        r.set_strips(0, 1)
+        r.trace_primary(shadow=True)
+        if r.readback(IMG_HIT).tobytes() != full[IMG_HIT].tobytes():
+            status = "0"
+    with open(os.path.join(out_dir, f"ok_{rank}"), "w") as f:
+        f.write(status)
+    r.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_multicast_exchange_two_gpus(tmp_path):
+    """Needs two GPUs on an NVSwitch (run with `gpurun --gpus 2`); skipped on the single-GPU box."""
+    import torch
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    port = 35500 + (os.getpid() % 2000)
+    mp.spawn(_mc_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    got = [(tmp_path / f"ok_{k}").read_text() for k in range(2)]
+    if got == ["nomc", "nomc"]:
+        pytest.skip("no NVLink multicast support on this box")
+    assert got == ["1", "1"]

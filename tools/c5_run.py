@@ -56,8 +56,8 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--check", type=int, default=20000)
-    ap.add_argument("--exchange", default="fused", choices=["fused", "gather"],
-                    help="fused: kernels store into every rank's image over NVLink (blokb_set_peers); gather: NCCL all-gather of strips")
+    ap.add_argument("--exchange", default="fused", choices=["multicast", "fused", "gather"],
+                    help="multicast: kernels store once to an NVLink multicast address (blokb_bind_image); fused: kernels store into every rank's image over NVLink (blokb_set_peers); gather: NCCL all-gather of strips")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "c5.json"))
     a = ap.parse_args()
 
@@ -113,9 +113,18 @@ def main():
     sh_t = torch.as_tensor(r.device_array(IMG_SHADOW), device=dev)
     acc_t = torch.as_tensor(r.device_array(IMG_ACCUM), device=dev)
     gathered = {}
-    fused = G > 1 and a.exchange == "fused"
+    fused = G > 1 and a.exchange in ("fused", "multicast")
     token = torch.zeros(1, device=dev)
-    if fused:
+    mc_keep = None
+    if G > 1 and a.exchange == "multicast":
+        mc_keep = sharding.connect_multicast(r, (IMG_HIT, IMG_SHADOW, IMG_ACCUM))
+        if mc_keep is None:
+            print("no multicast support: falling back to P2P stores", flush=True)
+        else:   # the images moved: refresh the views
+            hit_t = torch.as_tensor(r.device_array(IMG_HIT), device=dev)
+            sh_t = torch.as_tensor(r.device_array(IMG_SHADOW), device=dev)
+            acc_t = torch.as_tensor(r.device_array(IMG_ACCUM), device=dev)
+    if fused and mc_keep is None:
         sharding.connect_peers(r, (IMG_HIT, IMG_SHADOW, IMG_ACCUM))
 
     def fence():
@@ -169,7 +178,7 @@ def main():
         return allmax(sum(s.elapsed_time(e) for s, e in ev) / a.steps)
 
     res = {"workload": f"c5: {N}^3 terrain shell ({nvox} voxels), {W}x{H}, one frame tiled over {G} GPU(s) in interleaved 8-row strips",
-           "n_gpus": G, "exchange": ("fused: kernels store strips into every rank's image over NVLink (CUDA IPC), one 4-byte all-reduce as the frame fence" if fused else "NCCL all-gather of strips after the kernel" if G > 1 else "none"), "steps": a.steps, "warmup": a.warmup, "scene_gen_s": t_gen, "device_build_wall_s": t_build,
+           "n_gpus": G, "exchange": ("multicast: kernels store each record once to an NVLink multicast address (multimem.st, symmetric memory), one 4-byte all-reduce as the frame fence" if mc_keep else "fused: kernels store strips into every rank's image over NVLink (CUDA IPC), one 4-byte all-reduce as the frame fence" if fused else "NCCL all-gather of strips after the kernel" if G > 1 else "none"), "steps": a.steps, "warmup": a.warmup, "scene_gen_s": t_gen, "device_build_wall_s": t_build,
            "world": {k: stats[k] for k in ("nodes", "subChunks", "voxels", "bricks", "compactBytes", "levels", "buildMs", "uploadMs")},
            "l2": f"per-step output {W * H * 16 / 1e6:.0f} MB of hit records exceeds the 126 MB L2", "passes": {}}
 
@@ -217,7 +226,11 @@ def main():
         with open(a.out, "w") as f:
             json.dump(res, f, indent=1)
         print(json.dumps(res))
-    if fused:
+    if mc_keep:
+        del hit_t, sh_t, acc_t
+        gathered.clear()
+        sharding.disconnect_multicast(r, mc_keep)
+    elif fused:
         sharding.disconnect_peers(r, (IMG_HIT, IMG_SHADOW, IMG_ACCUM))
     r.close()
     if G > 1:
