@@ -434,6 +434,61 @@ def extra_device_build(name, r, env):
             "identical_to_host_path": bool(same), "nodes_reference_format": int(st["nodes"])}
 
 
+def extra_tiled_frame(name, r, env, steps=30, warmup=3):
+    """N > 1: ONE frame of the workload tiled over the GPUs (strong scaling; SURVEY.md 8(e) pixel partition). Rank g renders
+    the 8-row strips g, g + G, ... (blokb_set_strips) and the kernel stores every hit record into all ranks' images — through
+    an NVLink multicast address when the box supports it (blokb_bind_image), else P2P stores to the peers' IPC-mapped
+    images (blokb_set_peers); a 4-byte all-reduce on the dispatch stream is the frame fence. Parity: the assembled image on
+    every rank is byte-identical to the rank's own undivided dispatch."""
+    import blok_b200
+    from blok_b200 import IMG_HIT, sharding, workloads
+    torch, dist = env["torch"], env["dist"]
+    rank, G, dev = env["rank"], env["world_size"], env["dev"]
+    wl = workloads.WORKLOADS[name]
+    W, H = wl["width"], wl["height"]
+    r.set_strips(0, 1)
+    r.set_frame(workloads.camera_for(name, 0).frame(W, H, 0, 1))
+    r.trace_primary()
+    full = r.readback(IMG_HIT).copy()
+    keep = sharding.connect_multicast(r, (IMG_HIT,))
+    if keep is None:
+        sharding.connect_peers(r, (IMG_HIT,))
+    r.set_strips(*sharding.strip_set(rank, G))
+    stream = torch.cuda.Stream(device=dev)
+    token = torch.zeros(1, device=dev)
+
+    def step():
+        r.trace_primary(stream=stream.cuda_stream)
+        with torch.cuda.stream(stream):
+            sharding.frame_barrier(token)
+
+    for _ in range(warmup):
+        step()
+    env["barrier"]()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for a, b in ev:
+        a.record(stream)
+        step()
+        b.record(stream)
+    env["barrier"]()
+    ms = sum(a.elapsed_time(b) for a, b in ev) / steps
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    same = torch.tensor([int(r.readback(IMG_HIT).tobytes() == full.tobytes())], device=dev)
+    dist.all_reduce(same, op=dist.ReduceOp.MIN)
+    if keep is None:
+        sharding.disconnect_peers(r, (IMG_HIT,))
+    else:
+        sharding.disconnect_multicast(r, keep)
+    r.set_strips(0, 1)
+    return {"what": f"one {W}x{H} frame of {name} tiled over {G} GPUs in interleaved 8-row strips, exchange fused into the traversal kernel",
+            "exchange": "NVLink multicast (multimem.st into symmetric memory)" if keep is not None else "P2P stores into IPC-mapped peer images",
+            "ms_per_frame": ms, "value": W * H / ms / 1e3, "unit": "Mrays/s", "scaling": "strong", "steps": steps,
+            "identical_on_every_rank": bool(int(same.item())),
+            "nvlink_ingress_bytes_per_gpu": int(W * H * 16 * (G - 1) / G)}
+
+
 def extra_full_frame(name, r, env):
     """The reference's whole frame (Renderer::render, blok/src/renderer_draw.cpp): raygen at the reference's 8 spp, Denoiser::denoise,
     PostProcess::process, over a slow dolly so that both temporal passes are live. Per stage, CUDA events on the launching stream."""
@@ -562,7 +617,6 @@ def main():
                 extras[key] = fn(name, r, env)
             except Exception as ex:  # an extra must never cost the headline line
                 extras[key] = {"error": repr(ex)}
-    r.close()
     if not args.no_extras:
         for other, st, wu in (("c2", 20, 3), ("c4", 2, 1)):
             if other == name:
@@ -586,6 +640,27 @@ def main():
                            "timing": "CUDA events on the launching stream around each step, summed; max over ranks",
                            "parallelism": f"{world_size} GPU(s), scene replicated, one frame per GPU per step"},
                 "e2e": e2e, "gpu_launches": m["launches"], "clocks": m["clocks"], "roofline": roof, "cpu_baseline": cpu, "extras": extras}
+    if world_size > 1 and not args.no_extras:
+        # last, with everything else already in `line`: the one extra that adds collectives of its own. A watchdog makes sure a
+        # hang in it (one rank failing inside a collective) costs the extra, never the line.
+        import threading
+
+        def bail():
+            if rank == 0:
+                extras["tiled_frame"] = {"error": "watchdog: no result within 180 s"}
+                emit(line)
+            os._exit(0)
+        wd = threading.Timer(180.0, bail)
+        wd.daemon = True
+        wd.start()
+        try:
+            res = extra_tiled_frame(name, r, env)
+        except Exception as ex:
+            res = {"error": repr(ex)}
+        wd.cancel()
+        extras["tiled_frame"] = res
+    r.close()
+    if rank == 0:
         emit(line)
     if world_size > 1:
         env["dist"].barrier()
