@@ -23,7 +23,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libblokb200.so")
+LIB_PATH = os.environ.get("BLOKB_LIB_PATH") or os.path.join(HERE, "libblokb200.so")  # override: kernel experiments (tools/)
 
 NODE_DT = np.dtype([("childMask", "<u4"), ("firstChild", "<u4"), ("materialId", "<u4"), ("occupancy", "<f4")])
 SUB_DT = np.dtype([("nodeOffset", "<u4"), ("rootNodeIndex", "<u4"), ("nodeCount", "<u4"), ("startDepth", "<u4"),
@@ -121,7 +121,8 @@ EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_wo
            "blokb_worldgen_free", "blokb_pipeline_create", "blokb_pipeline_submit", "blokb_pipeline_wait", "blokb_pipeline_drain",
            "blokb_pipeline_destroy", "blokb_host_alloc", "blokb_host_free", "blokb_post_settings_default", "blokb_denoise",
            "blokb_postprocess", "blokb_end_frame", "blokb_reset_history", "blokb_write_image", "blokb_upload_voxels", "blokb_upload_dense", "blokb_world_export", "blokb_vox_load", "blokb_vox_parse",
-           "blokb_vox_counts", "blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free", "blokb_vox_last_error", "blokb_upload_vox", "blokb_set_strips", "blokb_ipc_export", "blokb_set_peers", "blokb_bind_image"]
+           "blokb_vox_counts", "blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free", "blokb_vox_last_error", "blokb_upload_vox", "blokb_set_strips", "blokb_ipc_export", "blokb_set_peers", "blokb_bind_image",
+           "blokb_world_save", "blokb_world_load"]
 
 _lib = None
 
@@ -163,6 +164,8 @@ def load_library():
     L.blokb_trace_path.argtypes = [_vp, C.c_uint32, C.c_uint32, _vp]
     L.blokb_set_strips.argtypes = [_vp, C.c_uint32, C.c_uint32]
     L.blokb_ipc_export.argtypes = [_vp, C.c_int, _vp]
+    L.blokb_world_save.argtypes = [_vp, C.c_char_p]
+    L.blokb_world_load.argtypes = [_vp, C.c_char_p]
     L.blokb_bind_image.argtypes = [_vp, C.c_int, _vp, _vp]
     L.blokb_set_peers.argtypes = [_vp, C.c_int, _vp, C.c_uint32, C.c_uint32]
     L.blokb_trace_rays.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp, _vp]
@@ -327,6 +330,14 @@ class Renderer:
         mats = np.ascontiguousarray(materials, dtype=MAT_DT)
         assert len(mid) == len(xyz)
         _ck(self.L.blokb_upload_voxels(self._ctx, _ptr(xyz), _ptr(mid), len(mid), _ptr(mats), len(mats)))
+
+    def save_world(self, path):
+        """Scene dump: the device-resident compact world to one file (blokb_world_save)."""
+        _ck(self.L.blokb_world_save(self._ctx, os.fspath(path).encode()))
+
+    def load_world(self, path):
+        """File -> device, no builder involved (blokb_world_load); traces exactly like the world that was saved."""
+        _ck(self.L.blokb_world_load(self._ctx, os.fspath(path).encode()))
 
     def add_dense(self, chunks, materials):
         """chunks: {(cx, cy, cz): (density f32[128^3], materialIds u32[128^3])} — ChunkManager::chunks as the reference holds them

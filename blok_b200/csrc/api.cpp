@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cstdlib>
+#include <cstdio>
 #include <cstring>
 #include <new>
 #include <string>
@@ -359,6 +360,118 @@ int blokb_world_export(blokb_ctx* c, int which, void* host, size_t bytes, size_t
     CK(cudaSetDevice(c->device));
     if (sz) CK(cudaMemcpyAsync(host, src, sz, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+// ---- scene dump: the device-resident compact world, as is, to a file and back ---------------
+namespace {
+struct DumpHeader {
+    char magic[8];          // "BLOKBWD1"
+    uint32_t version;       // 1
+    uint32_t headerBytes;   // sizeof(DumpHeader)
+    int32_t origin[3], dim[3], levels, matWide;
+    uint64_t nNodes, nBlocks, nVoxels, nMaterials, nSubs;  // element counts of the five payload arrays, in this order
+    blokb_world_stats stats;
+    uint64_t payloadBytes;  // sum of the arrays' byte sizes, each padded to 16
+    uint64_t fnv1a;         // FNV-1a 64 of the payload
+};
+inline size_t pad16(size_t n) { return (n + 15) & ~size_t(15); }
+uint64_t fnv1a64(const unsigned char* p, size_t n) {
+    uint64_t h = 1469598103934665603ull;
+    for (size_t i = 0; i < n; i++) { h ^= p[i]; h *= 1099511628211ull; }
+    return h;
+}
+}  // namespace
+
+int blokb_world_save(blokb_ctx* c, const char* path) {
+    if (!c || !path) return fail(BLOKB_E_ARG, "null argument");
+    if (!c->haveWorld) return fail(BLOKB_E_STATE, "no world uploaded");
+    CK(cudaSetDevice(c->device));
+    DumpHeader h{};
+    std::memcpy(h.magic, "BLOKBWD1", 8);
+    h.version = 1; h.headerBytes = sizeof(DumpHeader);
+    for (int a = 0; a < 3; a++) { h.origin[a] = c->dw.origin[a]; h.dim[a] = c->dw.dim[a]; }
+    h.levels = c->dw.levels; h.matWide = c->dw.matWide;
+    h.nNodes = c->nNodesCompact; h.nBlocks = c->nBlocks; h.nVoxels = c->nVoxels; h.nMaterials = c->dw.nMaterials;
+    h.nSubs = c->dSubs ? c->nSubsDev : 0;
+    h.stats = c->stats;
+    const void* src[5] = {c->dw.nodes, c->dw.blockFirstLeaf, c->dw.voxelMat, c->dw.materials, c->dSubs};
+    const size_t sz[5] = {size_t(h.nNodes) * sizeof(Node), size_t(h.nBlocks) * 4, size_t(h.nVoxels) * (h.matWide ? 4 : 2),
+                          size_t(h.nMaterials) * sizeof(blokb_material), size_t(h.nSubs) * sizeof(blokb_subchunk)};
+    size_t total = 0;
+    for (size_t b : sz) total += pad16(b);
+    std::vector<unsigned char> buf(total, 0);
+    size_t off = 0;
+    for (int k = 0; k < 5; k++) {
+        if (sz[k]) CK(cudaMemcpyAsync(buf.data() + off, src[k], sz[k], cudaMemcpyDeviceToHost, c->stream));
+        off += pad16(sz[k]);
+    }
+    CK(cudaStreamSynchronize(c->stream));
+    h.payloadBytes = total;
+    h.fnv1a = fnv1a64(buf.data(), total);
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return fail(BLOKB_E_ARG, std::string("cannot open for writing: ") + path);
+    const bool ok = std::fwrite(&h, sizeof(h), 1, f) == 1 && (total == 0 || std::fwrite(buf.data(), 1, total, f) == total);
+    if (std::fclose(f) != 0 || !ok) return fail(BLOKB_E_ARG, std::string("write failed: ") + path);
+    return 0;
+}
+
+int blokb_world_load(blokb_ctx* c, const char* path) {
+    if (!c || !path) return fail(BLOKB_E_ARG, "null argument");
+    CK(cudaSetDevice(c->device));
+    const auto t0 = std::chrono::steady_clock::now();
+    FILE* f = std::fopen(path, "rb");
+    if (!f) return fail(BLOKB_E_ARG, std::string("cannot open: ") + path);
+    DumpHeader h{};
+    std::vector<unsigned char> buf;
+    std::string why;
+    if (std::fread(&h, sizeof(h), 1, f) != 1) why = "truncated header";
+    else if (std::memcmp(h.magic, "BLOKBWD1", 8) != 0) why = "not a blok-b200 scene dump";
+    else if (h.version != 1 || h.headerBytes != sizeof(DumpHeader)) why = "unsupported dump version";
+    else if (h.levels < 3 || h.levels > kMaxLevels || h.nNodes == 0 || h.nNodes > (1ull << 32) || h.nBlocks > (1ull << 32) || h.nVoxels > (1ull << 32) ||
+             h.nMaterials == 0 || h.nMaterials > (1ull << 24) || h.nSubs > (1ull << 32) || (h.matWide != 0 && h.matWide != 1)) why = "implausible header";
+    size_t sz[5] = {};
+    if (why.empty()) {
+        sz[0] = size_t(h.nNodes) * sizeof(Node); sz[1] = size_t(h.nBlocks) * 4; sz[2] = size_t(h.nVoxels) * (h.matWide ? 4 : 2);
+        sz[3] = size_t(h.nMaterials) * sizeof(blokb_material); sz[4] = size_t(h.nSubs) * sizeof(blokb_subchunk);
+        size_t total = 0;
+        for (size_t b : sz) total += pad16(b);
+        if (total != h.payloadBytes) why = "payload size does not match the header";
+        else {
+            buf.resize(total);
+            if (total && std::fread(buf.data(), 1, total, f) != total) why = "truncated payload";
+            else if (std::fgetc(f) != EOF) why = "trailing bytes after the payload";
+            else if (fnv1a64(buf.data(), total) != h.fnv1a) why = "checksum mismatch";
+        }
+    }
+    std::fclose(f);
+    if (!why.empty()) return fail(BLOKB_E_ARG, std::string(path) + ": " + why);
+    const auto t1 = std::chrono::steady_clock::now();
+    CK(cudaStreamSynchronize(c->stream));
+    free_world(c);
+    void* dst[5] = {};
+    size_t off = 0;
+    for (int k = 0; k < 5; k++) {
+        if (k == 4 && sz[k] == 0) break;
+        CK(cudaMalloc(&dst[k], std::max<size_t>(sz[k], 16)));
+        c->worldAllocs.push_back(dst[k]);
+        if (sz[k]) CK(cudaMemcpyAsync(dst[k], buf.data() + off, sz[k], cudaMemcpyHostToDevice, c->stream));
+        off += pad16(sz[k]);
+    }
+    CK(cudaStreamSynchronize(c->stream));
+    DeviceWorld& d = c->dw;
+    d = DeviceWorld{};
+    for (int a = 0; a < 3; a++) { d.origin[a] = h.origin[a]; d.dim[a] = h.dim[a]; }
+    d.levels = h.levels; d.matWide = h.matWide;
+    d.nodes = static_cast<const uint4*>(dst[0]); d.blockFirstLeaf = static_cast<const uint32_t*>(dst[1]); d.voxelMat = dst[2];
+    d.materials = static_cast<const float4*>(dst[3]); d.nMaterials = uint32_t(h.nMaterials);
+    c->nNodesCompact = h.nNodes; c->nBlocks = h.nBlocks; c->nVoxels = h.nVoxels;
+    c->dSubs = static_cast<const blokb_subchunk*>(dst[4]); c->nSubsDev = h.nSubs;
+    c->stats = h.stats;
+    const auto t2 = std::chrono::steady_clock::now();
+    c->stats.buildMs = std::chrono::duration<float, std::milli>(t1 - t0).count();   // file read + checksum
+    c->stats.uploadMs = std::chrono::duration<float, std::milli>(t2 - t1).count();
+    c->haveWorld = true;
     return 0;
 }
 

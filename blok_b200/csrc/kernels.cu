@@ -14,8 +14,12 @@ namespace blokb {
 // output addresses are those of the full frame, so any partition of the strips over launches or GPUs writes the same bytes.
 __device__ __forceinline__ bool thread_pixel(const FrameDev& F, uint32_t& px, uint32_t& py) {
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    px = blockIdx.x * 32u + (warp & 3u) * 8u + (lane & 7u);
-    py = (F.stripFirst + blockIdx.y * F.stripStride) * 8u + (warp >> 2) * 4u + (lane >> 3);
+#ifndef BLOKB_TILE_W_LOG2
+#define BLOKB_TILE_W_LOG2 3  // warp tile = 8 x 4 pixels (measured against 4x8, 16x2 and 32x1: DESIGN.md 5)
+#endif
+    constexpr uint32_t TW = 1u << BLOKB_TILE_W_LOG2, TH = 32u / TW, tilesX = 32u / TW;
+    px = blockIdx.x * 32u + (warp % tilesX) * TW + (lane & (TW - 1u));
+    py = (F.stripFirst + blockIdx.y * F.stripStride) * 8u + (warp / tilesX) * TH + (lane >> BLOKB_TILE_W_LOG2);
     return px < F.width && py < F.height;
 }
 
@@ -41,8 +45,10 @@ __device__ __forceinline__ void store16_all(const PeerOut& o, size_t index, uint
                      : "memory");
         return;
     }
+    reinterpret_cast<uint4*>(o.dst[0])[index] = v;
+    if (o.n == 1) return;  // the single-GPU dispatch: one store, no peer loop
 #pragma unroll
-    for (uint32_t k = 0; k < kMaxPeers; k++)
+    for (uint32_t k = 1; k < kMaxPeers; k++)
         if (k < o.n) reinterpret_cast<uint4*>(o.dst[k])[index] = v;
 }
 // One byte per pixel. multimem.st has no byte form: with a multicast binding the four pixels of a lane quad (x = 4q..4q+3
@@ -57,8 +63,10 @@ __device__ __forceinline__ void store8_all(const PeerOut& o, size_t index, uint8
             asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(static_cast<uint8_t*>(o.mc) + index), "r"(w) : "memory");
         return;
     }
+    static_cast<uint8_t*>(o.dst[0])[index] = b;
+    if (o.n == 1) return;
 #pragma unroll
-    for (uint32_t k = 0; k < kMaxPeers; k++)
+    for (uint32_t k = 1; k < kMaxPeers; k++)
         if (k < o.n) static_cast<uint8_t*>(o.dst[k])[index] = b;
 }
 __device__ __forceinline__ void store_hit_all(const PeerOut& o, size_t index, bool hit, const HitRec& h) {
@@ -81,7 +89,10 @@ __global__ void __launch_bounds__(256) k_trace_rays(const __grid_constant__ Devi
 
 // Sample-0 primary rays (raygen.rgen:193-229) -> hit records; optionally the sun shadow ray of :280-298.
 template <bool kShadow, bool kStats>
-__global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
+#ifndef BLOKB_PRIMARY_MIN_BLOCKS
+#define BLOKB_PRIMARY_MIN_BLOCKS 1
+#endif
+__global__ void __launch_bounds__(256, BLOKB_PRIMARY_MIN_BLOCKS) k_primary(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
                                                  const __grid_constant__ PeerOut out, const __grid_constant__ PeerOut shadow,
                                                  unsigned long long* stats) {
     uint32_t px, py;

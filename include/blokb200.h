@@ -205,6 +205,13 @@ enum blokb_world_array {
     BLOKB_WORLD_VOXELMAT = 2,       /* u16 (u32 if any id > 65535) material id per filled voxel */
     BLOKB_WORLD_SUBCHUNKS = 3       /* blokb_subchunk records (worlds built by blokb_upload_voxels) */
 };
+/* Scene dump: the GPU-resident compact world — nodes, blockFirstLeaf, voxelMat, materials and, for
+ * device-built worlds, the SubChunkGpu records — written to / read from one file (64-bit FNV-1a checked), so an asset built
+ * once (from the reference's arrays, a voxel list, dense chunks or a .vox file) loads without any builder: file -> device.
+ * The reference has no scene file of its own (it re-imports .vox files at start-up, app.cpp:100-126). A loaded world traces
+ * exactly like the one that was saved (same hit records). Bad files are BLOKB_E_ARG with the reason in blokb_last_error(). */
+int blokb_world_save(blokb_ctx* ctx, const char* path);
+int blokb_world_load(blokb_ctx* ctx, const char* path);
 int blokb_world_export(blokb_ctx* ctx, int which, void* host, size_t bytes, size_t* bytesOut);
 
 /* Frame in (binding 3). (Re)allocates the output images when the size changes. */

@@ -218,3 +218,67 @@ def test_dense_density_and_empty_chunk_follow_the_reference(renderer_factory, re
         from blok_b200.api import DenseChunkC, _ck
         arr = (DenseChunkC * 2)(DenseChunkC(0, 0, 0, z[0].ctypes.data, z[1].ctypes.data), DenseChunkC(0, 0, 0, z[0].ctypes.data, z[1].ctypes.data))
         _ck(b.L.blokb_upload_dense(b._ctx, C.cast(arr, C.c_void_p), 2, None, 0))
+
+
+# ---- scene dump: blokb_world_save / blokb_world_load -----------------------------------------
+def _trace_all(r, cam, w=96, h=64):
+    r.trace_primary(cam.frame(w, h, 0, 1), shadow=True)
+    return r.readback(IMG_HIT).tobytes(), r.readback(blok_b200.IMG_SHADOW).tobytes()
+
+
+@pytest.mark.parametrize("name", ["terrain96", "sparse_cloud_negative", "wide_material_ids", "single_voxel_negative"])
+@pytest.mark.parametrize("built_on", ["device", "host"])
+def test_scene_dump_round_trip(tmp_path, name, built_on):
+    xyz, mid, mats = CASES[name]
+    a = blok_b200.Renderer(96, 64, 0)
+    if built_on == "device":
+        a.add_voxels(xyz, mid, mats)
+    else:
+        a.add_world(WorldSvoGpu.from_voxels(xyz, mid, mats))
+    lo, hi = xyz.min(0).astype(np.float64), xyz.max(0).astype(np.float64)
+    cam = Camera(tuple((lo + hi) / 2 + np.array([0.0, (hi - lo).max() * 0.8 + 20, -(hi - lo).max() * 0.9 - 20])), 90.0, -35.0)
+    want = _trace_all(a, cam)
+    path = tmp_path / "world.blokb"
+    a.save_world(path)
+    b = blok_b200.Renderer(96, 64, 0)
+    b.load_world(path)
+    ea, eb = _export(a), _export(b)
+    for k in ea:
+        assert ea[k].tobytes() == eb[k].tobytes()
+    sa, sb = a.world_stats(), b.world_stats()
+    for k in ("nodes", "subChunks", "materials", "bricks", "blocks", "voxels", "compactBytes", "levels"):
+        assert sa[k] == sb[k], k
+    if built_on == "device":
+        assert a.world_export(WORLD_SUBCHUNKS).tobytes() == b.world_export(WORLD_SUBCHUNKS).tobytes()
+    assert _trace_all(b, cam) == want
+    # a dump of the loaded world is the same file
+    path2 = tmp_path / "again.blokb"
+    b.save_world(path2)
+    r1, r2 = path.read_bytes(), path2.read_bytes()   # 200-byte header; bytes 172..184 are the stats' two timing floats
+    assert r1[:8] == b"BLOKBWD1" and r1[:172] == r2[:172] and r1[184:] == r2[184:]
+    a.close(); b.close()
+
+
+def test_scene_dump_rejects_damaged_files(tmp_path):
+    xyz, mid, mats = CASES["terrain96"]
+    a = blok_b200.Renderer(64, 64, 0)
+    a.add_voxels(xyz, mid, mats)
+    path = tmp_path / "w.blokb"
+    a.save_world(path)
+    raw = path.read_bytes()
+    b = blok_b200.Renderer(64, 64, 0)
+    with pytest.raises(BlokbError, match="no world"):
+        b.save_world(tmp_path / "none.blokb")
+    cases = {"truncated payload": raw[:-100], "truncated header": raw[:40], "not a blok-b200": b"XXXXXXXX" + raw[8:],
+             "checksum": raw[:-9] + bytes([raw[-9] ^ 1]) + raw[-8:], "trailing": raw + b"\0", "version": raw[:8] + b"\x07" + raw[9:]}
+    for why, data in cases.items():
+        p = tmp_path / "bad.blokb"
+        p.write_bytes(data)
+        with pytest.raises(BlokbError, match=why.split()[0]):
+            b.load_world(p)
+    with pytest.raises(BlokbError, match="cannot open"):
+        b.load_world(tmp_path / "missing.blokb")
+    # a failed load leaves the context usable
+    b.load_world(path)
+    assert b.world_stats()["voxels"] == a.world_stats()["voxels"]
+    a.close(); b.close()
