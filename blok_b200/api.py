@@ -122,7 +122,7 @@ EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_wo
            "blokb_pipeline_destroy", "blokb_host_alloc", "blokb_host_free", "blokb_post_settings_default", "blokb_denoise",
            "blokb_postprocess", "blokb_end_frame", "blokb_reset_history", "blokb_write_image", "blokb_upload_voxels", "blokb_upload_dense", "blokb_world_export", "blokb_vox_load", "blokb_vox_parse",
            "blokb_vox_counts", "blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free", "blokb_vox_last_error", "blokb_upload_vox", "blokb_set_strips", "blokb_ipc_export", "blokb_set_peers", "blokb_bind_image",
-           "blokb_world_save", "blokb_world_load"]
+           "blokb_world_save", "blokb_world_load", "blokb_update_dense"]
 
 _lib = None
 
@@ -165,6 +165,7 @@ def load_library():
     L.blokb_set_strips.argtypes = [_vp, C.c_uint32, C.c_uint32]
     L.blokb_ipc_export.argtypes = [_vp, C.c_int, _vp]
     L.blokb_world_save.argtypes = [_vp, C.c_char_p]
+    L.blokb_update_dense.argtypes = [_vp, _vp, C.c_size_t]
     L.blokb_world_load.argtypes = [_vp, C.c_char_p]
     L.blokb_bind_image.argtypes = [_vp, C.c_int, _vp, _vp]
     L.blokb_set_peers.argtypes = [_vp, C.c_int, _vp, C.c_uint32, C.c_uint32]
@@ -339,19 +340,30 @@ class Renderer:
         """File -> device, no builder involved (blokb_world_load); traces exactly like the world that was saved."""
         _ck(self.L.blokb_world_load(self._ctx, os.fspath(path).encode()))
 
-    def add_dense(self, chunks, materials):
-        """chunks: {(cx, cy, cz): (density f32[128^3], materialIds u32[128^3])} — ChunkManager::chunks as the reference holds them
-        (index x + 128 y + 16384 z). rebuildDirtyChunks + packChunksToGpuSvo + addWorld, on the device."""
+    @staticmethod
+    def _dense_array(chunks):
         keep = []
-        arr = (DenseChunkC * len(chunks))()
+        arr = (DenseChunkC * max(len(chunks), 1))()
         for k, ((cx, cy, cz), (den, ids)) in enumerate(chunks.items()):
             den = np.ascontiguousarray(den, np.float32).reshape(-1)
             ids = np.ascontiguousarray(ids, np.uint32).reshape(-1)
             assert den.size == 128 ** 3 and ids.size == 128 ** 3
             keep += [den, ids]
             arr[k] = DenseChunkC(cx, cy, cz, den.ctypes.data, ids.ctypes.data)
+        return arr, keep
+
+    def add_dense(self, chunks, materials):
+        """chunks: {(cx, cy, cz): (density f32[128^3], materialIds u32[128^3])} — ChunkManager::chunks as the reference holds them
+        (index x + 128 y + 16384 z). rebuildDirtyChunks + packChunksToGpuSvo + addWorld, on the device."""
+        arr, keep = self._dense_array(chunks)
         mats = np.ascontiguousarray(materials, dtype=MAT_DT)
         _ck(self.L.blokb_upload_dense(self._ctx, C.cast(arr, _vp), len(chunks), _ptr(mats), len(mats)))
+
+    def update_dense(self, dirty_chunks):
+        """Renderer::updateWorld after an edit: only the dirty chunks (same dict form as add_dense) travel; the world is rebuilt on
+        the device from the voxel list kept since add_dense. Equal to add_dense of all chunks."""
+        arr, keep = self._dense_array(dirty_chunks)
+        _ck(self.L.blokb_update_dense(self._ctx, C.cast(arr, _vp), len(dirty_chunks)))
 
     def add_vox(self, path, model_index=0, offset=(0.0, 0.0, 0.0)):
         """loadAndImportVox + rebuild + pack + addWorld (blok/src/app.cpp:100-126): the file's voxels go straight to the device builder."""

@@ -75,6 +75,10 @@ struct blokb_ctx {
         void* mc = nullptr;
         bool on = false;
     } bound[3];
+    // editable worlds (blokb_upload_dense keeps the voxel list on the device; blokb_update_dense replaces dirty chunks in it)
+    build::VoxelList edit;
+    std::vector<blokb_material> editMaterials;
+    bool editable = false;
     // scratch for host-ray calls
     float* dRays = nullptr;
     blokb_hit* dHits = nullptr;
@@ -90,6 +94,9 @@ static void free_world(blokb_ctx* c) {
     c->haveWorld = false;
     c->nNodesCompact = c->nBlocks = c->nVoxels = c->nSubsDev = 0;
     c->dSubs = nullptr;
+    c->edit.release();   // a replaced world is editable again only through blokb_upload_dense
+    c->editMaterials.clear();
+    c->editable = false;
 }
 static int peer_slot(int image) {
     return image == BLOKB_IMG_HIT ? 0 : image == BLOKB_IMG_SHADOW ? 1 : image == BLOKB_IMG_ACCUM ? 2 : -1;
@@ -263,10 +270,45 @@ int blokb_upload_dense(blokb_ctx* c, const blokb_dense_chunk* chunks, size_t nCh
     const auto t0 = std::chrono::steady_clock::now();
     CK(cudaStreamSynchronize(c->stream));
     build::DeviceBuild B;
+    build::VoxelList L;
     std::string err;
-    int rc = build::from_dense(chunks, nChunks, c->stream, B, err);
+    int rc = build::from_dense(chunks, nChunks, c->stream, B, err, &L);
     if (rc) return fail(rc, err);
-    return finish_device_build(c, B, materials, nMaterials, t0);
+    std::vector<blokb_material> mats(materials, materials + nMaterials);
+    rc = finish_device_build(c, B, materials, nMaterials, t0);   // frees the previous world (and its voxel list)
+    if (rc) { L.release(); return rc; }
+    c->edit = std::move(L);
+    L = build::VoxelList{};
+    c->editMaterials = std::move(mats);
+    c->editable = true;
+    return 0;
+}
+
+int blokb_update_dense(blokb_ctx* c, const blokb_dense_chunk* chunks, size_t nChunks) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    if (nChunks && !chunks) return fail(BLOKB_E_ARG, "null array with non-zero count");
+    if (!c->haveWorld || !c->editable) return fail(BLOKB_E_STATE, "the current world was not uploaded with blokb_upload_dense");
+    if (nChunks == 0) return 0;
+    CK(cudaSetDevice(c->device));
+    const auto t0 = std::chrono::steady_clock::now();
+    CK(cudaStreamSynchronize(c->stream));   // updateWorld waits idle before replacing buffers (renderer.hpp:55-71)
+    std::string err;
+    int rc = build::replace_chunks(c->edit, chunks, nChunks, c->stream, err);   // on failure the list is unchanged
+    if (rc) return fail(rc, err);
+    build::DeviceBuild B;
+    rc = build::from_list(c->edit, c->stream, B, err);
+    if (rc) return fail(rc, err);
+    // finish_device_build replaces the world and with it the editable state: carry the list and the materials across
+    build::VoxelList L = std::move(c->edit);
+    c->edit = build::VoxelList{};
+    std::vector<blokb_material> mats = std::move(c->editMaterials);
+    rc = finish_device_build(c, B, mats.data(), mats.size(), t0);
+    c->edit = std::move(L);
+    L = build::VoxelList{};
+    c->editMaterials = std::move(mats);
+    c->editable = rc == 0;
+    if (rc) { c->edit.release(); c->editMaterials.clear(); }
+    return rc;
 }
 
 static int finish_device_build(blokb_ctx* c, build::DeviceBuild& B, const blokb_material* materials, size_t nMaterials,

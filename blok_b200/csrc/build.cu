@@ -26,6 +26,7 @@
 
 #include <algorithm>
 #include <cstring>
+#include <iterator>
 
 namespace blokb {
 namespace build {
@@ -497,44 +498,123 @@ __global__ void k_dense_emit(const float* __restrict__ density, const uint32_t* 
         mat[o] = ids[t];
     }
 }
+// keep[i] = 1 unless voxel i lies in one of the listed chunks (sorted keys, chunk key = voxel key >> 21)
+__global__ void k_flag_outside(const int32_t* __restrict__ xyz, size_t n, const uint64_t* __restrict__ chunkKeys, uint32_t nKeys, uint8_t* __restrict__ keep) {
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int cx = floordiv128(xyz[3 * i]), cy = floordiv128(xyz[3 * i + 1]), cz = floordiv128(xyz[3 * i + 2]);
+    const uint64_t key = uint64_t(cz + kBias) << 28 | uint64_t(cy + kBias) << 14 | uint64_t(cx + kBias);
+    uint32_t lo = 0, hi = nKeys;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (chunkKeys[mid] < key) lo = mid + 1; else hi = mid;
+    }
+    keep[i] = (lo < nKeys && chunkKeys[lo] == key) ? 0 : 1;
+}
+struct V3 { int32_t x, y, z; };
 }  // namespace
 
-int from_dense(const blokb_dense_chunk* chunks, size_t nChunks, cudaStream_t st, DeviceBuild& out, std::string& err) {
-    out = DeviceBuild{};
+void VoxelList::release() {
+    if (xyz) cudaFree(xyz);
+    if (mat) cudaFree(mat);
+    xyz = nullptr; mat = nullptr; n = 0;
+    emptyKeys.clear();
+}
+
+#undef BCK
+#undef BNULL
+#define LCK(expr)                                                                                          \
+    do {                                                                                                   \
+        cudaError_t e_ = (expr);                                                                           \
+        if (e_ != cudaSuccess) { err = std::string(#expr) + ": " + cudaGetErrorString(e_); return BLOKB_E_CUDA; } \
+    } while (0)
+#define LNULL(p) \
+    if (!(p)) { err = std::string("cudaMalloc: ") + cudaGetErrorString(A.last); return BLOKB_E_CUDA; }
+
+int replace_chunks(VoxelList& L, const blokb_dense_chunk* chunks, size_t nChunks, cudaStream_t st, std::string& err) {
     constexpr size_t kCells = size_t(128) * 128 * 128;
-    size_t n = 0;
-    std::vector<uint64_t> emptyKeys;
+    size_t nNew = 0;
+    std::vector<uint64_t> keys(nChunks), nowEmpty;
     for (size_t c = 0; c < nChunks; c++) {
         if (!chunks[c].density || !chunks[c].materialIds) { err = "dense chunk " + std::to_string(c) + ": null array"; return BLOKB_E_ARG; }
-        for (size_t d = 0; d < c; d++)
-            if (chunks[d].cx == chunks[c].cx && chunks[d].cy == chunks[c].cy && chunks[d].cz == chunks[c].cz) { err = "dense chunk listed twice"; return BLOKB_E_ARG; }
+        const int cx = chunks[c].cx, cy = chunks[c].cy, cz = chunks[c].cz;
+        if (cx < -kBias || cx >= kBias || cy < -kBias || cy >= kBias || cz < -kBias || cz >= kBias) { err = "chunk index outside [-8192, 8191]"; return BLOKB_E_UNSUPPORTED; }
+        keys[c] = uint64_t(cz + kBias) << 28 | uint64_t(cy + kBias) << 14 | uint64_t(cx + kBias);
         const float* dn = chunks[c].density;
         size_t k = 0;
         for (size_t i = 0; i < kCells; i++) k += dn[i] > 0.0f;
-        n += k;
-        const int cx = chunks[c].cx, cy = chunks[c].cy, cz = chunks[c].cz;
-        if (cx < -kBias || cx >= kBias || cy < -kBias || cy >= kBias || cz < -kBias || cz >= kBias) { err = "chunk index outside [-8192, 8191]"; return BLOKB_E_UNSUPPORTED; }
-        if (k == 0) emptyKeys.push_back(uint64_t(cz + kBias) << 28 | uint64_t(cy + kBias) << 14 | uint64_t(cx + kBias));
+        nNew += k;
+        if (k == 0) nowEmpty.push_back(keys[c]);
     }
-    std::sort(emptyKeys.begin(), emptyKeys.end());
-    if (n == 0) { out.refNodes = emptyKeys.size(); return 0; }
-    Arena A;
-    int32_t* dXyz = A.get<int32_t>(3 * n); BNULL(dXyz)
-    uint32_t* dMat = A.get<uint32_t>(n); BNULL(dMat)
-    float* dDen = A.get<float>(kCells); BNULL(dDen)
-    uint32_t* dIds = A.get<uint32_t>(kCells); BNULL(dIds)
-    unsigned long long* dCount = A.get<unsigned long long>(1); BNULL(dCount)
-    BCK(cudaMemsetAsync(dCount, 0, 8, st));
-    for (size_t c = 0; c < nChunks; c++) {
-        BCK(cudaMemcpyAsync(dDen, chunks[c].density, kCells * 4, cudaMemcpyHostToDevice, st));
-        BCK(cudaMemcpyAsync(dIds, chunks[c].materialIds, kCells * 4, cudaMemcpyHostToDevice, st));
-        k_dense_emit<<<(unsigned)(kCells / 256), 256, 0, st>>>(dDen, dIds, chunks[c].cx, chunks[c].cy, chunks[c].cz, dXyz, dMat, dCount);
+    std::vector<uint64_t> sortedKeys = keys;
+    std::sort(sortedKeys.begin(), sortedKeys.end());
+    if (std::adjacent_find(sortedKeys.begin(), sortedKeys.end()) != sortedKeys.end()) { err = "dense chunk listed twice"; return BLOKB_E_ARG; }
+    if (L.n + nNew > 0xFFFFFFF0ull) { err = "too many voxels"; return BLOKB_E_UNSUPPORTED; }
+
+    Arena A;  // temporaries; the new list arrays are taken out of it on success
+    const size_t cap = L.n + nNew;
+    int32_t* nx = A.get<int32_t>(3 * std::max<size_t>(cap, 1)); LNULL(nx)
+    uint32_t* nm = A.get<uint32_t>(std::max<size_t>(cap, 1)); LNULL(nm)
+    unsigned long long* dCount = A.get<unsigned long long>(1); LNULL(dCount)
+    unsigned long long kept = 0;
+    if (L.n) {
+        // stable compaction of the voxels that stay (order matters: a voxel listed twice keeps its last material)
+        uint64_t* dKeys = A.get<uint64_t>(std::max<size_t>(nChunks, 1)); LNULL(dKeys)
+        uint8_t* keep = A.get<uint8_t>(L.n); LNULL(keep)
+        if (nChunks) LCK(cudaMemcpyAsync(dKeys, sortedKeys.data(), nChunks * 8, cudaMemcpyHostToDevice, st));
+        k_flag_outside<<<blocks_for(L.n, 256), 256, 0, st>>>(L.xyz, L.n, dKeys, (uint32_t)nChunks, keep);
+        size_t t1 = 0, t2 = 0;
+        LCK(cub::DeviceSelect::Flagged(nullptr, t1, reinterpret_cast<const V3*>(L.xyz), keep, reinterpret_cast<V3*>(nx), dCount, (int64_t)L.n, st));
+        LCK(cub::DeviceSelect::Flagged(nullptr, t2, L.mat, keep, nm, dCount, (int64_t)L.n, st));
+        void* tmp = A.get<uint8_t>(std::max(t1, t2)); LNULL(tmp)
+        LCK(cub::DeviceSelect::Flagged(tmp, t1, reinterpret_cast<const V3*>(L.xyz), keep, reinterpret_cast<V3*>(nx), dCount, (int64_t)L.n, st));
+        LCK(cub::DeviceSelect::Flagged(tmp, t2, L.mat, keep, nm, dCount, (int64_t)L.n, st));
+        LCK(cudaMemcpyAsync(&kept, dCount, 8, cudaMemcpyDeviceToHost, st));
+        LCK(cudaStreamSynchronize(st));
+    }
+    // dCount now doubles as the append cursor of k_dense_emit (64-bit; DeviceSelect wrote the kept count into it)
+    LCK(cudaMemcpyAsync(dCount, &kept, 8, cudaMemcpyHostToDevice, st));
+    if (nNew) {
+        float* dDen = A.get<float>(kCells); LNULL(dDen)
+        uint32_t* dIds = A.get<uint32_t>(kCells); LNULL(dIds)
+        for (size_t c = 0; c < nChunks; c++) {
+            LCK(cudaMemcpyAsync(dDen, chunks[c].density, kCells * 4, cudaMemcpyHostToDevice, st));
+            LCK(cudaMemcpyAsync(dIds, chunks[c].materialIds, kCells * 4, cudaMemcpyHostToDevice, st));
+            k_dense_emit<<<(unsigned)(kCells / 256), 256, 0, st>>>(dDen, dIds, chunks[c].cx, chunks[c].cy, chunks[c].cz, nx, nm, dCount);
+        }
     }
     unsigned long long got = 0;
-    BCK(cudaMemcpyAsync(&got, dCount, 8, cudaMemcpyDeviceToHost, st));
-    BCK(cudaStreamSynchronize(st));
-    if (got != n) { err = "dense chunk arrays changed during the upload"; return BLOKB_E_ARG; }
-    return from_device_voxels(dXyz, dMat, n, st, out, err, &emptyKeys);
+    LCK(cudaMemcpyAsync(&got, dCount, 8, cudaMemcpyDeviceToHost, st));
+    LCK(cudaStreamSynchronize(st));
+    LCK(cudaGetLastError());
+    if (got != kept + nNew) { err = "dense chunk arrays changed during the upload"; return BLOKB_E_ARG; }
+    // commit: the list takes the new arrays, the old ones go
+    for (auto& p : A.ptrs) if (p == nx || p == nm) p = nullptr;
+    if (L.xyz) cudaFree(L.xyz);
+    if (L.mat) cudaFree(L.mat);
+    L.xyz = nx; L.mat = nm; L.n = size_t(got);
+    std::vector<uint64_t> e;
+    std::set_difference(L.emptyKeys.begin(), L.emptyKeys.end(), sortedKeys.begin(), sortedKeys.end(), std::back_inserter(e));
+    std::sort(nowEmpty.begin(), nowEmpty.end());
+    L.emptyKeys.clear();
+    std::merge(e.begin(), e.end(), nowEmpty.begin(), nowEmpty.end(), std::back_inserter(L.emptyKeys));
+    return 0;
+}
+
+int from_list(const VoxelList& L, cudaStream_t st, DeviceBuild& out, std::string& err) {
+    out = DeviceBuild{};
+    if (L.n == 0) { out.refNodes = L.emptyKeys.size(); return 0; }
+    return from_device_voxels(L.xyz, L.mat, L.n, st, out, err, &L.emptyKeys);
+}
+
+int from_dense(const blokb_dense_chunk* chunks, size_t nChunks, cudaStream_t st, DeviceBuild& out, std::string& err, VoxelList* keep) {
+    out = DeviceBuild{};
+    VoxelList L;
+    int rc = replace_chunks(L, chunks, nChunks, st, err);
+    if (!rc) rc = from_list(L, st, out, err);
+    if (!rc && keep) { keep->release(); *keep = std::move(L); L = VoxelList{}; }
+    L.release();
+    return rc;
 }
 
 }  // namespace build

@@ -34,8 +34,21 @@ int from_voxels(const int32_t* xyz, const uint32_t* mat, size_t n, cudaStream_t 
 // emptyChunkKeys (sorted, optional): chunks the reference would pack as a lone root node; they shift later chunks' node offsets.
 int from_device_voxels(const int32_t* dXyz, const uint32_t* dMat, size_t n, cudaStream_t st, DeviceBuild& out, std::string& err,
                        const std::vector<uint64_t>* emptyChunkKeys = nullptr);
-// Dense 128^3 chunks in the reference's Chunk layout (host pointers): cells with density > 0 are filled.
-int from_dense(const blokb_dense_chunk* chunks, size_t nChunks, cudaStream_t st, DeviceBuild& out, std::string& err);
+// The voxel list a world was built from, kept on the device so that dirty chunks can be replaced later
+// (Renderer::updateWorld after ChunkManager::rebuildDirtyChunks) without the host resending the rest of the world.
+struct VoxelList {
+    int32_t* xyz = nullptr;            // n x int32[3], in write order (later entries win)
+    uint32_t* mat = nullptr;
+    size_t n = 0;
+    std::vector<uint64_t> emptyKeys;   // sorted keys of chunks that exist but hold no filled cell
+    void release();
+};
+// Replaces every voxel of the listed chunks by the chunks' cells with density > 0 (chunks new to L are added).
+int replace_chunks(VoxelList& L, const blokb_dense_chunk* chunks, size_t nChunks, cudaStream_t st, std::string& err);
+int from_list(const VoxelList& L, cudaStream_t st, DeviceBuild& out, std::string& err);
+// Dense 128^3 chunks in the reference's Chunk layout (host pointers): cells with density > 0 are filled. keep != nullptr
+// receives the voxel list (caller releases it).
+int from_dense(const blokb_dense_chunk* chunks, size_t nChunks, cudaStream_t st, DeviceBuild& out, std::string& err, VoxelList* keep = nullptr);
 void release(DeviceBuild& b);
 
 }  // namespace build

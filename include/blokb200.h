@@ -181,6 +181,13 @@ typedef struct blokb_dense_chunk {
     const uint32_t* materialIds;
 } blokb_dense_chunk;
 int blokb_upload_dense(blokb_ctx* ctx, const blokb_dense_chunk* chunks, size_t nChunks, const blokb_material* materials, size_t nMaterials);
+/* Editing (applyBrush marks chunks dirty, brush.cpp:13-63; rebuildDirtyChunks rebuilds them and the reference then re-packs and
+ * re-uploads the WHOLE world, chunk_manager.cpp:106-140, renderer.hpp:55-71): after blokb_upload_dense the voxel list stays on the
+ * device, and this call takes only the dirty chunks — their voxels are replaced in the list (chunks not seen before are added,
+ * chunks that became empty keep their lone root node) and the world is rebuilt on the GPU. The result is byte-identical to
+ * blokb_upload_dense of all chunks; the host sends 16 MB per dirty chunk instead of the world. Materials stay as uploaded.
+ * BLOKB_E_STATE unless the current world came from blokb_upload_dense. */
+int blokb_update_dense(blokb_ctx* ctx, const blokb_dense_chunk* chunks, size_t nChunks);
 /* MagicaVoxel .vox import: loadVoxFile + importVoxMaterials + importVoxToChunks of the reference
  * (blok/src/vox_loader.cpp:151-430) restated as "file -> voxel list + material table", the inputs of blokb_upload_voxels.
  * Material id i = palette entry i (1..255) and id 0 = the library's default grey, as in a fresh MaterialLibrary

@@ -282,3 +282,85 @@ def test_scene_dump_rejects_damaged_files(tmp_path):
     b.load_world(path)
     assert b.world_stats()["voxels"] == a.world_stats()["voxels"]
     a.close(); b.close()
+
+
+# ---- editing: dirty chunks only (blokb_update_dense) ------------------------------------------------------------------
+def _brush(chunks, centre, radius, mode, value):
+    """applyBrush (blok/src/brush.cpp:13-63) on the dict-of-dense-arrays stand-in for ChunkManager (voxelSize 1): every chunk the
+    bounding box touches is created, cells within `radius` of the centre get max(d, value) / min(d, value). Returns dirty keys."""
+    c = np.asarray(centre, np.float32)
+    lo = np.floor(c - np.float32(radius)).astype(int)
+    hi = np.floor(c + np.float32(radius)).astype(int) + 1
+    dirty = set()
+    for gz in range(lo[2], hi[2]):
+        for gy in range(lo[1], hi[1]):
+            gx = np.arange(lo[0], hi[0])
+            cz, cy = gz // 128, gy // 128
+            for cx in np.unique(gx // 128):
+                key = (int(cx), int(cy), int(cz))
+                if key not in chunks:
+                    chunks[key] = (np.zeros(128 ** 3, np.float32), np.zeros(128 ** 3, np.uint32))
+                xs = gx[gx // 128 == cx]
+                ws = np.stack([xs + 0.5, np.full(len(xs), gy + 0.5), np.full(len(xs), gz + 0.5)], 1).astype(np.float32)
+                inside = np.sqrt(((ws - c) ** 2).sum(1, dtype=np.float32)) <= np.float32(radius)
+                if not inside.any():
+                    continue
+                t = (xs[inside] - cx * 128) + 128 * (gy - cy * 128) + 16384 * (gz - cz * 128)
+                d = chunks[key][0]
+                d[t] = np.maximum(d[t], value) if mode == "add" else np.minimum(d[t], value)
+                dirty.add(key)
+    return dirty
+
+
+def test_update_dense_equals_full_upload(renderer_factory):
+    """A session of brush edits: after each one only the dirty chunks go to blokb_update_dense; the world must be byte-identical
+    (compact arrays, SubChunkGpu records, stats, traced frame) to blokb_upload_dense of ALL chunks into a fresh context."""
+    xyz, mid, mats = scenes.terrain(200)
+    chunks = _dense_from_voxels(xyz, mid)
+    r = renderer_factory(96, 64)
+    r.add_dense(chunks, mats)
+    cam = Camera((100.0, 160.0, -60.0), 90.0, -35.0)
+    edits = [((100.0, 70.0, 100.0), 9.0, "sub", 0.0),      # dig a crater (inside chunk (0,0,0))
+             ((126.0, 80.0, 126.0), 6.0, "add", 1.0),      # a ball of material-0 voxels across the 8-chunk corner
+             ((300.0, 40.0, 40.0), 3.0, "add", 0.5),       # a brand-new chunk far away (fractional density fills)
+             ((300.0, 40.0, 40.0), 4.0, "sub", 0.0),       # ... erased again: that chunk stays, as a lone root node
+             ((-20.0, 60.0, 30.0), 5.0, "add", 1.0)]       # negative coordinates
+    for k, (centre, radius, mode, value) in enumerate(edits):
+        dirty = _brush(chunks, centre, radius, mode, value)
+        assert dirty
+        r.update_dense({key: chunks[key] for key in dirty})
+        full = blok_b200.Renderer(96, 64, 0)
+        full.add_dense(chunks, mats)
+        ea, eb = _export(r), _export(full)
+        for which in ea:
+            assert ea[which].tobytes() == eb[which].tobytes(), (k, which)
+        assert r.world_export(WORLD_SUBCHUNKS).tobytes() == full.world_export(WORLD_SUBCHUNKS).tobytes(), k
+        sa, sb = r.world_stats(), full.world_stats()
+        for key in ("nodes", "subChunks", "bricks", "blocks", "voxels", "compactBytes", "levels"):
+            assert sa[key] == sb[key], (k, key)
+        assert _trace_all(r, cam) == _trace_all(full, cam), k
+        full.close()
+    # the erased far chunk still counts one node (checked against the reference's ChunkManager in
+    # test_dense_density_and_empty_chunk_follow_the_reference): total = sum over chunks of 1 + 8 * interior
+    assert any(not (d > 0).any() for d, _ in chunks.values())
+
+
+def test_update_dense_needs_an_editable_world(renderer_factory):
+    xyz, mid, mats = CASES["terrain96"]
+    r = renderer_factory(64, 64)
+    z = {(0, 0, 0): (np.zeros(128 ** 3, np.float32), np.zeros(128 ** 3, np.uint32))}
+    with pytest.raises(BlokbError):
+        r.update_dense(z)                    # no world at all
+    r.add_voxels(xyz, mid, mats)
+    with pytest.raises(BlokbError, match="blokb_upload_dense"):
+        r.update_dense(z)                    # world not uploaded as dense chunks
+    r.add_dense(_dense_from_voxels(xyz, mid), mats)
+    r.update_dense({})                       # nothing dirty: no-op
+    want = _export(r)
+    r.update_dense(_dense_from_voxels(xyz, mid))   # the same content again: unchanged world
+    got = _export(r)
+    for k in want:
+        assert want[k].tobytes() == got[k].tobytes()
+    r.add_voxels(xyz, mid, mats)             # replaced by a non-editable world again
+    with pytest.raises(BlokbError, match="blokb_upload_dense"):
+        r.update_dense(z)
