@@ -645,7 +645,7 @@ int blokb_render(blokb_ctx* c, void* stream) {
     if (int rc = ready(c, true)) return rc;
     if (c->frame.sampleCount == 0) return fail(BLOKB_E_ARG, "frame.sampleCount is 0");
     CK(launch_render(c->dw, c->frame, c->buf.color, c->buf.worldPos, c->buf.normalRough, c->buf.albedoMetal, c->buf.motion, st(c), pick(c, stream)));
-    c->launches++;
+    c->launches += 2;  // k_gbuffer + k_path<.., kColor>
     return 0;
 }
 int blokb_trace_path(blokb_ctx* c, uint32_t sampleBegin, uint32_t sampleEnd, void* stream) {
