@@ -89,10 +89,7 @@ __global__ void __launch_bounds__(256) k_trace_rays(const __grid_constant__ Devi
 
 // Sample-0 primary rays (raygen.rgen:193-229) -> hit records; optionally the sun shadow ray of :280-298.
 template <bool kShadow, bool kStats>
-#ifndef BLOKB_PRIMARY_MIN_BLOCKS
-#define BLOKB_PRIMARY_MIN_BLOCKS 1
-#endif
-__global__ void __launch_bounds__(256, BLOKB_PRIMARY_MIN_BLOCKS) k_primary(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
+__global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
                                                  const __grid_constant__ PeerOut out, const __grid_constant__ PeerOut shadow,
                                                  unsigned long long* stats) {
     uint32_t px, py;
@@ -176,6 +173,8 @@ __global__ void __launch_bounds__(256) k_gbuffer(const __grid_constant__ DeviceW
 // sample) seeding so that any partition of the sample range over launches or GPUs draws the same paths.
 // kColor: the launch covers ALL of the frame's samples and stores color = sum / count with the firefly clamp
 // (raygen.rgen:383-392) into accum.dst[0] — the colour image — instead of accumulating.
+// No minBlocksPerSM on purpose: left alone, ptxas settles on 64 registers (4 blocks per SM, a few spilled words) = 21.4 ms for
+// 8 spp at 4K; __launch_bounds__(256, 1) gives 90 registers / 25.9 ms, (256, 2) 22.2, (256, 3) 22.6, (256, 5) 24.1.
 template <bool kStats, bool kColor>
 __global__ void __launch_bounds__(256) k_path(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F, uint32_t sBegin, uint32_t sEnd,
                                               const __grid_constant__ PeerOut accum, unsigned long long* stats) {
