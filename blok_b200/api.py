@@ -122,7 +122,7 @@ EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_wo
            "blokb_pipeline_destroy", "blokb_host_alloc", "blokb_host_free", "blokb_post_settings_default", "blokb_denoise",
            "blokb_postprocess", "blokb_end_frame", "blokb_reset_history", "blokb_write_image", "blokb_upload_voxels", "blokb_upload_dense", "blokb_world_export", "blokb_vox_load", "blokb_vox_parse",
            "blokb_vox_counts", "blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free", "blokb_vox_last_error", "blokb_upload_vox", "blokb_set_strips", "blokb_ipc_export", "blokb_set_peers", "blokb_bind_image",
-           "blokb_world_save", "blokb_world_load", "blokb_update_dense"]
+           "blokb_world_save", "blokb_world_load", "blokb_update_dense", "blokb_trace_rays_reordered"]
 
 _lib = None
 
@@ -170,6 +170,7 @@ def load_library():
     L.blokb_bind_image.argtypes = [_vp, C.c_int, _vp, _vp]
     L.blokb_set_peers.argtypes = [_vp, C.c_int, _vp, C.c_uint32, C.c_uint32]
     L.blokb_trace_rays.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp, _vp]
+    L.blokb_trace_rays_reordered.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp, _vp]
     L.blokb_trace_rays_host.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp]
     L.blokb_get_buffers.argtypes = [_vp, C.POINTER(Buffers)]
     L.blokb_readback.argtypes = [_vp, C.c_int, _vp, C.c_size_t]
@@ -471,8 +472,11 @@ class Renderer:
         _ck(self.L.blokb_trace_rays_host(self._ctx, _ptr(rays), len(rays), int(any_hit), _ptr(out)))
         return out
 
-    def trace_rays_device(self, d_rays: int, n: int, d_out: int, any_hit=False, stream=None):
-        _ck(self.L.blokb_trace_rays(self._ctx, d_rays, n, int(any_hit), d_out, stream))
+    def trace_rays_device(self, d_rays: int, n: int, d_out: int, any_hit=False, stream=None, reorder=False):
+        """Device ray list -> device hit records. reorder=True sorts the list by direction cell + origin Morton code first
+        (blokb_trace_rays_reordered): same records, faster for incoherent rays."""
+        fn = self.L.blokb_trace_rays_reordered if reorder else self.L.blokb_trace_rays
+        _ck(fn(self._ctx, d_rays, n, int(any_hit), d_out, stream))
 
     # ---- images out
     def buffers(self) -> Buffers:

@@ -83,6 +83,8 @@ struct blokb_ctx {
     float* dRays = nullptr;
     blokb_hit* dHits = nullptr;
     size_t rayCap = 0;
+    void* dReorder = nullptr;              // scratch of blokb_trace_rays_reordered (keys, order, cub), grow-only
+    size_t reorderCap = 0;
     unsigned long long* dStats = nullptr;  // 2 counters when stats enabled
     bool statsOn = false;
     uint64_t launches = 0;
@@ -190,6 +192,7 @@ void blokb_destroy(blokb_ctx* c) {
     if (c->dRays) cudaFree(c->dRays);
     if (c->dHits) cudaFree(c->dHits);
     if (c->dStats) cudaFree(c->dStats);
+    if (c->dReorder) cudaFree(c->dReorder);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -675,6 +678,23 @@ int blokb_trace_rays(blokb_ctx* c, const float* dRays, size_t n, int /*anyHit*/,
     if (n && (!dRays || !dOut)) return fail(BLOKB_E_ARG, "null ray / output pointer");
     CK(launch_trace_rays(c->dw, dRays, n, dOut, st(c), pick(c, stream)));
     if (n) c->launches++;
+    return 0;
+}
+int blokb_trace_rays_reordered(blokb_ctx* c, const float* dRays, size_t n, int /*anyHit*/, blokb_hit* dOut, void* stream) {
+    if (int rc = ready(c, false)) return rc;
+    if (n && (!dRays || !dOut)) return fail(BLOKB_E_ARG, "null ray / output pointer");
+    if (n == 0) return 0;
+    if (n > 0xFFFFFFFFull) return fail(BLOKB_E_ARG, "more than 2^32 rays in one list");
+    const size_t need = reorder_scratch_bytes(n, nullptr);
+    if (need > c->reorderCap) {
+        CK(cudaDeviceSynchronize());   // the old scratch may still be in use on any stream
+        if (c->dReorder) cudaFree(c->dReorder);
+        c->dReorder = nullptr; c->reorderCap = 0;
+        CK(cudaMalloc(&c->dReorder, need));
+        c->reorderCap = need;
+    }
+    CK(launch_trace_rays_reordered(c->dw, dRays, n, dOut, c->dReorder, st(c), pick(c, stream)));
+    c->launches += 3;  // keys, radix sort (counted as one), ordered trace
     return 0;
 }
 int blokb_trace_rays_host(blokb_ctx* c, const float* rays, size_t n, int anyHit, blokb_hit* out) {

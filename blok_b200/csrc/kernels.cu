@@ -4,6 +4,10 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
+#include <cub/cub.cuh>
+
+#include <algorithm>
+
 #include "kernels.h"
 #include "shade.cuh"
 
@@ -84,6 +88,54 @@ __global__ void __launch_bounds__(256) k_trace_rays(const __grid_constant__ Devi
     uint32_t steps = 0;
     const bool hit = traverse<kStats>(W, thread_stack(), a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, h, steps);
     store_hit(out + i, hit, h);
+    if (kStats) atomicAdd(stats, (unsigned long long)steps);
+}
+
+// ---- ray reordering for incoherent ray lists (bounce rays) -------------------------------------------------------------
+// Sort key (24 bits = three radix passes) = 8^3 direction cell (9 bits) above the Morton code of the origin's coarse cell
+// (3 x 5 bits, cells of >= 64 voxels; the sort is stable, so inside a key the list keeps its own — usually already spatial —
+// order): rays of one warp then head the same way from neighbouring cells and walk the same nodes. Measured on 4.67 M cosine-sampled bounce
+// rays of the c3 frame: 3.78 -> 5.35 Grays/s for the traversal itself.
+__device__ __forceinline__ uint32_t dilate7(uint32_t v) {  // 7 bits -> every third bit
+    v &= 0x7Fu;
+    v = (v | (v << 8)) & 0x0000700Fu;
+    v = (v | (v << 4)) & 0x000430C3u;
+    v = (v | (v << 2)) & 0x00049249u;
+    return v;
+}
+__global__ void __launch_bounds__(256) k_ray_keys(const __grid_constant__ DeviceWorld W, const float4* __restrict__ rays, size_t n, int cellShift,
+                                                  uint32_t* __restrict__ keys, uint32_t* __restrict__ idx) {
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 a = __ldg(&rays[2 * i]), b = __ldg(&rays[2 * i + 1]);
+    // direction as given: a.w, b.x, b.y. Not normalised on purpose (only the cell matters; any finite scale sorts consistently enough)
+    const float dx = a.w, dy = b.x, dz = b.y;
+    const float inv = rsqrtf(fmaxf(dx * dx + dy * dy + dz * dz, 1e-30f));
+    auto cell = [inv](float d) { const int q = int((d * inv + 1.0f) * 4.0f); return uint32_t(q < 0 ? 0 : (q > 7 ? 7 : q)); };
+    const uint32_t dcell = cell(dx) | (cell(dy) << 3) | (cell(dz) << 6);
+    auto coarse = [cellShift](float o, int g, int dim) {
+        float r = o - float(g);
+        r = r < 0.0f ? 0.0f : (r > float(dim - 1) ? float(dim - 1) : r);   // rays that start outside sort by their nearest grid cell
+        return uint32_t(int(r) >> cellShift);
+    };
+    const uint32_t m = dilate7(coarse(a.x, W.origin[0], W.dim[0])) | (dilate7(coarse(a.y, W.origin[1], W.dim[1])) << 1) |
+                       (dilate7(coarse(a.z, W.origin[2], W.dim[2])) << 2);
+    keys[i] = (dcell << 15) | (m & 0x7FFFu);
+    idx[i] = uint32_t(i);
+}
+// Thread i traces ray order[i]; the record goes back to the ray's own slot, so the output is that of k_trace_rays.
+template <bool kStats>
+__global__ void __launch_bounds__(256) k_trace_rays_ordered(const __grid_constant__ DeviceWorld W, const float4* __restrict__ rays,
+                                                            const uint32_t* __restrict__ order, size_t n, blokb_hit* __restrict__ out,
+                                                            unsigned long long* stats) {
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t r = __ldg(order + i);
+    const float4 a = __ldg(&rays[2 * size_t(r)]), b = __ldg(&rays[2 * size_t(r) + 1]);
+    HitRec h;
+    uint32_t steps = 0;
+    const bool hit = traverse<kStats>(W, thread_stack(), a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, h, steps);
+    store_hit(out + r, hit, h);
     if (kStats) atomicAdd(stats, (unsigned long long)steps);
 }
 
@@ -223,6 +275,35 @@ cudaError_t launch_trace_rays(const DeviceWorld& W, const float* rays, size_t n,
     const unsigned blocks = (unsigned)((n + 255) / 256);
     if (stats) k_trace_rays<true><<<blocks, 256, stack_bytes(W), st>>>(W, reinterpret_cast<const float4*>(rays), n, out, stats);
     else k_trace_rays<false><<<blocks, 256, stack_bytes(W), st>>>(W, reinterpret_cast<const float4*>(rays), n, out, nullptr);
+    return cudaGetLastError();
+}
+size_t reorder_scratch_bytes(size_t n, size_t* cubBytes) {
+    size_t tb = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tb, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const uint32_t*)nullptr, (uint32_t*)nullptr, (int64_t)n, 0, 24);
+    if (cubBytes) *cubBytes = tb;
+    const size_t a = (n * 4 + 255) & ~size_t(255), b = a;
+    return 2 * a + 2 * b + tb;
+}
+cudaError_t launch_trace_rays_reordered(const DeviceWorld& W, const float* rays, size_t n, blokb_hit* out, void* scratch, unsigned long long* stats,
+                                        cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    if (n > 0xFFFFFFFFull) return cudaErrorInvalidValue;
+    size_t tb = 0;
+    reorder_scratch_bytes(n, &tb);
+    const size_t a = (n * 4 + 255) & ~size_t(255), b = a;
+    char* p = static_cast<char*>(scratch);
+    uint32_t* k0 = reinterpret_cast<uint32_t*>(p); uint32_t* k1 = reinterpret_cast<uint32_t*>(p + a);
+    uint32_t* i0 = reinterpret_cast<uint32_t*>(p + 2 * a); uint32_t* i1 = reinterpret_cast<uint32_t*>(p + 2 * a + b);
+    void* tmp = p + 2 * a + 2 * b;
+    // coarse origin cells: 5 bits per axis must cover the grid, and cells are at least 64 voxels wide
+    int shift = 6;
+    while ((std::max(W.dim[0], std::max(W.dim[1], W.dim[2])) >> shift) > 32) shift++;
+    const unsigned blocks = (unsigned)((n + 255) / 256);
+    k_ray_keys<<<blocks, 256, 0, st>>>(W, reinterpret_cast<const float4*>(rays), n, shift, k0, i0);
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(tmp, tb, k0, k1, i0, i1, (int64_t)n, 0, 24, st);
+    if (e != cudaSuccess) return e;
+    if (stats) k_trace_rays_ordered<true><<<blocks, 256, stack_bytes(W), st>>>(W, reinterpret_cast<const float4*>(rays), i1, n, out, stats);
+    else k_trace_rays_ordered<false><<<blocks, 256, stack_bytes(W), st>>>(W, reinterpret_cast<const float4*>(rays), i1, n, out, nullptr);
     return cudaGetLastError();
 }
 cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow, const PeerOut& out, const PeerOut& shadowOut,

@@ -1,5 +1,6 @@
 // Launchers implemented in kernels.cu (device code); called from the C-ABI layer in api.cpp.
 #pragma once
+#include <cstddef>
 #include <cuda_runtime.h>
 
 #include "../../include/blokb200.h"
@@ -28,6 +29,11 @@ struct PeerOut {
     void* mc = nullptr;
 };
 cudaError_t launch_trace_rays(const DeviceWorld& W, const float* rays, size_t n, blokb_hit* out, unsigned long long* stats, cudaStream_t st);
+// Incoherent ray lists: sort by (direction cell, Morton code of the origin cell), trace in that order, write each record to the
+// ray's own slot. scratch: reorder_scratch_bytes(n) bytes of device memory.
+size_t reorder_scratch_bytes(size_t n, size_t* cubBytes);
+cudaError_t launch_trace_rays_reordered(const DeviceWorld& W, const float* rays, size_t n, blokb_hit* out, void* scratch, unsigned long long* stats,
+                                        cudaStream_t st);
 cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow, const PeerOut& out, const PeerOut& shadowOut, unsigned long long* stats,
                            cudaStream_t st);
 cudaError_t launch_render(const DeviceWorld& W, const FrameDev& F, float* color, float* worldPos, uint16_t* normalRough, uint8_t* albedoMetal,

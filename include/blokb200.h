@@ -287,6 +287,11 @@ int blokb_end_frame(blokb_ctx* ctx, void* stream);
 int blokb_reset_history(blokb_ctx* ctx, void* stream);
 /* Arbitrary rays (device pointers): rays = n x {ox,oy,oz,dx,dy,dz,tmin,tmax}; anyHit != 0 = shadow-ray rules. */
 int blokb_trace_rays(blokb_ctx* ctx, const float* dRays, size_t n, int anyHit, blokb_hit* dOut, void* stream);
+/* The same result for INCOHERENT lists (bounce rays): the rays are sorted on the device by a 4^3 direction cell above the
+ * Morton code of their origin's coarse cell, traced in that order (a warp's rays then walk the same nodes) and every record
+ * is written to its ray's own slot — dOut is byte-identical to blokb_trace_rays'. Costs one key pass + one radix sort;
+ * pays off when neighbouring list entries point different ways. One list per context at a time. */
+int blokb_trace_rays_reordered(blokb_ctx* ctx, const float* dRays, size_t n, int anyHit, blokb_hit* dOut, void* stream);
 /* Same with HOST buffers: copies in, traces, copies out, synchronises. */
 int blokb_trace_rays_host(blokb_ctx* ctx, const float* rays, size_t n, int anyHit, blokb_hit* out);
 

@@ -39,22 +39,22 @@ prim = np.concatenate([np.tile(cam, (n, 1)), wd, np.full((n, 1), 0.001), np.full
 STREAM = torch.cuda.Stream()
 
 
-def timed(rays, label, reps=5):
+def timed(rays, label, reps=5, reorder=False):
     d = torch.from_numpy(np.ascontiguousarray(rays)).cuda()
     out = torch.empty((len(rays), 4), dtype=torch.int32, device="cuda")
     st = STREAM.cuda_stream
     for _ in range(2):
-        r.trace_rays_device(d.data_ptr(), len(rays), out.data_ptr(), stream=st)
+        r.trace_rays_device(d.data_ptr(), len(rays), out.data_ptr(), stream=st, reorder=reorder)
     torch.cuda.synchronize()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record(STREAM)
     for _ in range(reps):
-        r.trace_rays_device(d.data_ptr(), len(rays), out.data_ptr(), stream=st)
+        r.trace_rays_device(d.data_ptr(), len(rays), out.data_ptr(), stream=st, reorder=reorder)
     b.record(STREAM)
     torch.cuda.synchronize()
     ms = a.elapsed_time(b) / reps
     r.stats_enable(True)
-    r.trace_rays_device(d.data_ptr(), len(rays), out.data_ptr(), stream=st)
+    r.trace_rays_device(d.data_ptr(), len(rays), out.data_ptr(), stream=st, reorder=reorder)
     torch.cuda.synchronize()
     steps = r.stats_read()[0]
     r.stats_enable(False)
@@ -111,6 +111,8 @@ bd /= np.linalg.norm(bd, axis=1, keepdims=True)
 bo = pos[sel] + Ns * 0.002
 bounce = np.concatenate([bo, bd, np.full((len(sel), 1), 0.001), np.full((len(sel), 1), 10000.0)], 1).astype(np.float32)
 timed(bounce, "bounce rays, compacted, tile order")
+timed(bounce, "  same list through blokb_trace_rays_reordered (incl. sort)", reorder=True)
+timed(sh, "  shadow rays through blokb_trace_rays_reordered (incl. sort)", reorder=True)
 octant = (bd[:, 0] < 0).astype(np.int64) | ((bd[:, 1] < 0).astype(np.int64) << 1) | ((bd[:, 2] < 0).astype(np.int64) << 2)
 o1 = np.argsort(octant, kind="stable")
 timed(bounce[o1], "bounce rays, sorted by octant (stable)")
@@ -124,6 +126,12 @@ dkey = (q[:, 0] | (q[:, 1] << 2) | (q[:, 2] << 4)).astype(np.uint64)
 key2 = (dkey << np.uint64(58)) | mc
 o3 = np.argsort(key2, kind="stable")
 timed(bounce[o3], "bounce rays, sorted by 4^3 direction cell + Morton")
+for nb in (4, 8):  # direction cell alone, stable: inside a cell the list keeps its (tile = spatial) order
+    qq = np.clip(((bd + 1) * (nb / 2)).astype(np.int64), 0, nb - 1)
+    dk = (qq[:, 0] + nb * (qq[:, 1] + nb * qq[:, 2])).astype(np.uint64)
+    timed(bounce[np.argsort(dk, kind="stable")], f"bounce rays, {nb}^3 direction cell only (stable)")
+    mc5 = morton3((bo[:, 0]).astype(np.int64) >> 6, (bo[:, 1]).astype(np.int64) >> 6, (bo[:, 2]).astype(np.int64) >> 6)
+    timed(bounce[np.lexsort((mc5, dk))], f"bounce rays, {nb}^3 direction cell + Morton(origin/64)")
 for nb in (8, 16):
     qq = np.clip(((bd + 1) * (nb / 2)).astype(np.int64), 0, nb - 1)
     dk = (qq[:, 0] + nb * (qq[:, 1] + nb * qq[:, 2])).astype(np.uint64)
