@@ -31,6 +31,16 @@ def test_cabi_library_exports_every_declared_symbol():
         assert hasattr(lib, name), name
 
 
+def test_cabi_header_is_plain_c():
+    """The drop-in boundary is a C ABI: the header must compile as C11 on its own (no C++ types, no torch, no CUDA headers)."""
+    import subprocess
+    hdr = os.path.join(ROOT, "include", "blokb200.h")
+    r = subprocess.run(["gcc", "-x", "c", "-std=c11", "-fsyntax-only", "-Wall", "-Werror", hdr], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    src = open(hdr).read()
+    assert "torch" not in src and "cuda_runtime" not in src and "std::" not in src
+
+
 def test_no_cpu_fallback_without_device():
     """On a box without a GPU the product must fail loudly, not compute on the CPU."""
     import torch
