@@ -1,3 +1,5 @@
+"""Probe: does this box give torch symmetric memory an NVLink multicast address? (run under torchrun, >= 2 ranks)
+Prints every rank's peer buffer pointers and multicast pointer; sharding.connect_multicast relies on the latter."""
 import os, torch, torch.distributed as dist
 rank=int(os.environ["RANK"]); local=int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local); dev=torch.device("cuda",local)
