@@ -15,7 +15,15 @@ __global__ void __launch_bounds__(kBX* kBY, 4) k_temporal_variance(const __grid_
     if (x >= (int)P.width || y >= (int)P.height) return;
     temporal_variance_pixel(P, io, x, y);
 }
-__global__ void __launch_bounds__(kBX* kBY, 4) k_atrous(const __grid_constant__ PostFrame P, int stepSize, const float* __restrict__ in,
+#ifndef BLOKB_ATROUS_MIN_BLOCKS
+#define BLOKB_ATROUS_MIN_BLOCKS 5  // measured at 4K: 3 blocks/SM 4.43 ms, 4 (63 regs) 3.77, none (58 regs) 3.83, 5 (48 regs) 3.49, 6 (40 regs) 3.48 per denoise
+#endif
+#if BLOKB_ATROUS_MIN_BLOCKS > 0
+#define BLOKB_ATROUS_BOUNDS __launch_bounds__(kBX* kBY, BLOKB_ATROUS_MIN_BLOCKS)
+#else
+#define BLOKB_ATROUS_BOUNDS __launch_bounds__(kBX* kBY)
+#endif
+__global__ void BLOKB_ATROUS_BOUNDS k_atrous(const __grid_constant__ PostFrame P, int stepSize, const float* __restrict__ in,
                                                      const float* __restrict__ variance, const float* __restrict__ worldPos,
                                                      const uint16_t* __restrict__ normalRough, float* __restrict__ out) {
     const int x = blockIdx.x * kBX + threadIdx.x, y = blockIdx.y * kBY + threadIdx.y;
