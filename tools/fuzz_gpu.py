@@ -19,6 +19,24 @@ from blok_b200 import WORLD_BLOCKFIRSTLEAF, WORLD_NODES, WORLD_VOXELMAT, WorldSv
 from oracle import pyoracle  # noqa: E402
 from tests.conftest import make_rays, to_scene  # noqa: E402
 
+from bench import shadow_rays  # noqa: E402  (raygen.rgen:280-298 restated in numpy for the checker side)
+
+
+def _lit_mask(rays, h, t):
+    """Which primary hits cast a sun shadow ray (the selection inside bench.shadow_rays, exposed as a mask)."""
+    normals = np.array([[1, 0, 0], [-1, 0, 0], [0, 1, 0], [0, -1, 0], [0, 0, 1], [0, 0, -1]], np.float32)
+    hit = t >= 0
+    N = normals[np.where(hit, h[:, 3], 0)]
+    d = rays[:, 3:6]
+    flip = ((N[:, 0] * d[:, 0] + N[:, 1] * d[:, 1]) + N[:, 2] * d[:, 2]) > 0
+    N = np.where(flip[:, None], -N, N)
+    s = np.array([0.5, 0.8, 0.3], np.float32)
+    sun = (s * (np.float32(1.0) / np.sqrt((s[0] * s[0] + s[1] * s[1]) + s[2] * s[2], dtype=np.float32))).astype(np.float32)
+    return ((N[:, 0] * sun[0] + N[:, 1] * sun[1]) + N[:, 2] * sun[2]) > 0
+
+
+FRAME = {}
+frames_total = 0
 budget = float(sys.argv[1]) if len(sys.argv) > 1 else 60.0
 seed0 = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 O = pyoracle.RefLib() if os.path.exists(pyoracle.REF_SO) else pyoracle.OracleLib()
@@ -73,9 +91,42 @@ while time.time() < t_end:
             if any(mm):
                 print(f"MISMATCH seed {seed} ({label}, reorder={reorder}): node/t/material/prim/face = {mm}; voxels {len(xyz)} extent {extent} offset {off}")
                 sys.exit(1)
+    # ---- frame kernels: a random camera, primary + sun-shadow pass (k_primary<true>) vs the checker's primary rays and shadow rays
+    centre = off + extent / 2.0
+    dist = rng.uniform(0.2, 2.5) * extent
+    ang, elev = rng.uniform(0, 2 * np.pi), rng.uniform(-0.3, 1.2)
+    pos = centre + dist * np.array([np.cos(ang) * np.cos(elev), np.sin(elev), np.sin(ang) * np.cos(elev)])
+    look = centre + rng.normal(size=3) * extent * 0.2 - pos
+    yaw = float(np.degrees(np.arctan2(look[2], look[0])))
+    pitch = float(np.clip(np.degrees(np.arctan2(look[1], np.hypot(look[0], look[2]))), -89, 89))
+    cam = blok_b200.Camera(tuple(float(v) for v in pos), yaw, pitch, fov=float(rng.choice([30.0, 60.0, 90.0, 110.0])))
+    fw, fh = (int(v) for v in rng.choice([[64, 64], [200, 120], [133, 77], [256, 144]]))
+    ubo = cam.frame(fw, fh, int(rng.integers(0, 1000)), 1)
+    prays = O.primary_rays(ubo.to_numpy())
+    ph, pt, _ = O.trace(to_scene(world), prays, threads=os.cpu_count() or 1)
+    srays = shadow_rays(prays, ph, pt)
+    lit_idx = np.nonzero((pt >= 0) & _lit_mask(prays, ph, pt))[0]
+    _, st, _ = O.trace(to_scene(world), srays, any_hit=True, threads=os.cpu_count() or 1) if len(srays) else (None, np.zeros(0, np.float32), None)
+    want_shadow = np.zeros(fw * fh, np.uint8)
+    want_shadow[lit_idx] = np.where(st >= 0, 2, 1)
+    for r, label in ((a, "host-built world"), (b, "device-built world")):
+        if (label, fw, fh) not in FRAME:
+            FRAME[(label, fw, fh)] = blok_b200.Renderer(fw, fh, 0)
+        r2 = FRAME[(label, fw, fh)]
+        (r2.add_world(world) if label.startswith("host") else r2.add_voxels(xyz, mid, mats))
+        r2.trace_primary(ubo, shadow=True)
+        out = r2.readback(blok_b200.IMG_HIT).reshape(-1)
+        sh = r2.readback(blok_b200.IMG_SHADOW).reshape(-1)
+        phit = pt >= 0
+        mm = [int((out["node"] != ph[:, 1]).sum()), int((out["t"].view(np.uint32) != pt.view(np.uint32)).sum()),
+              int((out["material"] != ph[:, 2]).sum()), int(((out["facePrim"] & 7)[phit] != ph[phit, 3]).sum()), int((sh != want_shadow).sum())]
+        if any(mm):
+            print(f"MISMATCH seed {seed} frame ({label}): node/t/material/face/shadow = {mm}; camera {pos} yaw {yaw} pitch {pitch} {fw}x{fh}")
+            sys.exit(1)
+    frames_total += 2
     rounds += 1
     rays_total += 4 * n
     seed += 1
-print(f"fuzz ok: {rounds} random worlds (seeds {seed0}..{seed - 1}), {rays_total} ray traces bit-exact against the checker "
+print(f"fuzz ok: {rounds} random worlds (seeds {seed0}..{seed - 1}), {rays_total} ray traces and {frames_total} primary+shadow frames bit-exact against the checker "
       f"({type(O).__name__}), device-built == host-built on every world")
 a.close(); b.close()
