@@ -122,7 +122,10 @@ BLOKB_HD F3 face_normal(uint32_t face) {  // hit.rchit:46-53
 struct Surface { F3 albedo, emission; float roughness, metallic; };
 BLOKB_HD Surface fetch_surface(const DeviceWorld& W, uint32_t materialId) {  // hit.rchit:62-75
     const uint32_t id = materialId < 65535u ? materialId : 65535u;
-    const float4 a = __ldg(&W.materials[2 * id]), b = __ldg(&W.materials[2 * id + 1]);
+    // An id beyond the uploaded table is outside the shader's storage buffer: undefined in the reference, an all-zero record
+    // under Vulkan's robustBufferAccess. Same here (never a wild read): black, non-emissive, roughness floor.
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+    if (id < W.nMaterials) { a = __ldg(&W.materials[2 * id]); b = __ldg(&W.materials[2 * id + 1]); }
     const uint32_t flags = __float_as_uint(a.w);
     Surface s;
     s.albedo = f3(a.x, a.y, a.z);

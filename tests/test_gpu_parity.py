@@ -240,3 +240,25 @@ def test_reordered_ray_list_gives_the_same_records(renderer_factory):
         assert torch.equal(a, b)
         assert int((a[:, 0] != -1).sum()) > 0 or n == 1
     r.trace_rays_device(0, 0, 0, reorder=True)  # empty list: no-op
+
+
+def test_material_ids_beyond_the_table_read_as_zero_records(renderer_factory):
+    """Found by tools/fuzz_gpu.py: a voxel whose material id has no entry in the uploaded table made the shading kernels read
+    past the table. The reference's behaviour is undefined there (storage-buffer overrun); the product reads an all-zero record
+    (robustBufferAccess semantics): the frame renders, geometry images are unaffected, albedo is black."""
+    xyz, mid, mats = scenes.terrain(96)
+    r = renderer_factory(64, 64)
+    cam = Camera((48.0, 70.0, -30.0), 90.0, -25.0)
+    f = cam.frame(64, 64, 0, 4)
+    r.add_voxels(xyz, mid, mats)
+    r.render(f)
+    wp = r.readback(IMG_WORLDPOS).copy()
+    r.add_voxels(xyz, (mid + 70000).astype(np.uint32), mats)   # clamps to 65535 in hit.rchit:62 — far beyond the 17 entries
+    r.render(f)
+    r.sync()
+    assert r.readback(IMG_WORLDPOS).tobytes() == wp.tobytes()
+    am = r.readback(IMG_ALBEDOMETAL)
+    hit = wp[..., 3] < 9999.0
+    assert hit.any() and np.all(am[hit][:, :3] == 0)
+    assert np.isfinite(r.readback(IMG_COLOR)).all()
+    r.reset_accum(); r.trace_path(0, 2); r.resolve(); r.sync()

@@ -37,6 +37,7 @@ def _lit_mask(rays, h, t):
 
 FRAME = {}
 frames_total = 0
+renders_total = 0
 budget = float(sys.argv[1]) if len(sys.argv) > 1 else 60.0
 seed0 = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 O = pyoracle.RefLib() if os.path.exists(pyoracle.REF_SO) else pyoracle.OracleLib()
@@ -124,9 +125,39 @@ while time.time() < t_end:
             print(f"MISMATCH seed {seed} frame ({label}): node/t/material/face/shadow = {mm}; camera {pos} yaw {yaw} pitch {pitch} {fw}x{fh}")
             sys.exit(1)
     frames_total += 2
+    # ---- every 8th world: the full raygen (blokb_render = k_gbuffer + k_path<kColor>) against the checker's, 64x64, 4 spp
+    if rounds % 8 == 0:
+        prev_cam = blok_b200.Camera(tuple(float(v) + 0.37 for v in pos), yaw + 1.5, pitch - 0.5, fov=cam.fov)
+        ubo_r = cam.frame(64, 64, int(rng.integers(0, 1000)), 4, prev=prev_cam)
+        ref = O.render(to_scene(world), ubo_r.to_numpy(), threads=os.cpu_count() or 1)
+        rr = FRAME.get(("render",)) or FRAME.setdefault(("render",), blok_b200.Renderer(64, 64, 0))
+        rr.add_voxels(xyz, mid, mats)
+        rr.render(ubo_r)
+        wp = rr.readback(blok_b200.IMG_WORLDPOS)
+        nr = rr.readback(blok_b200.IMG_NORMALROUGH).astype(np.float32)
+        am = rr.readback(blok_b200.IMG_ALBEDOMETAL).astype(np.int32)
+        mv = rr.readback(blok_b200.IMG_MOTION).astype(np.float32)
+        col = rr.readback(blok_b200.IMG_COLOR)
+        rel = np.abs(col[..., :3] - ref["color"][..., :3]) / (np.abs(ref["color"][..., :3]) + 1e-3)
+        problems = []
+        in_table = int(mid.max()) < len(mats)   # ids beyond the material table are undefined in the reference (its checker reads past the array)
+        if wp.tobytes() != ref["worldPos"].tobytes(): problems.append("worldPos bits")
+        if not np.array_equal(nr, ref["normalRough"].astype(np.float16).astype(np.float32)): problems.append("normalRough")
+        if np.abs(am - np.rint(np.clip(ref["albedoMetal"], 0, 1) * 255).astype(np.int32)).max() > 1: problems.append("albedoMetal")
+        with np.errstate(over="ignore", invalid="ignore"):
+            mref = ref["motion"][..., :2].astype(np.float16).astype(np.float32)   # the image is rg16f: compare at its precision
+            mbad = ~np.isclose(mv, mref, rtol=4e-3, atol=2e-3, equal_nan=True)
+        if mbad.any():
+            i = tuple(np.argwhere(mbad)[0])
+            problems.append(f"motion ({int(mbad.sum())} texels, first {i}: got {mv[i]} want {mref[i]})")
+        if np.mean(rel.max(-1) < 2e-3) < 0.99: problems.append(f"radiance ({np.mean(rel.max(-1) < 2e-3):.4f} of pixels within 2e-3)")
+        if problems and in_table:
+            print(f"MISMATCH seed {seed} render: {problems}; camera {pos} yaw {yaw} pitch {pitch}")
+            sys.exit(1)
+        renders_total += 1
     rounds += 1
     rays_total += 4 * n
     seed += 1
-print(f"fuzz ok: {rounds} random worlds (seeds {seed0}..{seed - 1}), {rays_total} ray traces and {frames_total} primary+shadow frames bit-exact against the checker "
+print(f"fuzz ok: {rounds} random worlds (seeds {seed0}..{seed - 1}), {rays_total} ray traces and {frames_total} primary+shadow frames bit-exact against the checker, {renders_total} full-raygen frames (G-buffer exact, radiance within tolerance) "
       f"({type(O).__name__}), device-built == host-built on every world")
 a.close(); b.close()
