@@ -379,6 +379,10 @@ int blokb_upload_vox(blokb_ctx* c, const char* path, uint32_t modelIndex, const 
     if (int rc = blokb_vox_load(path, modelIndex, offset3, &v)) return fail(rc, blokb_vox_last_error());
     uint64_t n = 0, nm = 0;
     blokb_vox_counts(v, &n, &nm, nullptr, nullptr);
+    if (n == 0) {  // loadAndImportVox: `return count > 0` (vox_loader.cpp:457) — the app reports the load as failed
+        blokb_vox_free(v);
+        return fail(BLOKB_E_ARG, std::string(path) + ": model " + std::to_string(modelIndex) + " imports no voxels");
+    }
     const int rc = blokb_upload_voxels(c, blokb_vox_xyz(v), blokb_vox_material_ids(v), (size_t)n, blokb_vox_materials(v), (size_t)nm);
     blokb_vox_free(v);
     return rc;

@@ -364,3 +364,20 @@ def test_update_dense_needs_an_editable_world(renderer_factory):
     r.add_voxels(xyz, mid, mats)             # replaced by a non-editable world again
     with pytest.raises(BlokbError, match="blokb_upload_dense"):
         r.update_dense(z)
+
+
+def test_vox_model_without_voxels_is_a_failed_load(renderer_factory, tmp_path):
+    """loadAndImportVox returns `count > 0` (vox_loader.cpp:457): a model that imports nothing is a failed load in the reference's
+    app; blokb_upload_vox reports it the same way and leaves the previous world in place. (Found by tools/fuzz_vox.py.)"""
+    from tests.voxfile import write_vox
+    xyz, mid, mats = CASES["terrain96"]
+    r = renderer_factory(64, 64)
+    r.add_voxels(xyz, mid, mats)
+    before = _export(r)
+    p = tmp_path / "empty.vox"
+    p.write_bytes(write_vox([((8, 8, 8), np.zeros((0, 4), np.uint8))]))
+    with pytest.raises(BlokbError, match="imports no voxels"):
+        r.add_vox(str(p))
+    after = _export(r)
+    for k in before:
+        assert before[k].tobytes() == after[k].tobytes()
