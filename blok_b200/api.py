@@ -31,6 +31,8 @@ SUB_DT = np.dtype([("nodeOffset", "<u4"), ("rootNodeIndex", "<u4"), ("nodeCount"
 MAT_DT = np.dtype([("albedo", "<f4", 3), ("flags", "<u4"), ("emission", "<f4", 3), ("ior", "<f4")])
 HIT_DT = np.dtype([("node", "<u4"), ("material", "<u4"), ("t", "<f4"), ("facePrim", "<u4")])
 assert NODE_DT.itemsize == 16 and SUB_DT.itemsize == 48 and MAT_DT.itemsize == 32 and HIT_DT.itemsize == 16
+PACKED_DT = np.dtype([("nodeFace", "<u4"), ("t", "<f4")])  # blokb_hit_packed
+PACKED_MAX_NODES = 0x1FFFFFFF
 
 IMG_HIT, IMG_SHADOW, IMG_COLOR, IMG_WORLDPOS, IMG_NORMALROUGH, IMG_ALBEDOMETAL, IMG_MOTION, IMG_ACCUM = range(8)
 (IMG_HISTORY_COLOR, IMG_MOMENTS, IMG_HISTORY_LENGTH, IMG_VARIANCE, IMG_DENOISED, IMG_TAA_HISTORY, IMG_TAA_OUTPUT, IMG_TONEMAPPED,
@@ -122,7 +124,8 @@ EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_wo
            "blokb_pipeline_destroy", "blokb_host_alloc", "blokb_host_free", "blokb_post_settings_default", "blokb_denoise",
            "blokb_postprocess", "blokb_end_frame", "blokb_reset_history", "blokb_write_image", "blokb_upload_voxels", "blokb_upload_dense", "blokb_world_export", "blokb_vox_load", "blokb_vox_parse",
            "blokb_vox_counts", "blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free", "blokb_vox_last_error", "blokb_upload_vox", "blokb_set_strips", "blokb_ipc_export", "blokb_set_peers", "blokb_bind_image",
-           "blokb_world_save", "blokb_world_load", "blokb_update_dense", "blokb_trace_rays_reordered"]
+           "blokb_world_save", "blokb_world_load", "blokb_update_dense", "blokb_trace_rays_reordered",
+           "blokb_pipeline_create_packed", "blokb_pipeline_submit_packed", "blokb_node_prims", "blokb_unpack_hits"]
 
 _lib = None
 
@@ -198,6 +201,10 @@ def load_library():
     L.blokb_worldgen_free.restype = None
     L.blokb_pipeline_create.argtypes = [_vp, C.c_int, C.c_uint32, C.c_uint32, C.POINTER(_vp)]
     L.blokb_pipeline_submit.argtypes = [_vp, C.POINTER(FrameUBO), _vp, C.POINTER(C.c_uint64)]
+    L.blokb_pipeline_create_packed.argtypes = L.blokb_pipeline_create.argtypes
+    L.blokb_pipeline_submit_packed.argtypes = L.blokb_pipeline_submit.argtypes
+    L.blokb_node_prims.argtypes = [_vp, C.c_size_t, _vp, C.c_size_t, _vp]
+    L.blokb_unpack_hits.argtypes = [_vp, C.c_size_t, _vp, C.c_size_t, _vp, _vp]
     L.blokb_pipeline_wait.argtypes = [_vp, C.c_uint64]
     L.blokb_pipeline_drain.argtypes = [_vp]
     L.blokb_pipeline_destroy.argtypes = [_vp]
@@ -246,6 +253,25 @@ class WorldSvoGpu:
         finally:
             L.blokb_worldgen_free(h)
         return WorldSvoGpu(nodes, subs, materials)
+
+    def node_prims(self) -> np.ndarray:
+        """primOfNode (blokb_node_prims): the sub-chunk (gl_PrimitiveID) whose subtree holds each node; cached."""
+        if getattr(self, "_prims", None) is None:
+            L = load_library()
+            prims = np.empty(len(self.globalNodes), np.uint32)
+            _ck(L.blokb_node_prims(_ptr(self.globalNodes), len(self.globalNodes), _ptr(self.globalSubChunks), len(self.globalSubChunks),
+                                   _ptr(prims)))
+            self._prims = prims
+        return self._prims
+
+    def unpack_hits(self, packed: np.ndarray, with_prim: bool = True) -> np.ndarray:
+        """blokb_unpack_hits: PACKED_DT records -> HIT_DT records (material and gl_PrimitiveID looked up in this world's arrays)."""
+        L = load_library()
+        src = np.ascontiguousarray(packed, PACKED_DT)
+        out = np.empty(src.shape, HIT_DT)
+        prims = self.node_prims() if with_prim else None
+        _ck(L.blokb_unpack_hits(_ptr(src), src.size, _ptr(self.globalNodes), len(self.globalNodes), _ptr(prims) if with_prim else None, _ptr(out)))
+        return out
 
 
 def load_vox(source, model_index=0, offset=(0.0, 0.0, 0.0)):
@@ -546,11 +572,14 @@ class FramePipeline:
     the tracing of frame i+1. result(ticket) waits for that frame's copy and returns its (h, w) HIT_DT view (valid until
     `depth` more frames have been submitted)."""
 
-    def __init__(self, renderer: Renderer, width: int, height: int, depth: int = 2):
+    def __init__(self, renderer: Renderer, width: int, height: int, depth: int = 2, packed: bool = False):
         self.L, self.r, self.width, self.height, self.depth = renderer.L, renderer, width, height, depth
         self._p = _vp()
-        _ck(self.L.blokb_pipeline_create(renderer._ctx, depth, width, height, C.byref(self._p)))
-        self.nbytes = width * height * HIT_DT.itemsize
+        self.packed = packed  # 8-byte blokb_hit_packed records (PACKED_DT) instead of HIT_DT; WorldSvoGpu.unpack_hits restores the rest
+        self.dtype = PACKED_DT if packed else HIT_DT
+        create = self.L.blokb_pipeline_create_packed if packed else self.L.blokb_pipeline_create
+        _ck(create(renderer._ctx, depth, width, height, C.byref(self._p)))
+        self.nbytes = width * height * self.dtype.itemsize
         self._host = []
         for _ in range(depth):
             h = self.L.blokb_host_alloc(self.nbytes)
@@ -563,14 +592,15 @@ class FramePipeline:
             frame = frame.frame(self.width, self.height)
         t = C.c_uint64()
         n = getattr(self, "_n", 0)
-        _ck(self.L.blokb_pipeline_submit(self._p, C.byref(frame), self._host[n % self.depth], C.byref(t)))
+        submit = self.L.blokb_pipeline_submit_packed if self.packed else self.L.blokb_pipeline_submit
+        _ck(submit(self._p, C.byref(frame), self._host[n % self.depth], C.byref(t)))
         self._n = n + 1
         return int(t.value)
 
     def result(self, ticket: int) -> np.ndarray:
         _ck(self.L.blokb_pipeline_wait(self._p, ticket))
         buf = (C.c_char * self.nbytes).from_address(self._host[ticket % self.depth])
-        return np.frombuffer(buf, dtype=HIT_DT).reshape(self.height, self.width)
+        return np.frombuffer(buf, dtype=self.dtype).reshape(self.height, self.width)
 
     def drain(self):
         _ck(self.L.blokb_pipeline_drain(self._p))

@@ -931,23 +931,25 @@ struct blokb_pipeline {
     std::vector<cudaEvent_t> traced, copied;
     cudaStream_t copyStream = nullptr;
     uint64_t submitted = 0;
+    bool packed = false;  // 8-byte blokb_hit_packed records instead of blokb_hit
+    size_t recordBytes() const { return packed ? sizeof(blokb_hit_packed) : sizeof(blokb_hit); }
 };
 
-int blokb_pipeline_create(blokb_ctx* c, int depth, uint32_t width, uint32_t height, blokb_pipeline** out) {
+static int pipeline_create(blokb_ctx* c, int depth, uint32_t width, uint32_t height, bool packed, blokb_pipeline** out) {
     if (!c || !out) return fail(BLOKB_E_ARG, "null argument");
     *out = nullptr;
     if (depth < 1 || depth > 8 || width == 0 || height == 0 || width > 65536 || height > 65536) return fail(BLOKB_E_ARG, "bad pipeline shape");
     CK(cudaSetDevice(c->device));
     blokb_pipeline* p = new (std::nothrow) blokb_pipeline;
     if (!p) return fail(BLOKB_E_ARG, "out of host memory");
-    p->ctx = c; p->depth = depth; p->width = width; p->height = height;
+    p->ctx = c; p->depth = depth; p->width = width; p->height = height; p->packed = packed;
     auto bail = [&](cudaError_t e) { blokb_pipeline_destroy(p); return fail(BLOKB_E_CUDA, cudaGetErrorString(e)); };
     cudaError_t e = cudaStreamCreateWithFlags(&p->copyStream, cudaStreamNonBlocking);
     if (e != cudaSuccess) return bail(e);
     for (int i = 0; i < depth; i++) {
         blokb_hit* d = nullptr;
         cudaEvent_t a = nullptr, b = nullptr;
-        if ((e = cudaMalloc((void**)&d, size_t(width) * height * sizeof(blokb_hit))) != cudaSuccess) return bail(e);
+        if ((e = cudaMalloc((void**)&d, size_t(width) * height * p->recordBytes())) != cudaSuccess) return bail(e);
         p->dHit.push_back(d);
         if ((e = cudaEventCreateWithFlags(&a, cudaEventDisableTiming)) != cudaSuccess) return bail(e);
         p->traced.push_back(a);
@@ -958,9 +960,19 @@ int blokb_pipeline_create(blokb_ctx* c, int depth, uint32_t width, uint32_t heig
     return 0;
 }
 
-int blokb_pipeline_submit(blokb_pipeline* p, const blokb_frame_ubo* f, blokb_hit* hostOut, uint64_t* ticket) {
+int blokb_pipeline_create(blokb_ctx* c, int depth, uint32_t width, uint32_t height, blokb_pipeline** out) {
+    return pipeline_create(c, depth, width, height, false, out);
+}
+int blokb_pipeline_create_packed(blokb_ctx* c, int depth, uint32_t width, uint32_t height, blokb_pipeline** out) {
+    return pipeline_create(c, depth, width, height, true, out);
+}
+
+static int pipeline_submit(blokb_pipeline* p, const blokb_frame_ubo* f, void* hostOut, bool packed, uint64_t* ticket) {
     if (!p || !f || !hostOut) return fail(BLOKB_E_ARG, "null argument");
+    if (p->packed != packed) return fail(BLOKB_E_ARG, packed ? "pipeline was not created with blokb_pipeline_create_packed"
+                                                             : "packed pipeline: use blokb_pipeline_submit_packed");
     blokb_ctx* c = p->ctx;
+    if (packed && c->stats.nodes > BLOKB_PACKED_MAX_NODES) return fail(BLOKB_E_UNSUPPORTED, "world has more nodes than a packed record can address");
     if (!c->haveWorld) return fail(BLOKB_E_STATE, "no world uploaded (blokb_upload_world)");
     if (f->screenWidth != p->width || f->screenHeight != p->height) return fail(BLOKB_E_ARG, "frame size differs from the pipeline's");
     CK(cudaSetDevice(c->device));
@@ -972,15 +984,23 @@ int blokb_pipeline_submit(blokb_pipeline* p, const blokb_frame_ubo* f, blokb_hit
     std::memcpy(d.camPos, f->camPos, 12);
     d.frameCount = f->frameCount; d.sampleCount = f->sampleCount; d.width = f->screenWidth; d.height = f->screenHeight;
     if (p->submitted >= uint64_t(p->depth)) CK(cudaStreamWaitEvent(c->stream, p->copied[slot], 0));  // slot's previous copy must have drained
-    CK(launch_primary(c->dw, d, false, own_only(p->dHit[slot]), own_only(nullptr), st(c), c->stream));
+    if (packed) CK(launch_primary_packed(c->dw, d, reinterpret_cast<blokb_hit_packed*>(p->dHit[slot]), c->stream));
+    else CK(launch_primary(c->dw, d, false, own_only(p->dHit[slot]), own_only(nullptr), st(c), c->stream));
     c->launches++;
     CK(cudaEventRecord(p->traced[slot], c->stream));
     CK(cudaStreamWaitEvent(p->copyStream, p->traced[slot], 0));
-    CK(cudaMemcpyAsync(hostOut, p->dHit[slot], size_t(p->width) * p->height * sizeof(blokb_hit), cudaMemcpyDeviceToHost, p->copyStream));
+    CK(cudaMemcpyAsync(hostOut, p->dHit[slot], size_t(p->width) * p->height * p->recordBytes(), cudaMemcpyDeviceToHost, p->copyStream));
     CK(cudaEventRecord(p->copied[slot], p->copyStream));
     if (ticket) *ticket = p->submitted;
     p->submitted++;
     return 0;
+}
+
+int blokb_pipeline_submit(blokb_pipeline* p, const blokb_frame_ubo* f, blokb_hit* hostOut, uint64_t* ticket) {
+    return pipeline_submit(p, f, hostOut, false, ticket);
+}
+int blokb_pipeline_submit_packed(blokb_pipeline* p, const blokb_frame_ubo* f, blokb_hit_packed* hostOut, uint64_t* ticket) {
+    return pipeline_submit(p, f, hostOut, true, ticket);
 }
 
 int blokb_pipeline_wait(blokb_pipeline* p, uint64_t ticket) {
@@ -1009,6 +1029,17 @@ void blokb_pipeline_destroy(blokb_pipeline* p) {
     for (auto e : p->copied) cudaEventDestroy(e);
     if (p->copyStream) cudaStreamDestroy(p->copyStream);
     delete p;
+}
+
+int blokb_node_prims(const blokb_svo_node* nodes, size_t nNodes, const blokb_subchunk* subs, size_t nSubs, uint32_t* primOfNode) {
+    if (node_prims(nodes, nNodes, subs, nSubs, primOfNode) != 0) return fail(BLOKB_E_ARG, "null array with non-zero count");
+    return 0;
+}
+int blokb_unpack_hits(const blokb_hit_packed* in, size_t n, const blokb_svo_node* nodes, size_t nNodes, const uint32_t* primOfNode,
+                      blokb_hit* out) {
+    if (n && (!in || !out || !nodes)) return fail(BLOKB_E_ARG, "null array with non-zero count");
+    if (unpack_hits(in, n, nodes, nNodes, primOfNode, out) != 0) return fail(BLOKB_E_ARG, "packed record names a node outside the array (stored as a miss)");
+    return 0;
 }
 
 void* blokb_host_alloc(size_t bytes) {

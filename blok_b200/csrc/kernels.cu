@@ -170,6 +170,19 @@ __global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceW
     if (kStats) atomicAdd(stats, (unsigned long long)steps);
 }
 
+// k_primary<false> with the 8-byte record of blokb_hit_packed (the readback is PCIe-bound: half the bytes per frame).
+__global__ void __launch_bounds__(256) k_primary_packed(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
+                                                        uint2* __restrict__ out) {
+    uint32_t px, py;
+    if (!thread_pixel(F, px, py)) return;
+    const F3 d = primary_dir(F, float(px) + 0.5f, float(py) + 0.5f);
+    HitRec h;
+    uint32_t steps = 0;
+    const bool hit = traverse<false>(W, thread_stack(), F.camPos[0], F.camPos[1], F.camPos[2], d.x, d.y, d.z, 0.001f, 10000.0f, h, steps, false);
+    out[size_t(py) * F.width + px] = hit ? make_uint2(h.node | (h.facePrim & 7u) << 29, __float_as_uint(h.t))
+                                         : make_uint2(0xFFFFFFFFu, __float_as_uint(-1.0f));
+}
+
 __device__ __forceinline__ uint32_t unorm8(float v) { return __float2uint_rn(__saturatef(v) * 255.0f); }
 
 // raygen.rgen as two kernels (blokb_render): the four G-buffer images that describe the FIRST hit of sample 0 (:253-263,
@@ -317,6 +330,12 @@ cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow,
         if (shadow) k_primary<true, false><<<g, 256, stack_bytes(W), st>>>(W, F, out, shadowOut, nullptr);
         else k_primary<false, false><<<g, 256, stack_bytes(W), st>>>(W, F, out, shadowOut, nullptr);
     }
+    return cudaGetLastError();
+}
+cudaError_t launch_primary_packed(const DeviceWorld& W, const FrameDev& F, blokb_hit_packed* out, cudaStream_t st) {
+    const dim3 g = pixel_grid(F);
+    if (g.y == 0) return cudaSuccess;
+    k_primary_packed<<<g, 256, stack_bytes(W), st>>>(W, F, reinterpret_cast<uint2*>(out));
     return cudaGetLastError();
 }
 cudaError_t launch_render(const DeviceWorld& W, const FrameDev& F, float* color, float* worldPos, uint16_t* normalRough, uint8_t* albedoMetal,

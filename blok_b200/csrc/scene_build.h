@@ -33,4 +33,8 @@ int build_host_world(const blokb_svo_node* nodes, size_t nNodes, const blokb_sub
 
 int build_top(const blokb_subchunk* subs, size_t nSubs, uint64_t nBricks, HostWorld& out, uint64_t& brickStart, std::string& err);
 
+// Host half of the packed readback (unpack.cpp); return 0 or BLOKB_E_ARG.
+int node_prims(const blokb_svo_node* nodes, size_t nNodes, const blokb_subchunk* subs, size_t nSubs, uint32_t* primOfNode);
+int unpack_hits(const blokb_hit_packed* in, size_t n, const blokb_svo_node* nodes, size_t nNodes, const uint32_t* primOfNode, blokb_hit* out);
+
 }  // namespace blokb

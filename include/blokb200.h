@@ -322,6 +322,24 @@ int blokb_pipeline_submit(blokb_pipeline* p, const blokb_frame_ubo* frame, blokb
 int blokb_pipeline_wait(blokb_pipeline* p, uint64_t ticket);
 int blokb_pipeline_drain(blokb_pipeline* p);
 void blokb_pipeline_destroy(blokb_pipeline* p);
+/* Packed records for the PCIe-bound readback: 8 bytes per ray instead of 16.
+ * nodeFace = node | face << 29 (node and face as in blokb_hit); a miss is nodeFace = 0xFFFFFFFF, t = -1.
+ * material and gl_PrimitiveID are functions of the leaf node and are re-derived on the host from the arrays the caller
+ * uploaded (blokb_node_prims + blokb_unpack_hits). Worlds with more than BLOKB_PACKED_MAX_NODES nodes are refused. */
+typedef struct blokb_hit_packed {
+    uint32_t nodeFace;
+    float t;
+} blokb_hit_packed;
+#define BLOKB_PACKED_MAX_NODES 0x1FFFFFFFu
+int blokb_pipeline_create_packed(blokb_ctx* ctx, int depth, uint32_t width, uint32_t height, blokb_pipeline** out);
+int blokb_pipeline_submit_packed(blokb_pipeline* p, const blokb_frame_ubo* frame, blokb_hit_packed* hostOut, uint64_t* ticket);
+/* Host helpers (no GPU involved). blokb_node_prims: primOfNode[i] = index of the sub-chunk whose subtree holds node i
+ * (the walk of intersect.rint:114-196: root = nodeOffset + rootNodeIndex, child = nodeOffset + firstChild + octant),
+ * 0xFFFFFFFF for nodes no sub-chunk reaches. blokb_unpack_hits: packed -> blokb_hit; primOfNode may be NULL, in which
+ * case facePrim carries the face only (prim bits zero). Returns BLOKB_E_ARG on a record whose node is out of range. */
+int blokb_node_prims(const blokb_svo_node* nodes, size_t nNodes, const blokb_subchunk* subs, size_t nSubs, uint32_t* primOfNode);
+int blokb_unpack_hits(const blokb_hit_packed* in, size_t n, const blokb_svo_node* nodes, size_t nNodes, const uint32_t* primOfNode,
+                      blokb_hit* out);
 /* Page-locked host memory (cudaHostAlloc / cudaFreeHost). */
 void* blokb_host_alloc(size_t bytes);
 void blokb_host_free(void* p);

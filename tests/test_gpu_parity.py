@@ -1,4 +1,5 @@
 """GPU: parity of the CUDA path (through the C-ABI) with the oracle and with the reference's golden vectors."""
+import ctypes as C
 import glob
 import os
 
@@ -215,6 +216,37 @@ def test_frame_pipeline_matches_blocking_path(renderer_factory):
         want = r.readback(IMG_HIT)
         assert np.array_equal(g.view(np.uint32), want.view(np.uint32))
     assert sum(int((g["node"] != 0xFFFFFFFF).sum()) for g in got) > 1000
+
+
+def test_packed_frame_pipeline_loses_nothing(renderer_factory):
+    """blokb_pipeline_*_packed: the 8-byte records of k_primary_packed, unpacked on the host against the uploaded arrays,
+    are byte for byte the 16-byte records of trace_primary; frame sizes that are not a multiple of the 32x8 block."""
+    z, w = _gold(GOLD[2])
+    r = renderer_factory(150, 91)
+    r.add_world(w)
+    cams = [Camera((-60 + 3 * i, 40, 30 - 2 * i), 0.0 + 2 * i, -10.0) for i in range(4)]
+    pipe = blok_b200.FramePipeline(r, 150, 91, depth=2, packed=True)
+    assert pipe.nbytes == 150 * 91 * 8
+    tickets = [pipe.submit(c.frame(150, 91, 0, 1)) for c in cams[:2]]
+    got = [pipe.result(tickets[0]).copy()]
+    for c in cams[2:]:
+        tickets.append(pipe.submit(c.frame(150, 91, 0, 1)))
+        got.append(pipe.result(tickets[-2]).copy())
+    got.append(pipe.result(tickets[-1]).copy())
+    pipe.drain()
+    pipe.close()
+    plain = blok_b200.FramePipeline(r, 150, 91, depth=1)
+    f0 = cams[0].frame(150, 91, 0, 1)
+    rc = plain.L.blokb_pipeline_submit_packed(plain._p, C.byref(f0), plain._host[0], None)  # record formats do not mix
+    assert rc == -1 and b"packed" in plain.L.blokb_last_error()
+    plain.close()
+    hits = 0
+    for c, g in zip(cams, got):
+        r.trace_primary(c.frame(150, 91, 0, 1))
+        want = r.readback(IMG_HIT)
+        assert np.array_equal(w.unpack_hits(g).view(np.uint32), want.view(np.uint32))
+        hits += int((want["node"] != 0xFFFFFFFF).sum())
+    assert hits > 1000
 
 
 def test_reordered_ray_list_gives_the_same_records(renderer_factory):

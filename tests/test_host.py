@@ -125,6 +125,44 @@ def test_dda_logic_random_and_degenerate_rays(emul, oracle):
         assert np.array_equal(out["material"], h[:, 2])
 
 
+def _pack(hits):
+    """HIT_DT -> PACKED_DT the way k_primary_packed stores it (kernels.cu)."""
+    from blok_b200.api import PACKED_DT
+    p = np.empty(hits.shape, PACKED_DT)
+    miss = hits["node"] == 0xFFFFFFFF
+    p["nodeFace"] = np.where(miss, 0xFFFFFFFF, hits["node"] | (hits["facePrim"] & 7) << 29)
+    p["t"] = hits["t"]
+    return p
+
+
+@pytest.mark.parametrize("path", GOLD, ids=lambda p: os.path.basename(p)[:-4])
+def test_packed_records_unpack_to_the_full_records(emul, oracle, path):
+    """blokb_node_prims + blokb_unpack_hits (host side of the packed readback): the 8-byte record loses nothing —
+    material and gl_PrimitiveID come back from the uploaded arrays, equal to the reference's own records."""
+    z, w = _gold(path)
+    e = emul.world(w)
+    out, _ = e.trace(oracle.primary_rays(z["ubo_s"]))
+    assert (out["node"] != 0xFFFFFFFF).sum() > 100 and (out["node"] == 0xFFFFFFFF).sum() > 0
+    back = w.unpack_hits(_pack(out))
+    assert np.array_equal(back.view(np.uint32), out.view(np.uint32))
+    g = z["hits_s"]  # the reference's records: prim, node, material, face, t bits
+    hit = g[:, 0] != 0xFFFFFFFF
+    assert np.array_equal(back["facePrim"][hit] >> 3, g[hit, 0]) and np.array_equal(back["material"], g[:, 2])
+    no_prim = w.unpack_hits(_pack(out), with_prim=False)
+    assert np.array_equal(no_prim["facePrim"][hit], g[hit, 3]) and np.all(no_prim["facePrim"][~hit] == 0xFFFFFFFF)
+    # every node below a sub-chunk root maps to exactly that sub-chunk; roots map to themselves
+    prims = w.node_prims()
+    subs = w.globalSubChunks
+    roots = (subs["nodeOffset"].astype(np.int64) + subs["rootNodeIndex"]).astype(np.int64)
+    assert np.array_equal(prims[roots], np.arange(len(subs), dtype=np.uint32))
+    # a record naming a node outside the array is refused (and stored as a miss)
+    from blok_b200.api import PACKED_DT
+    bad = np.array([(len(w.globalNodes), 1.0)], PACKED_DT)
+    with pytest.raises(blok_b200.BlokbError):
+        w.unpack_hits(bad)
+    assert len(w.unpack_hits(np.zeros(0, PACKED_DT))) == 0
+
+
 def test_dda_path_samples_match_oracle(emul, oracle):
     """path_sample (shade.cuh) compiled for the host uses the same libm as the oracle => radiance sums agree to fp32
     rounding of the sum; also: any split of the sample range reproduces the whole (sharding invariant)."""
