@@ -613,7 +613,20 @@ def main():
         tr = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tr):
             with open(tr) as f:
-                roof["traffic"] = json.load(f).get(name)
+                t = json.load(f).get(name)
+            if t:  # T = dram__bytes_read.sum + dram__bytes_write.sum of one launch (ncu --set full); the split and its source beside it
+                roof["traffic"] = t["total"]
+                roof["traffic_detail"] = t
+                if t.get("warp_instructions") and (m.get("clocks") or {}).get("sm_mhz"):
+                    # the bound this kernel actually sits under: warp instructions of one launch (smsp__inst_executed.sum of
+                    # the same ncu capture; deterministic for this scene and camera) / the live kernel time, against 4 issue slots per SM
+                    # per clock at the SM clock sampled during the timed region
+                    import torch
+                    sms = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
+                    ach = t["warp_instructions"] / (m["ms_per_step_rank"] * 1e-3) / 1e9
+                    pk = sms * 4 * m["clocks"]["sm_mhz"] * 1e6 / 1e9
+                    roof["issue"] = {"achieved": ach, "peak": pk, "unit": "G warp-instr/s", "frac": ach / pk,
+                                     "threads_per_instruction": t.get("threads_per_instruction")}
 
     extras = {"warm_l2": {"value": m["value_warm_l2"], "ms_per_step": m["ms_per_step_warm_l2"],
                           "what": "same frames back to back without the L2 flush (steady-state render loop)"},
