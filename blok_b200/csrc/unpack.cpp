@@ -1,6 +1,8 @@
 // Host half of the packed readback (blokb_hit_packed): the two fields the 8-byte record leaves out are
 // functions of the hit leaf, so the host re-derives them from the arrays it uploaded. No GPU involved.
+#include <algorithm>
 #include <cstring>
+#include <thread>
 #include <vector>
 
 #include "scene_build.h"
@@ -36,11 +38,11 @@ int node_prims(const blokb_svo_node* nodes, size_t nNodes, const blokb_subchunk*
     return 0;
 }
 
-int unpack_hits(const blokb_hit_packed* in, size_t n, const blokb_svo_node* nodes, size_t nNodes, const uint32_t* primOfNode,
-                      blokb_hit* out) {
-    if (n && (!in || !out || !nodes)) return BLOKB_E_ARG;
+// Records are independent: large batches are split over the host's cores (a 4K frame is 8.3 M random lookups into the node array).
+static int unpack_range(const blokb_hit_packed* in, size_t begin, size_t end, const blokb_svo_node* nodes, size_t nNodes,
+                        const uint32_t* primOfNode, blokb_hit* out) {
     int rc = 0;
-    for (size_t i = 0; i < n; i++) {
+    for (size_t i = begin; i < end; i++) {
         const uint32_t nf = in[i].nodeFace;
         if (nf == 0xFFFFFFFFu) {
             out[i] = blokb_hit{0xFFFFFFFFu, 0xFFFFFFFFu, -1.0f, 0xFFFFFFFFu};
@@ -51,5 +53,22 @@ int unpack_hits(const blokb_hit_packed* in, size_t n, const blokb_svo_node* node
         out[i] = blokb_hit{node, nodes[node].materialId, in[i].t, face | (primOfNode ? primOfNode[node] << 3 : 0u)};
     }
     return rc;
+}
+
+int unpack_hits(const blokb_hit_packed* in, size_t n, const blokb_svo_node* nodes, size_t nNodes, const uint32_t* primOfNode,
+                blokb_hit* out) {
+    if (n && (!in || !out || !nodes)) return BLOKB_E_ARG;
+    const size_t kMinPerThread = size_t(1) << 16;
+    size_t nt = std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), 32);
+    nt = std::min(nt, (n + kMinPerThread - 1) / kMinPerThread);
+    if (nt <= 1) return unpack_range(in, 0, n, nodes, nNodes, primOfNode, out);
+    std::vector<int> rcs(nt, 0);
+    std::vector<std::thread> pool;
+    for (size_t k = 0; k < nt; k++)
+        pool.emplace_back([&, k] { rcs[k] = unpack_range(in, n * k / nt, n * (k + 1) / nt, nodes, nNodes, primOfNode, out); });
+    for (auto& t : pool) t.join();
+    for (int rc : rcs)
+        if (rc) return rc;
+    return 0;
 }
 }  // namespace blokb

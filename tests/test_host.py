@@ -161,6 +161,14 @@ def test_packed_records_unpack_to_the_full_records(emul, oracle, path):
     with pytest.raises(blok_b200.BlokbError):
         w.unpack_hits(bad)
     assert len(w.unpack_hits(np.zeros(0, PACKED_DT))) == 0
+    # batches large enough to be split over the host's cores: same records, and a bad one anywhere is still reported
+    big = np.tile(_pack(out), 400_000 // len(out) + 1)
+    assert len(big) > 4 * (1 << 16)
+    want = np.tile(out, 400_000 // len(out) + 1)
+    assert np.array_equal(w.unpack_hits(big).view(np.uint32), want.view(np.uint32))
+    big[-5] = (len(w.globalNodes), 1.0)
+    with pytest.raises(blok_b200.BlokbError):
+        w.unpack_hits(big)
 
 
 def test_dda_path_samples_match_oracle(emul, oracle):
