@@ -13,9 +13,13 @@
 
 namespace blokb {
 
-// pixel of this thread: block = 32x8 pixels, warp = 8x4 tile
+// pixel of this thread: block = 32 x BLOKB_BLOCK_ROWS pixels (4 warps of 8x4 pixels by default), two such blocks per 8-row strip
 // blockIdx.y counts the strips THIS launch renders (FrameDev::stripFirst / stripStride): pixel coordinates, seeds and
 // output addresses are those of the full frame, so any partition of the strips over launches or GPUs writes the same bytes.
+#ifndef BLOKB_BLOCK_ROWS
+#define BLOKB_BLOCK_ROWS 4  // pixel kernels: block = 32 x BLOKB_BLOCK_ROWS pixels (4 or 8 rows of an 8-row strip; 4 measured 0.6-0.9 % faster: DESIGN.md 5)
+#endif
+constexpr uint32_t kBlocksPerStrip = 8u / BLOKB_BLOCK_ROWS, kPixThreads = 32u * BLOKB_BLOCK_ROWS;
 __device__ __forceinline__ bool thread_pixel(const FrameDev& F, uint32_t& px, uint32_t& py) {
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
 #ifndef BLOKB_TILE_W_LOG2
@@ -23,7 +27,8 @@ __device__ __forceinline__ bool thread_pixel(const FrameDev& F, uint32_t& px, ui
 #endif
     constexpr uint32_t TW = 1u << BLOKB_TILE_W_LOG2, TH = 32u / TW, tilesX = 32u / TW;
     px = blockIdx.x * 32u + (warp % tilesX) * TW + (lane & (TW - 1u));
-    py = (F.stripFirst + blockIdx.y * F.stripStride) * 8u + (warp / tilesX) * TH + (lane >> BLOKB_TILE_W_LOG2);
+    py = (F.stripFirst + (blockIdx.y / kBlocksPerStrip) * F.stripStride) * 8u + (blockIdx.y % kBlocksPerStrip) * BLOKB_BLOCK_ROWS +
+         (warp / tilesX) * TH + (lane >> BLOKB_TILE_W_LOG2);
     return px < F.width && py < F.height;
 }
 
@@ -141,7 +146,7 @@ __global__ void __launch_bounds__(256) k_trace_rays_ordered(const __grid_constan
 
 // Sample-0 primary rays (raygen.rgen:193-229) -> hit records; optionally the sun shadow ray of :280-298.
 template <bool kShadow, bool kStats>
-__global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
+__global__ void __launch_bounds__(kPixThreads) k_primary(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
                                                  const __grid_constant__ PeerOut out, const __grid_constant__ PeerOut shadow,
                                                  unsigned long long* stats) {
     uint32_t px, py;
@@ -171,7 +176,7 @@ __global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceW
 }
 
 // k_primary<false> with the 8-byte record of blokb_hit_packed (the readback is PCIe-bound: half the bytes per frame).
-__global__ void __launch_bounds__(256) k_primary_packed(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
+__global__ void __launch_bounds__(kPixThreads) k_primary_packed(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
                                                         uint2* __restrict__ out) {
     uint32_t px, py;
     if (!thread_pixel(F, px, py)) return;
@@ -190,7 +195,7 @@ __device__ __forceinline__ uint32_t unorm8(float v) { return __float2uint_rn(__s
 // running the frame's samples. One kernel doing both kept the first-hit record alive across every sample's traversals:
 // 103 registers, 2 blocks per SM, 26.4 ms for 8 spp at 4K against 21.4 ms for the same samples in k_path. Sample 0's
 // primary ray is traced twice (0.7 ms); every stored value is computed by the same expressions as before.
-__global__ void __launch_bounds__(256) k_gbuffer(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F, float4* __restrict__ worldPos,
+__global__ void __launch_bounds__(kPixThreads) k_gbuffer(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F, float4* __restrict__ worldPos,
                                                  uint2* __restrict__ normalRough, uint32_t* __restrict__ albedoMetal, uint32_t* __restrict__ motion) {
     uint32_t px, py;
     if (!thread_pixel(F, px, py)) return;
@@ -241,7 +246,7 @@ __global__ void __launch_bounds__(256) k_gbuffer(const __grid_constant__ DeviceW
 // No minBlocksPerSM on purpose: left alone, ptxas settles on 64 registers (4 blocks per SM, a few spilled words) = 21.4 ms for
 // 8 spp at 4K; __launch_bounds__(256, 1) gives 90 registers / 25.9 ms, (256, 2) 22.2, (256, 3) 22.6, (256, 5) 24.1.
 template <bool kStats, bool kColor>
-__global__ void __launch_bounds__(256) k_path(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F, uint32_t sBegin, uint32_t sEnd,
+__global__ void __launch_bounds__(kPixThreads) k_path(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F, uint32_t sBegin, uint32_t sEnd,
                                               const __grid_constant__ PeerOut accum, unsigned long long* stats) {
     uint32_t px, py;
     if (!thread_pixel(F, px, py)) return;
@@ -279,8 +284,9 @@ __global__ void __launch_bounds__(256) k_resolve(const float4* __restrict__ accu
 static inline dim3 pixel_grid(const FrameDev& F) {
     const uint32_t strips = (F.height + 7) / 8;
     const uint32_t mine = F.stripFirst < strips ? (strips - F.stripFirst + F.stripStride - 1) / F.stripStride : 0;
-    return dim3((F.width + 31) / 32, mine);
+    return dim3((F.width + 31) / 32, mine * kBlocksPerStrip);
 }
+static inline size_t pix_stack_bytes(const DeviceWorld& W) { return size_t(W.levels) * kPixThreads * sizeof(uint4); }
 static inline size_t stack_bytes(const DeviceWorld& W) { return size_t(W.levels) * 256 * sizeof(uint4); }  // <= 48 KB (kMaxLevels = 12)
 
 cudaError_t launch_trace_rays(const DeviceWorld& W, const float* rays, size_t n, blokb_hit* out, unsigned long long* stats, cudaStream_t st) {
@@ -324,37 +330,37 @@ cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow,
     const dim3 g = pixel_grid(F);
     if (g.y == 0) return cudaSuccess;
     if (stats) {
-        if (shadow) k_primary<true, true><<<g, 256, stack_bytes(W), st>>>(W, F, out, shadowOut, stats);
-        else k_primary<false, true><<<g, 256, stack_bytes(W), st>>>(W, F, out, shadowOut, stats);
+        if (shadow) k_primary<true, true><<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, out, shadowOut, stats);
+        else k_primary<false, true><<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, out, shadowOut, stats);
     } else {
-        if (shadow) k_primary<true, false><<<g, 256, stack_bytes(W), st>>>(W, F, out, shadowOut, nullptr);
-        else k_primary<false, false><<<g, 256, stack_bytes(W), st>>>(W, F, out, shadowOut, nullptr);
+        if (shadow) k_primary<true, false><<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, out, shadowOut, nullptr);
+        else k_primary<false, false><<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, out, shadowOut, nullptr);
     }
     return cudaGetLastError();
 }
 cudaError_t launch_primary_packed(const DeviceWorld& W, const FrameDev& F, blokb_hit_packed* out, cudaStream_t st) {
     const dim3 g = pixel_grid(F);
     if (g.y == 0) return cudaSuccess;
-    k_primary_packed<<<g, 256, stack_bytes(W), st>>>(W, F, reinterpret_cast<uint2*>(out));
+    k_primary_packed<<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, reinterpret_cast<uint2*>(out));
     return cudaGetLastError();
 }
 cudaError_t launch_render(const DeviceWorld& W, const FrameDev& F, float* color, float* worldPos, uint16_t* normalRough, uint8_t* albedoMetal,
                           uint16_t* motion, unsigned long long* stats, cudaStream_t st) {
     const dim3 g = pixel_grid(F);
     if (g.y == 0) return cudaSuccess;
-    k_gbuffer<<<g, 256, stack_bytes(W), st>>>(W, F, (float4*)worldPos, (uint2*)normalRough, (uint32_t*)albedoMetal, (uint32_t*)motion);
+    k_gbuffer<<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, (float4*)worldPos, (uint2*)normalRough, (uint32_t*)albedoMetal, (uint32_t*)motion);
     PeerOut out;
     out.dst[0] = color;
-    if (stats) k_path<true, true><<<g, 256, stack_bytes(W), st>>>(W, F, 0u, F.sampleCount, out, stats);
-    else k_path<false, true><<<g, 256, stack_bytes(W), st>>>(W, F, 0u, F.sampleCount, out, nullptr);
+    if (stats) k_path<true, true><<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, 0u, F.sampleCount, out, stats);
+    else k_path<false, true><<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, 0u, F.sampleCount, out, nullptr);
     return cudaGetLastError();
 }
 cudaError_t launch_path(const DeviceWorld& W, const FrameDev& F, uint32_t sBegin, uint32_t sEnd, const PeerOut& accum, unsigned long long* stats,
                         cudaStream_t st) {
     const dim3 g = pixel_grid(F);
     if (g.y == 0) return cudaSuccess;
-    if (stats) k_path<true, false><<<g, 256, stack_bytes(W), st>>>(W, F, sBegin, sEnd, accum, stats);
-    else k_path<false, false><<<g, 256, stack_bytes(W), st>>>(W, F, sBegin, sEnd, accum, nullptr);
+    if (stats) k_path<true, false><<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, sBegin, sEnd, accum, stats);
+    else k_path<false, false><<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, sBegin, sEnd, accum, nullptr);
     return cudaGetLastError();
 }
 cudaError_t launch_resolve(const float* accum, float* color, size_t n, cudaStream_t st) {

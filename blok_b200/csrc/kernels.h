@@ -12,7 +12,7 @@ struct FrameDev {
     float invView[16], invProj[16], prevViewProj[16];
     float camPos[3];
     uint32_t frameCount, sampleCount, width, height;
-    // tile scheduler: of the frame's 8-row strips (one row of 32x8-pixel blocks each) this launch renders strips
+    // tile scheduler: of the frame's 8-row strips (32-pixel-wide blocks, 8 / BLOKB_BLOCK_ROWS of them stacked per strip) this launch renders strips
     // stripFirst, stripFirst + stripStride, ... — the whole frame by default (blokb_set_strips)
     uint32_t stripFirst = 0, stripStride = 1;
 };
