@@ -41,6 +41,16 @@ class Emu:
         steps = self.lib.emu_trace(self.h, rays.ctypes.data_as(_vp), len(rays), out.ctypes.data_as(_vp), threads, int(locate))
         return out, steps
 
+    def walk_profile(self, rays, locate=True):
+        """Per child-cell size (row index = sh / 2: 0 voxels, 1 bricks, ...): descents, descents that needed plane tests,
+        steps, climbs landing there. Returns (counts[4, kMaxLevels + 1], hits). Single-threaded."""
+        rays = np.ascontiguousarray(rays, np.float32)
+        prof = np.zeros((4, 13), np.uint64)  # kMaxLevels = 12 (scene.h)
+        self.lib.emu_walk_profile.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp]
+        self.lib.emu_walk_profile.restype = C.c_uint64
+        hits = self.lib.emu_walk_profile(self.h, rays.ctypes.data_as(_vp), len(rays), int(locate), prof.ctypes.data_as(_vp))
+        return prof, int(hits)
+
     def path(self, ubo, s_begin, s_end, threads=8):
         from blok_b200.api import FrameUBO
         f = ubo if isinstance(ubo, FrameUBO) else FrameUBO.from_bytes(ubo)

@@ -70,6 +70,37 @@ uint64_t emu_trace(void* p, const float* rays, size_t n, blokb_hit* out, int nTh
     });
     return total;
 }
+// Where the walk spends its decisions (profiling aid, tools/walk_profile.py): the loop of traverse() restated around the
+// Walker's own methods, counting per child-cell size (index = sh / 2: 0 = voxels, 1 = 4^3 bricks, ...) the descents into a
+// cell of that child size, how many of them needed plane tests (select) rather than m's bits, the steps taken at that size
+// and the climbs that landed there. prof = 4 x (kMaxLevels + 1) counters; returns the number of hits.
+uint64_t emu_walk_profile(void* p, const float* rays, size_t n, int locate, uint64_t* prof) {
+    Emu* e = (Emu*)p;
+    constexpr int K = kMaxLevels + 1;
+    uint64_t hits = 0;
+    for (size_t i = 0; i < n; i++) {
+        const float* r = rays + 8 * i;
+        uint4 stackMem[kMaxLevels]; const NodeStack stk{stackMem, 1};
+        Walker wk;
+        if (!wk.init(e->dw, r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7], locate != 0)) continue;
+        for (;;) {
+            bool hit = false;
+            while (wk.occupied()) {
+                if (wk.sh == 0) { hit = true; break; }
+                const bool tests = wk.sh - 2 < wk.rs;
+                wk.descend(e->dw, stk);
+                prof[0 * K + wk.sh / 2]++;
+                if (tests) prof[1 * K + wk.sh / 2]++;
+            }
+            if (hit) { hits++; break; }
+            const int before = wk.sh;
+            prof[2 * K + wk.sh / 2]++;
+            if (!wk.step(e->dw, stk)) break;
+            if (wk.sh != before) prof[3 * K + wk.sh / 2]++;
+        }
+    }
+    return hits;
+}
 // per-ray DDA step counts (profiling aid for warp-divergence estimates)
 void emu_trace_steps(void* p, const float* rays, size_t n, uint32_t* stepsOut, int nThreads) {
     Emu* e = (Emu*)p;

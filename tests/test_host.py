@@ -171,6 +171,18 @@ def test_packed_records_unpack_to_the_full_records(emul, oracle, path):
         w.unpack_hits(big)
 
 
+def test_walk_profile_counts_the_same_walk(emul, oracle):
+    """tools/walk_profile.py's per-level counters restate traverse()'s loop around the Walker: same hits, same step total."""
+    z, w = _gold(GOLD[0])
+    e = emul.world(w)
+    rays = oracle.primary_rays(z["ubo_s"])
+    for locate in (False, True):
+        out, steps = e.trace(rays, threads=1, locate=locate)
+        prof, hits = e.walk_profile(rays, locate=locate)
+        assert hits == int((out["node"] != 0xFFFFFFFF).sum()) and int(prof[2].sum()) == steps
+        assert np.all(prof[1] <= prof[0]) and prof[0, 0] >= hits  # every hit descended into a brick; tests are a subset of descents
+
+
 def test_dda_path_samples_match_oracle(emul, oracle):
     """path_sample (shade.cuh) compiled for the host uses the same libm as the oracle => radiance sums agree to fp32
     rounding of the sum; also: any split of the sample range reproduces the whole (sharding invariant)."""
