@@ -101,6 +101,48 @@ uint64_t emu_walk_profile(void* p, const float* rays, size_t n, int locate, uint
     }
     return hits;
 }
+// The same loop run by 32 Walkers in lock step, the way a warp executes traverse(): rays[32 * w + l] is lane l of warp w. For each
+// decision kind the counters hold {warp-level issues, lane-level executions}: utilisation = lanes / (32 * issues).
+// out[0..1] descend, [2..3] select inside descend, [4..5] step, [6..7] widen inside step, [8..9] climb inside step, [10] warps.
+void emu_warp_profile(void* p, const float* rays, size_t nWarps, int locate, uint64_t* out) {
+    Emu* e = (Emu*)p;
+    for (size_t w = 0; w < nWarps; w++) {
+        Walker wk[32]; uint4 stackMem[32][kMaxLevels]; bool live[32];
+        for (int l = 0; l < 32; l++) {
+            const float* r = rays + 8 * (32 * w + l);
+            live[l] = wk[l].init(e->dw, r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7], locate != 0);
+        }
+        out[10]++;
+        for (;;) {
+            for (;;) {  // while (occupied) descend: one issue per iteration in which any lane still descends
+                uint32_t nDesc = 0, nSel = 0;
+                for (int l = 0; l < 32; l++) {
+                    if (!live[l] || !wk[l].occupied()) continue;
+                    if (wk[l].sh == 0) { live[l] = false; continue; }  // hit: leaves the loop, waits for the warp
+                    nSel += wk[l].sh - 2 < wk[l].rs;
+                    wk[l].descend(e->dw, NodeStack{stackMem[l], 1});
+                    nDesc++;
+                }
+                if (!nDesc) break;
+                out[0]++; out[1] += nDesc;
+                if (nSel) { out[2]++; out[3] += nSel; }
+            }
+            uint32_t nStep = 0, nWiden = 0, nClimb = 0;
+            for (int l = 0; l < 32; l++) {
+                if (!live[l]) continue;
+                nStep++;
+                nWiden += wk[l].sh > wk[l].rs;
+                const int before = wk[l].sh;
+                if (!wk[l].step(e->dw, NodeStack{stackMem[l], 1})) { live[l] = false; continue; }
+                nClimb += wk[l].sh != before;
+            }
+            if (!nStep) break;
+            out[4]++; out[5] += nStep;
+            if (nWiden) { out[6]++; out[7] += nWiden; }
+            if (nClimb) { out[8]++; out[9] += nClimb; }
+        }
+    }
+}
 // per-ray DDA step counts (profiling aid for warp-divergence estimates)
 void emu_trace_steps(void* p, const float* rays, size_t n, uint32_t* stepsOut, int nThreads) {
     Emu* e = (Emu*)p;

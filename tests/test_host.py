@@ -181,6 +181,12 @@ def test_walk_profile_counts_the_same_walk(emul, oracle):
         prof, hits = e.walk_profile(rays, locate=locate)
         assert hits == int((out["node"] != 0xFFFFFFFF).sum()) and int(prof[2].sum()) == steps
         assert np.all(prof[1] <= prof[0]) and prof[0, 0] >= hits  # every hit descended into a brick; tests are a subset of descents
+        n32 = len(rays) // 32 * 32  # the lock-step (warp) restatement executes the same lane-level decisions
+        p32, _ = e.walk_profile(rays[:n32], locate=locate)
+        wp = e.warp_profile(rays[:n32], locate=locate)
+        assert int(wp[1]) == int(p32[0].sum()) and int(wp[3]) == int(p32[1].sum()) and int(wp[5]) == int(p32[2].sum())
+        assert int(wp[9]) == int(p32[3].sum()) and int(wp[10]) == n32 // 32
+        assert all(int(wp[2 * k]) <= int(wp[2 * k + 1]) <= 32 * int(wp[2 * k]) for k in range(5))
 
 
 def test_dda_path_samples_match_oracle(emul, oracle):

@@ -1,7 +1,8 @@
 """Where the walk spends its decisions, per level, counted on the CPU build of the product's own Walker (tests/host_emul):
 descents, descents that needed plane tests, DDA steps and climbs by child-cell size, for a strided sample of a workload's
 primary rays and for the sun shadow rays of their hits. Input for DESIGN.md 12 (what a different leaf size would remove).
-  python tools/walk_profile.py [c3] [stride]"""
+  python tools/walk_profile.py [c3] [stride]            per-ray counts by level
+  python tools/walk_profile.py --warps [c3] [stride]    32 Walkers in lock step per 8x4 tile: lanes per issued decision"""
 import os
 import sys
 
@@ -49,5 +50,34 @@ def main():
         table(f"{name} sun shadow rays of those hits", prof, hits, len(sh))
 
 
+def warp_table(title, c):
+    names = ("descend", "  select inside descend", "step", "  widen inside step", "  climb inside step")
+    print(f"\n{title}: {int(c[10])} warps in lock step")
+    print(f"{'decision':>26} {'warp issues':>12} {'lane execs':>12} {'lanes / issue':>14} {'issues / warp':>14}")
+    for k, nm in enumerate(names):
+        iss, ln = int(c[2 * k]), int(c[2 * k + 1])
+        print(f"{nm:>26} {iss:>12} {ln:>12} {ln / max(iss, 1):>14.2f} {iss / max(int(c[10]), 1):>14.2f}")
+
+
+def warps(name="c3", stride=37):
+    """The same walk as a warp executes it: 8x4-pixel tiles (lane = x + 8 y, as thread_pixel maps them), every stride-th tile."""
+    wl = workloads.WORKLOADS[name]
+    W, H = wl["width"], wl["height"]
+    world = workloads.build_world(name)
+    emu.build()
+    e = emu.load().world(world)
+    if not os.path.exists(pyoracle.ORACLE_SO):
+        pyoracle.build(ref=False)
+    ubo = workloads.camera_for(name).frame(W, H, 0, 1).to_numpy()
+    rays = pyoracle.OracleLib().primary_rays(ubo).reshape(H, W, 8)
+    assert H % 4 == 0 and W % 8 == 0
+    tiles = rays.reshape(H // 4, 4, W // 8, 8, 8).transpose(0, 2, 1, 3, 4).reshape(-1, 32, 8)[::stride]
+    warp_table(f"{name} primary rays, every {stride}th 8x4 tile", e.warp_profile(tiles.reshape(-1, 8), locate=False))
+
+
 if __name__ == "__main__":
-    main()
+    if "--warps" in sys.argv:
+        sys.argv.remove("--warps")
+        warps(sys.argv[1] if len(sys.argv) > 1 else "c3", int(sys.argv[2]) if len(sys.argv) > 2 else 37)
+    else:
+        main()
