@@ -51,15 +51,15 @@ class Emu:
         hits = self.lib.emu_walk_profile(self.h, rays.ctypes.data_as(_vp), len(rays), int(locate), prof.ctypes.data_as(_vp))
         return prof, int(hits)
 
-    def warp_profile(self, rays, locate=True):
+    def warp_profile(self, rays, locate=True, max_desc_passes=0):
         """32 Walkers in lock step per warp (rays[32 * w + l] = lane l of warp w): {warp issues, lane executions} of
         descend, select-in-descend, step, widen-in-step, climb-in-step, and the warp count (11 counters)."""
         rays = np.ascontiguousarray(rays, np.float32)
         assert len(rays) % 32 == 0
         out = np.zeros(11, np.uint64)
-        self.lib.emu_warp_profile.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp]
+        self.lib.emu_warp_profile.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp, C.c_int]
         self.lib.emu_warp_profile.restype = None
-        self.lib.emu_warp_profile(self.h, rays.ctypes.data_as(_vp), len(rays) // 32, int(locate), out.ctypes.data_as(_vp))
+        self.lib.emu_warp_profile(self.h, rays.ctypes.data_as(_vp), len(rays) // 32, int(locate), out.ctypes.data_as(_vp), int(max_desc_passes))
         return out
 
     def path(self, ubo, s_begin, s_end, threads=8):

@@ -104,7 +104,9 @@ uint64_t emu_walk_profile(void* p, const float* rays, size_t n, int locate, uint
 // The same loop run by 32 Walkers in lock step, the way a warp executes traverse(): rays[32 * w + l] is lane l of warp w. For each
 // decision kind the counters hold {warp-level issues, lane-level executions}: utilisation = lanes / (32 * issues).
 // out[0..1] descend, [2..3] select inside descend, [4..5] step, [6..7] widen inside step, [8..9] climb inside step, [10] warps.
-void emu_warp_profile(void* p, const float* rays, size_t nWarps, int locate, uint64_t* out) {
+// maxDescPasses <= 0: the product's loop shape (descend until no lane sits on an occupied cell, then step). > 0: a what-if shape in
+// which at most that many descend passes precede each step pass and lanes still on an occupied cell skip the step.
+void emu_warp_profile(void* p, const float* rays, size_t nWarps, int locate, uint64_t* out, int maxDescPasses) {
     Emu* e = (Emu*)p;
     for (size_t w = 0; w < nWarps; w++) {
         Walker wk[32]; uint4 stackMem[32][kMaxLevels]; bool live[32];
@@ -114,7 +116,7 @@ void emu_warp_profile(void* p, const float* rays, size_t nWarps, int locate, uin
         }
         out[10]++;
         for (;;) {
-            for (;;) {  // while (occupied) descend: one issue per iteration in which any lane still descends
+            for (int pass = 0; maxDescPasses <= 0 || pass < maxDescPasses; pass++) {  // while (occupied) descend: one issue per pass in which any lane descends
                 uint32_t nDesc = 0, nSel = 0;
                 for (int l = 0; l < 32; l++) {
                     if (!live[l] || !wk[l].occupied()) continue;
@@ -128,15 +130,21 @@ void emu_warp_profile(void* p, const float* rays, size_t nWarps, int locate, uin
                 if (nSel) { out[2]++; out[3] += nSel; }
             }
             uint32_t nStep = 0, nWiden = 0, nClimb = 0;
+            uint32_t nWait = 0;
             for (int l = 0; l < 32; l++) {
                 if (!live[l]) continue;
+                if (wk[l].occupied()) {  // only with a bounded descend loop (a what-if shape): still descending, or a hit found late
+                    if (wk[l].sh == 0) live[l] = false; else nWait++;
+                    continue;
+                }
                 nStep++;
                 nWiden += wk[l].sh > wk[l].rs;
                 const int before = wk[l].sh;
                 if (!wk[l].step(e->dw, NodeStack{stackMem[l], 1})) { live[l] = false; continue; }
                 nClimb += wk[l].sh != before;
             }
-            if (!nStep) break;
+            if (!nStep && !nWait) break;
+            if (!nStep) continue;
             out[4]++; out[5] += nStep;
             if (nWiden) { out[6]++; out[7] += nWiden; }
             if (nClimb) { out[8]++; out[9] += nClimb; }

@@ -73,6 +73,14 @@ def warps(name="c3", stride=37):
     assert H % 4 == 0 and W % 8 == 0
     tiles = rays.reshape(H // 4, 4, W // 8, 8, 8).transpose(0, 2, 1, 3, 4).reshape(-1, 32, 8)[::stride]
     warp_table(f"{name} primary rays, every {stride}th 8x4 tile", e.warp_profile(tiles.reshape(-1, 8), locate=False))
+    # what-if loop shapes: at most K descend passes before each step pass (K = 1 is the `if occupied descend else step` loop §5 dropped).
+    # Cost in issue slots with rough per-decision instruction counts read off the SASS (descend 24, select 42, step 40, widen 14, climb 10).
+    wts = np.array([24, 42, 40, 14, 10], np.float64)
+    print("\nloop shape (descend passes per step pass) -> weighted issues per warp; lanes-per-issue of descend / step")
+    for k in (0, 1, 2, 3, 4):
+        c = e.warp_profile(tiles.reshape(-1, 8), locate=False, max_desc_passes=k).astype(np.float64)
+        cost = float((c[0:10:2] * wts).sum() / c[10])
+        print(f"  K = {'inf (product)' if k == 0 else k:<14} {cost:8.1f}   {c[1] / c[0]:5.2f} / {c[5] / c[4]:5.2f}")
 
 
 if __name__ == "__main__":
