@@ -87,6 +87,15 @@ class PostSettings(C.Structure):
             setattr(self, k, v)
 
 
+PATH_WAVEFRONT, PATH_FUSED = 0, 1
+
+
+class PathOptions(C.Structure):
+    """blokb_path_options: how render / trace_path schedule a sample's rays (wavefront with sorted bounce rays, or fused)."""
+    _fields_ = [("mode", C.c_int32), ("batchSamples", C.c_uint32), ("dirCells", C.c_uint32), ("originCellShift", C.c_int32),
+                ("mortonBitsPerAxis", C.c_uint32)]
+
+
 class DenseChunkC(C.Structure):
     """blokb_dense_chunk: one blok::Chunk (chunk.hpp:33-42) — index + its density / materialIds arrays (128^3 each)."""
     _fields_ = [("cx", C.c_int32), ("cy", C.c_int32), ("cz", C.c_int32), ("density", _vp), ("materialIds", _vp)]
@@ -125,7 +134,8 @@ EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_wo
            "blokb_postprocess", "blokb_end_frame", "blokb_reset_history", "blokb_write_image", "blokb_upload_voxels", "blokb_upload_dense", "blokb_world_export", "blokb_vox_load", "blokb_vox_parse",
            "blokb_vox_counts", "blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free", "blokb_vox_last_error", "blokb_upload_vox", "blokb_set_strips", "blokb_ipc_export", "blokb_set_peers", "blokb_bind_image",
            "blokb_world_save", "blokb_world_load", "blokb_update_dense", "blokb_trace_rays_reordered",
-           "blokb_pipeline_create_packed", "blokb_pipeline_submit_packed", "blokb_node_prims", "blokb_unpack_hits"]
+           "blokb_pipeline_create_packed", "blokb_pipeline_submit_packed", "blokb_node_prims", "blokb_unpack_hits",
+           "blokb_path_options_default", "blokb_set_path_options", "blokb_get_path_options"]
 
 _lib = None
 
@@ -166,6 +176,10 @@ def load_library():
         getattr(L, f).argtypes = [_vp, _vp]
     L.blokb_trace_path.argtypes = [_vp, C.c_uint32, C.c_uint32, _vp]
     L.blokb_set_strips.argtypes = [_vp, C.c_uint32, C.c_uint32]
+    L.blokb_path_options_default.argtypes = [C.POINTER(PathOptions)]
+    L.blokb_path_options_default.restype = None
+    L.blokb_set_path_options.argtypes = [_vp, C.POINTER(PathOptions)]
+    L.blokb_get_path_options.argtypes = [_vp, C.POINTER(PathOptions)]
     L.blokb_ipc_export.argtypes = [_vp, C.c_int, _vp]
     L.blokb_world_save.argtypes = [_vp, C.c_char_p]
     L.blokb_update_dense.argtypes = [_vp, _vp, C.c_size_t]
@@ -459,6 +473,18 @@ class Renderer:
         if frame is not None:
             self.set_frame(frame)
         _ck((self.L.blokb_trace_primary_shadow if shadow else self.L.blokb_trace_primary)(self._ctx, stream))
+
+    def set_path_options(self, mode=None, batch_samples=None, dir_cells=None, origin_cell_shift=None, morton_bits_per_axis=None):
+        """blokb_set_path_options; arguments left None keep their current value. Returns the options now in force."""
+        o = PathOptions()
+        _ck(self.L.blokb_get_path_options(self._ctx, C.byref(o)))
+        for name, v in (("mode", mode), ("batchSamples", batch_samples), ("dirCells", dir_cells), ("originCellShift", origin_cell_shift),
+                        ("mortonBitsPerAxis", morton_bits_per_axis)):
+            if v is not None:
+                setattr(o, name, int(v))
+        _ck(self.L.blokb_set_path_options(self._ctx, C.byref(o)))
+        _ck(self.L.blokb_get_path_options(self._ctx, C.byref(o)))
+        return {n: getattr(o, n) for n, _ in PathOptions._fields_}
 
     def trace_path(self, sample_begin, sample_end, stream=None):
         _ck(self.L.blokb_trace_path(self._ctx, sample_begin, sample_end, stream))

@@ -86,9 +86,45 @@ struct blokb_ctx {
     void* dReorder = nullptr;              // scratch of blokb_trace_rays_reordered (keys, order, cub), grow-only
     size_t reorderCap = 0;
     unsigned long long* dStats = nullptr;  // 2 counters when stats enabled
+    // wavefront path tracing (blokb_set_path_options): slot arrays of one batch, grow-only
+    blokb_path_options pathOpt{BLOKB_PATH_WAVEFRONT, 8, 8, 6, 5};
+    void* dWave = nullptr;
+    size_t waveCap = 0;
+    uint32_t waveBatch = 0;   // batch the current scratch was sized for (<= pathOpt.batchSamples)
+    size_t waveThreads = 0;   // ... and the launch size (threads of the pixel grid)
+    bool waveLimited = false; // the device could not hold the configured batch: waveBatch is all it gets at this size
     bool statsOn = false;
     uint64_t launches = 0;
+    // Dispatches enqueued on caller-supplied streams: one event per foreign stream, recorded after every dispatch on it. Calls that
+    // run on the context's own stream (readback, write_image, stats_read, uploads, reallocation) first make that stream wait
+    // for these events, so "dispatch on my stream, then blokb_readback" is ordered without the caller synchronising.
+    struct Foreign { cudaStream_t s; cudaEvent_t ev; bool dirty; };
+    std::vector<Foreign> foreign;
 };
+
+// After a dispatch on stream q: remember it if q is not the context's own stream.
+static int dispatched(blokb_ctx* c, cudaStream_t q) {
+    if (q == c->stream) return 0;
+    for (auto& f : c->foreign)
+        if (f.s == q) { f.dirty = true; CK(cudaEventRecord(f.ev, q)); return 0; }
+    cudaEvent_t ev = nullptr;
+    CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    c->foreign.push_back({q, ev, true});
+    CK(cudaEventRecord(ev, q));
+    return 0;
+}
+// Before work on the context's own stream that reads or replaces what dispatches wrote.
+static int join_dispatches(blokb_ctx* c) {
+    for (auto& f : c->foreign)
+        if (f.dirty) { CK(cudaStreamWaitEvent(c->stream, f.ev, 0)); f.dirty = false; }
+    return 0;
+}
+// Everything this context enqueued anywhere has finished (before buffers are freed or replaced).
+static int idle(blokb_ctx* c) {
+    if (int rc = join_dispatches(c)) return rc;
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
 
 static void free_world(blokb_ctx* c) {
     for (void* p : c->worldAllocs) cudaFree(p);
@@ -186,13 +222,15 @@ int blokb_create(int device, blokb_ctx** out) {
 void blokb_destroy(blokb_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaStreamSynchronize(c->stream);
+    idle(c);
+    for (auto& f : c->foreign) cudaEventDestroy(f.ev);
     free_world(c);
     free_images(c);
     if (c->dRays) cudaFree(c->dRays);
     if (c->dHits) cudaFree(c->dHits);
     if (c->dStats) cudaFree(c->dStats);
     if (c->dReorder) cudaFree(c->dReorder);
+    if (c->dWave) cudaFree(c->dWave);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -208,7 +246,7 @@ int blokb_upload_world(blokb_ctx* c, const blokb_svo_node* nodes, size_t nNodes,
     int rc = build_host_world(nodes, nNodes, subs, nSubs, hw, err);
     if (rc) return fail(rc, err);
     const auto t1 = std::chrono::steady_clock::now();
-    CK(cudaStreamSynchronize(c->stream));  // updateWorld waits idle before replacing buffers (renderer.hpp:55-71)
+    if (int rc2 = idle(c)) return rc2;  // updateWorld waits idle before replacing buffers (renderer.hpp:55-71)
     free_world(c);
     DeviceWorld& d = c->dw;
     d = DeviceWorld{};
@@ -258,7 +296,7 @@ int blokb_upload_voxels(blokb_ctx* c, const int32_t* xyz, const uint32_t* materi
     if ((n && (!xyz || !materialId)) || (nMaterials && !materials)) return fail(BLOKB_E_ARG, "null array with non-zero count");
     CK(cudaSetDevice(c->device));
     const auto t0 = std::chrono::steady_clock::now();
-    CK(cudaStreamSynchronize(c->stream));
+    if (int rc2 = idle(c)) return rc2;
     build::DeviceBuild B;
     std::string err;
     int rc = build::from_voxels(xyz, materialId, n, c->stream, B, err);
@@ -271,7 +309,7 @@ int blokb_upload_dense(blokb_ctx* c, const blokb_dense_chunk* chunks, size_t nCh
     if ((nChunks && !chunks) || (nMaterials && !materials)) return fail(BLOKB_E_ARG, "null array with non-zero count");
     CK(cudaSetDevice(c->device));
     const auto t0 = std::chrono::steady_clock::now();
-    CK(cudaStreamSynchronize(c->stream));
+    if (int rc2 = idle(c)) return rc2;
     build::DeviceBuild B;
     build::VoxelList L;
     std::string err;
@@ -294,7 +332,7 @@ int blokb_update_dense(blokb_ctx* c, const blokb_dense_chunk* chunks, size_t nCh
     if (nChunks == 0) return 0;
     CK(cudaSetDevice(c->device));
     const auto t0 = std::chrono::steady_clock::now();
-    CK(cudaStreamSynchronize(c->stream));   // updateWorld waits idle before replacing buffers (renderer.hpp:55-71)
+    if (int rc2 = idle(c)) return rc2;   // updateWorld waits idle before replacing buffers (renderer.hpp:55-71)
     std::string err;
     int rc = build::replace_chunks(c->edit, chunks, nChunks, c->stream, err);   // on failure the list is unchanged
     if (rc) return fail(rc, err);
@@ -432,6 +470,49 @@ uint64_t fnv1a64(const unsigned char* p, size_t n) {
 }
 }  // namespace
 
+// A dump is trusted only as far as its checksum (accidental damage); before its arrays go to the device every index the
+// traversal follows is range-checked here, so that a stale, truncated-and-rechecksummed or crafted file is refused with
+// BLOKB_E_ARG instead of making traverse() read nodes[base + rank], voxelMat[..] or blockFirstLeaf[aux + rank] out of bounds.
+// Layout being checked (scene.h): breadth-first levels L, L-1, ..., 2 (sub-chunks), 1 (bricks); children of a node are
+// nodes[base .. base + popcount(mask)) inside the next level's range; a brick's base / aux index voxelMat / blockFirstLeaf.
+static std::string validate_dump(const DumpHeader& h, const Node* nodes) {
+    for (int a = 0; a < 3; a++) {
+        if (h.dim[a] <= 0 || (h.dim[a] & 15) || (h.origin[a] & 15)) return "grid origin / extent is not a positive multiple of 16";
+        if (int64_t(h.dim[a]) > (int64_t(1) << (2 * h.levels))) return "grid extent exceeds 4^levels";
+        const int64_t lo = h.origin[a], hi = int64_t(h.origin[a]) + (int64_t(1) << (2 * h.levels));
+        if (lo <= -(int64_t(1) << 23) || hi >= (int64_t(1) << 24)) return "grid coordinates outside the float-exact range";
+    }
+    auto block_count = [](uint64_t m) {
+        int n = 0;
+        for (uint32_t b = 0; b < 8; b++) n += (m & (0x0000000000330033ull << (2u * (b & 1u) + 8u * ((b >> 1) & 1u) + 32u * ((b >> 2) & 1u)))) ? 1 : 0;
+        return n;
+    };
+    uint64_t start = 0, end = 1;   // node range of the level being checked
+    for (int level = h.levels; level >= 1; level--) {
+        if (end > h.nNodes) return "node levels run past the node array";
+        uint64_t kids = 0;
+        for (uint64_t i = start; i < end; i++) kids += uint64_t(__builtin_popcountll(nodes[i].mask));
+        if (level == 1) {
+            for (uint64_t i = start; i < end; i++) {
+                const Node& n = nodes[i];
+                if (uint64_t(n.base) + uint64_t(__builtin_popcountll(n.mask)) > h.nVoxels) return "brick " + std::to_string(i) + " indexes past voxelMat";
+                if (uint64_t(n.aux) + uint64_t(block_count(n.mask)) > h.nBlocks) return "brick " + std::to_string(i) + " indexes past blockFirstLeaf";
+            }
+            if (end != h.nNodes) return "node array is longer than its levels";
+            break;
+        }
+        const uint64_t cs = end, ce = end + kids;   // the next level's range
+        if (ce > h.nNodes) return "level " + std::to_string(level) + " has more children than nodes follow";
+        for (uint64_t i = start; i < end; i++) {
+            const Node& n = nodes[i];
+            const uint64_t k = uint64_t(__builtin_popcountll(n.mask));
+            if (k && (n.base < cs || uint64_t(n.base) + k > ce)) return "node " + std::to_string(i) + " points outside level " + std::to_string(level - 1);
+        }
+        start = cs; end = ce;
+    }
+    return "";
+}
+
 int blokb_world_save(blokb_ctx* c, const char* path) {
     if (!c || !path) return fail(BLOKB_E_ARG, "null argument");
     if (!c->haveWorld) return fail(BLOKB_E_STATE, "no world uploaded");
@@ -491,12 +572,13 @@ int blokb_world_load(blokb_ctx* c, const char* path) {
             if (total && std::fread(buf.data(), 1, total, f) != total) why = "truncated payload";
             else if (std::fgetc(f) != EOF) why = "trailing bytes after the payload";
             else if (fnv1a64(buf.data(), total) != h.fnv1a) why = "checksum mismatch";
+            else why = validate_dump(h, reinterpret_cast<const Node*>(buf.data()));
         }
     }
     std::fclose(f);
     if (!why.empty()) return fail(BLOKB_E_ARG, std::string(path) + ": " + why);
     const auto t1 = std::chrono::steady_clock::now();
-    CK(cudaStreamSynchronize(c->stream));
+    if (int rc2 = idle(c)) return rc2;
     free_world(c);
     void* dst[5] = {};
     size_t off = 0;
@@ -536,18 +618,28 @@ int blokb_set_frame(blokb_ctx* c, const blokb_frame_ubo* f) {
     if (f->screenWidth == 0 || f->screenHeight == 0 || f->screenWidth > 65536 || f->screenHeight > 65536) return fail(BLOKB_E_ARG, "bad screen size");
     CK(cudaSetDevice(c->device));
     if (c->buf.width != f->screenWidth || c->buf.height != f->screenHeight) {
-        CK(cudaStreamSynchronize(c->stream));
+        if (int rc = idle(c)) return rc;
+        // From here until every image exists the context has NO frame: a failed allocation must not leave the previous frame's
+        // size paired with null or partial images (the next dispatch would write through them).
+        c->haveFrame = false;
         free_images(c);
         const size_t n = size_t(f->screenWidth) * f->screenHeight;
-        CK(cudaMalloc((void**)&c->buf.hit, n * sizeof(blokb_hit)));
-        CK(cudaMalloc((void**)&c->buf.shadow, n));
-        CK(cudaMalloc((void**)&c->buf.color, n * 16));
-        CK(cudaMalloc((void**)&c->buf.worldPos, n * 16));
-        CK(cudaMalloc((void**)&c->buf.normalRough, n * 8));
-        CK(cudaMalloc((void**)&c->buf.albedoMetal, n * 4));
-        CK(cudaMalloc((void**)&c->buf.motion, n * 4));
-        CK(cudaMalloc((void**)&c->buf.accum, n * 16));
-        CK(cudaMemsetAsync(c->buf.accum, 0, n * 16, c->stream));
+        void** slots[] = {(void**)&c->buf.hit, (void**)&c->buf.shadow, (void**)&c->buf.color, (void**)&c->buf.worldPos, (void**)&c->buf.normalRough,
+                          (void**)&c->buf.albedoMetal, (void**)&c->buf.motion, (void**)&c->buf.accum};
+        const size_t bytes[] = {n * sizeof(blokb_hit), n, n * 16, n * 16, n * 8, n * 4, n * 4, n * 16};
+        for (int k = 0; k < 8; k++) {
+            const cudaError_t e = cudaMalloc(slots[k], bytes[k]);
+            if (e != cudaSuccess) {
+                *slots[k] = nullptr;
+                free_images(c);
+                return fail(BLOKB_E_CUDA, std::string("cudaMalloc of frame image ") + std::to_string(k) + ": " + cudaGetErrorString(e));
+            }
+        }
+        // zero-filled before any dispatch can touch it, whatever stream that dispatch uses
+        if (cudaMemsetAsync(c->buf.accum, 0, n * 16, c->stream) != cudaSuccess || cudaStreamSynchronize(c->stream) != cudaSuccess) {
+            free_images(c);
+            return fail(BLOKB_E_CUDA, "zero-fill of the accumulation image failed");
+        }
         c->buf.width = f->screenWidth; c->buf.height = f->screenHeight;
     }
     FrameDev& d = c->frame;
@@ -595,7 +687,7 @@ int blokb_set_peers(blokb_ctx* c, int image, const void* handles, uint32_t n, ui
     const int slot = peer_slot(image);
     if (slot < 0) return fail(BLOKB_E_ARG, "image is not exchangeable (hit, shadow, accum)");
     CK(cudaSetDevice(c->device));
-    CK(cudaStreamSynchronize(c->stream));
+    if (int rc = idle(c)) return rc;
     close_peers(c, slot);
     if (n == 0) return 0;
     if (!handles) return fail(BLOKB_E_ARG, "handles is null");
@@ -625,7 +717,7 @@ int blokb_bind_image(blokb_ctx* c, int image, void* local, void* multicast) {
     if (multicast && image == BLOKB_IMG_SHADOW && (c->buf.width & 3u)) return fail(BLOKB_E_ARG, "multicast shadow image needs width % 4 == 0");
     if ((reinterpret_cast<uintptr_t>(local) | reinterpret_cast<uintptr_t>(multicast)) & 15u) return fail(BLOKB_E_ARG, "addresses must be 16-byte aligned");
     CK(cudaSetDevice(c->device));
-    CK(cudaStreamSynchronize(c->stream));
+    if (int rc = idle(c)) return rc;
     close_peers(c, slot);
     unbind(c, slot);
     if (!local) return 0;
@@ -640,41 +732,102 @@ int blokb_trace_primary(blokb_ctx* c, void* stream) {
     if (int rc = ready(c, true)) return rc;
     CK(launch_primary(c->dw, c->frame, false, out_for(c, 0, c->buf.hit), own_only(c->buf.shadow), st(c), pick(c, stream)));
     c->launches++;
-    return 0;
+    return dispatched(c, pick(c, stream));
 }
 int blokb_trace_primary_shadow(blokb_ctx* c, void* stream) {
     if (int rc = ready(c, true)) return rc;
     CK(launch_primary(c->dw, c->frame, true, out_for(c, 0, c->buf.hit), out_for(c, 1, c->buf.shadow), st(c), pick(c, stream)));
     c->launches++;
+    return dispatched(c, pick(c, stream));
+}
+// Scratch of the wavefront schedule for the current launch size (frame size / strip set): grow-only, sized for the configured
+// batch; when the device cannot hold that, the batch is halved until it fits and the smaller batch is remembered.
+static int wave_ready(blokb_ctx* c, uint32_t samples, uint32_t* batchOut) {
+    const size_t nT = std::max<size_t>(wave_threads(c->frame), 1);
+    const uint32_t maxBatch = uint32_t(std::min<size_t>(0xFFFFFFFFull / nT, 1u << 16));
+    if (maxBatch == 0) return fail(BLOKB_E_UNSUPPORTED, "frame too large for the wavefront schedule (use BLOKB_PATH_FUSED)");
+    const uint32_t cfg = std::max(1u, std::min(c->pathOpt.batchSamples, maxBatch));
+    uint32_t want = std::max(1u, std::min(cfg, samples));
+    if (c->dWave && c->waveLimited && nT >= c->waveThreads) want = std::min(want, std::max(1u, uint32_t(size_t(c->waveBatch) * c->waveThreads / nT)));
+    if (c->dWave && wave_scratch_bytes(nT, want) <= c->waveCap) { *batchOut = want; return 0; }
+    CK(cudaDeviceSynchronize());   // the old scratch may still be in use on any stream
+    if (c->dWave) cudaFree(c->dWave);
+    c->dWave = nullptr; c->waveCap = 0; c->waveBatch = 0; c->waveThreads = 0; c->waveLimited = false;
+    for (uint32_t b = cfg;; b = (b + 1) / 2) {
+        const size_t need = wave_scratch_bytes(nT, b);
+        if (cudaMalloc(&c->dWave, need) == cudaSuccess) { c->waveCap = need; c->waveBatch = b; c->waveThreads = nT; c->waveLimited = b < cfg; break; }
+        cudaGetLastError();
+        c->dWave = nullptr;
+        if (b == 1) return fail(BLOKB_E_CUDA, "out of device memory for the wavefront scratch (" + std::to_string(need) + " bytes at batch 1)");
+    }
+    *batchOut = std::min(want, c->waveBatch);
     return 0;
 }
 int blokb_render(blokb_ctx* c, void* stream) {
     if (int rc = ready(c, true)) return rc;
     if (c->frame.sampleCount == 0) return fail(BLOKB_E_ARG, "frame.sampleCount is 0");
-    CK(launch_render(c->dw, c->frame, c->buf.color, c->buf.worldPos, c->buf.normalRough, c->buf.albedoMetal, c->buf.motion, st(c), pick(c, stream)));
-    c->launches += 2;  // k_gbuffer + k_path<.., kColor>
-    return 0;
+    if (c->pathOpt.mode == BLOKB_PATH_FUSED) {
+        CK(launch_render(c->dw, c->frame, c->buf.color, c->buf.worldPos, c->buf.normalRough, c->buf.albedoMetal, c->buf.motion, st(c), pick(c, stream)));
+        c->launches += 2;  // k_gbuffer + k_path<.., kColor>
+        return dispatched(c, pick(c, stream));
+    }
+    uint32_t batch = 0;
+    if (int rc = wave_ready(c, c->frame.sampleCount, &batch)) return rc;
+    CK(launch_gbuffer(c->dw, c->frame, c->buf.worldPos, c->buf.normalRough, c->buf.albedoMetal, c->buf.motion, pick(c, stream)));
+    c->launches++;
+    const WaveKey K = make_wave_key(c->dw, c->pathOpt.dirCells, c->pathOpt.originCellShift, c->pathOpt.mortonBitsPerAxis);
+    CK(launch_path_wavefront(c->dw, c->frame, 0u, c->frame.sampleCount, true, own_only(c->buf.color), c->dWave, batch, K, st(c), &c->launches, pick(c, stream)));
+    return dispatched(c, pick(c, stream));
 }
 int blokb_trace_path(blokb_ctx* c, uint32_t sampleBegin, uint32_t sampleEnd, void* stream) {
     if (int rc = ready(c, true)) return rc;
     if (sampleEnd < sampleBegin) return fail(BLOKB_E_ARG, "sampleEnd < sampleBegin");
     if (sampleEnd == sampleBegin) return 0;
-    CK(launch_path(c->dw, c->frame, sampleBegin, sampleEnd, out_for(c, 2, c->buf.accum), st(c), pick(c, stream)));
-    c->launches++;
+    if (c->pathOpt.mode == BLOKB_PATH_FUSED) {
+        CK(launch_path(c->dw, c->frame, sampleBegin, sampleEnd, out_for(c, 2, c->buf.accum), st(c), pick(c, stream)));
+        c->launches++;
+        return dispatched(c, pick(c, stream));
+    }
+    uint32_t batch = 0;
+    if (int rc = wave_ready(c, sampleEnd - sampleBegin, &batch)) return rc;
+    const WaveKey K = make_wave_key(c->dw, c->pathOpt.dirCells, c->pathOpt.originCellShift, c->pathOpt.mortonBitsPerAxis);
+    CK(launch_path_wavefront(c->dw, c->frame, sampleBegin, sampleEnd, false, out_for(c, 2, c->buf.accum), c->dWave, batch, K, st(c), &c->launches,
+                             pick(c, stream)));
+    return dispatched(c, pick(c, stream));
+}
+void blokb_path_options_default(blokb_path_options* o) {
+    if (o) *o = blokb_path_options{BLOKB_PATH_WAVEFRONT, 8, 8, 6, 5};
+}
+int blokb_set_path_options(blokb_ctx* c, const blokb_path_options* o) {
+    if (!c || !o) return fail(BLOKB_E_ARG, "null argument");
+    if (o->mode != BLOKB_PATH_WAVEFRONT && o->mode != BLOKB_PATH_FUSED) return fail(BLOKB_E_ARG, "unknown path mode");
+    if (o->dirCells > 16 || o->mortonBitsPerAxis > 6 || o->originCellShift < 0 || o->originCellShift > 20) return fail(BLOKB_E_ARG, "sort-key shape out of range");
+    blokb_path_options d;
+    blokb_path_options_default(&d);
+    c->pathOpt.mode = o->mode;
+    c->pathOpt.batchSamples = o->batchSamples ? o->batchSamples : d.batchSamples;
+    c->pathOpt.dirCells = o->dirCells ? o->dirCells : d.dirCells;
+    c->pathOpt.originCellShift = o->originCellShift ? o->originCellShift : d.originCellShift;
+    c->pathOpt.mortonBitsPerAxis = o->mortonBitsPerAxis ? o->mortonBitsPerAxis : d.mortonBitsPerAxis;
+    return 0;
+}
+int blokb_get_path_options(blokb_ctx* c, blokb_path_options* o) {
+    if (!c || !o) return fail(BLOKB_E_ARG, "null argument");
+    *o = c->pathOpt;
     return 0;
 }
 int blokb_resolve(blokb_ctx* c, void* stream) {
     if (int rc = ready(c, true)) return rc;
     CK(launch_resolve(c->buf.accum, c->buf.color, size_t(c->buf.width) * c->buf.height, pick(c, stream)));
     c->launches++;
-    return 0;
+    return dispatched(c, pick(c, stream));
 }
 int blokb_reset_accum(blokb_ctx* c, void* stream) {
     if (!c) return fail(BLOKB_E_ARG, "ctx is null");
     if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
     CK(cudaSetDevice(c->device));
     CK(cudaMemsetAsync(c->buf.accum, 0, size_t(c->buf.width) * c->buf.height * 16, pick(c, stream)));
-    return 0;
+    return dispatched(c, pick(c, stream));
 }
 int blokb_trace_rays(blokb_ctx* c, const float* dRays, size_t n, int /*anyHit*/, blokb_hit* dOut, void* stream) {
     // The walk is strictly front to back: the first filled voxel answers both closest-hit and any-hit queries.
@@ -682,7 +835,7 @@ int blokb_trace_rays(blokb_ctx* c, const float* dRays, size_t n, int /*anyHit*/,
     if (n && (!dRays || !dOut)) return fail(BLOKB_E_ARG, "null ray / output pointer");
     CK(launch_trace_rays(c->dw, dRays, n, dOut, st(c), pick(c, stream)));
     if (n) c->launches++;
-    return 0;
+    return dispatched(c, pick(c, stream));
 }
 int blokb_trace_rays_reordered(blokb_ctx* c, const float* dRays, size_t n, int /*anyHit*/, blokb_hit* dOut, void* stream) {
     if (int rc = ready(c, false)) return rc;
@@ -699,7 +852,7 @@ int blokb_trace_rays_reordered(blokb_ctx* c, const float* dRays, size_t n, int /
     }
     CK(launch_trace_rays_reordered(c->dw, dRays, n, dOut, c->dReorder, st(c), pick(c, stream)));
     c->launches += 3;  // keys, radix sort (counted as one), ordered trace
-    return 0;
+    return dispatched(c, pick(c, stream));
 }
 int blokb_trace_rays_host(blokb_ctx* c, const float* rays, size_t n, int anyHit, blokb_hit* out) {
     if (int rc = ready(c, false)) return rc;
@@ -785,7 +938,7 @@ int blokb_denoise(blokb_ctx* c, const blokb_post_settings* s, void* stream) {
         src = dst;
     }
     P.denoised = src;
-    return 0;
+    return dispatched(c, q);
 }
 int blokb_postprocess(blokb_ctx* c, const blokb_post_settings* s, void* stream) {
     cudaStream_t q = c ? pick(c, stream) : nullptr;
@@ -810,7 +963,7 @@ int blokb_postprocess(blokb_ctx* c, const blokb_post_settings* s, void* stream) 
     } else {
         P.final = P.taaOut; P.finalBytesPerPixel = 16;
     }
-    return 0;
+    return dispatched(c, q);
 }
 int blokb_end_frame(blokb_ctx* c, void* /*stream*/) {
     if (!c) return fail(BLOKB_E_ARG, "ctx is null");
@@ -830,7 +983,8 @@ int blokb_reset_history(blokb_ctx* c, void* stream) {
     if (!c) return fail(BLOKB_E_ARG, "ctx is null");
     if (!c->post.alloc) return 0;
     CK(cudaSetDevice(c->device));
-    return post_zero(c, pick(c, stream));
+    if (int rc = post_zero(c, pick(c, stream))) return rc;
+    return dispatched(c, pick(c, stream));
 }
 
 int blokb_get_buffers(blokb_ctx* c, blokb_buffers* out) {
@@ -868,6 +1022,7 @@ int blokb_readback(blokb_ctx* c, int image, void* host, size_t bytes) {
     if (!src) return fail(BLOKB_E_STATE, "image not produced yet (blokb_denoise / blokb_postprocess of the current frame)");
     if (bytes != sz) return fail(BLOKB_E_ARG, "host buffer size mismatch: expected " + std::to_string(sz));
     CK(cudaSetDevice(c->device));
+    if (int rc = join_dispatches(c)) return rc;   // ordered after dispatches enqueued on caller streams
     CK(cudaMemcpyAsync(host, src, sz, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     return 0;
@@ -891,6 +1046,7 @@ int blokb_write_image(blokb_ctx* c, int image, const void* host, size_t bytes) {
     }
     if (bytes != sz) return fail(BLOKB_E_ARG, "host buffer size mismatch: expected " + std::to_string(sz));
     CK(cudaSetDevice(c->device));
+    if (int rc = join_dispatches(c)) return rc;
     CK(cudaMemcpyAsync(dst, host, sz, cudaMemcpyHostToDevice, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     return 0;
@@ -898,8 +1054,7 @@ int blokb_write_image(blokb_ctx* c, int image, const void* host, size_t bytes) {
 int blokb_sync(blokb_ctx* c) {
     if (!c) return fail(BLOKB_E_ARG, "ctx is null");
     CK(cudaSetDevice(c->device));
-    CK(cudaStreamSynchronize(c->stream));
-    return 0;
+    return idle(c);   // the context's own stream and every dispatch enqueued on a caller stream
 }
 uint64_t blokb_launch_count(blokb_ctx* c) { return c ? c->launches : 0; }
 
@@ -908,13 +1063,16 @@ int blokb_stats_enable(blokb_ctx* c, int on) {
     if (!c) return fail(BLOKB_E_ARG, "ctx is null");
     c->statsOn = on != 0;
     CK(cudaSetDevice(c->device));
+    if (int rc = join_dispatches(c)) return rc;
     CK(cudaMemsetAsync(c->dStats, 0, 4 * sizeof(unsigned long long), c->stream));
+    CK(cudaStreamSynchronize(c->stream));   // zeroed before a dispatch on any stream can add to them
     return 0;
 }
 int blokb_stats_read(blokb_ctx* c, uint64_t* stepsAndRays /*[2]*/) {
     if (!c || !stepsAndRays) return fail(BLOKB_E_ARG, "null argument");
     CK(cudaSetDevice(c->device));
     unsigned long long v[2];
+    if (int rc = join_dispatches(c)) return rc;
     CK(cudaMemcpyAsync(v, c->dStats, sizeof v, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     stepsAndRays[0] = v[0]; stepsAndRays[1] = v[1];

@@ -269,6 +269,122 @@ __global__ void __launch_bounds__(kPixThreads) k_path(const __grid_constant__ De
     if (kStats) { atomicAdd(stats, (unsigned long long)steps); atomicAdd(stats + 1, (unsigned long long)rays); }
 }
 
+// ---- wavefront path tracing: bounce rays regrouped before they are traced ------------------------------------------------
+// k_path walks camera, shadow and bounce ray of a sample back to back in one thread; the bounce rays of a warp's 32 pixels
+// scatter over the hemisphere, and the warp then issues with ~12 of 32 lanes (profiles/r01t_ncu_k_path_c4_8spp.txt). Here a batch
+// of `nS` samples of every pixel runs as three stages over one slot array (slot = sample-in-batch * nT + launch-wide thread id):
+//   k_path_front   iteration 0 of raygen's loop for every (pixel, sample) of the batch — coherent camera + sun shadow rays —
+//                  stores the radiance gathered so far (front[slot].rgb, .w = "a bounce ray follows") and, for paths that go
+//                  on, the bounce ray {origin, direction, throughput} and its sort key;
+//   radix sort     of (key, slot) over the whole batch: key = direction cell above the Morton code of the origin's coarse
+//                  cell, so that consecutive rays leave neighbouring surface points in about the same direction; slots
+//                  without a bounce ray carry the key 0xFFFFFFFF and end up behind every ray;
+//   k_bounce       thread i walks ray order[i] (iteration 1: only a miss or an emissive hit still changes the radiance,
+//                  shade.cuh:path_bounce) and adds its term into front[slot] — one writer per slot, no atomics;
+//   k_path_gather  per pixel, the batch's slots are summed in sample order into the running sum of the call; the last batch
+//                  applies k_path's epilogue (accumulate into accum, or colour = mean with the firefly clamp).
+// Same expressions, same order of additions as k_path: the accumulated image is bit-identical (tests/test_gpu_wavefront.py).
+constexpr uint32_t kDeadKey = 0xFFFFFFFFu;
+__device__ __forceinline__ uint32_t dilate10(uint32_t v) {  // 10 bits -> every third bit
+    v &= 0x3FFu;
+    v = (v | (v << 16)) & 0x030000FFu;
+    v = (v | (v << 8)) & 0x0300F00Fu;
+    v = (v | (v << 4)) & 0x030C30C3u;
+    v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+__device__ __forceinline__ uint32_t wave_key(const DeviceWorld& W, const WaveKey& K, const F3& o, const F3& d) {
+    // d is unit length (sample_cosine / reflect3 of unit vectors)
+    auto cell = [&K](float v) { const int q = int((v + 1.0f) * K.dirScale); return uint32_t(q < 0 ? 0 : (q >= int(K.dirCells) ? int(K.dirCells) - 1 : q)); };
+    const uint32_t dcell = cell(d.x) + K.dirCells * (cell(d.y) + K.dirCells * cell(d.z));
+    auto coarse = [&K](float p, int g, int dim) {
+        float r = p - float(g);
+        r = r < 0.0f ? 0.0f : (r > float(dim - 1) ? float(dim - 1) : r);
+        return uint32_t(int(r) >> K.cellShift);
+    };
+    const uint32_t m = dilate10(coarse(o.x, W.origin[0], W.dim[0])) | (dilate10(coarse(o.y, W.origin[1], W.dim[1])) << 1) |
+                       (dilate10(coarse(o.z, W.origin[2], W.dim[2])) << 2);
+    return (dcell << K.mortonBits) | (m & ((1u << K.mortonBits) - 1u));
+}
+__device__ __forceinline__ uint32_t launch_thread_id() { return (blockIdx.y * gridDim.x + blockIdx.x) * kPixThreads + threadIdx.x; }
+
+template <bool kStats>
+__global__ void __launch_bounds__(kPixThreads) k_path_front(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F, uint32_t s0, uint32_t nS,
+                                                            const __grid_constant__ WaveBufs B, const __grid_constant__ WaveKey K, unsigned long long* stats) {
+    const uint32_t gtid = launch_thread_id();
+    uint32_t px, py;
+    const bool inFrame = thread_pixel(F, px, py);
+    uint32_t rays = 0, steps = 0;
+    const NodeStack stk = thread_stack();
+    for (uint32_t k = 0; k < nS; k++) {
+        const size_t slot = size_t(k) * B.nT + gtid;
+        F3 rad = f3(0.f);
+        BounceRay br;
+        bool alive = false;
+        if (inFrame) alive = path_front<kStats>(W, stk, F, px, py, s0 + k, nullptr, rays, steps, rad, br);
+        B.front[slot] = make_float4(rad.x, rad.y, rad.z, alive ? 1.0f : 0.0f);
+        B.order[slot] = uint32_t(slot);
+        uint32_t key = kDeadKey;
+        if (alive) {
+            key = wave_key(W, K, br.origin, br.dir);
+            float4* r = B.rec + 3 * slot;
+            r[0] = make_float4(br.origin.x, br.origin.y, br.origin.z, br.dir.x);
+            r[1] = make_float4(br.dir.y, br.dir.z, br.thr.x, br.thr.y);
+            r[2] = make_float4(br.thr.z, 0.f, 0.f, 0.f);
+        }
+        B.keys[slot] = key;
+    }
+    if (kStats) { atomicAdd(stats, (unsigned long long)steps); atomicAdd(stats + 1, (unsigned long long)rays); }
+}
+
+template <bool kStats>
+__global__ void __launch_bounds__(256) k_bounce(const __grid_constant__ DeviceWorld W, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ order,
+                                                size_t n, const float4* __restrict__ rec, float4* __restrict__ front, unsigned long long* stats) {
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (__ldg(keys + i) == kDeadKey) return;  // slots without a bounce ray sort behind every ray: whole warps leave here
+    const uint32_t slot = __ldg(order + i);
+    const float4 a = __ldg(rec + 3 * size_t(slot)), b = __ldg(rec + 3 * size_t(slot) + 1), c = __ldg(rec + 3 * size_t(slot) + 2);
+    BounceRay br;
+    br.origin = f3(a.x, a.y, a.z); br.dir = f3(a.w, b.x, b.y); br.thr = f3(b.z, b.w, c.x);
+    uint32_t rays = 0, steps = 0;
+    bool add;
+    const F3 t = path_bounce<kStats>(W, thread_stack(), br, rays, steps, add);
+    if (add) {
+        float4 f = front[slot];
+        f.x += t.x; f.y += t.y; f.z += t.z;
+        front[slot] = f;
+    }
+    if (kStats) { atomicAdd(stats, (unsigned long long)steps); atomicAdd(stats + 1, (unsigned long long)rays); }
+}
+
+// firstBatch / lastBatch: position of this batch inside one blokb_trace_path / blokb_render call (sTotal samples in all).
+template <bool kColor>
+__global__ void __launch_bounds__(kPixThreads) k_path_gather(const __grid_constant__ FrameDev F, uint32_t nS, bool firstBatch, bool lastBatch, uint32_t sTotal,
+                                                             const __grid_constant__ WaveBufs B, const __grid_constant__ PeerOut accum) {
+    const uint32_t gtid = launch_thread_id();
+    uint32_t px, py;
+    if (!thread_pixel(F, px, py)) return;
+    F3 acc = f3(0.f);
+    if (!firstBatch) { const float4 p = B.partial[gtid]; acc = f3(p.x, p.y, p.z); }
+    for (uint32_t k = 0; k < nS; k++) {
+        const float4 r = B.front[size_t(k) * B.nT + gtid];
+        acc = acc + f3(r.x, r.y, r.z);
+    }
+    if (!lastBatch) { B.partial[gtid] = make_float4(acc.x, acc.y, acc.z, 0.f); return; }
+    const size_t pi = size_t(py) * F.width + px;
+    if (kColor) {
+        F3 c = acc / float(sTotal);
+        const float mv = max3(c);
+        if (mv > 100.0f) c = c * (100.0f / mv);
+        static_cast<float4*>(accum.dst[0])[pi] = make_float4(c.x, c.y, c.z, 1.0f);
+        return;
+    }
+    float4 a = static_cast<const float4*>(accum.dst[0])[pi];
+    a.x += acc.x; a.y += acc.y; a.z += acc.z; a.w += float(sTotal);
+    store16_all(accum, pi, make_uint4(__float_as_uint(a.x), __float_as_uint(a.y), __float_as_uint(a.z), __float_as_uint(a.w)));
+}
+
 // color = sum / spp, firefly clamp (raygen.rgen:383-392).
 __global__ void __launch_bounds__(256) k_resolve(const float4* __restrict__ accum, float4* __restrict__ color, size_t n) {
     const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -361,6 +477,81 @@ cudaError_t launch_path(const DeviceWorld& W, const FrameDev& F, uint32_t sBegin
     if (g.y == 0) return cudaSuccess;
     if (stats) k_path<true, false><<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, sBegin, sEnd, accum, stats);
     else k_path<false, false><<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, sBegin, sEnd, accum, nullptr);
+    return cudaGetLastError();
+}
+// ---- wavefront launchers --------------------------------------------------------------------------------------------
+WaveKey make_wave_key(const DeviceWorld& W, uint32_t dirCells, int cellShift, uint32_t mortonBitsPerAxis) {
+    WaveKey K;
+    K.dirCells = std::min(std::max(dirCells, 1u), 16u);
+    K.dirScale = 0.5f * float(K.dirCells);
+    K.mortonBits = 3u * std::min(std::max(mortonBitsPerAxis, 1u), 6u);
+    // the coarse origin cells must cover the grid with mortonBitsPerAxis bits per axis
+    int shift = std::max(cellShift, 0);
+    const int maxDim = std::max(W.dim[0], std::max(W.dim[1], W.dim[2]));
+    while (((maxDim - 1) >> shift) >= (1 << (K.mortonBits / 3))) shift++;
+    K.cellShift = shift;
+    uint32_t dbits = 0;
+    while ((1u << dbits) < K.dirCells * K.dirCells * K.dirCells) dbits++;
+    K.bits = dbits + K.mortonBits;
+    return K;
+}
+size_t wave_threads(const FrameDev& F) {
+    const dim3 g = pixel_grid(F);
+    return size_t(g.x) * g.y * kPixThreads;
+}
+static inline size_t al256(size_t b) { return (b + 255) & ~size_t(255); }
+size_t wave_scratch_bytes(size_t nT, uint32_t batch) {
+    const size_t n = nT * batch;
+    size_t tb = 0;
+    cub::DoubleBuffer<uint32_t> dk(nullptr, nullptr), dv(nullptr, nullptr);
+    cub::DeviceRadixSort::SortPairs(nullptr, tb, dk, dv, (int64_t)n, 0, 32);
+    return al256(n * 16) + al256(n * 48) + 4 * al256(n * 4) + al256(nT * 16) + al256(tb);
+}
+cudaError_t launch_path_wavefront(const DeviceWorld& W, const FrameDev& F, uint32_t sBegin, uint32_t sEnd, bool toColor, const PeerOut& accum,
+                                  void* scratch, uint32_t batch, const WaveKey& K, unsigned long long* stats, uint64_t* launches, cudaStream_t st) {
+    const dim3 g = pixel_grid(F);
+    if (g.y == 0 || sEnd <= sBegin) return cudaSuccess;
+    const size_t nT = size_t(g.x) * g.y * kPixThreads;
+    if (nT * batch > 0xFFFFFFFFull) return cudaErrorInvalidValue;
+    const size_t cap = nT * batch;
+    char* p = static_cast<char*>(scratch);
+    WaveBufs B;
+    B.nT = uint32_t(nT);
+    B.front = reinterpret_cast<float4*>(p); p += al256(cap * 16);
+    B.rec = reinterpret_cast<float4*>(p); p += al256(cap * 48);
+    uint32_t* k0 = reinterpret_cast<uint32_t*>(p); p += al256(cap * 4);
+    uint32_t* k1 = reinterpret_cast<uint32_t*>(p); p += al256(cap * 4);
+    uint32_t* i0 = reinterpret_cast<uint32_t*>(p); p += al256(cap * 4);
+    uint32_t* i1 = reinterpret_cast<uint32_t*>(p); p += al256(cap * 4);
+    B.partial = reinterpret_cast<float4*>(p); p += al256(nT * 16);
+    void* tmp = p;
+    B.keys = k0; B.order = i0;
+    const uint32_t sTotal = sEnd - sBegin;
+    for (uint32_t s0 = sBegin; s0 < sEnd; s0 += batch) {
+        const uint32_t nS = std::min(batch, sEnd - s0);
+        const size_t n = nT * nS;
+        if (stats) k_path_front<true><<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, s0, nS, B, K, stats);
+        else k_path_front<false><<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, s0, nS, B, K, nullptr);
+        size_t tb = 0;
+        cub::DoubleBuffer<uint32_t> dk(k0, k1), dv(i0, i1);
+        cub::DeviceRadixSort::SortPairs(nullptr, tb, dk, dv, (int64_t)n, 0, int(K.bits));
+        cudaError_t e = cub::DeviceRadixSort::SortPairs(tmp, tb, dk, dv, (int64_t)n, 0, int(K.bits), st);
+        if (e != cudaSuccess) return e;
+        const unsigned blocks = (unsigned)((n + 255) / 256);
+        if (stats) k_bounce<true><<<blocks, 256, stack_bytes(W), st>>>(W, dk.Current(), dv.Current(), n, B.rec, B.front, stats);
+        else k_bounce<false><<<blocks, 256, stack_bytes(W), st>>>(W, dk.Current(), dv.Current(), n, B.rec, B.front, nullptr);
+        const bool first = s0 == sBegin, last = s0 + nS == sEnd;
+        if (toColor) k_path_gather<true><<<g, kPixThreads, 0, st>>>(F, nS, first, last, sTotal, B, accum);
+        else k_path_gather<false><<<g, kPixThreads, 0, st>>>(F, nS, first, last, sTotal, B, accum);
+        if (launches) *launches += 4;  // front, radix sort (counted as one), bounce, gather
+    }
+    return cudaGetLastError();
+}
+cudaError_t launch_gbuffer(const DeviceWorld& W, const FrameDev& F, float* worldPos, uint16_t* normalRough, uint8_t* albedoMetal, uint16_t* motion,
+                           cudaStream_t st) {
+    const dim3 g = pixel_grid(F);
+    if (g.y == 0) return cudaSuccess;
+    k_gbuffer<<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, (float4*)worldPos, (uint2*)normalRough, (uint32_t*)albedoMetal, (uint32_t*)motion);
     return cudaGetLastError();
 }
 cudaError_t launch_resolve(const float* accum, float* color, size_t n, cudaStream_t st) {

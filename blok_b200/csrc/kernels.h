@@ -41,5 +41,30 @@ cudaError_t launch_render(const DeviceWorld& W, const FrameDev& F, float* color,
                           uint16_t* motion, unsigned long long* stats, cudaStream_t st);
 cudaError_t launch_path(const DeviceWorld& W, const FrameDev& F, uint32_t sBegin, uint32_t sEnd, const PeerOut& accum, unsigned long long* stats,
                         cudaStream_t st);
+// Wavefront path tracing (kernels.cu): slot arrays of one batch of samples. nT = threads of the pixel grid of the launch.
+struct WaveBufs {
+    float4* front = nullptr;     // [batch * nT]     (radiance.rgb of iteration 0, 1 = a bounce ray follows)
+    float4* rec = nullptr;       // [batch * nT * 3] bounce ray: origin.xyz dir.x | dir.yz thr.xy | thr.z
+    uint32_t* keys = nullptr;    // [batch * nT]     sort key, 0xFFFFFFFF = no bounce ray
+    uint32_t* order = nullptr;   // [batch * nT]     slot index (the radix sort's values)
+    float4* partial = nullptr;   // [nT]             running per-pixel sum across the batches of one call
+    uint32_t nT = 0;
+};
+// key = direction cell (dirCells^3, x fastest) << mortonBits | Morton code of the origin's (1 << cellShift)-voxel cell
+struct WaveKey {
+    uint32_t dirCells = 8;
+    float dirScale = 4.0f;
+    int cellShift = 6;
+    uint32_t mortonBits = 15;
+    uint32_t bits = 24;  // key bits the radix sort looks at
+};
+WaveKey make_wave_key(const DeviceWorld& W, uint32_t dirCells, int cellShift, uint32_t mortonBitsPerAxis);
+size_t wave_threads(const FrameDev& F);
+size_t wave_scratch_bytes(size_t nT, uint32_t batch);
+// samples [sBegin, sEnd) in batches of `batch`; toColor: colour = mean + firefly clamp into accum.dst[0] (blokb_render) instead of accumulating
+cudaError_t launch_path_wavefront(const DeviceWorld& W, const FrameDev& F, uint32_t sBegin, uint32_t sEnd, bool toColor, const PeerOut& accum,
+                                  void* scratch, uint32_t batch, const WaveKey& K, unsigned long long* stats, uint64_t* launches, cudaStream_t st);
+cudaError_t launch_gbuffer(const DeviceWorld& W, const FrameDev& F, float* worldPos, uint16_t* normalRough, uint8_t* albedoMetal, uint16_t* motion,
+                           cudaStream_t st);
 cudaError_t launch_resolve(const float* accum, float* color, size_t n, cudaStream_t st);
 }  // namespace blokb

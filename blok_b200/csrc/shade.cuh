@@ -135,13 +135,21 @@ BLOKB_HD Surface fetch_surface(const DeviceWorld& W, uint32_t materialId) {  // 
     return s;
 }
 
-// One sample of raygen.rgen's path loop (:188-380). Returns the sample's radiance. When `first` is non-null
-// and the primary ray hits, *first receives the G-buffer first-hit data (:253-263).
+// One sample of raygen.rgen's path loop (:188-380), cut where the wavefront formulation cuts it (kernels.cu, k_path_front /
+// k_bounce): path_front() is everything up to and including the choice of the bounce ray (loop iteration bounce == 0: camera
+// ray, shading, sun shadow ray, lobe sampling), path_bounce() is iteration bounce == 1, of which only two statements can
+// still change the radiance — the sky term of a miss (:231-235) and the emission of an emissive hit (:265-277); the
+// Russian roulette, lobe choice and next origin computed after them (:329-376) feed an iteration that never runs
+// (bounce < 2) and a generator that is re-seeded per sample (:92-99). path_sample() = front, then bounce: the fused form.
+// Every expression is the shader's, in the shader's order, so both forms add the same fp32 values in the same order.
+// When `first` is non-null and the primary ray hits, *first receives the G-buffer first-hit data (:253-263).
 struct FirstHit { F3 pos, N, albedo, emission; float roughness, metallic, depth; bool had, emissive; };
+struct BounceRay { F3 origin, dir, thr; };
 
+// Returns true when the path goes on with `br` (radiance so far in `radiance`), false when it ended inside iteration 0.
 template <bool kStats>
-BLOKB_HD F3 path_sample(const DeviceWorld& W, const NodeStack& stk, const FrameDev& f, uint32_t px, uint32_t py, uint32_t s,
-                                          FirstHit* first, uint32_t& rays, uint32_t& steps) {
+BLOKB_HD bool path_front(const DeviceWorld& W, const NodeStack& stk, const FrameDev& f, uint32_t px, uint32_t py, uint32_t s,
+                         FirstHit* first, uint32_t& rays, uint32_t& steps, F3& radiance, BounceRay& br) {
     uint32_t rng = init_rng(px, py, f.width, f.frameCount, s);
     float pcx, pcy;
     if (s == 0u) { pcx = float(px) + 0.5f; pcy = float(py) + 0.5f; }
@@ -150,83 +158,107 @@ BLOKB_HD F3 path_sample(const DeviceWorld& W, const NodeStack& stk, const FrameD
         const float jy = random_float(rng) - 0.5f;
         pcx = float(px) + 0.5f + jx * 0.5f; pcy = float(py) + 0.5f + jy * 0.5f;
     }
-    F3 rayDir = primary_dir(f, pcx, pcy);
-    F3 rayOrigin = f3(f.camPos[0], f.camPos[1], f.camPos[2]);
-    F3 radiance = f3(0.f), thr = f3(1.f);
+    const F3 rayDir = primary_dir(f, pcx, pcy);
+    const F3 rayOrigin = f3(f.camPos[0], f.camPos[1], f.camPos[2]);
+    radiance = f3(0.f);
+    F3 thr = f3(1.f);
     const F3 sunDir = sun_dir();
     const F3 sunRad = f3(3.0f, 2.9f, 2.7f);
-    for (uint32_t bounce = 0u; bounce < 2u; bounce++) {
-        HitRec h;
+    HitRec h;
+    rays++;
+    // the camera ray enters the grid from outside: start cell found level by level (Walker::init, locate = false)
+    const bool hit = traverse<kStats>(W, stk, rayOrigin.x, rayOrigin.y, rayOrigin.z, rayDir.x, rayDir.y, rayDir.z, 0.001f, 10000.0f, h, steps,
+                                      /*locate=*/false);
+    if (!hit) {
+        radiance = radiance + thr * sky_color(rayDir);
+        return false;
+    }
+    const Surface m = fetch_surface(W, h.material);
+    F3 N = face_normal(h.facePrim & 7u);
+    const F3 hitPos = rayOrigin + rayDir * h.t;
+    if (dot3(N, rayDir) > 0.0f) N = -N;
+    if (first && s == 0u && !first->had) {
+        first->had = true; first->pos = hitPos; first->N = N; first->albedo = m.albedo; first->emission = m.emission;
+        first->roughness = m.roughness; first->metallic = m.metallic; first->depth = h.t; first->emissive = is_emissive(m.emission);
+    }
+    if (is_emissive(m.emission)) {
+        radiance = radiance + thr * m.emission;
+        if (luminance(m.emission) > 5.0f) return false;
+    }
+    const float NdotL = fmaxf(dot3(N, sunDir), 0.0f);
+    if (NdotL > 0.0f) {
+        const F3 so = hitPos + N * 0.001f;
+        HitRec sh;
         rays++;
-        // the camera ray enters the grid from outside, the bounce ray starts on geometry: different start-cell strategies
-        const bool hit = traverse<kStats>(W, stk, rayOrigin.x, rayOrigin.y, rayOrigin.z, rayDir.x, rayDir.y, rayDir.z, 0.001f, 10000.0f, h, steps,
-                                          /*locate=*/bounce > 0u);
-        if (!hit) {
-            radiance = radiance + thr * sky_color(rayDir);
-            break;
-        }
-        const Surface m = fetch_surface(W, h.material);
-        F3 N = face_normal(h.facePrim & 7u);
-        const F3 hitPos = rayOrigin + rayDir * h.t;
-        if (dot3(N, rayDir) > 0.0f) N = -N;
-        if (bounce == 0u && first && s == 0u && !first->had) {
-            first->had = true; first->pos = hitPos; first->N = N; first->albedo = m.albedo; first->emission = m.emission;
-            first->roughness = m.roughness; first->metallic = m.metallic; first->depth = h.t; first->emissive = is_emissive(m.emission);
-        }
-        if (is_emissive(m.emission)) {
-            radiance = radiance + thr * m.emission;
-            if (luminance(m.emission) > 5.0f || bounce > 0u) break;
-        }
-        const float NdotL = fmaxf(dot3(N, sunDir), 0.0f);
-        if (NdotL > 0.0f && bounce == 0u) {
-            const F3 so = hitPos + N * 0.001f;
-            HitRec sh;
-            rays++;
-            if (!traverse<kStats>(W, stk, so.x, so.y, so.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps, true)) {
-                const F3 diffuse = m.albedo * (1.0f - m.metallic);
-                radiance = radiance + thr * diffuse * sunRad * NdotL * BLOKB_INV_PI;
-                if (m.roughness < 0.9f) {
-                    const F3 Hh = normalize3(sunDir - rayDir);
-                    const float NdotH = fmaxf(dot3(N, Hh), 0.0f), VdotH = fmaxf(dot3(-rayDir, Hh), 0.0f);
-                    const float a = m.roughness * m.roughness, a2 = a * a;
-                    const float denom = NdotH * NdotH * (a2 - 1.0f) + 1.0f;
-                    const float D = a2 / (BLOKB_PI * denom * denom);
-                    const F3 F0 = mix3(f3(0.04f), m.albedo, m.metallic);
-                    const F3 F = fresnel(VdotH, F0);
-                    radiance = radiance + thr * F * D * 0.25f * sunRad * NdotL;
-                }
+        if (!traverse<kStats>(W, stk, so.x, so.y, so.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps, true)) {
+            const F3 diffuse = m.albedo * (1.0f - m.metallic);
+            radiance = radiance + thr * diffuse * sunRad * NdotL * BLOKB_INV_PI;
+            if (m.roughness < 0.9f) {
+                const F3 Hh = normalize3(sunDir - rayDir);
+                const float NdotH = fmaxf(dot3(N, Hh), 0.0f), VdotH = fmaxf(dot3(-rayDir, Hh), 0.0f);
+                const float a = m.roughness * m.roughness, a2 = a * a;
+                const float denom = NdotH * NdotH * (a2 - 1.0f) + 1.0f;
+                const float D = a2 / (BLOKB_PI * denom * denom);
+                const F3 F0 = mix3(f3(0.04f), m.albedo, m.metallic);
+                const F3 F = fresnel(VdotH, F0);
+                radiance = radiance + thr * F * D * 0.25f * sunRad * NdotL;
             }
         }
-        if (bounce > 0u) {
-            const float p = fminf(max3(thr), 0.95f);
-            if (random_float(rng) > p) break;
-            thr = thr / p;
-        }
-        const float ux = random_float(rng);
-        const float uy = random_float(rng);
-        const F3 F0 = mix3(f3(0.04f), m.albedo, m.metallic);
-        const F3 V = -rayDir;
-        const float NdotV = fmaxf(dot3(N, V), 0.001f);
-        const F3 F = fresnel(NdotV, F0);
-        float sw = (F.x + F.y + F.z) / 3.0f;
-        sw = sw * (1.0f - m.metallic) + 1.0f * m.metallic;
-        if (random_float(rng) < sw) {
-            const F3 Hh = sample_ggx(ux, uy, N, fmaxf(m.roughness, 0.04f));
-            const F3 nd = reflect3(rayDir, Hh);
-            if (dot3(nd, N) <= 0.0f) break;
-            const float HdotV = fmaxf(dot3(Hh, V), 0.0f);
-            const F3 Fh = fresnel(HdotV, F0);
-            thr = thr * (Fh / fmaxf(sw, 0.001f));
-            rayDir = nd;
-        } else {
-            const F3 nd = sample_cosine(ux, uy, N);
-            const F3 diffuse = m.albedo * (1.0f - m.metallic);
-            thr = thr * (diffuse / fmaxf(1.0f - sw, 0.001f));
-            rayDir = nd;
-        }
-        const float mt = max3(thr);
-        if (mt > 10.0f) thr = thr * (10.0f / mt);
-        rayOrigin = hitPos + N * 0.002f;
+    }
+    // no Russian roulette on iteration 0 (:329: bounce > 0)
+    const float ux = random_float(rng);
+    const float uy = random_float(rng);
+    const F3 F0 = mix3(f3(0.04f), m.albedo, m.metallic);
+    const F3 V = -rayDir;
+    const float NdotV = fmaxf(dot3(N, V), 0.001f);
+    const F3 F = fresnel(NdotV, F0);
+    float sw = (F.x + F.y + F.z) / 3.0f;
+    sw = sw * (1.0f - m.metallic) + 1.0f * m.metallic;
+    F3 nd;
+    if (random_float(rng) < sw) {
+        const F3 Hh = sample_ggx(ux, uy, N, fmaxf(m.roughness, 0.04f));
+        nd = reflect3(rayDir, Hh);
+        if (dot3(nd, N) <= 0.0f) return false;
+        const float HdotV = fmaxf(dot3(Hh, V), 0.0f);
+        const F3 Fh = fresnel(HdotV, F0);
+        thr = thr * (Fh / fmaxf(sw, 0.001f));
+    } else {
+        nd = sample_cosine(ux, uy, N);
+        const F3 diffuse = m.albedo * (1.0f - m.metallic);
+        thr = thr * (diffuse / fmaxf(1.0f - sw, 0.001f));
+    }
+    const float mt = max3(thr);
+    if (mt > 10.0f) thr = thr * (10.0f / mt);
+    br.origin = hitPos + N * 0.002f;
+    br.dir = nd;
+    br.thr = thr;
+    return true;
+}
+
+// Iteration bounce == 1: the term it adds to the sample's radiance (`add` = whether it adds one at all; adding is kept apart
+// from "adds zero" so that both forms perform exactly the shader's additions).
+template <bool kStats>
+BLOKB_HD F3 path_bounce(const DeviceWorld& W, const NodeStack& stk, const BounceRay& br, uint32_t& rays, uint32_t& steps, bool& add) {
+    HitRec h;
+    rays++;
+    // the bounce ray starts on geometry: start voxel located once (Walker::init, locate = true)
+    const bool hit = traverse<kStats>(W, stk, br.origin.x, br.origin.y, br.origin.z, br.dir.x, br.dir.y, br.dir.z, 0.001f, 10000.0f, h, steps,
+                                      /*locate=*/true);
+    if (!hit) { add = true; return br.thr * sky_color(br.dir); }
+    const Surface m = fetch_surface(W, h.material);
+    add = is_emissive(m.emission);
+    return br.thr * m.emission;
+}
+
+template <bool kStats>
+BLOKB_HD F3 path_sample(const DeviceWorld& W, const NodeStack& stk, const FrameDev& f, uint32_t px, uint32_t py, uint32_t s,
+                        FirstHit* first, uint32_t& rays, uint32_t& steps) {
+    F3 radiance;
+    BounceRay br;
+    if (path_front<kStats>(W, stk, f, px, py, s, first, rays, steps, radiance, br)) {
+        bool add;
+        const F3 c = path_bounce<kStats>(W, stk, br, rays, steps, add);
+        if (add) radiance = radiance + c;
     }
     return radiance;
 }

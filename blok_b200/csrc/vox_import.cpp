@@ -94,14 +94,14 @@ int blokb_vox_parse(const void* data, size_t bytes, uint32_t modelIndex, const f
     Reader r{static_cast<const uint8_t*>(data), bytes};
     char magic[4] = {0, 0, 0, 0};
     for (char& c : magic) c = (char)r.get<uint8_t>();
-    if (!r.ok || std::memcmp(magic, "VOX ", 4) != 0) { g_voxErr = "Invalid VOX file: bad magic number"; return BLOKB_E_ARG; }
+    if (!r.ok || std::memcmp(magic, "VOX ", 4) != 0) { g_voxErr = "not a MagicaVoxel file (the first four bytes are not the \"VOX \" magic)"; return BLOKB_E_ARG; }
     const int32_t version = r.get<int32_t>();
-    if (!r.ok) { g_voxErr = "Failed to read VOX version"; return BLOKB_E_ARG; }
-    if (version < 150) { g_voxErr = "Unsupported VOX version: " + std::to_string(version) + " (need >= 150)"; return BLOKB_E_UNSUPPORTED; }
+    if (!r.ok) { g_voxErr = "file ends before the format version"; return BLOKB_E_ARG; }
+    if (version < 150) { g_voxErr = "format version " + std::to_string(version) + " is older than 150, the oldest this importer reads"; return BLOKB_E_UNSUPPORTED; }
     for (char& c : magic) c = (char)r.get<uint8_t>();
-    if (!r.ok || std::memcmp(magic, "MAIN", 4) != 0) { g_voxErr = "Invalid VOX file: missing MAIN chunk"; return BLOKB_E_ARG; }
+    if (!r.ok || std::memcmp(magic, "MAIN", 4) != 0) { g_voxErr = "the chunk after the header is not MAIN"; return BLOKB_E_ARG; }
     const int32_t mainContent = r.get<int32_t>(), mainChildren = r.get<int32_t>();
-    if (!r.ok) { g_voxErr = "Failed to read MAIN chunk header"; return BLOKB_E_ARG; }
+    if (!r.ok) { g_voxErr = "file ends inside the MAIN chunk's size fields"; return BLOKB_E_ARG; }
     if (mainContent > 0) r.pos = std::min(r.n, r.pos + size_t(mainContent));
     const size_t end = std::min(r.n, r.pos + size_t(mainChildren > 0 ? mainChildren : 0));
 
@@ -127,7 +127,7 @@ int blokb_vox_parse(const void* data, size_t bytes, uint32_t modelIndex, const f
             cur.sized = true;
         } else if (!std::memcmp(id, "XYZI", 4)) {
             const int32_t nv = r.get<int32_t>();
-            if (!r.ok) { g_voxErr = "Failed to read voxel count"; return BLOKB_E_ARG; }
+            if (!r.ok) { g_voxErr = "XYZI chunk ends before its voxel count"; return BLOKB_E_ARG; }
             const size_t avail = r.pos < r.n ? (r.n - r.pos) / 4 : 0;
             const size_t take = std::min<size_t>(nv > 0 ? size_t(nv) : 0, avail);
             cur.xyzi.insert(cur.xyzi.end(), r.p + r.pos, r.p + r.pos + 4 * take);
@@ -157,8 +157,8 @@ int blokb_vox_parse(const void* data, size_t bytes, uint32_t modelIndex, const f
         if (children > 0) r.pos = std::min(r.n, r.pos + size_t(children));
     }
     if (cur.sized || !cur.xyzi.empty()) { models.push_back(std::move(cur)); sizes.insert(sizes.end(), curSize, curSize + 3); }
-    if (models.empty()) { g_voxErr = "No models found in VOX file"; return BLOKB_E_ARG; }
-    if (modelIndex >= models.size()) { g_voxErr = "Invalid model index: " + std::to_string(modelIndex) + " (only " + std::to_string(models.size()) + " models)"; return BLOKB_E_ARG; }
+    if (models.empty()) { g_voxErr = "the file holds no model (no SIZE + XYZI pair with voxels)"; return BLOKB_E_ARG; }
+    if (modelIndex >= models.size()) { g_voxErr = "model " + std::to_string(modelIndex) + " requested, but the file has " + std::to_string(models.size()); return BLOKB_E_ARG; }
 
     blokb_vox* v = new (std::nothrow) blokb_vox;
     if (!v) { g_voxErr = "out of host memory"; return BLOKB_E_ARG; }
@@ -207,7 +207,7 @@ int blokb_vox_load(const char* path, uint32_t modelIndex, const float* offset, b
     if (!path || !out) { g_voxErr = "null argument"; return BLOKB_E_ARG; }
     *out = nullptr;
     FILE* f = std::fopen(path, "rb");
-    if (!f) { g_voxErr = std::string("Failed to open file ") + path; return BLOKB_E_ARG; }
+    if (!f) { g_voxErr = std::string("cannot open ") + path; return BLOKB_E_ARG; }
     std::vector<uint8_t> buf;
     uint8_t tmp[1 << 16];
     size_t k;

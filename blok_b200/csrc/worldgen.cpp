@@ -8,7 +8,7 @@
 //   packChunksToGpuSvo + subChunkHasGeometry + findSubChunkRootNode   chunk_manager.cpp:144-314
 // The reference iterates chunks in std::unordered_map order (chunk_manager.cpp:249), which is unspecified; this
 // builder emits chunks sorted by (z, y, x). Single-chunk worlds are therefore bit-identical to the reference's
-// arrays; multi-chunk worlds are identical up to that chunk permutation (tests/test_worldgen.py checks both).
+// arrays; multi-chunk worlds are identical up to that chunk permutation (tests/test_host.py::test_worldgen_* check both).
 #include <algorithm>
 #include <cstdint>
 #include <cstring>

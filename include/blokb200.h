@@ -16,6 +16,12 @@
  * thread-local message. No exceptions cross the boundary. A context is single-owner (not thread-safe);
  * one context per GPU. "Enqueue" calls are asynchronous on the given CUDA stream (a cudaStream_t passed as
  * void*; NULL = the context's own stream) exactly like recording into the reference's command buffer.
+ * Streams: a dispatch on a caller stream is ordered after earlier work on THAT stream only. Calls that move data for the
+ * caller — blokb_readback, blokb_write_image, blokb_stats_read, blokb_world_export, the uploads, blokb_set_frame when it
+ * reallocates, blokb_set_peers / blokb_bind_image — run on the context's own stream, which first waits (cudaStreamWaitEvent)
+ * for every dispatch this context enqueued on any caller stream; so "dispatch on my stream, then blokb_readback" returns that
+ * dispatch's output without a synchronisation by the caller, and blokb_sync waits for caller-stream dispatches too. The
+ * reverse direction needs nothing: those calls have completed when they return.
  * There is no CPU fallback: without a CUDA device every compute entry point fails with BLOKB_E_CUDA.
  */
 #ifndef BLOKB200_H
@@ -269,6 +275,29 @@ int blokb_render(blokb_ctx* ctx, void* stream);               /* full raygen.rge
 int blokb_trace_path(blokb_ctx* ctx, uint32_t sampleBegin, uint32_t sampleEnd, void* stream); /* accum += samples */
 int blokb_resolve(blokb_ctx* ctx, void* stream);              /* color = accum.rgb / accum.a, firefly clamp */
 int blokb_reset_accum(blokb_ctx* ctx, void* stream);          /* CudaTracer::resetAccum */
+/* How blokb_render / blokb_trace_path schedule the rays of a sample (the reference leaves this to the driver's ray-tracing
+ * pipeline, renderer_raytracing.cpp:666-685). Either way the images are those of raygen.rgen:188-392, bit for bit the same.
+ *   BLOKB_PATH_WAVEFRONT (default)  batches of `batchSamples` samples of every pixel: camera + sun-shadow rays per pixel tile,
+ *                                   then the bounce rays of the whole batch sorted by a key — direction cell (dirCells^3) above
+ *                                   the Morton code (mortonBitsPerAxis bits per axis) of the origin's 2^originCellShift-voxel
+ *                                   cell — and traced in that order, so a warp's rays walk the same nodes.
+ *                                   Needs scratch memory: 80 bytes x pixels x batchSamples, allocated on first use, grow-only;
+ *                                   the batch is halved if the allocation fails.
+ *   BLOKB_PATH_FUSED                one thread walks camera, shadow and bounce ray of a sample back to back; no scratch.
+ * Zero fields mean "default". Takes effect from the next dispatch. */
+#define BLOKB_PATH_WAVEFRONT 0
+#define BLOKB_PATH_FUSED 1
+typedef struct blokb_path_options {
+    int32_t mode;
+    uint32_t batchSamples;      /* default 8 */
+    uint32_t dirCells;          /* 1..16, default 8 */
+    int32_t originCellShift;    /* default 6 (64-voxel cells); raised as needed to cover the grid */
+    uint32_t mortonBitsPerAxis; /* 1..6, default 5 */
+} blokb_path_options;
+void blokb_path_options_default(blokb_path_options* out);
+int blokb_set_path_options(blokb_ctx* ctx, const blokb_path_options* opt);
+int blokb_get_path_options(blokb_ctx* ctx, blokb_path_options* out);
+
 /* Denoiser + post-process, enqueue only. Frame order as in Renderer::render
  * (blok/src/renderer_draw.cpp:141-213, 314-328): blokb_set_frame, blokb_render, blokb_denoise, blokb_postprocess,
  * blokb_end_frame. History images start zero-filled; frameCount == 0 in the FrameUBO disables both reprojections.
@@ -287,7 +316,7 @@ int blokb_end_frame(blokb_ctx* ctx, void* stream);
 int blokb_reset_history(blokb_ctx* ctx, void* stream);
 /* Arbitrary rays (device pointers): rays = n x {ox,oy,oz,dx,dy,dz,tmin,tmax}; anyHit != 0 = shadow-ray rules. */
 int blokb_trace_rays(blokb_ctx* ctx, const float* dRays, size_t n, int anyHit, blokb_hit* dOut, void* stream);
-/* The same result for INCOHERENT lists (bounce rays): the rays are sorted on the device by a 4^3 direction cell above the
+/* The same result for INCOHERENT lists (bounce rays): the rays are sorted on the device by an 8^3 direction cell above the
  * Morton code of their origin's coarse cell, traced in that order (a warp's rays then walk the same nodes) and every record
  * is written to its ray's own slot — dOut is byte-identical to blokb_trace_rays'. Costs one key pass + one radix sort;
  * pays off when neighbouring list entries point different ways. One list per context at a time. */
@@ -297,7 +326,7 @@ int blokb_trace_rays_host(blokb_ctx* ctx, const float* rays, size_t n, int anyHi
 
 /* Images out. */
 int blokb_get_buffers(blokb_ctx* ctx, blokb_buffers* out);
-int blokb_readback(blokb_ctx* ctx, int image, void* host, size_t bytes); /* stream-ordered copy + sync */
+int blokb_readback(blokb_ctx* ctx, int image, void* host, size_t bytes); /* copy + sync, ordered after every dispatch of this context (any stream) */
 /* Inverse of blokb_readback for the G-buffer images (COLOR, WORLDPOS, NORMALROUGH, ALBEDOMETAL, MOTION, ACCUM): lets a
  * caller that produced the G-buffer elsewhere (or a test) feed blokb_denoise / blokb_postprocess. Copy + sync. */
 int blokb_write_image(blokb_ctx* ctx, int image, const void* host, size_t bytes);

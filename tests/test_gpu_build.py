@@ -278,6 +278,39 @@ def test_scene_dump_rejects_damaged_files(tmp_path):
             b.load_world(p)
     with pytest.raises(BlokbError, match="cannot open"):
         b.load_world(tmp_path / "missing.blokb")
+    # files that pass the checksum but would send the traversal out of bounds: every index it follows is range-checked on load
+    import struct
+
+    def fnv(payload):
+        h = 1469598103934665603
+        for byte in payload:
+            h = ((h ^ byte) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+        return h
+
+    def crafted(edit_header=None, edit_payload=None):
+        head, payload = bytearray(raw[:200]), bytearray(raw[200:])
+        if edit_payload:
+            edit_payload(payload)
+            head[192:200] = struct.pack("<Q", fnv(payload))
+        if edit_header:
+            edit_header(head)
+        return bytes(head) + bytes(payload)
+
+    n_nodes = struct.unpack_from("<Q", raw, 48)[0]
+    assert fnv(raw[200:]) == struct.unpack_from("<Q", raw, 192)[0]
+    forged = {
+        "points outside": crafted(edit_payload=lambda pl: struct.pack_into("<I", pl, 8, 0x7FFFFF00)),                     # root.base
+        "past voxelMat": crafted(edit_payload=lambda pl: struct.pack_into("<I", pl, 16 * (n_nodes - 1) + 8, 0xFFFFFF00)),    # last brick.base
+        "past blockFirstLeaf": crafted(edit_payload=lambda pl: struct.pack_into("<I", pl, 16 * (n_nodes - 1) + 12, 0xFFFFFF00)),
+        "children|points outside|past|longer|run past": crafted(edit_payload=lambda pl: struct.pack_into("<Q", pl, 0, 0xFFFFFFFFFFFFFFFF)),  # root.mask
+        "multiple of 16": crafted(edit_header=lambda h: struct.pack_into("<i", h, 16, 8)),                                  # origin.x
+        "exceeds 4": crafted(edit_header=lambda h: struct.pack_into("<i", h, 28, 1 << 20)),                                 # dim.x
+    }
+    for why, data in forged.items():
+        p = tmp_path / "forged.blokb"
+        p.write_bytes(data)
+        with pytest.raises(BlokbError, match=why):
+            b.load_world(p)
     # a failed load leaves the context usable
     b.load_world(path)
     assert b.world_stats()["voxels"] == a.world_stats()["voxels"]

@@ -70,7 +70,7 @@ def test_errors(tmp_path):
     assert e.value.code == -3
     with pytest.raises(BlokbError) as e:
         load_vox(write_vox([((4, 4, 4), v)]), model_index=3)
-    assert "model index" in str(e.value)
+    assert "model 3 requested" in str(e.value)
     with pytest.raises(BlokbError):
         load_vox(b"VOX " + (150).to_bytes(4, "little") + b"MAIN" + b"\0" * 8)  # no models
     xyz, ids, mats, info = load_vox(write_vox([((4, 4, 4), v)], extra_chunks=False)[:-2])  # truncated voxel record: dropped, like a short read

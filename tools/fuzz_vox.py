@@ -89,7 +89,7 @@ while time.time() < t_end:
                 refused = False
             except RuntimeError:
                 pass
-        if "Invalid model index" not in str(ex) or not refused:
+        if "requested, but the file has" not in str(ex) or not refused:
             print(f"MISMATCH seed {seed}: importer refuses a file the reference loads: {ex}")
             sys.exit(1)
         files += 1
