@@ -7,4 +7,4 @@ sharding.py (tile / sample partition across GPUs).
 from .api import (BlokbError, Camera, FramePipeline, FrameUBO, PostSettings, Renderer, load_vox, WorldSvoGpu, load_library, HIT_DT, MAT_DT, NODE_DT, PACKED_DT, SUB_DT,  # noqa: F401
                   IMG_ACCUM, IMG_ALBEDOMETAL, IMG_COLOR, IMG_HIT, IMG_MOTION, IMG_NORMALROUGH, IMG_SHADOW, IMG_WORLDPOS,
                   IMG_DENOISED, IMG_FINAL, IMG_HISTORY_COLOR, IMG_HISTORY_LENGTH, IMG_MOMENTS, IMG_TAA_HISTORY, IMG_TAA_OUTPUT, IMG_TONEMAPPED,
-                  IMG_VARIANCE, PATH_FUSED, PATH_WAVEFRONT, PathOptions, WORLD_BLOCKFIRSTLEAF, WORLD_NODES, WORLD_SUBCHUNKS, WORLD_VOXELMAT)
+                  IMG_VARIANCE, IMG_HIT_PACKED, REDUCE_ALL, REDUCE_SLICE, PATH_FUSED, PATH_WAVEFRONT, PathOptions, WORLD_BLOCKFIRSTLEAF, WORLD_NODES, WORLD_SUBCHUNKS, WORLD_VOXELMAT)

@@ -36,7 +36,8 @@ PACKED_MAX_NODES = 0x1FFFFFFF
 
 IMG_HIT, IMG_SHADOW, IMG_COLOR, IMG_WORLDPOS, IMG_NORMALROUGH, IMG_ALBEDOMETAL, IMG_MOTION, IMG_ACCUM = range(8)
 (IMG_HISTORY_COLOR, IMG_MOMENTS, IMG_HISTORY_LENGTH, IMG_VARIANCE, IMG_DENOISED, IMG_TAA_HISTORY, IMG_TAA_OUTPUT, IMG_TONEMAPPED,
- IMG_FINAL) = range(8, 17)
+ IMG_FINAL, IMG_HIT_PACKED) = range(8, 18)
+REDUCE_ALL, REDUCE_SLICE = 0, 1
 
 WORLD_NODES, WORLD_BLOCKFIRSTLEAF, WORLD_VOXELMAT, WORLD_SUBCHUNKS = range(4)
 CNODE_DT = np.dtype([("mask", "<u8"), ("base", "<u4"), ("aux", "<u4")])  # blok_b200/csrc/scene.h Node
@@ -107,7 +108,7 @@ class CameraC(C.Structure):
 
 class Buffers(C.Structure):
     _fields_ = [("hit", _vp), ("shadow", _vp), ("color", _vp), ("worldPos", _vp), ("normalRough", _vp), ("albedoMetal", _vp),
-                ("motion", _vp), ("accum", _vp), ("width", C.c_uint32), ("height", C.c_uint32)]
+                ("motion", _vp), ("accum", _vp), ("width", C.c_uint32), ("height", C.c_uint32), ("hitPacked", _vp)]
 
 
 class WorldStats(C.Structure):
@@ -135,9 +136,54 @@ EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_wo
            "blokb_vox_counts", "blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free", "blokb_vox_last_error", "blokb_upload_vox", "blokb_set_strips", "blokb_ipc_export", "blokb_set_peers", "blokb_bind_image",
            "blokb_world_save", "blokb_world_load", "blokb_update_dense", "blokb_trace_rays_reordered",
            "blokb_pipeline_create_packed", "blokb_pipeline_submit_packed", "blokb_node_prims", "blokb_unpack_hits",
-           "blokb_path_options_default", "blokb_set_path_options", "blokb_get_path_options"]
+           "blokb_path_options_default", "blokb_set_path_options", "blokb_get_path_options", "blokb_trace_primary_packed",
+           "blokb_comm_unique_id", "blokb_comm_init", "blokb_set_comm", "blokb_comm_rank", "blokb_reduce_accum", "blokb_reduce_slice",
+           "blokb_readback_slice", "blokb_readback_strips"]
 
 _lib = None
+_host = None
+HOST_LIB_PATH = os.path.join(HERE, "libblokbhost.so")
+
+
+def _bind_host(L):
+    """Prototypes of the host-only helpers (present in libblokb200.so and, without any CUDA, in libblokbhost.so)."""
+    L.blokb_vox_load.argtypes = [C.c_char_p, C.c_uint32, _vp, C.POINTER(_vp)]
+    L.blokb_vox_parse.argtypes = [_vp, C.c_size_t, C.c_uint32, _vp, C.POINTER(_vp)]
+    L.blokb_vox_counts.argtypes = [_vp, _vp, _vp, _vp, _vp]
+    L.blokb_vox_counts.restype = None
+    for f, t in (("blokb_vox_xyz", _vp), ("blokb_vox_material_ids", _vp), ("blokb_vox_materials", _vp), ("blokb_vox_last_error", C.c_char_p)):
+        getattr(L, f).restype = t
+    for f in ("blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free"):
+        getattr(L, f).argtypes = [_vp]
+    L.blokb_vox_free.restype = None
+    L.blokb_camera_frame.argtypes = [C.POINTER(CameraC), C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(FrameUBO)]
+    L.blokb_camera_frame_seq.argtypes = [C.POINTER(CameraC), C.POINTER(CameraC), C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int32,
+                                         C.POINTER(FrameUBO)]
+    L.blokb_worldgen_pack.argtypes = [_vp, _vp, C.c_size_t]
+    L.blokb_worldgen_pack.restype = _vp
+    L.blokb_worldgen_counts.argtypes = [_vp, _vp, _vp]
+    L.blokb_worldgen_counts.restype = None
+    L.blokb_worldgen_copy.argtypes = [_vp, _vp, _vp]
+    L.blokb_worldgen_copy.restype = None
+    L.blokb_worldgen_free.argtypes = [_vp]
+    L.blokb_worldgen_free.restype = None
+
+
+def load_host_library():
+    """The host-only helpers (scene generator, Camera -> FrameUBO, .vox import). Served by libblokb200.so when it is already loaded
+    (or when libblokbhost.so is absent); otherwise by libblokbhost.so — same sources compiled without CUDA — so that a process
+    that only prepares inputs (bench.py --impl reference, the CPU tests) never maps the product's CUDA binary."""
+    global _host
+    if _lib is not None:
+        return _lib
+    if _host is not None:
+        return _host
+    if not os.path.exists(HOST_LIB_PATH):
+        return load_library()
+    L = C.CDLL(HOST_LIB_PATH)
+    _bind_host(L)
+    _host = L
+    return L
 
 
 def load_library():
@@ -159,20 +205,17 @@ def load_library():
     L.blokb_upload_voxels.argtypes = [_vp, _vp, _vp, C.c_size_t, _vp, C.c_size_t]
     L.blokb_world_export.argtypes = [_vp, C.c_int, _vp, C.c_size_t, C.POINTER(C.c_size_t)]
     L.blokb_upload_dense.argtypes = [_vp, _vp, C.c_size_t, _vp, C.c_size_t]
-    L.blokb_vox_load.argtypes = [C.c_char_p, C.c_uint32, _vp, C.POINTER(_vp)]
-    L.blokb_vox_parse.argtypes = [_vp, C.c_size_t, C.c_uint32, _vp, C.POINTER(_vp)]
-    L.blokb_vox_counts.argtypes = [_vp, _vp, _vp, _vp, _vp]
-    L.blokb_vox_counts.restype = None
-    for f, t in (("blokb_vox_xyz", _vp), ("blokb_vox_material_ids", _vp), ("blokb_vox_materials", _vp), ("blokb_vox_last_error", C.c_char_p)):
-        getattr(L, f).restype = t
-    for f in ("blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free"):
-        getattr(L, f).argtypes = [_vp]
-    L.blokb_vox_free.restype = None
+    _bind_host(L)
     L.blokb_upload_vox.argtypes = [_vp, C.c_char_p, C.c_uint32, _vp]
-    L.blokb_camera_frame.argtypes = [C.POINTER(CameraC), C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(FrameUBO)]
-    L.blokb_camera_frame_seq.argtypes = [C.POINTER(CameraC), C.POINTER(CameraC), C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int32,
-                                         C.POINTER(FrameUBO)]
-    for f in ("blokb_trace_primary", "blokb_trace_primary_shadow", "blokb_render", "blokb_resolve", "blokb_reset_accum"):
+    L.blokb_comm_unique_id.argtypes = [_vp]
+    L.blokb_comm_init.argtypes = [_vp, _vp, C.c_int, C.c_int]
+    L.blokb_set_comm.argtypes = [_vp, _vp]
+    L.blokb_comm_rank.argtypes = [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.blokb_reduce_accum.argtypes = [_vp, C.c_int, _vp]
+    L.blokb_reduce_slice.argtypes = [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    L.blokb_readback_slice.argtypes = [_vp, C.c_int, _vp, C.c_size_t]
+    L.blokb_readback_strips.argtypes = [_vp, C.c_int, _vp, C.c_size_t]
+    for f in ("blokb_trace_primary", "blokb_trace_primary_shadow", "blokb_trace_primary_packed", "blokb_render", "blokb_resolve", "blokb_reset_accum"):
         getattr(L, f).argtypes = [_vp, _vp]
     L.blokb_trace_path.argtypes = [_vp, C.c_uint32, C.c_uint32, _vp]
     L.blokb_set_strips.argtypes = [_vp, C.c_uint32, C.c_uint32]
@@ -205,14 +248,6 @@ def load_library():
     L.blokb_stats_read.argtypes = [_vp, _vp]
     L.blokb_stream.argtypes = [_vp]
     L.blokb_stream.restype = _vp
-    L.blokb_worldgen_pack.argtypes = [_vp, _vp, C.c_size_t]
-    L.blokb_worldgen_pack.restype = _vp
-    L.blokb_worldgen_counts.argtypes = [_vp, _vp, _vp]
-    L.blokb_worldgen_counts.restype = None
-    L.blokb_worldgen_copy.argtypes = [_vp, _vp, _vp]
-    L.blokb_worldgen_copy.restype = None
-    L.blokb_worldgen_free.argtypes = [_vp]
-    L.blokb_worldgen_free.restype = None
     L.blokb_pipeline_create.argtypes = [_vp, C.c_int, C.c_uint32, C.c_uint32, C.POINTER(_vp)]
     L.blokb_pipeline_submit.argtypes = [_vp, C.POINTER(FrameUBO), _vp, C.POINTER(C.c_uint64)]
     L.blokb_pipeline_create_packed.argtypes = L.blokb_pipeline_create.argtypes
@@ -251,7 +286,7 @@ class WorldSvoGpu:
     @staticmethod
     def from_voxels(xyz, material_ids, materials):
         """ChunkManager(128,1).setVoxelMaterial per voxel + rebuildDirtyChunks + packChunksToGpuSvo (host, C++)."""
-        L = load_library()
+        L = load_host_library()
         xyz = np.ascontiguousarray(xyz, np.int32).reshape(-1, 3)
         mid = np.ascontiguousarray(material_ids, np.uint32)
         assert len(mid) == len(xyz)
@@ -291,7 +326,7 @@ class WorldSvoGpu:
 def load_vox(source, model_index=0, offset=(0.0, 0.0, 0.0)):
     """loadVoxFile + importVoxMaterials + importVoxToChunks (blok/src/vox_loader.cpp) as data: returns (xyz (n,3) i32, material ids
     (n,) u32, materials (256,) MAT_DT, info dict). source: a path or the file's bytes. Host only."""
-    L = load_library()
+    L = load_host_library()
     off = (C.c_float * 3)(*[float(v) for v in offset])
     h = _vp()
     if isinstance(source, (bytes, bytearray)):
@@ -327,12 +362,15 @@ class Camera:
         prev = the previous frame's camera (prev* matrices for reprojection), jitter_index >= 0 = TAA Halton jitter."""
         c = self._c()
         out = FrameUBO()
+        L = load_host_library()
         if prev is None and jitter_index < 0:
-            _ck(load_library().blokb_camera_frame(C.byref(c), width, height, frame_count, sample_count, C.byref(out)))
+            rc = L.blokb_camera_frame(C.byref(c), width, height, frame_count, sample_count, C.byref(out))
         else:
             pc = prev._c() if prev is not None else None
-            _ck(load_library().blokb_camera_frame_seq(C.byref(c), C.byref(pc) if pc is not None else None, width, height, frame_count,
-                                                      sample_count, jitter_index, C.byref(out)))
+            rc = L.blokb_camera_frame_seq(C.byref(c), C.byref(pc) if pc is not None else None, width, height, frame_count,
+                                          sample_count, jitter_index, C.byref(out))
+        if rc != 0:
+            raise BlokbError(rc, "blokb_camera_frame: bad argument")
         return out
 
 
@@ -469,10 +507,58 @@ class Renderer:
         assert len(blob) == 64 * len(handles)
         _ck(self.L.blokb_set_peers(self._ctx, image, blob, len(handles), self_index))
 
-    def trace_primary(self, frame=None, shadow=False, stream=None):
+    def trace_primary(self, frame=None, shadow=False, stream=None, packed=False):
+        """Sample-0 primary rays -> IMG_HIT (+ IMG_SHADOW with shadow=True), or 8-byte records -> IMG_HIT_PACKED with packed=True."""
         if frame is not None:
             self.set_frame(frame)
-        _ck((self.L.blokb_trace_primary_shadow if shadow else self.L.blokb_trace_primary)(self._ctx, stream))
+        fn = self.L.blokb_trace_primary_packed if packed else (self.L.blokb_trace_primary_shadow if shadow else self.L.blokb_trace_primary)
+        _ck(fn(self._ctx, stream))
+
+    # ---- cross-GPU reduction of the accumulation buffers (sample-sharded path tracing)
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        """128-byte ncclUniqueId (rank 0 makes it and ships it to the other ranks)."""
+        b = C.create_string_buffer(128)
+        _ck(load_library().blokb_comm_unique_id(b))
+        return b.raw
+
+    def comm_init(self, unique_id: bytes, rank: int, nranks: int):
+        """Library-owned NCCL communicator for this context (collective: every rank calls it with the same id)."""
+        assert len(unique_id) == 128
+        _ck(self.L.blokb_comm_init(self._ctx, unique_id, rank, nranks))
+
+    def set_comm(self, nccl_comm_ptr: int):
+        """Adopt a caller-owned ncclComm_t (0 / None detaches)."""
+        _ck(self.L.blokb_set_comm(self._ctx, nccl_comm_ptr or None))
+
+    def comm_rank(self):
+        r, n = C.c_int(), C.c_int()
+        _ck(self.L.blokb_comm_rank(self._ctx, C.byref(r), C.byref(n)))
+        return r.value, n.value
+
+    def reduce_accum(self, mode=REDUCE_ALL, stream=None):
+        """colour = resolve(sum over GPUs of accum): REDUCE_SLICE leaves each rank with its slice of pixels, REDUCE_ALL with the frame."""
+        _ck(self.L.blokb_reduce_accum(self._ctx, mode, stream))
+
+    def reduce_slice(self):
+        """(first pixel, pixel count) of the slice of the frame (row-major) this rank owns after reduce_accum."""
+        a, b = C.c_uint64(), C.c_uint64()
+        _ck(self.L.blokb_reduce_slice(self._ctx, C.byref(a), C.byref(b)))
+        return int(a.value), int(b.value)
+
+    def readback_slice(self, image: int = IMG_COLOR) -> np.ndarray:
+        """This rank's slice of an rgba32f image as (count, 4) float32."""
+        first, count = self.reduce_slice()
+        out = np.empty((count, 4), np.float32)
+        _ck(self.L.blokb_readback_slice(self._ctx, image, _ptr(out), out.nbytes))
+        return out
+
+    def readback_slice_into(self, image: int, host_ptr: int, nbytes: int):
+        _ck(self.L.blokb_readback_slice(self._ctx, image, host_ptr, nbytes))
+
+    def readback_strips_into(self, image: int, host_ptr: int, nbytes: int):
+        """Only this context's strips (set_strips) of an image, copied to their full-frame positions in a whole-image host buffer."""
+        _ck(self.L.blokb_readback_strips(self._ctx, image, host_ptr, nbytes))
 
     def set_path_options(self, mode=None, batch_samples=None, dir_cells=None, origin_cell_shift=None, morton_bits_per_axis=None):
         """blokb_set_path_options; arguments left None keep their current value. Returns the options now in force."""
@@ -538,7 +624,7 @@ class Renderer:
 
     def readback(self, image: int) -> np.ndarray:
         h, w = self.height, self.width
-        shape_dt = {IMG_HIT: ((h, w), HIT_DT), IMG_SHADOW: ((h, w), np.uint8), IMG_COLOR: ((h, w, 4), np.float32),
+        shape_dt = {IMG_HIT: ((h, w), HIT_DT), IMG_HIT_PACKED: ((h, w), PACKED_DT), IMG_SHADOW: ((h, w), np.uint8), IMG_COLOR: ((h, w, 4), np.float32),
                     IMG_WORLDPOS: ((h, w, 4), np.float32), IMG_NORMALROUGH: ((h, w, 4), np.float16),
                     IMG_ALBEDOMETAL: ((h, w, 4), np.uint8), IMG_MOTION: ((h, w, 2), np.float16), IMG_ACCUM: ((h, w, 4), np.float32),
                     IMG_HISTORY_COLOR: ((h, w, 4), np.float32), IMG_MOMENTS: ((h, w, 2), np.float32), IMG_HISTORY_LENGTH: ((h, w), np.float16),
@@ -561,7 +647,7 @@ class Renderer:
         hit records are exposed as (h, w, 4) int32 words (NCCL and torch index ops have no uint32)."""
         b = self.buffers()
         h, w = int(b.height), int(b.width)
-        table = {IMG_HIT: (b.hit, (h, w, 4), "<i4"), IMG_SHADOW: (b.shadow, (h, w), "|u1"), IMG_COLOR: (b.color, (h, w, 4), "<f4"),
+        table = {IMG_HIT: (b.hit, (h, w, 4), "<i4"), IMG_HIT_PACKED: (b.hitPacked, (h, w, 2), "<i4"), IMG_SHADOW: (b.shadow, (h, w), "|u1"), IMG_COLOR: (b.color, (h, w, 4), "<f4"),
                  IMG_WORLDPOS: (b.worldPos, (h, w, 4), "<f4"), IMG_NORMALROUGH: (b.normalRough, (h, w, 4), "<f2"),
                  IMG_ALBEDOMETAL: (b.albedoMetal, (h, w, 4), "|u1"), IMG_MOTION: (b.motion, (h, w, 2), "<f2"),
                  IMG_ACCUM: (b.accum, (h, w, 4), "<f4")}

@@ -13,6 +13,7 @@
 
 #include "../../include/blokb200.h"
 #include "build.h"
+#include "comm.h"
 #include "kernels.h"
 #include "post.h"
 #include "scene_build.h"
@@ -27,6 +28,8 @@ static int fail(int code, const std::string& msg) { g_err = msg; return code; }
         if (e_ != cudaSuccess) return fail(BLOKB_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
+constexpr int kSlots = 5;
+constexpr size_t kSlicePad = 64;  // >= the largest communicator size blokb_reduce_accum slices for
 struct blokb_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -64,17 +67,24 @@ struct blokb_ctx {
         const void* final = nullptr;                  // PostProcess::getOutputImage() of the current frame
         size_t finalBytesPerPixel = 0;
     } post;
-    // peer mappings of the exchanged images (blokb_set_peers): slot 0 hit, 1 shadow, 2 accum
+    // peer mappings of the exchanged images (blokb_set_peers): slot 0 hit, 1 shadow, 2 accum, 3 packed hit, 4 colour
     struct Peers {
         void* mapped[kMaxPeers] = {};   // cudaIpcOpenMemHandle results, nullptr at `self`
         uint32_t n = 0, self = 0;
-    } peers[3];
+    } peers[kSlots];
     // externally owned symmetric memory standing in for an image (blokb_bind_image); own = the context's allocation, kept aside
     struct Bound {
         void* own = nullptr;
         void* mc = nullptr;
         bool on = false;
-    } bound[3];
+    } bound[kSlots];
+    // cross-GPU reduction (blokb_set_comm / blokb_comm_init / blokb_reduce_accum)
+    NcclComm comm = nullptr;
+    bool commOwned = false;
+    int commRank = 0, commSize = 1;
+    float* dSlice = nullptr;      // reduce-scatter destination: this rank's slice of the summed accumulation image
+    size_t sliceCap = 0;          // pixels
+    float* dFence = nullptr;      // 4-byte all-reduce operand (fence around the multimem reduction)
     // editable worlds (blokb_upload_dense keeps the voxel list on the device; blokb_update_dense replaces dirty chunks in it)
     build::VoxelList edit;
     std::vector<blokb_material> editMaterials;
@@ -137,7 +147,8 @@ static void free_world(blokb_ctx* c) {
     c->editable = false;
 }
 static int peer_slot(int image) {
-    return image == BLOKB_IMG_HIT ? 0 : image == BLOKB_IMG_SHADOW ? 1 : image == BLOKB_IMG_ACCUM ? 2 : -1;
+    return image == BLOKB_IMG_HIT ? 0 : image == BLOKB_IMG_SHADOW ? 1 : image == BLOKB_IMG_ACCUM ? 2 : image == BLOKB_IMG_HIT_PACKED ? 3 :
+           image == BLOKB_IMG_COLOR ? 4 : -1;
 }
 static void close_peers(blokb_ctx* c, int slot) {
     auto& P = c->peers[slot];
@@ -160,7 +171,8 @@ static PeerOut out_for(blokb_ctx* c, int slot, void* own) {
     return o;
 }
 static void** image_slot_ptr(blokb_ctx* c, int slot) {
-    return slot == 0 ? reinterpret_cast<void**>(&c->buf.hit) : slot == 1 ? reinterpret_cast<void**>(&c->buf.shadow) : reinterpret_cast<void**>(&c->buf.accum);
+    return slot == 0 ? reinterpret_cast<void**>(&c->buf.hit) : slot == 1 ? reinterpret_cast<void**>(&c->buf.shadow) :
+           slot == 2 ? reinterpret_cast<void**>(&c->buf.accum) : slot == 3 ? reinterpret_cast<void**>(&c->buf.hitPacked) : reinterpret_cast<void**>(&c->buf.color);
 }
 static void unbind(blokb_ctx* c, int slot) {
     auto& B = c->bound[slot];
@@ -174,8 +186,8 @@ static PeerOut own_only(void* own) {
 }
 
 static void free_images(blokb_ctx* c) {
-    for (int sl = 0; sl < 3; sl++) { close_peers(c, sl); unbind(c, sl); }
-    void* ps[] = {c->buf.hit, c->buf.shadow, c->buf.color, c->buf.worldPos, c->buf.normalRough, c->buf.albedoMetal, c->buf.motion, c->buf.accum};
+    for (int sl = 0; sl < kSlots; sl++) { close_peers(c, sl); unbind(c, sl); }
+    void* ps[] = {c->buf.hit, c->buf.shadow, c->buf.color, c->buf.worldPos, c->buf.normalRough, c->buf.albedoMetal, c->buf.motion, c->buf.accum, c->buf.hitPacked};
     for (void* p : ps) if (p) cudaFree(p);
     c->buf = blokb_buffers{};
     auto& P = c->post;
@@ -231,6 +243,9 @@ void blokb_destroy(blokb_ctx* c) {
     if (c->dStats) cudaFree(c->dStats);
     if (c->dReorder) cudaFree(c->dReorder);
     if (c->dWave) cudaFree(c->dWave);
+    if (c->dSlice) cudaFree(c->dSlice);
+    if (c->dFence) cudaFree(c->dFence);
+    if (c->comm && c->commOwned) { std::string err; if (const NcclApi* N = nccl_api(err)) N->CommDestroy(c->comm); }
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -625,9 +640,10 @@ int blokb_set_frame(blokb_ctx* c, const blokb_frame_ubo* f) {
         free_images(c);
         const size_t n = size_t(f->screenWidth) * f->screenHeight;
         void** slots[] = {(void**)&c->buf.hit, (void**)&c->buf.shadow, (void**)&c->buf.color, (void**)&c->buf.worldPos, (void**)&c->buf.normalRough,
-                          (void**)&c->buf.albedoMetal, (void**)&c->buf.motion, (void**)&c->buf.accum};
-        const size_t bytes[] = {n * sizeof(blokb_hit), n, n * 16, n * 16, n * 8, n * 4, n * 4, n * 16};
-        for (int k = 0; k < 8; k++) {
+                          (void**)&c->buf.albedoMetal, (void**)&c->buf.motion, (void**)&c->buf.accum, (void**)&c->buf.hitPacked};
+        // colour and accum carry kSlicePad pixels of slack: blokb_reduce_accum slices them into G equal parts of ceil(n / G) pixels
+        const size_t bytes[] = {n * sizeof(blokb_hit), n, (n + kSlicePad) * 16, n * 16, n * 8, n * 4, n * 4, (n + kSlicePad) * 16, n * sizeof(blokb_hit_packed)};
+        for (int k = 0; k < 9; k++) {
             const cudaError_t e = cudaMalloc(slots[k], bytes[k]);
             if (e != cudaSuccess) {
                 *slots[k] = nullptr;
@@ -636,7 +652,7 @@ int blokb_set_frame(blokb_ctx* c, const blokb_frame_ubo* f) {
             }
         }
         // zero-filled before any dispatch can touch it, whatever stream that dispatch uses
-        if (cudaMemsetAsync(c->buf.accum, 0, n * 16, c->stream) != cudaSuccess || cudaStreamSynchronize(c->stream) != cudaSuccess) {
+        if (cudaMemsetAsync(c->buf.accum, 0, (n + kSlicePad) * 16, c->stream) != cudaSuccess || cudaStreamSynchronize(c->stream) != cudaSuccess) {
             free_images(c);
             return fail(BLOKB_E_CUDA, "zero-fill of the accumulation image failed");
         }
@@ -673,8 +689,9 @@ int blokb_set_strips(blokb_ctx* c, uint32_t first, uint32_t stride) {
 int blokb_ipc_export(blokb_ctx* c, int image, void* handle64) {
     if (!c || !handle64) return fail(BLOKB_E_ARG, "null argument");
     if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame allocates the images)");
-    void* p = image == BLOKB_IMG_HIT ? (void*)c->buf.hit : image == BLOKB_IMG_SHADOW ? (void*)c->buf.shadow : image == BLOKB_IMG_ACCUM ? (void*)c->buf.accum : nullptr;
-    if (!p) return fail(BLOKB_E_ARG, "image is not exchangeable (hit, shadow, accum)");
+    const int slot = peer_slot(image);
+    void* p = slot < 0 ? nullptr : *image_slot_ptr(c, slot);
+    if (!p) return fail(BLOKB_E_ARG, "image is not exchangeable (hit, shadow, accum, packed hit, colour)");
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
     CK(cudaSetDevice(c->device));
     cudaIpcMemHandle_t h;
@@ -685,7 +702,7 @@ int blokb_ipc_export(blokb_ctx* c, int image, void* handle64) {
 int blokb_set_peers(blokb_ctx* c, int image, const void* handles, uint32_t n, uint32_t self) {
     if (!c) return fail(BLOKB_E_ARG, "ctx is null");
     const int slot = peer_slot(image);
-    if (slot < 0) return fail(BLOKB_E_ARG, "image is not exchangeable (hit, shadow, accum)");
+    if (slot < 0) return fail(BLOKB_E_ARG, "image is not exchangeable (hit, shadow, accum, packed hit, colour)");
     CK(cudaSetDevice(c->device));
     if (int rc = idle(c)) return rc;
     close_peers(c, slot);
@@ -711,7 +728,7 @@ int blokb_set_peers(blokb_ctx* c, int image, const void* handles, uint32_t n, ui
 int blokb_bind_image(blokb_ctx* c, int image, void* local, void* multicast) {
     if (!c) return fail(BLOKB_E_ARG, "ctx is null");
     const int slot = peer_slot(image);
-    if (slot < 0) return fail(BLOKB_E_ARG, "image is not exchangeable (hit, shadow, accum)");
+    if (slot < 0) return fail(BLOKB_E_ARG, "image is not exchangeable (hit, shadow, accum, packed hit, colour)");
     if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame allocates the images)");
     if (!local && multicast) return fail(BLOKB_E_ARG, "a multicast address needs the local address of the same memory");
     if (multicast && image == BLOKB_IMG_SHADOW && (c->buf.width & 3u)) return fail(BLOKB_E_ARG, "multicast shadow image needs width % 4 == 0");
@@ -737,6 +754,13 @@ int blokb_trace_primary(blokb_ctx* c, void* stream) {
 int blokb_trace_primary_shadow(blokb_ctx* c, void* stream) {
     if (int rc = ready(c, true)) return rc;
     CK(launch_primary(c->dw, c->frame, true, out_for(c, 0, c->buf.hit), out_for(c, 1, c->buf.shadow), st(c), pick(c, stream)));
+    c->launches++;
+    return dispatched(c, pick(c, stream));
+}
+int blokb_trace_primary_packed(blokb_ctx* c, void* stream) {
+    if (int rc = ready(c, true)) return rc;
+    if (c->stats.nodes > BLOKB_PACKED_MAX_NODES) return fail(BLOKB_E_UNSUPPORTED, "world has more nodes than a packed record can address");
+    CK(launch_primary_packed(c->dw, c->frame, out_for(c, 3, c->buf.hitPacked), pick(c, stream)));
     c->launches++;
     return dispatched(c, pick(c, stream));
 }
@@ -993,14 +1017,14 @@ int blokb_get_buffers(blokb_ctx* c, blokb_buffers* out) {
     *out = c->buf;
     return 0;
 }
-int blokb_readback(blokb_ctx* c, int image, void* host, size_t bytes) {
-    if (!c || !host) return fail(BLOKB_E_ARG, "null argument");
-    if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
+// Device address and whole-image byte size of an image id (nullptr: not produced yet; sz == 0: unknown id).
+static void image_lookup(blokb_ctx* c, int image, const void** srcOut, size_t* szOut) {
     const size_t n = size_t(c->buf.width) * c->buf.height;
     const void* src = nullptr;
     size_t sz = 0;
     switch (image) {
         case BLOKB_IMG_HIT: src = c->buf.hit; sz = n * 16; break;
+        case BLOKB_IMG_HIT_PACKED: src = c->buf.hitPacked; sz = n * 8; break;
         case BLOKB_IMG_SHADOW: src = c->buf.shadow; sz = n; break;
         case BLOKB_IMG_COLOR: src = c->buf.color; sz = n * 16; break;
         case BLOKB_IMG_WORLDPOS: src = c->buf.worldPos; sz = n * 16; break;
@@ -1017,8 +1041,200 @@ int blokb_readback(blokb_ctx* c, int image, void* host, size_t bytes) {
         case BLOKB_IMG_TAA_OUTPUT: src = c->post.taaOut; sz = n * 16; break;
         case BLOKB_IMG_TONEMAPPED: src = c->post.tonemapOut; sz = n * 4; break;
         case BLOKB_IMG_FINAL: src = c->post.final; sz = n * c->post.finalBytesPerPixel; break;
-        default: return fail(BLOKB_E_ARG, "unknown image id");
+        default: break;
     }
+    *srcOut = src; *szOut = sz;
+}
+// Rows of the strips (first, first + stride, ...) of an image with `rowBytes` per pixel row: device -> host at the same offsets.
+static int copy_strips(const void* dev, void* host, size_t rowBytes, uint32_t height, uint32_t first, uint32_t stride, cudaStream_t q) {
+    const uint32_t strips = (height + 7) / 8;
+    if (first >= strips) return 0;
+    const size_t stripBytes = 8 * rowBytes;
+    uint32_t mine = (strips - first + stride - 1) / stride;
+    const uint32_t last = first + (mine - 1) * stride;
+    const uint32_t lastRows = std::min<uint32_t>(8, height - last * 8);
+    uint32_t full = lastRows == 8 ? mine : mine - 1;   // strips of 8 whole rows
+    const char* d = static_cast<const char*>(dev);
+    char* h = static_cast<char*>(host);
+    if (full) CK(cudaMemcpy2DAsync(h + size_t(first) * stripBytes, size_t(stride) * stripBytes, d + size_t(first) * stripBytes, size_t(stride) * stripBytes,
+                                   stripBytes, full, cudaMemcpyDeviceToHost, q));
+    if (full != mine) CK(cudaMemcpyAsync(h + size_t(last) * stripBytes, d + size_t(last) * stripBytes, size_t(lastRows) * rowBytes, cudaMemcpyDeviceToHost, q));
+    return 0;
+}
+int blokb_readback_strips(blokb_ctx* c, int image, void* host, size_t bytes) {
+    if (!c || !host) return fail(BLOKB_E_ARG, "null argument");
+    if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
+    const void* src; size_t sz;
+    image_lookup(c, image, &src, &sz);
+    if (sz == 0) return fail(BLOKB_E_ARG, "unknown image id");
+    if (!src) return fail(BLOKB_E_STATE, "image not produced yet (blokb_denoise / blokb_postprocess of the current frame)");
+    if (bytes != sz) return fail(BLOKB_E_ARG, "host buffer size mismatch: expected " + std::to_string(sz) + " (the whole image; only this context's strips are written)");
+    CK(cudaSetDevice(c->device));
+    if (int rc = join_dispatches(c)) return rc;
+    if (int rc = copy_strips(src, host, sz / c->buf.height, c->buf.height, c->frame.stripFirst, c->frame.stripStride, c->stream)) return rc;
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+// ---- cross-GPU reduction of the accumulation buffers -----------------------------------------------------
+static const NcclApi* nccl_or_fail() {
+    std::string err;
+    const NcclApi* a = nccl_api(err);
+    if (!a) fail(BLOKB_E_UNSUPPORTED, "NCCL unavailable: " + err);
+    return a;
+}
+#define NK(expr)                                                                                                         \
+    do {                                                                                                                 \
+        int r_ = (expr);                                                                                                 \
+        if (r_ != 0) return fail(BLOKB_E_CUDA, std::string(#expr) + ": " + (N->GetErrorString ? N->GetErrorString(r_) : "nccl error")); \
+    } while (0)
+static void drop_comm(blokb_ctx* c) {
+    if (c->comm && c->commOwned) {
+        std::string err;
+        if (const NcclApi* N = nccl_api(err)) N->CommDestroy(c->comm);
+    }
+    c->comm = nullptr; c->commOwned = false; c->commRank = 0; c->commSize = 1;
+}
+int blokb_comm_unique_id(void* id128) {
+    if (!id128) return fail(BLOKB_E_ARG, "null argument");
+    const NcclApi* N = nccl_or_fail();
+    if (!N) return BLOKB_E_UNSUPPORTED;
+    NcclId id;
+    NK(N->GetUniqueId(&id));
+    std::memcpy(id128, &id, sizeof id);
+    return 0;
+}
+int blokb_comm_init(blokb_ctx* c, const void* id128, int rank, int nranks) {
+    if (!c || !id128) return fail(BLOKB_E_ARG, "null argument");
+    if (nranks < 1 || rank < 0 || rank >= nranks || size_t(nranks) > kSlicePad) return fail(BLOKB_E_ARG, "bad rank / communicator size (at most 64 ranks)");
+    const NcclApi* N = nccl_or_fail();
+    if (!N) return BLOKB_E_UNSUPPORTED;
+    CK(cudaSetDevice(c->device));
+    if (int rc = idle(c)) return rc;
+    drop_comm(c);
+    NcclId id;
+    std::memcpy(&id, id128, sizeof id);
+    NcclComm comm = nullptr;
+    NK(N->CommInitRank(&comm, nranks, id, rank));
+    c->comm = comm; c->commOwned = true; c->commRank = rank; c->commSize = nranks;
+    return 0;
+}
+int blokb_set_comm(blokb_ctx* c, void* ncclComm) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    CK(cudaSetDevice(c->device));
+    if (int rc = idle(c)) return rc;
+    drop_comm(c);
+    if (!ncclComm) return 0;
+    const NcclApi* N = nccl_or_fail();
+    if (!N) return BLOKB_E_UNSUPPORTED;
+    int rank = 0, size = 1;
+    NK(N->CommUserRank(ncclComm, &rank));
+    NK(N->CommCount(ncclComm, &size));
+    if (size_t(size) > kSlicePad) return fail(BLOKB_E_ARG, "communicators of more than 64 ranks are not supported");
+    c->comm = ncclComm; c->commOwned = false; c->commRank = rank; c->commSize = size;
+    return 0;
+}
+int blokb_comm_rank(blokb_ctx* c, int* rank, int* nranks) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    if (rank) *rank = c->commRank;
+    if (nranks) *nranks = c->commSize;
+    return 0;
+}
+static void slice_of(blokb_ctx* c, size_t* per, size_t* first, size_t* count) {
+    const size_t n = size_t(c->buf.width) * c->buf.height, G = size_t(c->commSize);
+    *per = (n + G - 1) / G;
+    *first = std::min(n, *per * size_t(c->commRank));
+    *count = std::min(n, *first + *per) - *first;
+}
+int blokb_reduce_slice(blokb_ctx* c, uint64_t* firstPixel, uint64_t* nPixels) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
+    size_t per, first, count;
+    slice_of(c, &per, &first, &count);
+    if (firstPixel) *firstPixel = first;
+    if (nPixels) *nPixels = count;
+    return 0;
+}
+int blokb_reduce_accum(blokb_ctx* c, int mode, void* stream) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
+    if (mode != BLOKB_REDUCE_ALL && mode != BLOKB_REDUCE_SLICE) return fail(BLOKB_E_ARG, "unknown reduce mode");
+    CK(cudaSetDevice(c->device));
+    cudaStream_t q = pick(c, stream);
+    const size_t n = size_t(c->buf.width) * c->buf.height;
+    if (c->commSize == 1 || !c->comm) {   // one GPU: the reduction is the identity
+        if (c->commSize > 1) return fail(BLOKB_E_STATE, "no communicator (blokb_set_comm / blokb_comm_init)");
+        CK(launch_resolve(c->buf.accum, c->buf.color, n, q));
+        c->launches++;
+        return dispatched(c, q);
+    }
+    const NcclApi* N = nccl_or_fail();
+    if (!N) return BLOKB_E_UNSUPPORTED;
+    size_t per, first, count;
+    slice_of(c, &per, &first, &count);
+    const bool accumMc = c->bound[2].on && c->bound[2].mc, colorMc = c->bound[4].on && c->bound[4].mc;
+    if (accumMc) {
+        // in-switch sum + resolve in one kernel over peer memory, fenced by two tiny all-reduces: every rank's samples are in
+        // its accum before anyone reads through the multicast address, and nobody resets accum while a peer may still read it
+        if (!c->dFence) { CK(cudaMalloc((void**)&c->dFence, 16)); CK(cudaMemsetAsync(c->dFence, 0, 16, q)); }
+        NK(N->AllReduce(c->dFence, c->dFence, 1, kNcclFloat32, kNcclSum, c->comm, q));
+        CK(launch_reduce_resolve_mc(c->bound[2].mc, c->buf.color, (mode == BLOKB_REDUCE_ALL && colorMc) ? c->bound[4].mc : nullptr, first, count, q));
+        c->launches++;
+        if (mode == BLOKB_REDUCE_ALL && !colorMc) NK(N->AllGather(c->buf.color + 4 * first, c->buf.color, per * 4, kNcclFloat32, c->comm, q));
+        NK(N->AllReduce(c->dFence, c->dFence, 1, kNcclFloat32, kNcclSum, c->comm, q));
+        return dispatched(c, q);
+    }
+    const bool padded = !c->bound[2].on && !c->bound[4].on;   // the context's own allocations carry kSlicePad pixels of slack
+    if (!padded && n % size_t(c->commSize) != 0) {
+        // caller-owned images of exactly n pixels cannot be cut into G equal slices: all-reduce in place, resolve everywhere
+        NK(N->AllReduce(c->buf.accum, c->buf.accum, n * 4, kNcclFloat32, kNcclSum, c->comm, q));
+        CK(launch_resolve(c->buf.accum, c->buf.color, n, q));
+        c->launches++;
+        return dispatched(c, q);
+    }
+    if (per > c->sliceCap) {
+        CK(cudaDeviceSynchronize());
+        if (c->dSlice) cudaFree(c->dSlice);
+        c->dSlice = nullptr; c->sliceCap = 0;
+        CK(cudaMalloc((void**)&c->dSlice, per * 16));
+        c->sliceCap = per;
+    }
+    NK(N->ReduceScatter(c->buf.accum, c->dSlice, per * 4, kNcclFloat32, kNcclSum, c->comm, q));
+    CK(launch_resolve(c->dSlice, c->buf.color + 4 * size_t(c->commRank) * per, count, q));
+    c->launches++;
+    if (mode == BLOKB_REDUCE_ALL) NK(N->AllGather(c->buf.color + 4 * size_t(c->commRank) * per, c->buf.color, per * 4, kNcclFloat32, c->comm, q));
+    return dispatched(c, q);
+}
+int blokb_readback_slice(blokb_ctx* c, int image, void* host, size_t bytes) {
+    if (!c || !host) return fail(BLOKB_E_ARG, "null argument");
+    if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
+    const void* src; size_t sz;
+    image_lookup(c, image, &src, &sz);
+    if (sz == 0) return fail(BLOKB_E_ARG, "unknown image id");
+    if (!src) return fail(BLOKB_E_STATE, "image not produced yet (blokb_denoise / blokb_postprocess of the current frame)");
+    size_t per, first, count;
+    slice_of(c, &per, &first, &count);
+    const size_t bpp = sz / (size_t(c->buf.width) * c->buf.height);
+    if (bytes != count * bpp) return fail(BLOKB_E_ARG, "host buffer size mismatch: expected " + std::to_string(count * bpp));
+    CK(cudaSetDevice(c->device));
+    if (int rc = join_dispatches(c)) return rc;
+    if (count) CK(cudaMemcpyAsync(host, static_cast<const char*>(src) + first * bpp, count * bpp, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int blokb_readback(blokb_ctx* c, int image, void* host, size_t bytes) {
+    if (!c || !host) return fail(BLOKB_E_ARG, "null argument");
+    if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
+    const size_t n = size_t(c->buf.width) * c->buf.height;
+    const void* src = nullptr;
+    size_t sz = 0;
+    switch (image) {
+        default: break;
+    }
+    (void)n;
+    image_lookup(c, image, &src, &sz);
+    if (sz == 0) return fail(BLOKB_E_ARG, "unknown image id");
     if (!src) return fail(BLOKB_E_STATE, "image not produced yet (blokb_denoise / blokb_postprocess of the current frame)");
     if (bytes != sz) return fail(BLOKB_E_ARG, "host buffer size mismatch: expected " + std::to_string(sz));
     CK(cudaSetDevice(c->device));
@@ -1141,13 +1357,16 @@ static int pipeline_submit(blokb_pipeline* p, const blokb_frame_ubo* f, void* ho
     std::memcpy(d.prevViewProj, f->prevViewProj, 64);
     std::memcpy(d.camPos, f->camPos, 12);
     d.frameCount = f->frameCount; d.sampleCount = f->sampleCount; d.width = f->screenWidth; d.height = f->screenHeight;
+    d.stripFirst = c->frame.stripFirst; d.stripStride = c->frame.stripStride;   // a tiled frame: this GPU's strips only, traced AND copied
     if (p->submitted >= uint64_t(p->depth)) CK(cudaStreamWaitEvent(c->stream, p->copied[slot], 0));  // slot's previous copy must have drained
-    if (packed) CK(launch_primary_packed(c->dw, d, reinterpret_cast<blokb_hit_packed*>(p->dHit[slot]), c->stream));
+    if (packed) CK(launch_primary_packed(c->dw, d, own_only(p->dHit[slot]), c->stream));
     else CK(launch_primary(c->dw, d, false, own_only(p->dHit[slot]), own_only(nullptr), st(c), c->stream));
     c->launches++;
     CK(cudaEventRecord(p->traced[slot], c->stream));
     CK(cudaStreamWaitEvent(p->copyStream, p->traced[slot], 0));
-    CK(cudaMemcpyAsync(hostOut, p->dHit[slot], size_t(p->width) * p->height * p->recordBytes(), cudaMemcpyDeviceToHost, p->copyStream));
+    if (d.stripStride == 1 && d.stripFirst == 0)
+        CK(cudaMemcpyAsync(hostOut, p->dHit[slot], size_t(p->width) * p->height * p->recordBytes(), cudaMemcpyDeviceToHost, p->copyStream));
+    else if (int rc = copy_strips(p->dHit[slot], hostOut, size_t(p->width) * p->recordBytes(), p->height, d.stripFirst, d.stripStride, p->copyStream)) return rc;
     CK(cudaEventRecord(p->copied[slot], p->copyStream));
     if (ticket) *ticket = p->submitted;
     p->submitted++;

@@ -78,6 +78,20 @@ __device__ __forceinline__ void store8_all(const PeerOut& o, size_t index, uint8
     for (uint32_t k = 1; k < kMaxPeers; k++)
         if (k < o.n) static_cast<uint8_t*>(o.dst[k])[index] = b;
 }
+// One 8-byte record (blokb_hit_packed) to every destination: half the NVLink bytes of the 16-byte record.
+__device__ __forceinline__ void store8B_all(const PeerOut& o, size_t index, uint2 v) {
+    if (o.mc) {
+        asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(static_cast<uint2*>(o.mc) + index), "f"(__uint_as_float(v.x)),
+                     "f"(__uint_as_float(v.y))
+                     : "memory");
+        return;
+    }
+    reinterpret_cast<uint2*>(o.dst[0])[index] = v;
+    if (o.n == 1) return;
+#pragma unroll
+    for (uint32_t k = 1; k < kMaxPeers; k++)
+        if (k < o.n) reinterpret_cast<uint2*>(o.dst[k])[index] = v;
+}
 __device__ __forceinline__ void store_hit_all(const PeerOut& o, size_t index, bool hit, const HitRec& h) {
     store16_all(o, index, hit ? make_uint4(h.node, h.material, __float_as_uint(h.t), h.facePrim)
                               : make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, __float_as_uint(-1.0f), 0xFFFFFFFFu));
@@ -177,15 +191,15 @@ __global__ void __launch_bounds__(kPixThreads) k_primary(const __grid_constant__
 
 // k_primary<false> with the 8-byte record of blokb_hit_packed (the readback is PCIe-bound: half the bytes per frame).
 __global__ void __launch_bounds__(kPixThreads) k_primary_packed(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
-                                                        uint2* __restrict__ out) {
+                                                        const __grid_constant__ PeerOut out) {
     uint32_t px, py;
     if (!thread_pixel(F, px, py)) return;
     const F3 d = primary_dir(F, float(px) + 0.5f, float(py) + 0.5f);
     HitRec h;
     uint32_t steps = 0;
     const bool hit = traverse<false>(W, thread_stack(), F.camPos[0], F.camPos[1], F.camPos[2], d.x, d.y, d.z, 0.001f, 10000.0f, h, steps, false);
-    out[size_t(py) * F.width + px] = hit ? make_uint2(h.node | (h.facePrim & 7u) << 29, __float_as_uint(h.t))
-                                         : make_uint2(0xFFFFFFFFu, __float_as_uint(-1.0f));
+    store8B_all(out, size_t(py) * F.width + px, hit ? make_uint2(h.node | (h.facePrim & 7u) << 29, __float_as_uint(h.t))
+                                                    : make_uint2(0xFFFFFFFFu, __float_as_uint(-1.0f)));
 }
 
 __device__ __forceinline__ uint32_t unorm8(float v) { return __float2uint_rn(__saturatef(v) * 255.0f); }
@@ -396,6 +410,28 @@ __global__ void __launch_bounds__(256) k_resolve(const float4* __restrict__ accu
     color[i] = make_float4(c.x, c.y, c.z, 1.0f);
 }
 
+// Cross-GPU sum + resolve of a slice of the accumulation image in ONE pass over peer memory: every GPU's accum lives in
+// symmetric memory bound to one NVLink multicast object (blokb_bind_image), and multimem.ld_reduce returns the sum of all
+// GPUs' copies of a 16-byte texel — the NVSwitch adds them on the way — so rank g resolves pixels [first, first + n) without a
+// separate reduce-scatter. colour = sum.rgb / sum.a with the firefly clamp (raygen.rgen:383-392), written to this GPU's colour
+// image (and, when `colorMc` is set, to every GPU's through a multicast store: the all-gather of the slices).
+__global__ void __launch_bounds__(256) k_reduce_resolve_mc(const float4* __restrict__ accumMc, float4* __restrict__ color, float4* __restrict__ colorMc,
+                                                           size_t first, size_t n) {
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 a;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "l"(accumMc + first + i) : "memory");
+    F3 c = f3(a.x, a.y, a.z) / a.w;
+    const float mv = max3(c);
+    if (mv > 100.0f) c = c * (100.0f / mv);
+    if (colorMc) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(colorMc + first + i), "f"(c.x), "f"(c.y), "f"(c.z), "f"(1.0f) : "memory");
+    } else {
+        color[first + i] = make_float4(c.x, c.y, c.z, 1.0f);
+    }
+}
+
 // ---- launchers ------------------------------------------------------------------------------------
 static inline dim3 pixel_grid(const FrameDev& F) {
     const uint32_t strips = (F.height + 7) / 8;
@@ -454,10 +490,10 @@ cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow,
     }
     return cudaGetLastError();
 }
-cudaError_t launch_primary_packed(const DeviceWorld& W, const FrameDev& F, blokb_hit_packed* out, cudaStream_t st) {
+cudaError_t launch_primary_packed(const DeviceWorld& W, const FrameDev& F, const PeerOut& out, cudaStream_t st) {
     const dim3 g = pixel_grid(F);
     if (g.y == 0) return cudaSuccess;
-    k_primary_packed<<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, reinterpret_cast<uint2*>(out));
+    k_primary_packed<<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, out);
     return cudaGetLastError();
 }
 cudaError_t launch_render(const DeviceWorld& W, const FrameDev& F, float* color, float* worldPos, uint16_t* normalRough, uint8_t* albedoMetal,
@@ -552,6 +588,12 @@ cudaError_t launch_gbuffer(const DeviceWorld& W, const FrameDev& F, float* world
     const dim3 g = pixel_grid(F);
     if (g.y == 0) return cudaSuccess;
     k_gbuffer<<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, (float4*)worldPos, (uint2*)normalRough, (uint32_t*)albedoMetal, (uint32_t*)motion);
+    return cudaGetLastError();
+}
+cudaError_t launch_reduce_resolve_mc(const void* accumMc, float* color, void* colorMc, size_t first, size_t n, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    k_reduce_resolve_mc<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(static_cast<const float4*>(accumMc), reinterpret_cast<float4*>(color),
+                                                                    static_cast<float4*>(colorMc), first, n);
     return cudaGetLastError();
 }
 cudaError_t launch_resolve(const float* accum, float* color, size_t n, cudaStream_t st) {

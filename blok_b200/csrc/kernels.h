@@ -36,7 +36,7 @@ cudaError_t launch_trace_rays_reordered(const DeviceWorld& W, const float* rays,
                                         cudaStream_t st);
 cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow, const PeerOut& out, const PeerOut& shadowOut, unsigned long long* stats,
                            cudaStream_t st);
-cudaError_t launch_primary_packed(const DeviceWorld& W, const FrameDev& F, blokb_hit_packed* out, cudaStream_t st);
+cudaError_t launch_primary_packed(const DeviceWorld& W, const FrameDev& F, const PeerOut& out, cudaStream_t st);
 cudaError_t launch_render(const DeviceWorld& W, const FrameDev& F, float* color, float* worldPos, uint16_t* normalRough, uint8_t* albedoMetal,
                           uint16_t* motion, unsigned long long* stats, cudaStream_t st);
 cudaError_t launch_path(const DeviceWorld& W, const FrameDev& F, uint32_t sBegin, uint32_t sEnd, const PeerOut& accum, unsigned long long* stats,
@@ -67,4 +67,6 @@ cudaError_t launch_path_wavefront(const DeviceWorld& W, const FrameDev& F, uint3
 cudaError_t launch_gbuffer(const DeviceWorld& W, const FrameDev& F, float* worldPos, uint16_t* normalRough, uint8_t* albedoMetal, uint16_t* motion,
                            cudaStream_t st);
 cudaError_t launch_resolve(const float* accum, float* color, size_t n, cudaStream_t st);
+// colour[first, first + n) = resolve(sum over GPUs of accum) through an NVLink multicast address of the accumulation images
+cudaError_t launch_reduce_resolve_mc(const void* accumMc, float* color, void* colorMc, size_t first, size_t n, cudaStream_t st);
 }  // namespace blokb

@@ -101,30 +101,57 @@ def terrain(N=2048, seed=0xB10C, thickness=3, origin=(0, 0, 0)):
     return xyz, np.tile(band, thickness), default_materials(16)
 
 
-def blob_mesh(N=512, seed=0x51DE, blobs=24):
+def dense_mesh(N=512):
+    """The c2 scene: 40 large ellipsoids spread over the whole N^3 box — a solid that fills the frame from the c2 camera."""
+    return blob_mesh(N, blobs=40, centres=(0.15, 0.85), radii=(0.10, 0.22))
+
+
+def blob_mesh(N=512, seed=0x51DE, blobs=24, centres=(0.2, 0.8), radii=(0.06, 0.18)):
     """Solid union of ellipsoids in an N^3 box, voxelised as a 2-voxel surface shell plus every 8th interior
-    lattice line (keeps dense regions dense without billions of voxels)."""
+    lattice line (keeps dense regions dense without billions of voxels). centres / radii: ranges, in units of N, the
+    ellipsoid centres and semi-axes are drawn from. Each ellipsoid is evaluated inside its own bounding box only
+    (outside it the implicit function is >= 1 and can change nothing), z-slabs in parallel."""
     rng = np.random.Generator(np.random.PCG64(seed))
-    c = rng.uniform(0.2 * N, 0.8 * N, (blobs, 3))
-    r = rng.uniform(0.06 * N, 0.18 * N, (blobs, 3))
-    out_xyz, out_m = [], []
-    ys = np.arange(N, dtype=np.float32)
-    for z0 in range(0, N, 32):
-        zz = np.arange(z0, min(z0 + 32, N), dtype=np.float32)
-        Zg, Yg, Xg = np.meshgrid(zz, ys, ys, indexing="ij")
-        f = np.full(Zg.shape, np.inf, np.float32)
-        which = np.zeros(Zg.shape, np.uint8)
+    c = rng.uniform(centres[0] * N, centres[1] * N, (blobs, 3)).astype(np.float32)
+    r = rng.uniform(radii[0] * N, radii[1] * N, (blobs, 3)).astype(np.float32)
+    lo = np.clip(np.floor(c - r).astype(np.int64) - 1, 0, N)
+    hi = np.clip(np.ceil(c + r).astype(np.int64) + 2, 0, N)
+    rmin = r.min(axis=1)
+    SL = 32
+
+    def slab(z0):
+        z1 = min(z0 + SL, N)
+        f = np.full((z1 - z0, N, N), np.inf, np.float32)       # [z, y, x]
+        which = np.zeros((z1 - z0, N, N), np.uint8)
         for i in range(blobs):
-            d = ((Xg - c[i, 0]) / r[i, 0]) ** 2 + ((Yg - c[i, 1]) / r[i, 1]) ** 2 + ((Zg - c[i, 2]) / r[i, 2]) ** 2
-            upd = d < f
-            f = np.where(upd, d, f)
-            which = np.where(upd, np.uint8(i), which)
+            a, b = max(z0, int(lo[i, 2])), min(z1, int(hi[i, 2]))
+            if a >= b:
+                continue
+            ys, xs = slice(int(lo[i, 1]), int(hi[i, 1])), slice(int(lo[i, 0]), int(hi[i, 0]))
+            zz = np.arange(a, b, dtype=np.float32)[:, None, None]
+            yy = np.arange(ys.start, ys.stop, dtype=np.float32)[None, :, None]
+            xx = np.arange(xs.start, xs.stop, dtype=np.float32)[None, None, :]
+            d = ((xx - c[i, 0]) / r[i, 0]) ** 2 + ((yy - c[i, 1]) / r[i, 1]) ** 2 + ((zz - c[i, 2]) / r[i, 2]) ** 2
+            fs, ws = f[a - z0:b - z0, ys, xs], which[a - z0:b - z0, ys, xs]
+            upd = d < fs
+            fs[upd] = d[upd]
+            ws[upd] = i
         inside = f < 1.0
-        rmin = r.min(axis=1)[which]
-        shell = inside & (f > (1.0 - 2.5 / rmin) ** 2)
-        xi, yi, zi = Xg.astype(np.int32), Yg.astype(np.int32), Zg.astype(np.int32)
-        struts = inside & ((((xi & 7) == 0) & ((yi & 7) == 0)) | (((yi & 7) == 0) & ((zi & 7) == 0)) | (((xi & 7) == 0) & ((zi & 7) == 0)))
-        keep = shell | struts
-        out_xyz.append(np.stack([xi[keep], yi[keep], zi[keep]], 1))
-        out_m.append((which[keep].astype(np.uint32) % 16) + 1)
-    return np.concatenate(out_xyz).astype(np.int32), np.concatenate(out_m).astype(np.uint32), default_materials(16)
+        shell = inside & (f > ((1.0 - 2.5 / rmin) ** 2).astype(np.float32)[which])
+        zi, yi, xi = np.nonzero(inside)
+        zi = zi + z0
+        sh = shell[inside]
+        struts = (((xi & 7) == 0) & ((yi & 7) == 0)) | (((yi & 7) == 0) & ((zi & 7) == 0)) | (((xi & 7) == 0) & ((zi & 7) == 0))
+        keep = sh | struts
+        w = which[inside][keep]
+        return np.stack([xi[keep], yi[keep], zi[keep]], 1).astype(np.int32), (w.astype(np.uint32) % 16) + 1
+
+    starts = list(range(0, N, SL))
+    if len(starts) > 1:
+        from concurrent.futures import ThreadPoolExecutor
+        import os
+        with ThreadPoolExecutor(min(len(starts), os.cpu_count() or 1, 16)) as ex:
+            parts = list(ex.map(slab, starts))
+    else:
+        parts = [slab(0)]
+    return np.concatenate([p[0] for p in parts]), np.concatenate([p[1] for p in parts]), default_materials(16)

@@ -103,7 +103,8 @@ def connect_multicast(renderer, images, group=None):
         return None
     b = renderer.buffers()
     n = int(b.width) * int(b.height)
-    per_pixel = {IMG_HIT: 16, IMG_SHADOW: 1, IMG_ACCUM: 16}
+    from .api import IMG_COLOR, IMG_HIT_PACKED
+    per_pixel = {IMG_HIT: 16, IMG_SHADOW: 1, IMG_ACCUM: 16, IMG_HIT_PACKED: 8, IMG_COLOR: 16}
     pg = group if group is not None else dist.group.WORLD
     name = pg.group_name if hasattr(pg, "group_name") else pg
     dev = torch.device("cuda", torch.cuda.current_device())
@@ -124,6 +125,19 @@ def connect_multicast(renderer, images, group=None):
         renderer.bind_image(img, t.data_ptr(), int(h.multicast_ptr))
     dist.barrier(group=group)
     return keep
+
+
+def connect_comm(renderer, group=None):
+    """Gives the renderer's context its own NCCL communicator over the ranks of `group` (blokb_comm_init): rank 0 makes the
+    ncclUniqueId, torch.distributed only carries its 128 bytes to the other ranks. After this, Renderer.reduce_accum needs no
+    Python in the frame loop — exactly what a C++ host does with blokb_comm_unique_id / blokb_comm_init."""
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return
+    rank, size = dist.get_rank(group), dist.get_world_size(group)
+    box = [renderer.comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    renderer.comm_init(box[0], rank, size)
 
 
 def disconnect_multicast(renderer, keep, group=None):

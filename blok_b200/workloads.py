@@ -1,6 +1,8 @@
 """Named benchmark workloads = BASELINE.json's configs at full size; all synthetic and deterministic.
 
-  c2  512^3 dense blob "mesh", 1920x1080, primary + sun shadow rays          (BASELINE configs[1])
+  c2  512^3 dense voxelised "mesh" (union of 40 ellipsoids filling the box), 1920x1080, primary + sun shadow rays, camera
+      at (-0.4N, 0.6N, -0.4N) looking at the centre; the fov (40 degrees) frames the 512^3 box: 64 % of
+      the primary rays hit                                                   (BASELINE configs[1])
   c3  2048^3 heightfield-shell terrain, 3840x2160, primary rays              (configs[2])  <- bench.py headline
   c4  the c3 scene path traced: 64 spp, <=2 bounces + 1 shadow ray, spp sharded across GPUs   (configs[3])
   c5  8192^3 terrain, 7680x4320, 1 spp path (primary + shadow + incoherent bounce)            (configs[4]; ~6 GB of
@@ -14,9 +16,9 @@ from . import scenes
 from .api import Camera, WorldSvoGpu
 
 WORKLOADS = {
-    "c2": dict(scene="blob_mesh", N=512, width=1920, height=1080, kind="primary_shadow", spp=1,
-               cam=lambda N: Camera((-0.4 * N, 0.9 * N, -0.4 * N), 45.0, -25.0),
-               desc="512^3 dense voxelized blob mesh, 1920x1080 primary + sun shadow rays"),
+    "c2": dict(scene="dense_mesh", N=512, width=1920, height=1080, kind="primary_shadow", spp=1,
+               cam=lambda N: _look_at((-0.4 * N, 0.6 * N, -0.4 * N), (0.5 * N, 0.5 * N, 0.5 * N), 40.0),
+               desc="512^3 dense voxelized mesh (40 ellipsoids), 1920x1080 primary + sun shadow rays, camera (-0.4N, 0.6N, -0.4N) -> centre"),
     "c3": dict(scene="terrain", N=2048, width=3840, height=2160, kind="primary", spp=1,
                cam=lambda N: Camera((N / 2, 0.6 * N, -0.2 * N), 90.0, -25.0),
                desc="2048^3 SVO terrain shell, 3840x2160 primary rays"),
@@ -30,6 +32,13 @@ WORKLOADS = {
                cam=lambda N: Camera((N / 2, 0.7 * N, -0.3 * N), 90.0, -25.0),
                desc="96^3 terrain shell, 256x144 primary rays (test scale)"),
 }
+
+
+def _look_at(pos, target, fov=60.0) -> Camera:
+    """Camera at pos whose forward axis (camera.hpp:42-50: yaw about +y from +x, pitch up) points at target."""
+    import math
+    d = [t - p for t, p in zip(target, pos)]
+    return Camera(pos, math.degrees(math.atan2(d[2], d[0])), math.degrees(math.atan2(d[1], math.hypot(d[0], d[2]))), fov)
 
 
 def voxels(name: str):

@@ -98,6 +98,16 @@ typedef struct blokb_hit {
     uint32_t facePrim;
 } blokb_hit;
 
+/* Packed per-ray result for bandwidth-bound consumers (PCIe readback, NVLink exchange of a tiled frame): 8 bytes instead of 16.
+ * nodeFace = node | face << 29 (node and face as in blokb_hit); a miss is nodeFace = 0xFFFFFFFF, t = -1. material and
+ * gl_PrimitiveID are functions of the leaf node and are re-derived on the host from the arrays the caller uploaded
+ * (blokb_node_prims + blokb_unpack_hits). Worlds with more than BLOKB_PACKED_MAX_NODES nodes are refused. */
+typedef struct blokb_hit_packed {
+    uint32_t nodeFace;
+    float t;
+} blokb_hit_packed;
+#define BLOKB_PACKED_MAX_NODES 0x1FFFFFFFu
+
 /* Device pointers owned by the context (valid until the next set_frame with a different size / destroy). */
 typedef struct blokb_buffers {
     blokb_hit* hit;        /* w*h       primary-hit records (trace_primary / trace_primary_shadow) */
@@ -109,6 +119,7 @@ typedef struct blokb_buffers {
     uint16_t* motion;      /* w*h*2 f16 outMotionVectors  (binding 8, rg16f) */
     float* accum;          /* w*h*4 f32 (sum.rgb, spp)    (cuda_tracer.cu:372-380) */
     uint32_t width, height;
+    blokb_hit_packed* hitPacked; /* w*h   packed primary-hit records, written by blokb_trace_primary_packed */
 } blokb_buffers;
 
 /* Denoiser::Settings::atrousIterations (blok/include/renderer_denoising.hpp:71) + PostProcess::Settings
@@ -144,7 +155,8 @@ enum blokb_image {
     BLOKB_IMG_TAA_HISTORY = 13,   /* PostProcess currentHistory() rgba32f */
     BLOKB_IMG_TAA_OUTPUT = 14,    /* taaOutput rgba32f — only materialised when tonemapping is disabled */
     BLOKB_IMG_TONEMAPPED = 15,    /* tonemapOutput rgba8 */
-    BLOKB_IMG_FINAL = 16          /* PostProcess::getOutputImage(): sharpenOutput / tonemapOutput rgba8 (or taaOutput rgba32f) */
+    BLOKB_IMG_FINAL = 16,         /* PostProcess::getOutputImage(): sharpenOutput / tonemapOutput rgba8 (or taaOutput rgba32f) */
+    BLOKB_IMG_HIT_PACKED = 17     /* w*h packed 8-byte hit records, written by blokb_trace_primary_packed */
 };
 
 /* Sizes of the GPU-resident compact layout built by blokb_upload_world. */
@@ -264,13 +276,49 @@ int blokb_set_strips(blokb_ctx* ctx, uint32_t first, uint32_t stride);
  * `multicast`; the NVSwitch replicates it into every GPU's copy, so a rank's NVLink egress is its own strips, not
  * (G-1) copies of them. multicast == NULL just substitutes the memory; local == NULL restores the context's own
  * allocation. The memory must hold the whole image and outlive the binding. */
+/* Exchangeable images: BLOKB_IMG_HIT, _SHADOW, _ACCUM, _HIT_PACKED (stores of the dispatches) and _COLOR (the resolved slices of
+ * blokb_reduce_accum). */
 int blokb_bind_image(blokb_ctx* ctx, int image, void* local, void* multicast);
 int blokb_ipc_export(blokb_ctx* ctx, int image, void* handle64);
 int blokb_set_peers(blokb_ctx* ctx, int image, const void* handles, uint32_t n, uint32_t self);
 
+/* Cross-GPU reduction of the per-GPU accumulation buffers — the one exchange step of sample-sharded path tracing (SURVEY.md
+ * 8(e); BASELINE configs[3]): GPU g of G traced samples [spp*g/G, spp*(g+1)/G) of every pixel into its own accum image, and
+ * colour = (sum over GPUs of sum.rgb) / (sum over GPUs of spp) with the firefly clamp (raygen.rgen:383-392). The reference has no
+ * multi-GPU path; behind Renderer::render (blok/include/renderer.hpp:34) a C++ host calls, per frame and per GPU:
+ *   blokb_set_frame, blokb_reset_accum, blokb_trace_path(s0, s1), blokb_reduce_accum(mode), then reads the colour image.
+ * The communicator is NCCL's, reached through dlopen("libnccl.so.2") — no link-time dependency, and a process that already
+ * carries an NCCL (its own, or torch's) gets that one:
+ *   blokb_set_comm            adopts a caller-owned ncclComm_t (one rank per context / GPU); never destroyed by the library.
+ *   blokb_comm_unique_id /    for hosts without an NCCL of their own: rank 0 obtains a 128-byte ncclUniqueId, ships it to the
+ *   blokb_comm_init           other ranks by any means, and every rank creates its (library-owned) communicator with it.
+ *   blokb_reduce_accum        enqueue only. BLOKB_REDUCE_SLICE: reduce-scatter of accum (fp32 sum) into the slice of pixels this
+ *                             rank owns, resolved into that slice of the colour image — each rank ends with 1/G of the frame
+ *                             (blokb_reduce_slice tells which pixels; blokb_readback_slice copies just those).
+ *                             BLOKB_REDUCE_ALL: the same, then an all-gather of the resolved slices: every rank holds the frame.
+ *                             When accum is bound to an NVLink multicast address (blokb_bind_image) the sum and the resolve are
+ *                             ONE kernel over peer memory (multimem.ld_reduce: the NVSwitch adds the G copies of a texel on
+ *                             the way), fenced by two 4-byte all-reduces; with BLOKB_IMG_COLOR bound too, BLOKB_REDUCE_ALL
+ *                             broadcasts each resolved texel with one multicast store instead of the all-gather.
+ * Pixels are sliced in row-major order: rank g owns [g*ceil(n/G), min(n, (g+1)*ceil(n/G))). accum keeps the LOCAL sums (a later
+ * blokb_trace_path keeps accumulating); only colour holds the reduced result. */
+#define BLOKB_REDUCE_ALL 0
+#define BLOKB_REDUCE_SLICE 1
+int blokb_comm_unique_id(void* id128);
+int blokb_comm_init(blokb_ctx* ctx, const void* id128, int rank, int nranks);
+int blokb_set_comm(blokb_ctx* ctx, void* ncclComm);
+int blokb_comm_rank(blokb_ctx* ctx, int* rank, int* nranks);
+int blokb_reduce_accum(blokb_ctx* ctx, int mode, void* stream);
+int blokb_reduce_slice(blokb_ctx* ctx, uint64_t* firstPixel, uint64_t* nPixels);
+int blokb_readback_slice(blokb_ctx* ctx, int image, void* host, size_t bytes); /* image's pixels [first, first + n) -> host (n * bytes-per-pixel) */
+/* Only the strips this context renders (blokb_set_strips) of an image, copied to their full-frame positions in `host` (a buffer
+ * of the whole image; other rows are left untouched): what one GPU of a tiled frame hands to the host. */
+int blokb_readback_strips(blokb_ctx* ctx, int image, void* host, size_t bytes);
+
 /* Dispatch (enqueue only). */
 int blokb_trace_primary(blokb_ctx* ctx, void* stream);        /* sample-0 primary rays -> buffers.hit */
 int blokb_trace_primary_shadow(blokb_ctx* ctx, void* stream); /* + sun shadow ray per lit hit -> buffers.shadow */
+int blokb_trace_primary_packed(blokb_ctx* ctx, void* stream); /* sample-0 primary rays -> buffers.hitPacked (8-byte records) */
 int blokb_render(blokb_ctx* ctx, void* stream);               /* full raygen.rgen: frame.sampleCount spp -> 5 images */
 int blokb_trace_path(blokb_ctx* ctx, uint32_t sampleBegin, uint32_t sampleEnd, void* stream); /* accum += samples */
 int blokb_resolve(blokb_ctx* ctx, void* stream);              /* color = accum.rgb / accum.a, firefly clamp */
@@ -351,15 +399,7 @@ int blokb_pipeline_submit(blokb_pipeline* p, const blokb_frame_ubo* frame, blokb
 int blokb_pipeline_wait(blokb_pipeline* p, uint64_t ticket);
 int blokb_pipeline_drain(blokb_pipeline* p);
 void blokb_pipeline_destroy(blokb_pipeline* p);
-/* Packed records for the PCIe-bound readback: 8 bytes per ray instead of 16.
- * nodeFace = node | face << 29 (node and face as in blokb_hit); a miss is nodeFace = 0xFFFFFFFF, t = -1.
- * material and gl_PrimitiveID are functions of the leaf node and are re-derived on the host from the arrays the caller
- * uploaded (blokb_node_prims + blokb_unpack_hits). Worlds with more than BLOKB_PACKED_MAX_NODES nodes are refused. */
-typedef struct blokb_hit_packed {
-    uint32_t nodeFace;
-    float t;
-} blokb_hit_packed;
-#define BLOKB_PACKED_MAX_NODES 0x1FFFFFFFu
+/* The same pipeline with blokb_hit_packed records (8 bytes per ray: the readback is PCIe-bound). */
 int blokb_pipeline_create_packed(blokb_ctx* ctx, int depth, uint32_t width, uint32_t height, blokb_pipeline** out);
 int blokb_pipeline_submit_packed(blokb_pipeline* p, const blokb_frame_ubo* frame, blokb_hit_packed* hostOut, uint64_t* ticket);
 /* Host helpers (no GPU involved). blokb_node_prims: primOfNode[i] = index of the sub-chunk whose subtree holds node i

@@ -79,12 +79,12 @@ class _TraceMixin:
         self._render.restype = C.c_int
 
     def trace(self, scene: Scene, rays: np.ndarray, any_hit=False, threads=1):
-        """rays: (n,8) f32 {o,d,tmin,tmax}. Returns hit (n,4) u32 {prim,node,mat,face}, t (n,) f32, counters (3,) u64."""
+        """rays: (n,8) f32 {o,d,tmin,tmax}. Returns hit (n,4) u32 {prim,node,mat,face}, t (n,) f32, counters (4,) u64 {node fetches, AABB passes, MAX_ITER cap hits, rays traced}."""
         rays = np.ascontiguousarray(rays, dtype=np.float32)
         n = rays.shape[0]
         hit = np.empty((n, 4), np.uint32)
         t = np.empty(n, np.float32)
-        cnt = np.zeros(3, np.uint64)
+        cnt = np.zeros(4, np.uint64)
         rc = self._trace(_ptr(scene.nodes), len(scene.nodes), _ptr(scene.subs), len(scene.subs), _ptr(rays), n,
                          int(any_hit), _ptr(hit), _ptr(t), _ptr(cnt), threads)
         assert rc == 0
@@ -98,7 +98,7 @@ class _TraceMixin:
             pix_end = w * h
         imgs = {k: (np.full((h, w, 4), np.nan, np.float32) if k in want else None)
                 for k in ("color", "worldPos", "normalRough", "albedoMetal", "motion")}
-        cnt = np.zeros(3, np.uint64)
+        cnt = np.zeros(4, np.uint64)
         ubo = np.ascontiguousarray(ubo)
         rc = self._render(_ptr(scene.nodes), len(scene.nodes), _ptr(scene.subs), len(scene.subs), _ptr(scene.mats),
                           len(scene.mats), _ptr(ubo), _ptr(imgs["color"]), _ptr(imgs["worldPos"]),

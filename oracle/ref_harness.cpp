@@ -56,7 +56,7 @@ static thread_local float gl_HitTEXT;
 
 // instrumentation written by the (additively) instrumented intersect.rint
 static thread_local uint ref_cap_node;
-static thread_local uint64_t ref_cnt_fetch, ref_cnt_cap, ref_cnt_aabb;
+static thread_local uint64_t ref_cnt_fetch, ref_cnt_cap, ref_cnt_aabb, ref_cnt_rays;  // additive counters only: no effect on any result
 
 // committed-hit state of the current traceRayEXT
 static thread_local bool cur_any_hit;
@@ -204,6 +204,7 @@ static bool trace_one(const glm::vec3& o, const glm::vec3& d, float tmin, float 
     gl_WorldRayOriginEXT = o; gl_WorldRayDirectionEXT = d;
     gl_RayTminEXT = tmin; gl_RayTmaxEXT = tmax;
     cur_any_hit = anyHit; cur_terminated = false; hit_valid = false;
+    ref_cnt_rays++;
     g_world->grid.candidates(o, d, tmin, tmax, tl_cand);
     for (int32_t p : tl_cand) {
         gl_PrimitiveID = p;
@@ -412,13 +413,13 @@ static void bind_world(World& w, const void* nodes, size_t nNodes, const void* s
 
 // Arbitrary rays through intersect.rint. rays: n x {ox,oy,oz,dx,dy,dz,tmin,tmax}.
 // outHit: n x {prim, node, material, face} (0xFFFFFFFF x4 on miss); outT: n (-1 on miss).
-// counters[3] += {node fetches (intersect.rint:133), AABB root-test passes (:88), MAX_ITER cap hits}.
+// counters[4] += {node fetches (intersect.rint:133), AABB root-test passes (:88), MAX_ITER cap hits, rays traced (traceRayEXT calls)}.
 int ref_trace(const void* nodes, uint64_t nNodes, const void* subs, uint64_t nSub, const float* rays, uint64_t n,
               int anyHit, uint32_t* outHit, float* outT, uint64_t* counters, int nThreads) {
     World w; bind_world(w, nodes, nNodes, subs, nSub, nullptr, 0);
-    std::atomic<uint64_t> c0{0}, c1{0}, c2{0};
+    std::atomic<uint64_t> c0{0}, c1{0}, c2{0}, c3{0};
     parallel_for(n, nThreads, [&](size_t b, size_t e, int) {
-        glslenv::ref_cnt_fetch = glslenv::ref_cnt_aabb = glslenv::ref_cnt_cap = 0;
+        glslenv::ref_cnt_fetch = glslenv::ref_cnt_aabb = glslenv::ref_cnt_cap = glslenv::ref_cnt_rays = 0;
         for (size_t i = b; i < e; i++) {
             const float* r = rays + 8 * i;
             HitRec rec{};
@@ -427,9 +428,9 @@ int ref_trace(const void* nodes, uint64_t nNodes, const void* subs, uint64_t nSu
             if (hit) { o[0] = (uint32_t)rec.prim; o[1] = rec.node; o[2] = rec.mat; o[3] = rec.face; outT[i] = rec.t; }
             else { o[0] = o[1] = o[2] = o[3] = 0xFFFFFFFFu; outT[i] = -1.0f; }
         }
-        c0 += glslenv::ref_cnt_fetch; c1 += glslenv::ref_cnt_aabb; c2 += glslenv::ref_cnt_cap;
+        c0 += glslenv::ref_cnt_fetch; c1 += glslenv::ref_cnt_aabb; c2 += glslenv::ref_cnt_cap; c3 += glslenv::ref_cnt_rays;
     });
-    if (counters) { counters[0] += c0; counters[1] += c1; counters[2] += c2; }
+    if (counters) { counters[0] += c0; counters[1] += c1; counters[2] += c2; counters[3] += c3; }
     g_world = nullptr;
     return 0;
 }
@@ -448,18 +449,18 @@ int ref_render(const void* nodes, uint64_t nNodes, const void* subs, uint64_t nS
     rgen::outMotionVectors = {motion, (int)W};
     if (pixEnd > uint64_t(W) * H) pixEnd = uint64_t(W) * H;
     const uint64_t cnt = pixEnd > pixBegin ? (pixEnd - pixBegin + pixStep - 1) / pixStep : 0;
-    std::atomic<uint64_t> c0{0}, c1{0}, c2{0};
+    std::atomic<uint64_t> c0{0}, c1{0}, c2{0}, c3{0};
     parallel_for(cnt, nThreads, [&](size_t b, size_t e, int) {
-        ref_cnt_fetch = ref_cnt_aabb = ref_cnt_cap = 0;
+        ref_cnt_fetch = ref_cnt_aabb = ref_cnt_cap = ref_cnt_rays = 0;
         for (size_t i = b; i < e; i++) {
             uint64_t p = pixBegin + i * pixStep;
             gl_LaunchIDEXT = uvec3(uint32_t(p % W), uint32_t(p / W), 0u);
             gl_LaunchSizeEXT = uvec3(W, H, 1u);
             rgen::shader_main();
         }
-        c0 += ref_cnt_fetch; c1 += ref_cnt_aabb; c2 += ref_cnt_cap;
+        c0 += ref_cnt_fetch; c1 += ref_cnt_aabb; c2 += ref_cnt_cap; c3 += ref_cnt_rays;
     });
-    if (counters) { counters[0] += c0; counters[1] += c1; counters[2] += c2; }
+    if (counters) { counters[0] += c0; counters[1] += c1; counters[2] += c2; counters[3] += c3; }
     g_world = nullptr;
     return 0;
 }

@@ -54,7 +54,7 @@ struct Sub { uint32_t nodeOffset, rootNodeIndex, nodeCount, startDepth; V3 world
 struct Mat { V3 albedo; uint32_t flags; V3 emission; float ior; };                       // material.hpp:88-114
 static_assert(sizeof(Node) == 16 && sizeof(Sub) == 48 && sizeof(Mat) == 32, "layout");
 
-struct Counters { uint64_t fetch = 0, aabb = 0, cap = 0; };
+struct Counters { uint64_t fetch = 0, aabb = 0, cap = 0, rays = 0; };  // rays = World::trace calls (one per traceRayEXT)
 
 // State of one traceRayEXT: [tmin, tmax] shrinks as hits are accepted (reportIntersectionEXT semantics).
 struct RayState {
@@ -154,6 +154,7 @@ struct World {
     }
 
     void trace(RayState& r, Counters& cn) const {
+        cn.rays++;
         if (brute) {
             for (size_t i = 0; i < nSub && !r.done; i++) traverse_subchunk(nodes, subs[i], (int32_t)i, r, cn);
             return;
@@ -401,7 +402,7 @@ extern "C" {
 int orc_trace(const void* nodes, uint64_t, const void* subs, uint64_t nSub, const float* rays, uint64_t n, int anyHit,
               uint32_t* outHit, float* outT, uint64_t* counters, int nThreads) {
     World w{(const Node*)nodes, (const Sub*)subs, (size_t)nSub, nullptr, 0}; w.build(64);
-    std::atomic<uint64_t> c0{0}, c1{0}, c2{0};
+    std::atomic<uint64_t> c0{0}, c1{0}, c2{0}, c3{0};
     parallel_for(n, nThreads, [&](size_t b, size_t e) {
         Counters cn;
         for (size_t i = b; i < e; i++) {
@@ -412,9 +413,9 @@ int orc_trace(const void* nodes, uint64_t, const void* subs, uint64_t nSub, cons
             if (r.hit) { o[0] = (uint32_t)r.prim; o[1] = r.node; o[2] = r.mat; o[3] = r.face; outT[i] = r.tmax; }
             else { o[0] = o[1] = o[2] = o[3] = 0xFFFFFFFFu; outT[i] = -1.0f; }
         }
-        c0 += cn.fetch; c1 += cn.aabb; c2 += cn.cap;
+        c0 += cn.fetch; c1 += cn.aabb; c2 += cn.cap; c3 += cn.rays;
     });
-    if (counters) { counters[0] += c0; counters[1] += c1; counters[2] += c2; }
+    if (counters) { counters[0] += c0; counters[1] += c1; counters[2] += c2; counters[3] += c3; }
     return 0;
 }
 
@@ -427,16 +428,16 @@ int orc_render(const void* nodes, uint64_t, const void* subs, uint64_t nSub, con
     const uint64_t total = uint64_t(f.screenWidth) * f.screenHeight;
     if (pixEnd > total) pixEnd = total;
     const uint64_t cnt = pixEnd > pixBegin ? (pixEnd - pixBegin + pixStep - 1) / pixStep : 0;
-    std::atomic<uint64_t> c0{0}, c1{0}, c2{0};
+    std::atomic<uint64_t> c0{0}, c1{0}, c2{0}, c3{0};
     parallel_for(cnt, nThreads, [&](size_t b, size_t e) {
         Counters cn;
         for (size_t i = b; i < e; i++) {
             uint64_t p = pixBegin + i * pixStep;
             raygen_pixel(w, f, uint32_t(p % f.screenWidth), uint32_t(p / f.screenWidth), im, cn);
         }
-        c0 += cn.fetch; c1 += cn.aabb; c2 += cn.cap;
+        c0 += cn.fetch; c1 += cn.aabb; c2 += cn.cap; c3 += cn.rays;
     });
-    if (counters) { counters[0] += c0; counters[1] += c1; counters[2] += c2; }
+    if (counters) { counters[0] += c0; counters[1] += c1; counters[2] += c2; counters[3] += c3; }
     return 0;
 }
 

@@ -151,6 +151,52 @@ void emu_warp_profile(void* p, const float* rays, size_t nWarps, int locate, uin
         }
     }
 }
+// What-if schedule for the same 32 lock-step Walkers: ONE pass per iteration, chosen by vote — a descend pass when the lanes sitting on
+// an occupied cell number at least num/den of the lanes wanting a step, else a step pass; the minority waits. out as emu_warp_profile
+// plus out[11] = iterations (each costs the vote's own instructions).
+void emu_warp_vote(void* p, const float* rays, size_t nWarps, int locate, int num, int den, uint64_t* out) {
+    Emu* e = (Emu*)p;
+    for (size_t w = 0; w < nWarps; w++) {
+        Walker wk[32]; uint4 stackMem[32][kMaxLevels]; bool live[32];
+        for (int l = 0; l < 32; l++) {
+            const float* r = rays + 8 * (32 * w + l);
+            live[l] = wk[l].init(e->dw, r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7], locate != 0);
+        }
+        out[10]++;
+        for (;;) {
+            uint32_t nd = 0, ns = 0;
+            for (int l = 0; l < 32; l++) {
+                if (!live[l]) continue;
+                if (wk[l].occupied()) { if (wk[l].sh == 0) live[l] = false; else nd++; }
+                else ns++;
+            }
+            if (!nd && !ns) break;
+            out[11]++;
+            if (nd && (ns == 0 || uint64_t(nd) * den >= uint64_t(ns) * num)) {
+                uint32_t nSel = 0;
+                for (int l = 0; l < 32; l++) {
+                    if (!live[l] || !wk[l].occupied()) continue;
+                    nSel += wk[l].sh - 2 < wk[l].rs;
+                    wk[l].descend(e->dw, NodeStack{stackMem[l], 1});
+                }
+                out[0]++; out[1] += nd;
+                if (nSel) { out[2]++; out[3] += nSel; }
+            } else {
+                uint32_t nWiden = 0, nClimb = 0;
+                for (int l = 0; l < 32; l++) {
+                    if (!live[l] || wk[l].occupied()) continue;
+                    nWiden += wk[l].sh > wk[l].rs;
+                    const int before = wk[l].sh;
+                    if (!wk[l].step(e->dw, NodeStack{stackMem[l], 1})) { live[l] = false; continue; }
+                    nClimb += wk[l].sh != before;
+                }
+                out[4]++; out[5] += ns;
+                if (nWiden) { out[6]++; out[7] += nWiden; }
+                if (nClimb) { out[8]++; out[9] += nClimb; }
+            }
+        }
+    }
+}
 // per-ray DDA step counts (profiling aid for warp-divergence estimates)
 void emu_trace_steps(void* p, const float* rays, size_t n, uint32_t* stepsOut, int nThreads) {
     Emu* e = (Emu*)p;
