@@ -1,19 +1,26 @@
 #!/usr/bin/env python
 """bench.py — Mrays/s of the voxel ray-traversal hot path on N B200s (contract: see the task statement / DESIGN.md §6).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3|c2|c4] [--impl ours|reference] [--no-extras]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3|c2|c4|c5] [--impl ours|reference] [--no-extras] [--no-cpu]
 
-A step = one frame of the workload (default c3: 2048^3 SVO terrain, 3840x2160 primary rays = 8 294 400 rays per GPU).
-  value     rays/s with the scene and frame constants already resident in HBM; CUDA events on the launching stream
-            around every step, L2 flushed (256 MiB memset) between steps outside the event pairs; max over ranks.
-  e2e       the same frames through the public API with HOST buffers: per step the host fills a FrameUBO (560 B, pinned),
-            blokb_set_frame + blokb_trace_primary, then the hit-record image is read back into pinned host memory.
-  roofline  algorithmic bytes per ray B = 16 V + 48 A + O; V, A counted by the CPU oracle on the
+A step = one frame of the workload (default c3: 2048^3 SVO terrain, 3840x2160 primary rays = 8 294 400 rays).
+  N = 1     value: rays/s with the scene and frame constants resident in HBM; CUDA events on the launching stream around every
+            step, L2 flushed (256 MiB memset) between steps outside the event pairs.
+  N > 1     ONE frame tiled over the N GPUs (strong scaling): rank g traces the 8-row strips g, g + N, ... and its kernel stores
+            every hit record into all ranks' images through an NVLink multicast address (P2P stores where the box has no
+            multicast); a 4-byte all-reduce on the dispatch stream is the frame fence. value = the frame's rays / max over ranks
+            of the device time. The old headline — every rank its own frame, no exchange — is extras.replicas.
+  e2e       the same frames through the public API with HOST buffers, two frames in flight (blokb_pipeline_*): per step the
+            host builds a FrameUBO, submits it, and the hit records arrive in pinned host memory (at N > 1 each rank delivers
+            the strips it traced: the host receives the frame once).
+  roofline  algorithmic bytes per ray B = 16 V + 48 A + O; V, A counted by the CPU checker on the
             cpu_baseline sample of the same frame; achieved = rays * B / kernel time; peak = MEASURED_PEAKS.json hbm_gbs.
-  cpu_baseline / --impl reference   the reference's own sources compiled in place (oracle/_ref, kind "reference") or, when
-            that library is absent, the CPU restatement (kind "port"), all host threads, on a strided pixel sample.
-N > 1 (torchrun): one rank per GPU, scene replicated, each rank renders its own camera's frame per step (weak scaling,
-no data-path collective); extras.c4 shards 64 spp across ranks and all-reduces the accumulation buffer (NCCL).
+            roofline.issue = the bound the kernels actually sit under (warp instructions of one launch, from the committed ncu
+            capture in profiles/traffic.json, per second of live kernel time, against 148 SMs x 4 issue slots x the sampled clock).
+  cpu_baseline / --impl reference   the reference's own sources compiled in place (oracle/_ref, kind "reference") or, when that
+            library is absent, the CPU restatement (kind "port"), all host threads, on a strided pixel sample.
+  extras    c2 (primary + sun shadow) and c4 (64 spp path traced; at N > 1 spp-sharded and reduced through blokb_reduce_accum),
+            each with its own roofline and a parity block against the CPU checker at bench size; at N = 8 also c5 (8192^3, 8K).
 """
 import argparse
 import json
@@ -29,6 +36,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 CPU_SAMPLE_STRIDE = 7  # every 7th pixel in row-major order (3840 % 7 != 0 -> a diagonal lattice over the frame)
+PATH_SAMPLE_STRIDE = CPU_SAMPLE_STRIDE * 64  # path workloads: full raygen at 64 spp on every 448th pixel
 
 
 def parse_args():
@@ -38,8 +46,8 @@ def parse_args():
     p.add_argument("--warmup", type=int, default=5)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
     p.add_argument("--workload", default="c3", choices=["c2", "c3", "c4", "c5", "t1"])
-    p.add_argument("--no-extras", action="store_true", help="skip the secondary workloads (c2, c4) and warm-L2 numbers")
-    p.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (then roofline uses cached V, A)")
+    p.add_argument("--no-extras", action="store_true", help="skip the secondary workloads (c2, c4, c5) and warm-L2 numbers")
+    p.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (then roofline uses committed V, A)")
     p.add_argument("--write-counts", action="store_true", help="(--impl reference) store V, A in blok_b200/workload_counts.json")
     return p.parse_args()
 
@@ -104,6 +112,7 @@ class ClockSampler:
                 "samples": len(self.samples)}
 
 
+# ------------------------------------------------------------------------------------------ CPU checker legs
 def cpu_checker():
     """(library, kind): the reference's own sources compiled in place when present, else the restatement."""
     from oracle import pyoracle
@@ -114,49 +123,48 @@ def cpu_checker():
     return pyoracle.OracleLib(), "port"
 
 
-def cpu_sample_rays(lib, world, wl, cam, kind):
-    """The bounded CPU sample: strided pixels of the workload's frame (primary rays; for primary_shadow the oracle also
-    traces the sun shadow ray of every lit hit, for path it runs the full raygen on the strided pixels)."""
-    from oracle import pyoracle
-    sc = pyoracle.Scene(world.globalNodes, world.globalSubChunks, world.materials)
-    ubo = cam.frame(wl["width"], wl["height"], 0, wl["spp"]).to_numpy()
-    return sc, ubo
-
-
 def run_cpu(world, wl, cam, threads=None):
-    """Times the CPU checker on the strided sample. Returns dict(value Mrays/s, rays, seconds, V, A, kind, cores, sample)."""
+    """Times the CPU checker on the strided sample of the workload's frame. Returns its counts (V, A per ray, rays traced, MAX_ITER cap
+    hits) and results (hit records / shadow verdicts / radiance) for the parity blocks."""
+    from oracle import pyoracle
     lib, kind = cpu_checker()
-    sc, ubo = cpu_sample_rays(lib, world, wl, cam, wl["kind"])
-    threads = threads or os.cpu_count() or 1
+    sc = pyoracle.Scene(world.globalNodes, world.globalSubChunks, world.materials)
     W, H = wl["width"], wl["height"]
+    ubo = cam.frame(W, H, 0, wl["spp"]).to_numpy()
+    threads = threads or os.cpu_count() or 1
     if wl["kind"] == "path":
-        stride = CPU_SAMPLE_STRIDE * 64
+        stride = PATH_SAMPLE_STRIDE
         t0 = time.perf_counter()
         img = lib.render(sc, ubo, 0, W * H, stride, threads=threads, want=("color",))
         dt = time.perf_counter() - t0
         cnt = img["counters"]
         npx = (W * H + stride - 1) // stride
-        rays = None  # the oracle counts node fetches / AABB passes, not rays: filled in by the caller from the GPU's count
-        return dict(seconds=dt, pixels=npx, fetches=int(cnt[0]), aabbs=int(cnt[1]), kind=kind, cores=threads, rays=rays,
-                    sample=f"every {stride}th pixel of the {W}x{H} frame, {wl['spp']} spp full raygen ({npx} pixels)")
+        rays = int(cnt[3])
+        return dict(seconds=dt, pixels=npx, rays=rays, value=rays / dt / 1e6, V=int(cnt[0]) / rays, A=int(cnt[1]) / rays, cap_hits=int(cnt[2]),
+                    kind=kind, cores=threads, color=img["color"].reshape(-1, 4)[::stride, :3].copy(), stride=stride,
+                    rays_per_pixel=rays / npx,
+                    sample=f"every {stride}th pixel of the {W}x{H} frame, {wl['spp']} spp full raygen ({npx} pixels, {rays} rays)")
     rays = lib.primary_rays(ubo)[::CPU_SAMPLE_STRIDE]
     t0 = time.perf_counter()
     h, t, cnt = lib.trace(sc, rays, threads=threads)
     n = len(rays)
-    fetch, aabb = int(cnt[0]), int(cnt[1])
+    fetch, aabb, caps = int(cnt[0]), int(cnt[1]), int(cnt[2])
+    shadow = None
     if wl["kind"] == "primary_shadow":
-        srays = shadow_rays(rays, h, t)
-        _, _, c2 = lib.trace(sc, srays, any_hit=True, threads=threads)
+        srays, cast = shadow_rays(rays, h, t)
+        _, st, c2 = lib.trace(sc, srays, any_hit=True, threads=threads)
         n += len(srays)
-        fetch += int(c2[0]); aabb += int(c2[1])
+        fetch += int(c2[0]); aabb += int(c2[1]); caps += int(c2[2])
+        shadow = np.zeros(len(rays), np.uint8)       # the product's flag: 0 = no shadow ray cast, 1 = lit, 2 = shadowed
+        shadow[cast] = np.where(st >= 0, 2, 1)
     dt = time.perf_counter() - t0
-    return dict(seconds=dt, rays=n, value=n / dt / 1e6, V=fetch / n, A=aabb / n, kind=kind, cores=threads,
-                hit_fraction=float((t >= 0).mean()), hits=(h, t),
+    return dict(seconds=dt, rays=n, value=n / dt / 1e6, V=fetch / n, A=aabb / n, cap_hits=caps, kind=kind, cores=threads,
+                hit_fraction=float((t >= 0).mean()), hits=(h, t), shadow=shadow, rays_per_pixel=n / len(rays),
                 sample=f"every {CPU_SAMPLE_STRIDE}th pixel (row-major) of the {W}x{H} frame: {n} rays")
 
 
 def shadow_rays(rays, h, t):
-    """Sun shadow rays of the lit primary hits, built like raygen.rgen:280-298 (fp32, unfused)."""
+    """Sun shadow rays of the lit primary hits, built like raygen.rgen:280-298 (fp32, unfused). Returns (rays, cast mask)."""
     normals = np.array([[1, 0, 0], [-1, 0, 0], [0, 1, 0], [0, -1, 0], [0, 0, 1], [0, 0, -1]], np.float32)
     hit = t >= 0
     N = normals[np.where(hit, h[:, 3], 0)]
@@ -169,15 +177,48 @@ def shadow_rays(rays, h, t):
     cast = hit & (ndl > 0)
     o = (rays[:, 0:3] + d * t[:, None]).astype(np.float32) + (N * np.float32(0.001)).astype(np.float32)
     n = int(cast.sum())
-    return np.concatenate([o[cast], np.tile(sun, (n, 1)), np.full((n, 1), 0.001, np.float32), np.full((n, 1), 1000, np.float32)], 1).astype(np.float32)
+    out = np.concatenate([o[cast], np.tile(sun, (n, 1)), np.full((n, 1), 0.001, np.float32), np.full((n, 1), 1000, np.float32)], 1).astype(np.float32)
+    return out, cast
+
+
+def hit_parity(got, res, got_shadow=None):
+    """GPU hit records (HIT_DT, the cpu_baseline sample's pixels) against the CPU checker's: node, material, bits of t, face and
+    gl_PrimitiveID, all exact; for primary_shadow also the per-pixel shadow verdict."""
+    h, t = res["hits"]
+    miss = t < 0
+    want_fp = np.where(miss, np.uint32(0xFFFFFFFF), (h[:, 3] | (h[:, 0] << np.uint32(3))).astype(np.uint32))
+    bad = (got["node"] != h[:, 1]) | (got["material"] != h[:, 2]) | (got["t"].view(np.uint32) != t.view(np.uint32)) | (got["facePrim"] != want_fp)
+    out = {"checked_rays": int(len(t)), "mismatches": int(np.count_nonzero(bad)), "cap_hits": int(res["cap_hits"]),
+           "what": f"GPU hit records (node, material, bits of t, face | gl_PrimitiveID << 3) vs the CPU checker ({res['kind']}) on the "
+                   "cpu_baseline sample; cap_hits = rays on which the checker ran into the reference's MAX_ITER (outside the parity claim)"}
+    if got_shadow is not None and res.get("shadow") is not None:
+        out["shadow_checked"] = int(np.count_nonzero(res["shadow"]))
+        out["shadow_mismatches"] = int(np.count_nonzero(got_shadow != res["shadow"]))
+        out["mismatches"] += out["shadow_mismatches"]
+        out["what"] += "; shadow flags (0 none cast / 1 lit / 2 shadowed) vs the checker's any-hit trace of the same shadow rays"
+    return out
+
+
+def radiance_parity(got_rgb, res):
+    """Resolved colour of the sampled pixels against the CPU checker's full raygen (same seeds): relative error per pixel =
+    max over rgb of |gpu - ref| / (|ref| + 1e-3); tolerance 2e-3 on >= 99.5 % of pixels and on the image mean."""
+    ref = res["color"]
+    rel = (np.abs(got_rgb - ref) / (np.abs(ref) + 1e-3)).max(-1)
+    mean_rel = float(np.abs(got_rgb.mean(0) - ref.mean(0)).max() / (np.abs(ref.mean(0)).max() + 1e-12))
+    frac = float(np.mean(rel < 2e-3))
+    return {"checked_pixels": int(len(ref)), "max_rel_err": float(rel.max()), "p99_5_rel_err": float(np.percentile(rel, 99.5)),
+            "fraction_within_2e-3": frac, "mean_image_rel_err": mean_rel, "cap_hits": int(res["cap_hits"]),
+            "passed": bool(frac >= 0.995 and mean_rel < 2e-3 and res["cap_hits"] == 0),
+            "what": f"GPU colour (accum / spp, firefly clamp) vs the CPU checker's ({res['kind']}) full raygen on {res['sample']}; "
+                    "sinf/cosf differ from glibc's by <= 2 ulp, which can flip a lobe choice on a rare pixel"}
 
 
 COUNTS_PATH = os.path.join(ROOT, "blok_b200", "workload_counts.json")
 
 
 def committed_counts(name):
-    """V, A of the workload's strided sample as counted by the CPU checker in the build container (used only when the
-    cpu_baseline leg does not run: N > 1 or --no-cpu). Regenerate with `python bench.py --impl reference --write-counts`."""
+    """V, A (and rays per pixel) of the workload's strided sample as counted by the CPU checker in the build container — used when the
+    cpu_baseline leg does not run (N > 1 or --no-cpu). Regenerate with `python bench.py --impl reference --workload X --write-counts`."""
     if os.path.exists(COUNTS_PATH):
         with open(COUNTS_PATH) as f:
             return json.load(f).get(name)
@@ -194,8 +235,36 @@ def out_bytes_per_ray(kind, rays_per_pixel=1.0):
     return 32.0 / rays_per_pixel
 
 
+def roofline_for(name, kind, rays, ms, V, A, rays_per_pixel, va_src, clocks, sms):
+    """roofline block of one workload: algorithmic bytes / live kernel time against the measured HBM peak, plus the issue-slot bound."""
+    peak, peak_src = measured_peaks()
+    B = 16.0 * V + 48.0 * A + out_bytes_per_ray(kind, rays_per_pixel)
+    achieved = rays * B / (ms * 1e-3) / 1e9
+    roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+            "bytes_per_ray": B, "V": V, "A": A, "counts_source": va_src, "peak_source": peak_src,
+            "kernel": {"primary": "k_primary<false>", "primary_shadow": "k_primary<true>",
+                       "path": "k_path_front + radix sort + k_bounce + k_path_gather (wavefront)"}[kind],
+            "note": "algorithmic bytes are defined in the reference's 16-B-node / 48-B-sub-chunk format (SURVEY.md §8(d)); the kernels "
+                    "read a compact L2-resident layout instead, so DRAM traffic (profiles/) is far below this figure"}
+    tr = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tr):
+        with open(tr) as f:
+            t = json.load(f).get(name)
+        if t:  # T = dram__bytes_read.sum + dram__bytes_write.sum of one step's launches (ncu --set full), source beside it
+            roof["traffic"] = t.get("total")
+            roof["traffic_detail"] = t
+            if t.get("warp_instructions") and (clocks or {}).get("sm_mhz") and sms:
+                ach = t["warp_instructions"] / (ms * 1e-3) / 1e9
+                pk = sms * 4 * clocks["sm_mhz"] * 1e6 / 1e9
+                roof["issue"] = {"achieved": ach, "peak": pk, "unit": "G warp-instr/s", "frac": ach / pk,
+                                 "threads_per_instruction": t.get("threads_per_instruction")}
+    return roof
+
+
 # ------------------------------------------------------------------------------------------ reference arm
 def run_reference(args):
+    """The reference's own CPU code on the box's host cores. Maps oracle/ and the host-only helper library only — never the
+    product's CUDA binary (scene generator and camera come from blok_b200/libblokbhost.so, the same sources built without CUDA)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -211,225 +280,312 @@ def run_reference(args):
     dt = 0.0  # sum of the traced regions (ray set-up and result allocation are outside, as on the GPU arm)
     for _ in range(args.steps):
         res = run_cpu(world, wl, cam)
-        rays += res["rays"] or 0
+        rays += res["rays"]
         dt += res["seconds"]
-    if wl["kind"] == "path":
-        # the oracle does not count rays; 1 primary + <=1 shadow + <=1 bounce per sample: use the committed GPU count
-        cc = committed_counts(name) or {}
-        rpp = cc.get("rays_per_pixel", 2.5 * wl["spp"])
-        rays = res["pixels"] * rpp * args.steps
     value = rays / dt / 1e6
     line = {"impl": "reference", "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{name}: {wl['desc']}", "step": "one bounded CPU sample of the frame: " + res["sample"]},
             "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": res["cores"], "kind": res["kind"], "sample": res["sample"]},
             "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    if "V" in res:
-        line["counts"] = {"V": res["V"], "A": res["A"], "hit_fraction": res["hit_fraction"]}
-    if getattr(args, "write_counts", False) and "V" in res:
+    line["counts"] = {"V": res["V"], "A": res["A"], "rays_per_pixel": res["rays_per_pixel"], "cap_hits": res["cap_hits"]}
+    if "hit_fraction" in res:
+        line["counts"]["hit_fraction"] = res["hit_fraction"]
+    if getattr(args, "write_counts", False):
         allc = {}
         if os.path.exists(COUNTS_PATH):
             with open(COUNTS_PATH) as f:
                 allc = json.load(f)
-        allc.setdefault(name, {}).update({"V": res["V"], "A": res["A"], "hit_fraction": res["hit_fraction"], "kind": res["kind"],
-                                          "sample": res["sample"]})
+        allc.setdefault(name, {}).update(dict(line["counts"], kind=res["kind"], sample=res["sample"]))
         with open(COUNTS_PATH, "w") as f:
             json.dump(allc, f, indent=1, sort_keys=True)
     emit(line)
 
 
 # ------------------------------------------------------------------------------------------ our arm
-def run_ours(args):
-    import torch
-    import torch.distributed as dist
-    import blok_b200
-    from blok_b200 import IMG_ACCUM, IMG_HIT, IMG_SHADOW, sharding, workloads
+class Env:
+    """Per-process plumbing: device, torch.distributed group, launching stream, L2 flush, reductions over ranks."""
 
-    rank = int(os.environ.get("RANK", "0"))
-    world_size = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world_size > 1:
-        dist.init_process_group("nccl", device_id=dev)
+    def __init__(self):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world_size = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback (use --impl reference for the CPU arm)")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        if self.world_size > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.stream = torch.cuda.Stream(device=self.dev)
+        self.sp = self.stream.cuda_stream
+        self.flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)  # > 126 MB L2
+        self.sms = torch.cuda.get_device_properties(self.dev).multi_processor_count
 
-    def barrier():
-        if world_size > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+    def barrier(self):
+        if self.world_size > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
 
-    def max_over_ranks(x):
-        if world_size == 1:
+    def _all(self, x, op):
+        if self.world_size == 1:
             return float(x)
-        t = torch.tensor([float(x)], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t = self.torch.tensor([float(x)], device=self.dev, dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=op)
         return float(t.item())
 
-    def sum_over_ranks(x):
-        if world_size == 1:
-            return float(x)
-        t = torch.tensor([float(x)], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    def max(self, x):
+        return self._all(x, self.dist.ReduceOp.MAX)
 
-    stream = torch.cuda.Stream(device=dev)
-    sp = stream.cuda_stream
-    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    def min(self, x):
+        return self._all(x, self.dist.ReduceOp.MIN)
 
-    def flush_l2():
-        with torch.cuda.stream(stream):
-            flush_buf.zero_()
+    def sum(self, x):
+        return self._all(x, self.dist.ReduceOp.SUM)
 
-    def measure(name, steps, warmup, flush=True, e2e=True):
-        """Device-timed and end-to-end numbers of one workload on this rank's GPU."""
-        wl = workloads.WORKLOADS[name]
-        kind, W, H, spp = wl["kind"], wl["width"], wl["height"], wl["spp"]
-        t0 = time.perf_counter()
-        world = workloads.build_world(name)
-        t_gen = time.perf_counter() - t0
-        r = blok_b200.Renderer(W, H, local)
-        r.add_world(world)
-        stats = r.world_stats()
-        # weak-scaling kinds render one frame per GPU (own camera); the spp-sharded path frame is ONE frame for all ranks
-        cam = workloads.camera_for(name, 0 if kind == "path" else rank)
-        ubo = cam.frame(W, H, 0, spp)
-        r.set_frame(ubo)
-        s0, s1 = sharding.sample_range(rank, world_size, spp) if kind == "path" else (0, 1)
-        accum_t = torch.as_tensor(r.device_array(IMG_ACCUM), device=dev) if kind == "path" else None
+    def flush_l2(self):
+        with self.torch.cuda.stream(self.stream):
+            self.flush_buf.zero_()
 
-        def step():
-            if kind == "primary":
-                r.trace_primary(stream=sp)
-            elif kind == "primary_shadow":
-                r.trace_primary(shadow=True, stream=sp)
-            else:
-                r.reset_accum(stream=sp)
-                r.trace_path(s0, s1, stream=sp)
-                if world_size > 1:
-                    with torch.cuda.stream(stream):
-                        dist.all_reduce(accum_t, op=dist.ReduceOp.SUM)
-                r.resolve(stream=sp)
-
-        # rays per step on this rank (deterministic): primary rays + the shadow / bounce rays the kernels actually cast
-        step()
-        torch.cuda.synchronize()
-        rays = W * H
-        if kind == "primary_shadow":
-            rays += int(np.count_nonzero(r.readback(IMG_SHADOW)))
-        elif kind == "path":
-            r.stats_enable(True)
-            r.reset_accum(stream=sp)
-            r.trace_path(s0, s1, stream=sp)
-            torch.cuda.synchronize()
-            rays = r.stats_read()[1]
-            r.stats_enable(False)
+    def timed(self, step, steps, warmup, flush=True):
+        """W warm-up steps, then K steps each inside its own CUDA-event pair on the launching stream (L2 flushed between them, outside
+        the pairs), bracketed by barrier + synchronize on both sides. Returns (mean ms of this rank, max over ranks, clock summary)."""
+        torch = self.torch
         for _ in range(warmup):
             step()
-        barrier()
+        self.barrier()
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
-        l0 = r.launch_count()
-        with ClockSampler(local) as clk:
-            barrier()
+        with ClockSampler(self.local) as clk:
+            self.barrier()
             for a, b in ev:
                 if flush:
-                    flush_l2()
-                a.record(stream)
+                    self.flush_l2()
+                a.record(self.stream)
                 step()
-                b.record(stream)
-            barrier()
-        launches = r.launch_count() - l0
-        ms = sum(a.elapsed_time(b) for a, b in ev)
-        ms_step = max_over_ranks(ms / steps)
-        total_rays = sum_over_ranks(rays)
-        out = dict(name=name, wl=wl, world=world, renderer=r, cam=cam, stats=stats, rays_rank=rays, rays_total=total_rays,
-                   ms_per_step=ms_step, ms_per_step_rank=ms / steps, value=total_rays / (ms_step * 1e-3) / 1e6, launches=launches, clocks=clk.summary(),
-                   gen_s=t_gen, ubo=ubo)
-        if not flush:
-            return out
-        # warm-L2 variant: back-to-back frames, one event pair (what a render loop sees in steady state)
+                b.record(self.stream)
+            self.barrier()
+        ms = sum(a.elapsed_time(b) for a, b in ev) / steps
+        return ms, self.max(ms), clk.summary()
+
+    def timed_back_to_back(self, step, steps):
+        """Same steps without flushes inside ONE event pair (the steady state of a render loop)."""
+        torch = self.torch
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        barrier()
-        a.record(stream)
+        self.barrier()
+        a.record(self.stream)
         for _ in range(steps):
             step()
-        b.record(stream)
-        barrier()
-        out["ms_per_step_warm_l2"] = max_over_ranks(a.elapsed_time(b) / steps)
-        out["value_warm_l2"] = total_rays / (out["ms_per_step_warm_l2"] * 1e-3) / 1e6
-        if e2e and kind == "primary":
-            # frames in flight through the public API: per step the host builds the FrameUBO from the Camera, submits the
-            # frame (trace on the context's stream, hit records copied to pinned host memory on the copy stream) and reads
-            # the previous frame's records; the copy of frame i overlaps the tracing of frame i+1 (depth 2, like the
-            # reference's 2 frames in flight, blok/include/renderer.hpp:185)
-            def pipelined(packed):
-                rec = 8 if packed else 16
-                pipe = blok_b200.FramePipeline(r, W, H, depth=2, packed=packed)
-                key = "nodeFace" if packed else "node"
-                e2e_steps = max(3, min(steps, 50))
-                for i in range(2):
-                    pipe.result(pipe.submit(cam.frame(W, H, i, spp)))
-                pipe.drain()
-                barrier()
-                t0 = time.perf_counter()
-                last, seen = None, 0
-                for i in range(e2e_steps):
-                    tk = pipe.submit(cam.frame(W, H, i, spp))
-                    if last is not None:
-                        seen += int(pipe.result(last)[key][H // 2, W // 2] != 0xFFFFFFFF)
-                    last = tk
-                seen += int(pipe.result(last)[key][H // 2, W // 2] != 0xFFFFFFFF)
-                pipe.drain()
-                barrier()
-                dt = max_over_ranks(time.perf_counter() - t0)
-                pipe.close()
-                return {"value": total_rays * e2e_steps / dt / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 560,
-                        "d2h_bytes_per_step": W * H * rec, "steps": e2e_steps, "ms_per_step": dt / e2e_steps * 1e3}
-
-            out["e2e"] = pipelined(False)
-            out["e2e"]["what"] = ("FramePipeline (blokb_pipeline_*, 2 frames in flight): Camera -> FrameUBO on host, submit = primary pass + "
-                                  "async copy of the 16-B hit records to pinned host memory, result(previous frame) read on the host; "
-                                  "scene uploaded once beforehand (Renderer::addWorld)")
-            try:  # an extra: must never cost the headline line
-                out["e2e_packed"] = pipelined(True)
-                out["e2e_packed"]["what"] = ("the same loop with blokb_pipeline_*_packed: 8-B records (node | face << 29, t); material and "
-                                             "gl_PrimitiveID are looked up on the host from the uploaded arrays (blokb_unpack_hits), "
-                                             "outside the timed region")
-            except Exception as ex:
-                out["e2e_packed"] = {"error": repr(ex)}
-            r.set_frame(ubo)
-        elif e2e:
-            nbytes = W * H * 16
-            host = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
-            e2e_steps = 2
-            barrier()
-            t0 = time.perf_counter()
-            for i in range(e2e_steps):
-                r.set_frame(ubo)
-                step()
-                stream.synchronize()
-                r.readback_into(blok_b200.IMG_COLOR, host.data_ptr(), nbytes)
-            barrier()
-            dt = max_over_ranks(time.perf_counter() - t0)
-            out["e2e"] = {"value": total_rays * e2e_steps / dt / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 560,
-                          "d2h_bytes_per_step": nbytes, "steps": e2e_steps, "ms_per_step": dt / e2e_steps * 1e3,
-                          "what": "blokb_set_frame, reset_accum, trace_path(sample shard), all-reduce, resolve, readback of RGBA32F colour"}
-        return out
-
-    return measure, dict(rank=rank, world_size=world_size, local=local, dev=dev, barrier=barrier, torch=torch, dist=dist)
+        b.record(self.stream)
+        self.barrier()
+        return self.max(a.elapsed_time(b) / steps)
 
 
-def extra_device_build(name, r, env):
+def open_workload(env, name):
+    """Scene on this rank's GPU (replicated), renderer sized for the workload, frame constants of camera 0."""
+    import blok_b200
+    from blok_b200 import workloads
+    wl = workloads.WORKLOADS[name]
+    t0 = time.perf_counter()
+    world = workloads.build_world(name)
+    gen_s = time.perf_counter() - t0
+    r = blok_b200.Renderer(wl["width"], wl["height"], env.local)
+    r.add_world(world)
+    cam = workloads.camera_for(name, 0)
+    ubo = cam.frame(wl["width"], wl["height"], 0, wl["spp"])
+    r.set_frame(ubo)
+    return dict(name=name, wl=wl, world=world, renderer=r, cam=cam, ubo=ubo, gen_s=gen_s, stats=r.world_stats())
+
+
+def count_rays(env, ctx, s0=0, s1=None):
+    """Rays one step casts on this rank (deterministic): primary rays + the shadow / bounce rays the kernels actually trace."""
+    from blok_b200 import IMG_SHADOW
+    r, wl = ctx["renderer"], ctx["wl"]
+    n = wl["width"] * wl["height"]
+    if wl["kind"] == "primary":
+        return n
+    if wl["kind"] == "primary_shadow":
+        r.trace_primary(shadow=True)
+        return n + int(np.count_nonzero(r.readback(IMG_SHADOW)))
+    r.stats_enable(True)
+    r.reset_accum()
+    r.trace_path(s0, wl["spp"] if s1 is None else s1)
+    r.sync()
+    rays = r.stats_read()[1]
+    r.stats_enable(False)
+    return rays
+
+
+def measure_single(env, ctx, steps, warmup, cam_rank=0):
+    """Device-timed numbers of a primary / primary_shadow workload rendered whole on this rank's GPU (N = 1 headline; replicas extra)."""
+    from blok_b200 import workloads
+    r, wl = ctx["renderer"], ctx["wl"]
+    W, H = wl["width"], wl["height"]
+    if cam_rank:
+        r.set_frame(workloads.camera_for(ctx["name"], cam_rank).frame(W, H, 0, wl["spp"]))
+    shadow = wl["kind"] == "primary_shadow"
+    rays = count_rays(env, ctx)
+
+    def step():
+        r.trace_primary(shadow=shadow, stream=env.sp)
+
+    l0 = r.launch_count()
+    ms, ms_max, clocks = env.timed(step, steps, warmup)
+    launches = (r.launch_count() - l0) * steps // (steps + warmup)
+    warm = env.timed_back_to_back(step, steps)
+    if cam_rank:
+        r.set_frame(ctx["ubo"])
+    return dict(rays_rank=rays, ms_rank=ms, ms=ms_max, launches=launches, clocks=clocks, ms_warm_l2=warm)
+
+
+def e2e_pipeline(env, ctx, steps, packed=False):
+    """Frames in flight through the public API with host buffers (blokb_pipeline_*, depth 2 like the reference's 2 frames in flight,
+    blok/include/renderer.hpp:185): per step the host builds the FrameUBO from the Camera and submits the frame (primary pass on the
+    context's stream, hit records copied to pinned host memory on a copy stream), then reads the PREVIOUS frame's records. With strips
+    set (a tiled frame) each rank traces and delivers only its own strips: the host receives every frame exactly once."""
+    import blok_b200
+    r, wl, cam = ctx["renderer"], ctx["wl"], ctx["cam"]
+    W, H, spp = wl["width"], wl["height"], wl["spp"]
+    rec = 8 if packed else 16
+    pipe = blok_b200.FramePipeline(r, W, H, depth=2, packed=packed)
+    key = "nodeFace" if packed else "node"
+    G, g = env.world_size, env.rank
+    probe_row = min(H - 1, (g if G > 1 else (H // 16)) * 8)   # a row this rank delivers
+    n = max(3, min(steps, 50))
+    for i in range(2):
+        pipe.result(pipe.submit(cam.frame(W, H, i, spp)))
+    pipe.drain()
+    env.barrier()
+    t0 = time.perf_counter()
+    last, seen = None, 0
+    for i in range(n):
+        tk = pipe.submit(cam.frame(W, H, i, spp))
+        if last is not None:
+            seen += int(pipe.result(last)[key][probe_row, W // 2] != 0xFFFFFFFF)
+        last = tk
+    seen += int(pipe.result(last)[key][probe_row, W // 2] != 0xFFFFFFFF)
+    pipe.drain()
+    env.barrier()
+    dt = env.max(time.perf_counter() - t0)
+    pipe.close()
+    strips = (H + 7) // 8
+    mine = (strips - g + G - 1) // G if G > 1 else strips
+    d2h = min(mine * 8, H) * W * rec if G > 1 else W * H * rec
+    return {"value": W * H * n / dt / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 560, "d2h_bytes_per_step": int(env.sum(d2h)),
+            "d2h_bytes_per_step_per_gpu": int(d2h), "steps": n, "ms_per_step": dt / n * 1e3,
+            "what": ("FramePipeline (blokb_pipeline_*, 2 frames in flight): Camera -> FrameUBO on host, submit = primary pass + async copy of the "
+                     f"{rec}-B hit records to pinned host memory, result(previous frame) read on the host; scene uploaded once beforehand "
+                     "(Renderer::addWorld)" + ("; frame tiled over the GPUs: each rank traces and delivers its own 8-row strips" if G > 1 else ""))}
+
+
+def measure_tiled(env, ctx, steps, warmup, packed=False):
+    """ONE frame tiled over the G GPUs (pixel partition): rank g traces strips g, g + G, ... (blokb_set_strips) and its
+    kernel stores each record into every rank's image — one multimem.st through the NVSwitch when the box has NVLink multicast
+    (blokb_bind_image), else P2P stores into IPC-mapped peer images (blokb_set_peers); a 4-byte all-reduce on the dispatch stream is
+    the frame fence. Parity: the assembled image on every rank is byte-identical to that rank's own undivided dispatch."""
+    from blok_b200 import IMG_HIT, IMG_HIT_PACKED, sharding
+    torch = env.torch
+    r, wl = ctx["renderer"], ctx["wl"]
+    W, H = wl["width"], wl["height"]
+    G, rank = env.world_size, env.rank
+    img = IMG_HIT_PACKED if packed else IMG_HIT
+    r.set_strips(0, 1)
+    r.set_frame(ctx["ubo"])
+    r.trace_primary(packed=packed)
+    full = r.readback(img).copy()
+    keep = sharding.connect_multicast(r, (img,))
+    if keep is None:
+        sharding.connect_peers(r, (img,))
+    r.set_strips(*sharding.strip_set(rank, G))
+    token = torch.zeros(1, device=env.dev)
+
+    def step():
+        r.trace_primary(packed=packed, stream=env.sp)
+        with torch.cuda.stream(env.stream):
+            sharding.frame_barrier(token)
+
+    l0 = r.launch_count()
+    ms, ms_max, clocks = env.timed(step, steps, warmup)
+    launches = (r.launch_count() - l0) * steps // (steps + warmup)
+    warm = env.timed_back_to_back(step, steps)
+    # the traversal alone (no fence): what the exchange adds on top
+    def trace_only():
+        r.trace_primary(packed=packed, stream=env.sp)
+    _, trace_ms, _ = env.timed(trace_only, max(5, steps // 4), 2, flush=False)
+    step()
+    env.barrier()
+    same = env.min(int(r.readback(img).tobytes() == full.tobytes()))
+    if keep is None:
+        sharding.disconnect_peers(r, (img,))
+    else:
+        sharding.disconnect_multicast(r, keep)
+    r.set_strips(0, 1)
+    recb = 8 if packed else 16
+    return dict(ms=ms_max, ms_rank=ms, launches=launches, clocks=clocks, ms_warm_l2=warm, identical=bool(same), trace_only_ms=trace_ms,
+                exchange="NVLink multicast (multimem.st into symmetric memory)" if keep is not None else "P2P stores into IPC-mapped peer images",
+                nvlink_ingress_bytes_per_gpu=int(W * H * recb * (G - 1) / G), record_bytes=recb)
+
+
+def measure_path(env, ctx, steps, warmup, e2e_steps=2):
+    """c4: the frame's spp sharded over the ranks (raygen's per-(pixel, frame, sample) seeds => the union is the single-GPU sample set),
+    per-GPU accumulation buffers reduced and resolved through the C-ABI (blokb_reduce_accum over the context's own NCCL communicator).
+    value: device time of reset + trace + reduce (every rank ends with the whole colour image). e2e: the same frame with host buffers —
+    set_frame (560 B in), reduce to slices, every rank reads back ITS slice of the colour image (the host receives the frame once)."""
+    from blok_b200 import IMG_COLOR, REDUCE_ALL, REDUCE_SLICE, sharding
+    torch = env.torch
+    r, wl = ctx["renderer"], ctx["wl"]
+    W, H, spp = wl["width"], wl["height"], wl["spp"]
+    G, rank = env.world_size, env.rank
+    s0, s1 = sharding.sample_range(rank, G, spp)
+    if G > 1:
+        sharding.connect_comm(r)
+    rays = count_rays(env, ctx, s0, s1)
+
+    def step(mode=REDUCE_ALL):
+        r.reset_accum(stream=env.sp)
+        r.trace_path(s0, s1, stream=env.sp)
+        r.reduce_accum(mode, stream=env.sp)
+
+    l0 = r.launch_count()
+    ms, ms_max, clocks = env.timed(step, steps, warmup)
+    launches = (r.launch_count() - l0) * steps // (steps + warmup)
+    first, count = r.reduce_slice() if G > 1 else (0, W * H)
+    nbytes = count * 16
+    host = torch.empty(max(nbytes, 16), dtype=torch.uint8, pin_memory=True)
+    step(REDUCE_SLICE)
+    env.barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        r.set_frame(ctx["ubo"])
+        step(REDUCE_SLICE)
+        if G > 1:
+            r.readback_slice_into(IMG_COLOR, host.data_ptr(), nbytes)
+        else:
+            r.readback_into(IMG_COLOR, host.data_ptr(), nbytes)
+    env.barrier()
+    dt = env.max(time.perf_counter() - t0)
+    total = env.sum(rays)
+    e2e = {"value": total * e2e_steps / dt / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 560, "d2h_bytes_per_step": int(env.sum(nbytes)),
+           "d2h_bytes_per_step_per_gpu": int(nbytes), "steps": e2e_steps, "ms_per_step": dt / e2e_steps * 1e3,
+           "what": "blokb_set_frame, reset_accum, trace_path(sample shard), blokb_reduce_accum(SLICE) = reduce-scatter + resolve of the owned "
+                   "slice, blokb_readback_slice of the RGBA32F colour slice into pinned host memory"}
+    step(REDUCE_ALL)
+    env.barrier()
+    return dict(rays_rank=rays, rays_total=total, ms=ms_max, ms_rank=ms, launches=launches, clocks=clocks, e2e=e2e, samples=(s0, s1))
+
+
+def extra_device_build(env, ctx):
     """Scene upload on the device (blokb_upload_voxels) beside the host path the headline used, and the
     full-size parity property: both leave byte-identical compact arrays (incl. the reference node index of every leaf block)."""
     import hashlib
     import blok_b200
     from blok_b200 import WORLD_BLOCKFIRSTLEAF, WORLD_NODES, WORLD_VOXELMAT, workloads
-    xyz, mid, mats = workloads.voxels(name)
-    b = blok_b200.Renderer(64, 64, env["local"])
+    r = ctx["renderer"]
+    xyz, mid, mats = workloads.voxels(ctx["name"])
+    b = blok_b200.Renderer(64, 64, env.local)
     b.add_voxels(xyz[:4096], mid[:4096], mats)
     ts = []
     for _ in range(3):
@@ -445,70 +601,14 @@ def extra_device_build(name, r, env):
             "identical_to_host_path": bool(same), "nodes_reference_format": int(st["nodes"])}
 
 
-def extra_tiled_frame(name, r, env, steps=30, warmup=3):
-    """N > 1: ONE frame of the workload tiled over the GPUs (strong scaling; SURVEY.md 8(e) pixel partition). Rank g renders
-    the 8-row strips g, g + G, ... (blokb_set_strips) and the kernel stores every hit record into all ranks' images — through
-    an NVLink multicast address when the box supports it (blokb_bind_image), else P2P stores to the peers' IPC-mapped
-    images (blokb_set_peers); a 4-byte all-reduce on the dispatch stream is the frame fence. Parity: the assembled image on
-    every rank is byte-identical to the rank's own undivided dispatch."""
-    import blok_b200
-    from blok_b200 import IMG_HIT, sharding, workloads
-    torch, dist = env["torch"], env["dist"]
-    rank, G, dev = env["rank"], env["world_size"], env["dev"]
-    wl = workloads.WORKLOADS[name]
-    W, H = wl["width"], wl["height"]
-    r.set_strips(0, 1)
-    r.set_frame(workloads.camera_for(name, 0).frame(W, H, 0, 1))
-    r.trace_primary()
-    full = r.readback(IMG_HIT).copy()
-    keep = sharding.connect_multicast(r, (IMG_HIT,))
-    if keep is None:
-        sharding.connect_peers(r, (IMG_HIT,))
-    r.set_strips(*sharding.strip_set(rank, G))
-    stream = torch.cuda.Stream(device=dev)
-    token = torch.zeros(1, device=dev)
-
-    def step():
-        r.trace_primary(stream=stream.cuda_stream)
-        with torch.cuda.stream(stream):
-            sharding.frame_barrier(token)
-
-    for _ in range(warmup):
-        step()
-    env["barrier"]()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
-    for a, b in ev:
-        a.record(stream)
-        step()
-        b.record(stream)
-    env["barrier"]()
-    ms = sum(a.elapsed_time(b) for a, b in ev) / steps
-    t = torch.tensor([ms], device=dev, dtype=torch.float64)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    same = torch.tensor([int(r.readback(IMG_HIT).tobytes() == full.tobytes())], device=dev)
-    dist.all_reduce(same, op=dist.ReduceOp.MIN)
-    if keep is None:
-        sharding.disconnect_peers(r, (IMG_HIT,))
-    else:
-        sharding.disconnect_multicast(r, keep)
-    r.set_strips(0, 1)
-    return {"what": f"one {W}x{H} frame of {name} tiled over {G} GPUs in interleaved 8-row strips, exchange fused into the traversal kernel",
-            "exchange": "NVLink multicast (multimem.st into symmetric memory)" if keep is not None else "P2P stores into IPC-mapped peer images",
-            "ms_per_frame": ms, "value": W * H / ms / 1e3, "unit": "Mrays/s", "scaling": "strong", "steps": steps,
-            "identical_on_every_rank": bool(int(same.item())),
-            "nvlink_ingress_bytes_per_gpu": int(W * H * 16 * (G - 1) / G)}
-
-
-def extra_full_frame(name, r, env):
+def extra_full_frame(env, ctx):
     """The reference's whole frame (Renderer::render, blok/src/renderer_draw.cpp): raygen at the reference's 8 spp, Denoiser::denoise,
     PostProcess::process, over a slow dolly so that both temporal passes are live. Per stage, CUDA events on the launching stream."""
-    import blok_b200
     from blok_b200 import Camera, PostSettings, workloads
-    torch = env["torch"]
-    wl = workloads.WORKLOADS[name]
+    torch = env.torch
+    r, wl = ctx["renderer"], ctx["wl"]
     W, H = wl["width"], wl["height"]
-    base = workloads.camera_for(name)
+    base = workloads.camera_for(ctx["name"])
     frames = 8
     cams = [Camera((base.position[0] + 0.5 * k, base.position[1], base.position[2] + 0.25 * k), base.yaw + 0.02 * k, base.pitch) for k in range(frames)]
     st = PostSettings()
@@ -535,7 +635,172 @@ def extra_full_frame(name, r, env):
     out = {n + "_ms": float(np.median(times[n])) for n in names}
     out["frame_ms"] = sum(out.values())
     out["launches_per_frame"] = (r.launch_count() - l0) // frames
-    out["what"] = f"{W}x{H}, 8 spp raygen + temporal/variance + 4 a-trous + TAA/tonemap + sharpen (reference defaults)"
+    out["what"] = f"{W}x{H}, 8 spp raygen (wavefront) + temporal/variance + 4 a-trous + TAA/tonemap + sharpen (reference defaults)"
+    r.set_frame(ctx["ubo"])
+    return out
+
+
+def extra_workload(env, name, steps, warmup, do_cpu):
+    """A secondary workload measured like the headline: value, roofline (V, A from the CPU checker on this run's sample at N = 1,
+    else the committed counts) and a parity block against the checker at bench size."""
+    from blok_b200 import IMG_COLOR, IMG_HIT, IMG_SHADOW
+    ctx = open_workload(env, name)
+    r, wl = ctx["renderer"], ctx["wl"]
+    W, H, kind = wl["width"], wl["height"], wl["kind"]
+    G = env.world_size
+    try:
+        if kind == "path":
+            m = measure_path(env, ctx, steps, warmup)
+            rays_total, ms = m["rays_total"], m["ms"]
+            out = {"workload": wl["desc"], "value": rays_total / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ms, "rays_per_step": rays_total,
+                   "scaling": "strong (spp sharded over the ranks; blokb_reduce_accum: reduce-scatter + resolve + all-gather over NCCL)" if G > 1 else "one GPU",
+                   "samples_this_rank": list(m["samples"]), "gpu_launches": m["launches"], "e2e": m["e2e"], "clocks": m["clocks"],
+                   "path_options": r.set_path_options()}
+        else:
+            # replicas: every rank renders the whole frame (at N > 1 a weak-scaling figure; the strong one is the tiled headline)
+            m = measure_single(env, ctx, steps, warmup)
+            rays_total = env.sum(m["rays_rank"])
+            ms = m["ms"]
+            out = {"workload": wl["desc"], "value": rays_total / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ms, "rays_per_step": rays_total,
+                   "value_warm_l2": rays_total / (m["ms_warm_l2"] * 1e-3) / 1e6, "scaling": "weak (every rank renders the frame)" if G > 1 else "one GPU",
+                   "gpu_launches": m["launches"], "clocks": m["clocks"]}
+        res = None
+        if do_cpu:
+            res = run_cpu(ctx["world"], wl, ctx["cam"])
+            V, A, src = res["V"], res["A"], f"counted by the CPU checker ({res['kind']}) on this run's sample: {res['sample']}"
+            out["cpu_baseline"] = {"value": res["value"], "unit": "Mrays/s", "cores": res["cores"], "kind": res["kind"], "sample": res["sample"]}
+        else:
+            cc = committed_counts(name)
+            V, A, src = (cc["V"], cc["A"], "blok_b200/workload_counts.json (CPU checker counts of the same sample, committed)") if cc else (None, None, None)
+        if V is not None:
+            rpp = rays_total / (W * H) / (1 if kind == "path" else G)
+            out["roofline"] = roofline_for(name, kind, m["rays_rank"], m["ms_rank"], V, A, rpp, src, m["clocks"], env.sms)
+        if res is not None:
+            r.set_frame(ctx["ubo"])
+            if kind == "path":
+                got = r.readback(IMG_COLOR).reshape(-1, 4)[::res["stride"], :3]
+                out["parity"] = radiance_parity(got, res)
+            else:
+                r.trace_primary(shadow=(kind == "primary_shadow"))
+                got = r.readback(IMG_HIT).reshape(-1)[::CPU_SAMPLE_STRIDE]
+                sh = r.readback(IMG_SHADOW).reshape(-1)[::CPU_SAMPLE_STRIDE] if kind == "primary_shadow" else None
+                out["parity"] = hit_parity(got, res, sh)
+                out["hit_fraction"] = res["hit_fraction"]
+        return out
+    finally:
+        r.close()
+
+
+def extra_c5(env):
+    """BASELINE configs[4] under the bench: 8192^3 terrain (201 M voxels, built by the device builder from the voxel list), one
+    7680x4320 frame tiled over the ranks with the multicast exchange — primary rays, and a 1-spp path-traced frame whose incoherent
+    bounce rays go through the wavefront reordering. Parity at full size: (a) rank 0 packs the same voxel list into the reference's
+    arrays (host) and the CPU checker traces every 251st pixel: hit records bit-exact; (b) the size-independent heightfield properties
+    (tests/heightfield.py) on 20 000 random pixels."""
+    import blok_b200
+    from blok_b200 import IMG_ACCUM, IMG_HIT, sharding, workloads
+    from blok_b200.api import WorldSvoGpu
+    torch = env.torch
+    G, rank = env.world_size, env.rank
+    wl = workloads.WORKLOADS["c5"]
+    W, H, N = wl["width"], wl["height"], wl["N"]
+    t0 = time.perf_counter()
+    xyz, mid, mats = workloads.voxels("c5")
+    t_gen = time.perf_counter() - t0
+    r = blok_b200.Renderer(W, H, env.local)
+    t0 = time.perf_counter()
+    r.add_voxels(xyz, mid, mats)
+    r.sync()
+    t_build = time.perf_counter() - t0
+    stats = r.world_stats()
+    cam = workloads.camera_for("c5", 0)
+    ubo = cam.frame(W, H, 0, 1)
+    r.set_frame(ubo)
+    out = {"workload": wl["desc"], "n_gpus": G, "scene_gen_s": t_gen, "device_build_wall_s": t_build,
+           "world": {k: stats[k] for k in ("nodes", "subChunks", "voxels", "bricks", "compactBytes", "levels")}}
+    images = (IMG_HIT, IMG_ACCUM)
+    keep = None
+    if G > 1:
+        keep = sharding.connect_multicast(r, images)
+        if keep is None:
+            sharding.connect_peers(r, images)
+        out["exchange"] = "NVLink multicast (multimem.st)" if keep is not None else "P2P stores into IPC-mapped peer images"
+    r.set_strips(*sharding.strip_set(rank, G))
+    token = torch.zeros(1, device=env.dev)
+
+    def fence():
+        with torch.cuda.stream(env.stream):
+            sharding.frame_barrier(token)
+
+    def p_primary():
+        r.trace_primary(stream=env.sp)
+        fence()
+
+    def p_path():
+        fence()                         # nobody may still be reading last frame's accum when it is cleared
+        r.reset_accum(stream=env.sp)
+        fence()                         # every rank's clear has landed before peers store into it
+        r.trace_path(0, 1, stream=env.sp)
+        fence()
+        r.resolve(stream=env.sp)
+
+    _, ms, clocks = env.timed(p_primary, 10, 3)
+    out["primary"] = {"ms_per_frame": ms, "rays": W * H, "value": W * H / ms / 1e3, "unit": "Mrays/s"}
+    out["clocks"] = clocks
+    r.stats_enable(True)
+    r.reset_accum(stream=env.sp)
+    r.trace_path(0, 1, stream=env.sp)
+    torch.cuda.synchronize()
+    rays_path = env.sum(r.stats_read()[1])
+    r.stats_enable(False)
+    _, ms, _ = env.timed(p_path, 5, 2)
+    out["path_1spp"] = {"ms_per_frame": ms, "rays": rays_path, "value": rays_path / ms / 1e3, "unit": "Mrays/s", "path_options": r.set_path_options(),
+                        "what": "primary + sun shadow + one incoherent bounce ray per pixel; bounce rays sorted by direction cell + origin Morton code "
+                                "before they are traced (wavefront), accum strips exchanged by the kernel's stores, resolve"}
+    # ---- parity at full size (rank 0 holds the whole hit image after the fenced dispatch)
+    p_primary()
+    env.barrier()
+    if rank == 0:
+        full = r.readback(IMG_HIT)
+        try:
+            from oracle import pyoracle
+            lib, kind = cpu_checker()
+            t0 = time.perf_counter()
+            world = WorldSvoGpu.from_voxels(xyz, mid, mats)
+            t_pack = time.perf_counter() - t0
+            sc = pyoracle.Scene(world.globalNodes, world.globalSubChunks, world.materials)
+            rays = lib.primary_rays(ubo.to_numpy())[::251]
+            h, t, cnt = lib.trace(sc, rays, threads=os.cpu_count() or 1)
+            res = dict(hits=(h, t), cap_hits=int(cnt[2]), kind=kind)
+            par = hit_parity(full.reshape(-1)[::251], res)
+            par["what"] = par["what"].replace("on the cpu_baseline sample", f"on every 251st pixel of the 8K frame (reference-format arrays packed on the host in {t_pack:.0f} s)")
+            out["parity"] = par
+            del world, sc
+        except Exception as ex:
+            out["parity"] = {"error": repr(ex)}
+        try:
+            from tests import heightfield
+            from blok_b200 import scenes
+            rng = np.random.default_rng(7)
+            n = 20000
+            px, py = rng.integers(0, W, n), rng.integers(0, H, n)
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            from c5_run import primary_rays_np
+            rays = primary_rays_np(ubo, px, py)
+            img = full[py, px]
+            chk = heightfield.check_hits(scenes.terrain_heights(N), 3, rays, img["node"], img["material"], img["t"], img["facePrim"] & 7, eps=5e-2)
+            out["heightfield_properties"] = {k: chk[k] for k in ("bad_hit_voxel", "bad_material", "filled_before_hit", "filled_on_missed_ray", "unfinished")}
+            out["heightfield_properties"]["pixels"] = n
+            out["heightfield_properties"]["passed"] = bool(heightfield.passed(chk))
+        except Exception as ex:
+            out["heightfield_properties"] = {"error": repr(ex)}
+    env.barrier()
+    if G > 1:
+        if keep is None:
+            sharding.disconnect_peers(r, images)
+        else:
+            sharding.disconnect_multicast(r, keep)
+    r.close()
     return out
 
 
@@ -549,6 +814,25 @@ def emit(line: dict):
     os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
 
 
+def guarded(env, line, extras, key, fn, seconds=240.0):
+    """Runs an extra that holds collectives of its own under a watchdog: a hang in it (one rank failing inside a collective) costs the
+    extra, never the line."""
+    def bail():
+        if env.rank == 0:
+            extras[key] = {"error": f"watchdog: no result within {seconds:.0f} s"}
+            emit(line)
+        os._exit(0)
+    wd = threading.Timer(seconds, bail)
+    wd.daemon = True
+    wd.start()
+    try:
+        res = fn()
+    except Exception as ex:
+        res = {"error": repr(ex)}
+    wd.cancel()
+    extras[key] = res
+
+
 def main():
     global _REAL_STDOUT
     args = parse_args()
@@ -558,139 +842,131 @@ def main():
     if args.impl == "reference":
         run_reference(args)
         return
-    measure, env = run_ours(args)
-    rank, world_size = env["rank"], env["world_size"]
+    env = Env()
+    rank, G = env.rank, env.world_size
     name = args.workload
-    m = measure(name, args.steps, args.warmup)
-    wl, r = m["wl"], m["renderer"]
-    peak, peak_src = measured_peaks()
+    if name == "c5":   # the 8192^3 workload has no reference-format scene on the GPUs: it runs as the c5 leg alone
+        res = extra_c5(env)
+        if rank == 0:
+            pr = res.get("primary", {})
+            emit({"metric": "Mrays/s", "value": pr.get("value"), "unit": "Mrays/s", "n_gpus": G, "steps": 10, "warmup": 3, "ms_per_step": pr.get("ms_per_frame"),
+                  "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                  "config": {"workload": "c5: " + res["workload"]}, "extras": {"c5": res}})
+        return
+    ctx = open_workload(env, name)
+    wl, r = ctx["wl"], ctx["renderer"]
+    W, H, kind = wl["width"], wl["height"], wl["kind"]
+    do_cpu = rank == 0 and G == 1 and not args.no_cpu
+    extras = {"world": {k: ctx["stats"][k] for k in ("nodes", "subChunks", "voxels", "bricks", "compactBytes", "levels", "buildMs", "uploadMs")},
+              "scene_gen_s": ctx["gen_s"]}
+    tiled = G > 1 and kind == "primary"
+    e2e = None
+    if kind == "path":
+        m = measure_path(env, ctx, args.steps, args.warmup)
+        rays_total, ms, e2e = m["rays_total"], m["ms"], m["e2e"]
+        scaling = "strong" if G > 1 else "weak"
+        par = (f"{G} GPU(s), scene replicated, the frame's {wl['spp']} spp sharded over the ranks, accumulation buffers reduced by "
+               "blokb_reduce_accum (NCCL reduce-scatter + resolve + all-gather)")
+    elif tiled:
+        m = measure_tiled(env, ctx, args.steps, args.warmup)
+        m["rays_rank"] = W * H / G
+        rays_total, ms = W * H, m["ms"]
+        scaling = "strong"
+        par = (f"ONE frame tiled over {G} GPUs in interleaved 8-row strips, scene replicated; exchange fused into the traversal kernel: {m['exchange']}; "
+               "frame fence = 4-byte all-reduce")
+        extras["tiled"] = {"identical_on_every_rank": m["identical"], "trace_only_ms": m["trace_only_ms"], "exchange": m["exchange"],
+                           "nvlink_ingress_bytes_per_gpu": m["nvlink_ingress_bytes_per_gpu"], "record_bytes": 16}
+        from blok_b200 import sharding
+        r.set_strips(*sharding.strip_set(rank, G))
+        e2e = e2e_pipeline(env, ctx, args.steps)
+        r.set_strips(0, 1)
+    else:
+        m = measure_single(env, ctx, args.steps, args.warmup)
+        rays_total, ms = env.sum(m["rays_rank"]), m["ms"]
+        scaling = "weak"
+        par = f"{G} GPU(s), scene replicated, one frame per GPU per step"
+        if kind == "primary":
+            e2e = e2e_pipeline(env, ctx, args.steps)
+    value = rays_total / (ms * 1e-3) / 1e6
+    if "ms_warm_l2" in m:
+        extras["warm_l2"] = {"value": rays_total / (m["ms_warm_l2"] * 1e-3) / 1e6, "ms_per_step": m["ms_warm_l2"],
+                             "what": "same frames back to back without the L2 flush (steady-state render loop)"}
 
-    # ---- CPU leg (rank 0, N = 1): the oracle timed on a strided sample of the same frame; doubles as a parity check
-    cpu = None
-    parity = None
-    if rank == 0 and world_size == 1 and not args.no_cpu:
-        res = run_cpu(m["world"], wl, m["cam"])
-        if wl["kind"] == "path":
-            cc = committed_counts(name) or {}
-            rpp = m["rays_rank"] / (wl["width"] * wl["height"])
-            res["rays"] = res["pixels"] * rpp
-            res["value"] = res["rays"] / res["seconds"] / 1e6
-            res["V"], res["A"] = res["fetches"] / res["rays"], res["aabbs"] / res["rays"]
+    # ---- CPU leg (rank 0, N = 1): the checker timed on a strided sample of the same frame; doubles as the parity check
+    cpu, roof = None, None
+    if do_cpu:
+        from blok_b200 import IMG_COLOR, IMG_HIT, IMG_SHADOW
+        res = run_cpu(ctx["world"], wl, ctx["cam"])
+        r.set_frame(ctx["ubo"])
+        if kind == "path":
+            extras["parity"] = radiance_parity(r.readback(IMG_COLOR).reshape(-1, 4)[::res["stride"], :3], res)
         else:
-            import blok_b200
-            r.set_frame(m["ubo"])
-            if wl["kind"] == "primary":
-                r.trace_primary()
-            else:
-                r.trace_primary(shadow=True)
-            got = r.readback(blok_b200.IMG_HIT).reshape(-1)[::CPU_SAMPLE_STRIDE]
-            h, t = res["hits"]
-            bad = int(np.count_nonzero((got["node"] != h[:, 1]) | (got["material"] != h[:, 2]) |
-                                       (got["t"].view(np.uint32) != t.view(np.uint32))))
-            parity = {"checked_rays": int(len(t)), "mismatches": bad, "what": "GPU hit records (node, material, bits of t) vs the CPU "
-                      f"checker ({res['kind']}) on the cpu_baseline sample"}
-        cpu = {"value": res["value"], "unit": "Mrays/s", "cores": res["cores"], "kind": res["kind"], "sample": res["sample"],
-               "seconds": res["seconds"]}
+            r.trace_primary(shadow=(kind == "primary_shadow"))
+            sh = r.readback(IMG_SHADOW).reshape(-1)[::CPU_SAMPLE_STRIDE] if kind == "primary_shadow" else None
+            extras["parity"] = hit_parity(r.readback(IMG_HIT).reshape(-1)[::CPU_SAMPLE_STRIDE], res, sh)
+        cpu = {"value": res["value"], "unit": "Mrays/s", "cores": res["cores"], "kind": res["kind"], "sample": res["sample"], "seconds": res["seconds"]}
         V, A, va_src = res["V"], res["A"], f"counted by the CPU checker ({res['kind']}) on the cpu_baseline sample in this run"
     else:
         cc = committed_counts(name)
-        if cc:
-            V, A, va_src = cc["V"], cc["A"], "blok_b200/workload_counts.json (CPU checker counts of the same sample, committed)"
-        else:
-            V = A = None
-            va_src = "unavailable (no cpu leg and no committed counts)"
-
-    rays_per_pixel = m["rays_rank"] / (wl["width"] * wl["height"]) * (world_size if wl["kind"] == "path" else 1)
-    roof = None
+        V, A, va_src = (cc["V"], cc["A"], "blok_b200/workload_counts.json (CPU checker counts of the same sample, committed)") if cc else (None, None, None)
     if V is not None:
-        B = 16.0 * V + 48.0 * A + out_bytes_per_ray(wl["kind"], rays_per_pixel)
-        achieved = m["rays_rank"] * B / (m["ms_per_step_rank"] * 1e-3) / 1e9
-        roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                "bytes_per_ray": B, "V": V, "A": A, "counts_source": va_src, "peak_source": peak_src,
-                "kernel": {"primary": "k_primary<false>", "primary_shadow": "k_primary<true>", "path": "k_path"}[wl["kind"]],
-                "note": "algorithmic bytes are defined in the reference's 16-B-node / 48-B-sub-chunk format (SURVEY.md §8(d)); the kernel "
-                        "reads a compact L2-resident layout instead, so DRAM traffic (profiles/) is far below this figure"}
-        tr = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tr):
-            with open(tr) as f:
-                t = json.load(f).get(name)
-            if t:  # T = dram__bytes_read.sum + dram__bytes_write.sum of one launch (ncu --set full); the split and its source beside it
-                roof["traffic"] = t["total"]
-                roof["traffic_detail"] = t
-                if t.get("warp_instructions") and (m.get("clocks") or {}).get("sm_mhz"):
-                    # the bound this kernel actually sits under: warp instructions of one launch (smsp__inst_executed.sum of
-                    # the same ncu capture; deterministic for this scene and camera) / the live kernel time, against 4 issue slots per SM
-                    # per clock at the SM clock sampled during the timed region
-                    import torch
-                    sms = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
-                    ach = t["warp_instructions"] / (m["ms_per_step_rank"] * 1e-3) / 1e9
-                    pk = sms * 4 * m["clocks"]["sm_mhz"] * 1e6 / 1e9
-                    roof["issue"] = {"achieved": ach, "peak": pk, "unit": "G warp-instr/s", "frac": ach / pk,
-                                     "threads_per_instruction": t.get("threads_per_instruction")}
+        rpp = rays_total / (W * H) / (G if (kind != "path" and not tiled) else 1)
+        roof = roofline_for(name, kind, m["rays_rank"], m["ms_rank"], V, A, rpp, va_src, m["clocks"], env.sms)
 
-    extras = {"warm_l2": {"value": m["value_warm_l2"], "ms_per_step": m["ms_per_step_warm_l2"],
-                          "what": "same frames back to back without the L2 flush (steady-state render loop)"},
-              "world": {k: m["stats"][k] for k in ("nodes", "subChunks", "voxels", "bricks", "compactBytes", "levels", "buildMs", "uploadMs")},
-              "scene_gen_s": m["gen_s"]}
-    if parity:
-        extras["parity"] = parity
-    e2e = m.get("e2e")
-    if "e2e_packed" in m:
-        extras["e2e_packed"] = m["e2e_packed"]
-    if rank == 0 and world_size == 1 and not args.no_extras:
-        for key, fn in (("device_build", extra_device_build), ("frame", extra_full_frame)):
-            try:
-                extras[key] = fn(name, r, env)
-            except Exception as ex:  # an extra must never cost the headline line
-                extras[key] = {"error": repr(ex)}
+    line = None
+    if rank == 0:
+        line = {"metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": G, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms, "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": f"{name}: {wl['desc']}", "rays_per_step": rays_total, "rays_per_step_per_gpu": m["rays_rank"],
+                           "l2": "flushed between timed steps (256 MiB memset outside the event pairs); per-step output 132.7 MB also exceeds the 126 MB L2",
+                           "timing": "CUDA events on the launching stream around each step, summed; max over ranks", "parallelism": par},
+                "e2e": e2e, "gpu_launches": m["launches"], "clocks": m["clocks"], "roofline": roof, "cpu_baseline": cpu, "extras": extras}
+    else:
+        line = {}
+
     if not args.no_extras:
+        if rank == 0 and G == 1:
+            for key, fn in (("device_build", extra_device_build), ("frame", extra_full_frame)):
+                try:
+                    extras[key] = fn(env, ctx)
+                except Exception as ex:  # an extra must never cost the headline line
+                    extras[key] = {"error": repr(ex)}
+            if kind == "primary":
+                try:
+                    extras["e2e_packed"] = e2e_pipeline(env, ctx, args.steps, packed=True)
+                    extras["e2e_packed"]["what"] += ("; 8-B records (node | face << 29, t): material and gl_PrimitiveID are looked up on the host from "
+                                                     "the uploaded arrays (blokb_unpack_hits), outside the timed region — not a like-for-like e2e")
+                except Exception as ex:
+                    extras["e2e_packed"] = {"error": repr(ex)}
+        if tiled:
+            def packed_leg():
+                mp = measure_tiled(env, ctx, max(10, args.steps // 2), 3, packed=True)
+                return {"what": "the same tiled frame with 8-byte packed records (node | face << 29, t) through the exchange: half the NVLink bytes",
+                        "ms_per_frame": mp["ms"], "value": W * H / mp["ms"] / 1e3, "unit": "Mrays/s", "identical_on_every_rank": mp["identical"],
+                        "trace_only_ms": mp["trace_only_ms"], "exchange": mp["exchange"], "nvlink_ingress_bytes_per_gpu": mp["nvlink_ingress_bytes_per_gpu"]}
+            guarded(env, line, extras, "tiled_packed", packed_leg)
+
+            def replicas_leg():
+                mr = measure_single(env, ctx, 20, 3, cam_rank=rank)
+                tot = env.sum(mr["rays_rank"])
+                return {"what": "every rank renders its own camera's whole frame, no exchange (the frames in flight of a multi-GPU box): weak scaling",
+                        "value": tot / (mr["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": mr["ms"], "scaling": "weak"}
+            guarded(env, line, extras, "replicas", replicas_leg)
+        r.close()
+        ctx = None
         for other, st, wu in (("c2", 20, 3), ("c4", 2, 1)):
             if other == name:
                 continue
-            try:
-                o = measure(other, st, wu, flush=True, e2e=(other == "c4"))
-                extras[other] = {"workload": o["wl"]["desc"], "value": o["value"], "unit": "Mrays/s", "ms_per_step": o["ms_per_step"],
-                                 "rays_per_step": o["rays_total"], "value_warm_l2": o.get("value_warm_l2"),
-                                 "scaling": "strong (spp sharded, accum all-reduced)" if other == "c4" else "weak"}
-                if "e2e" in o:
-                    extras[other]["e2e"] = o["e2e"]
-                o["renderer"].close()
-            except Exception as ex:  # an extra must never cost the headline line
-                extras[other] = {"error": repr(ex)}
-    if rank == 0:
-        line = {"metric": "Mrays/s", "value": m["value"], "unit": "Mrays/s", "n_gpus": world_size, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": m["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-                "data": "synthetic",
-                "config": {"workload": f"{name}: {wl['desc']}", "rays_per_step_per_gpu": m["rays_rank"], "l2": "flushed between timed steps "
-                           "(256 MiB memset outside the event pairs); per-step output 132.7 MB also exceeds the 126 MB L2",
-                           "timing": "CUDA events on the launching stream around each step, summed; max over ranks",
-                           "parallelism": f"{world_size} GPU(s), scene replicated, one frame per GPU per step"},
-                "e2e": e2e, "gpu_launches": m["launches"], "clocks": m["clocks"], "roofline": roof, "cpu_baseline": cpu, "extras": extras}
-    if world_size > 1 and not args.no_extras:
-        # last, with everything else already in `line`: the one extra that adds collectives of its own. A watchdog makes sure a
-        # hang in it (one rank failing inside a collective) costs the extra, never the line.
-        import threading
-
-        def bail():
-            if rank == 0:
-                extras["tiled_frame"] = {"error": "watchdog: no result within 180 s"}
-                emit(line)
-            os._exit(0)
-        wd = threading.Timer(180.0, bail)
-        wd.daemon = True
-        wd.start()
-        try:
-            res = extra_tiled_frame(name, r, env)
-        except Exception as ex:
-            res = {"error": repr(ex)}
-        wd.cancel()
-        extras["tiled_frame"] = res
-    r.close()
+            guarded(env, line, extras, other, lambda o=other, s=st, w=wu: extra_workload(env, o, s, w, do_cpu), seconds=420.0)
+        if G == 8:
+            guarded(env, line, extras, "c5", lambda: extra_c5(env), seconds=420.0)
+    elif ctx is not None:
+        r.close()
     if rank == 0:
         emit(line)
-    if world_size > 1:
-        env["dist"].barrier()
-        env["dist"].destroy_process_group()
+    if G > 1:
+        env.dist.barrier()
+        env.dist.destroy_process_group()
 
 
 if __name__ == "__main__":

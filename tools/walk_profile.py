@@ -44,7 +44,7 @@ def main():
     table(f"{name} primary rays (every {stride}th pixel)", prof, hits, len(rays))
     out, _ = e.trace(rays, locate=False)
     h = np.stack([out["facePrim"] >> 3, out["node"], out["material"], out["facePrim"] & 7], 1)
-    sh = bench.shadow_rays(rays, h, out["t"])
+    sh, _ = bench.shadow_rays(rays, h, out["t"])
     if len(sh):
         prof, hits = e.walk_profile(sh, locate=True)
         table(f"{name} sun shadow rays of those hits", prof, hits, len(sh))
