@@ -1017,11 +1017,12 @@ int blokb_get_buffers(blokb_ctx* c, blokb_buffers* out) {
     *out = c->buf;
     return 0;
 }
-// Device address and whole-image byte size of an image id (nullptr: not produced yet; sz == 0: unknown id).
-static void image_lookup(blokb_ctx* c, int image, const void** srcOut, size_t* szOut) {
+// Device address and whole-image byte size of an image id (nullptr: not produced yet). Returns false for an unknown id.
+static bool image_lookup(blokb_ctx* c, int image, const void** srcOut, size_t* szOut) {
     const size_t n = size_t(c->buf.width) * c->buf.height;
     const void* src = nullptr;
     size_t sz = 0;
+    bool known = true;
     switch (image) {
         case BLOKB_IMG_HIT: src = c->buf.hit; sz = n * 16; break;
         case BLOKB_IMG_HIT_PACKED: src = c->buf.hitPacked; sz = n * 8; break;
@@ -1041,9 +1042,10 @@ static void image_lookup(blokb_ctx* c, int image, const void** srcOut, size_t* s
         case BLOKB_IMG_TAA_OUTPUT: src = c->post.taaOut; sz = n * 16; break;
         case BLOKB_IMG_TONEMAPPED: src = c->post.tonemapOut; sz = n * 4; break;
         case BLOKB_IMG_FINAL: src = c->post.final; sz = n * c->post.finalBytesPerPixel; break;
-        default: break;
+        default: known = false; break;
     }
     *srcOut = src; *szOut = sz;
+    return known;
 }
 // Rows of the strips (first, first + stride, ...) of an image with `rowBytes` per pixel row: device -> host at the same offsets.
 static int copy_strips(const void* dev, void* host, size_t rowBytes, uint32_t height, uint32_t first, uint32_t stride, cudaStream_t q) {
@@ -1065,8 +1067,7 @@ int blokb_readback_strips(blokb_ctx* c, int image, void* host, size_t bytes) {
     if (!c || !host) return fail(BLOKB_E_ARG, "null argument");
     if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
     const void* src; size_t sz;
-    image_lookup(c, image, &src, &sz);
-    if (sz == 0) return fail(BLOKB_E_ARG, "unknown image id");
+    if (!image_lookup(c, image, &src, &sz)) return fail(BLOKB_E_ARG, "unknown image id");
     if (!src) return fail(BLOKB_E_STATE, "image not produced yet (blokb_denoise / blokb_postprocess of the current frame)");
     if (bytes != sz) return fail(BLOKB_E_ARG, "host buffer size mismatch: expected " + std::to_string(sz) + " (the whole image; only this context's strips are written)");
     CK(cudaSetDevice(c->device));
@@ -1180,7 +1181,11 @@ int blokb_reduce_accum(blokb_ctx* c, int mode, void* stream) {
         NK(N->AllReduce(c->dFence, c->dFence, 1, kNcclFloat32, kNcclSum, c->comm, q));
         CK(launch_reduce_resolve_mc(c->bound[2].mc, c->buf.color, (mode == BLOKB_REDUCE_ALL && colorMc) ? c->bound[4].mc : nullptr, first, count, q));
         c->launches++;
-        if (mode == BLOKB_REDUCE_ALL && !colorMc) NK(N->AllGather(c->buf.color + 4 * first, c->buf.color, per * 4, kNcclFloat32, c->comm, q));
+        if (mode == BLOKB_REDUCE_ALL && !colorMc) {
+            if (c->bound[4].on && n % size_t(c->commSize) != 0)
+                return fail(BLOKB_E_UNSUPPORTED, "colour image in caller-owned memory without a multicast address and w*h not divisible by the ranks: bind it with one, or use BLOKB_REDUCE_SLICE");
+            NK(N->AllGather(c->buf.color + 4 * first, c->buf.color, per * 4, kNcclFloat32, c->comm, q));
+        }
         NK(N->AllReduce(c->dFence, c->dFence, 1, kNcclFloat32, kNcclSum, c->comm, q));
         return dispatched(c, q);
     }
@@ -1209,8 +1214,7 @@ int blokb_readback_slice(blokb_ctx* c, int image, void* host, size_t bytes) {
     if (!c || !host) return fail(BLOKB_E_ARG, "null argument");
     if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
     const void* src; size_t sz;
-    image_lookup(c, image, &src, &sz);
-    if (sz == 0) return fail(BLOKB_E_ARG, "unknown image id");
+    if (!image_lookup(c, image, &src, &sz)) return fail(BLOKB_E_ARG, "unknown image id");
     if (!src) return fail(BLOKB_E_STATE, "image not produced yet (blokb_denoise / blokb_postprocess of the current frame)");
     size_t per, first, count;
     slice_of(c, &per, &first, &count);
@@ -1226,15 +1230,9 @@ int blokb_readback_slice(blokb_ctx* c, int image, void* host, size_t bytes) {
 int blokb_readback(blokb_ctx* c, int image, void* host, size_t bytes) {
     if (!c || !host) return fail(BLOKB_E_ARG, "null argument");
     if (!c->haveFrame) return fail(BLOKB_E_STATE, "no frame constants (blokb_set_frame)");
-    const size_t n = size_t(c->buf.width) * c->buf.height;
     const void* src = nullptr;
     size_t sz = 0;
-    switch (image) {
-        default: break;
-    }
-    (void)n;
-    image_lookup(c, image, &src, &sz);
-    if (sz == 0) return fail(BLOKB_E_ARG, "unknown image id");
+    if (!image_lookup(c, image, &src, &sz)) return fail(BLOKB_E_ARG, "unknown image id");
     if (!src) return fail(BLOKB_E_STATE, "image not produced yet (blokb_denoise / blokb_postprocess of the current frame)");
     if (bytes != sz) return fail(BLOKB_E_ARG, "host buffer size mismatch: expected " + std::to_string(sz));
     CK(cudaSetDevice(c->device));

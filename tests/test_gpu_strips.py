@@ -155,7 +155,7 @@ def test_bind_image_substitutes_external_memory(renderer_factory):
     with pytest.raises(blok_b200.BlokbError):
         r.bind_image(IMG_HIT, ext.data_ptr() + 4, None)   # misaligned
     with pytest.raises(blok_b200.BlokbError):
-        r.bind_image(IMG_COLOR, ext.data_ptr(), None)     # not an exchangeable image
+        r.bind_image(blok_b200.IMG_WORLDPOS, ext.data_ptr(), None)     # not an exchangeable image
 
 
 def _mc_worker(rank, world, port, out_dir):
