@@ -13,6 +13,17 @@
 
 namespace blokb {
 
+// Register budgets of the traversal kernels of the path tracer (min resident blocks per SM -> registers per thread): measured on
+// the c4 frame with variant libraries, tools/wave_bench.py.
+#ifndef BLOKB_FRONT_MINBLOCKS
+#define BLOKB_FRONT_MINBLOCKS 1
+#endif
+#ifndef BLOKB_PATH_MINBLOCKS
+#define BLOKB_PATH_MINBLOCKS 1
+#endif
+#ifndef BLOKB_BOUNCE_MINBLOCKS
+#define BLOKB_BOUNCE_MINBLOCKS 1
+#endif
 // pixel of this thread: block = 32 x BLOKB_BLOCK_ROWS pixels (4 warps of 8x4 pixels by default), two such blocks per 8-row strip
 // blockIdx.y counts the strips THIS launch renders (FrameDev::stripFirst / stripStride): pixel coordinates, seeds and
 // output addresses are those of the full frame, so any partition of the strips over launches or GPUs writes the same bytes.
@@ -169,7 +180,9 @@ __global__ void __launch_bounds__(kPixThreads) k_primary(const __grid_constant__
     HitRec h;
     uint32_t steps = 0;
     const NodeStack stk = thread_stack();
-    const bool hit = traverse<kStats>(W, stk, F.camPos[0], F.camPos[1], F.camPos[2], d.x, d.y, d.z, 0.001f, 10000.0f, h, steps, /*locate=*/false);
+    WalkResume resume;
+    const bool hit = traverse<kStats>(W, stk, F.camPos[0], F.camPos[1], F.camPos[2], d.x, d.y, d.z, 0.001f, 10000.0f, h, steps, /*locate=*/false,
+                                      kShadow ? &resume : nullptr);
     const size_t pi = size_t(py) * F.width + px;
     store_hit_all(out, pi, hit, h);
     if (kShadow) {
@@ -181,7 +194,7 @@ __global__ void __launch_bounds__(kPixThreads) k_primary(const __grid_constant__
             if (fmaxf(dot3(N, sunDir), 0.0f) > 0.0f) {
                 const F3 o = f3(F.camPos[0], F.camPos[1], F.camPos[2]) + d * h.t + N * 0.001f;
                 HitRec sh;
-                sv = traverse<kStats>(W, stk, o.x, o.y, o.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps, true) ? 2 : 1;
+                sv = traverse<kStats>(W, stk, o.x, o.y, o.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps, true, &resume) ? 2 : 1;
             }
         }
         store8_all(shadow, pi, sv);
@@ -260,7 +273,7 @@ __global__ void __launch_bounds__(kPixThreads) k_gbuffer(const __grid_constant__
 // No minBlocksPerSM on purpose: left alone, ptxas settles on 64 registers (4 blocks per SM, a few spilled words) = 21.4 ms for
 // 8 spp at 4K; __launch_bounds__(256, 1) gives 90 registers / 25.9 ms, (256, 2) 22.2, (256, 3) 22.6, (256, 5) 24.1.
 template <bool kStats, bool kColor>
-__global__ void __launch_bounds__(kPixThreads) k_path(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F, uint32_t sBegin, uint32_t sEnd,
+__global__ void __launch_bounds__(kPixThreads, BLOKB_PATH_MINBLOCKS) k_path(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F, uint32_t sBegin, uint32_t sEnd,
                                               const __grid_constant__ PeerOut accum, unsigned long long* stats) {
     uint32_t px, py;
     if (!thread_pixel(F, px, py)) return;
@@ -323,7 +336,7 @@ __device__ __forceinline__ uint32_t wave_key(const DeviceWorld& W, const WaveKey
 __device__ __forceinline__ uint32_t launch_thread_id() { return (blockIdx.y * gridDim.x + blockIdx.x) * kPixThreads + threadIdx.x; }
 
 template <bool kStats>
-__global__ void __launch_bounds__(kPixThreads) k_path_front(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F, uint32_t s0, uint32_t nS,
+__global__ void __launch_bounds__(kPixThreads, BLOKB_FRONT_MINBLOCKS) k_path_front(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F, uint32_t s0, uint32_t nS,
                                                             const __grid_constant__ WaveBufs B, const __grid_constant__ WaveKey K, unsigned long long* stats) {
     const uint32_t gtid = launch_thread_id();
     uint32_t px, py;
@@ -333,26 +346,26 @@ __global__ void __launch_bounds__(kPixThreads) k_path_front(const __grid_constan
     for (uint32_t k = 0; k < nS; k++) {
         const size_t slot = size_t(k) * B.nT + gtid;
         F3 rad = f3(0.f);
-        BounceRay br;
-        bool alive = false;
-        if (inFrame) alive = path_front<kStats>(W, stk, F, px, py, s0 + k, nullptr, rays, steps, rad, br);
-        B.front[slot] = make_float4(rad.x, rad.y, rad.z, alive ? 1.0f : 0.0f);
-        B.order[slot] = uint32_t(slot);
         uint32_t key = kDeadKey;
-        if (alive) {
-            key = wave_key(W, K, br.origin, br.dir);
-            float4* r = B.rec + 3 * slot;
-            r[0] = make_float4(br.origin.x, br.origin.y, br.origin.z, br.dir.x);
-            r[1] = make_float4(br.dir.y, br.dir.z, br.thr.x, br.thr.y);
-            r[2] = make_float4(br.thr.z, 0.f, 0.f, 0.f);
-        }
-        B.keys[slot] = key;
+        B.order[slot] = uint32_t(slot);
+        if (inFrame)
+            path_front<kStats>(W, stk, F, px, py, s0 + k, nullptr, rays, steps, rad, [&](const BounceRay& br) {
+                // called before the sun shadow ray is traced: the bounce ray leaves the registers here
+                key = wave_key(W, K, br.origin, br.dir);
+                float4* r = B.rec + 3 * slot;
+                r[0] = make_float4(br.origin.x, br.origin.y, br.origin.z, br.dir.x);
+                r[1] = make_float4(br.dir.y, br.dir.z, br.thr.x, br.thr.y);
+                r[2] = make_float4(br.thr.z, 0.f, 0.f, 0.f);
+                B.keys[slot] = key;
+            });
+        if (key == kDeadKey) B.keys[slot] = kDeadKey;
+        B.front[slot] = make_float4(rad.x, rad.y, rad.z, key != kDeadKey ? 1.0f : 0.0f);
     }
     if (kStats) { atomicAdd(stats, (unsigned long long)steps); atomicAdd(stats + 1, (unsigned long long)rays); }
 }
 
 template <bool kStats>
-__global__ void __launch_bounds__(256) k_bounce(const __grid_constant__ DeviceWorld W, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ order,
+__global__ void __launch_bounds__(256, BLOKB_BOUNCE_MINBLOCKS) k_bounce(const __grid_constant__ DeviceWorld W, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ order,
                                                 size_t n, const float4* __restrict__ rec, float4* __restrict__ front, unsigned long long* stats) {
     const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= n) return;

@@ -146,10 +146,14 @@ BLOKB_HD Surface fetch_surface(const DeviceWorld& W, uint32_t materialId) {  // 
 struct FirstHit { F3 pos, N, albedo, emission; float roughness, metallic, depth; bool had, emissive; };
 struct BounceRay { F3 origin, dir, thr; };
 
-// Returns true when the path goes on with `br` (radiance so far in `radiance`), false when it ended inside iteration 0.
-template <bool kStats>
-BLOKB_HD bool path_front(const DeviceWorld& W, const NodeStack& stk, const FrameDev& f, uint32_t px, uint32_t py, uint32_t s,
-                         FirstHit* first, uint32_t& rays, uint32_t& steps, F3& radiance, BounceRay& br) {
+// `emit(br)` is called once, for a path that goes on, BEFORE the sun shadow ray is traced: the lobe sampling of :337-376 does not
+// depend on the shadow verdict and consumes the generator after nothing the shadow ray touches, so it is evaluated first (same
+// expressions, same values) and the bounce ray leaves the registers — into a record (k_path_front) or into the caller's variables —
+// before the second traversal begins; the two direct-light terms are formed before that traversal too and only ADDED after it,
+// in the shader's order. Radiance gathered by iteration 0 is returned in `radiance`.
+template <bool kStats, class Emit>
+BLOKB_HD void path_front(const DeviceWorld& W, const NodeStack& stk, const FrameDev& f, uint32_t px, uint32_t py, uint32_t s,
+                         FirstHit* first, uint32_t& rays, uint32_t& steps, F3& radiance, Emit&& emit, WalkResume* resumeOut = nullptr) {
     uint32_t rng = init_rng(px, py, f.width, f.frameCount, s);
     float pcx, pcy;
     if (s == 0u) { pcx = float(px) + 0.5f; pcy = float(py) + 0.5f; }
@@ -167,11 +171,12 @@ BLOKB_HD bool path_front(const DeviceWorld& W, const NodeStack& stk, const Frame
     HitRec h;
     rays++;
     // the camera ray enters the grid from outside: start cell found level by level (Walker::init, locate = false)
+    WalkResume resume;
     const bool hit = traverse<kStats>(W, stk, rayOrigin.x, rayOrigin.y, rayOrigin.z, rayDir.x, rayDir.y, rayDir.z, 0.001f, 10000.0f, h, steps,
-                                      /*locate=*/false);
+                                      /*locate=*/false, &resume);
     if (!hit) {
         radiance = radiance + thr * sky_color(rayDir);
-        return false;
+        return;
     }
     const Surface m = fetch_surface(W, h.material);
     F3 N = face_normal(h.facePrim & 7u);
@@ -183,67 +188,84 @@ BLOKB_HD bool path_front(const DeviceWorld& W, const NodeStack& stk, const Frame
     }
     if (is_emissive(m.emission)) {
         radiance = radiance + thr * m.emission;
-        if (luminance(m.emission) > 5.0f) return false;
+        if (luminance(m.emission) > 5.0f) return;
     }
     const float NdotL = fmaxf(dot3(N, sunDir), 0.0f);
+    // ---- direct light (:280-326), everything but the shadow verdict
+    F3 direct = f3(0.f), spec = f3(0.f);
+    bool haveSpec = false;
+    if (NdotL > 0.0f) {
+        const F3 diffuse = m.albedo * (1.0f - m.metallic);
+        direct = thr * diffuse * sunRad * NdotL * BLOKB_INV_PI;
+        if (m.roughness < 0.9f) {
+            const F3 Hh = normalize3(sunDir - rayDir);
+            const float NdotH = fmaxf(dot3(N, Hh), 0.0f), VdotH = fmaxf(dot3(-rayDir, Hh), 0.0f);
+            const float a = m.roughness * m.roughness, a2 = a * a;
+            const float denom = NdotH * NdotH * (a2 - 1.0f) + 1.0f;
+            const float D = a2 / (BLOKB_PI * denom * denom);
+            const F3 F0 = mix3(f3(0.04f), m.albedo, m.metallic);
+            const F3 F = fresnel(VdotH, F0);
+            spec = thr * F * D * 0.25f * sunRad * NdotL;
+            haveSpec = true;
+        }
+    }
+    // ---- the bounce ray (:329-376; no Russian roulette on iteration 0)
+    {
+        const float ux = random_float(rng);
+        const float uy = random_float(rng);
+        const F3 F0 = mix3(f3(0.04f), m.albedo, m.metallic);
+        const F3 V = -rayDir;
+        const float NdotV = fmaxf(dot3(N, V), 0.001f);
+        const F3 F = fresnel(NdotV, F0);
+        float sw = (F.x + F.y + F.z) / 3.0f;
+        sw = sw * (1.0f - m.metallic) + 1.0f * m.metallic;
+        F3 nd;
+        bool alive = true;
+        if (random_float(rng) < sw) {
+            const F3 Hh = sample_ggx(ux, uy, N, fmaxf(m.roughness, 0.04f));
+            nd = reflect3(rayDir, Hh);
+            alive = !(dot3(nd, N) <= 0.0f);
+            const float HdotV = fmaxf(dot3(Hh, V), 0.0f);
+            const F3 Fh = fresnel(HdotV, F0);
+            thr = thr * (Fh / fmaxf(sw, 0.001f));
+        } else {
+            nd = sample_cosine(ux, uy, N);
+            const F3 diffuse = m.albedo * (1.0f - m.metallic);
+            thr = thr * (diffuse / fmaxf(1.0f - sw, 0.001f));
+        }
+        if (alive) {
+            const float mt = max3(thr);
+            if (mt > 10.0f) thr = thr * (10.0f / mt);
+            BounceRay br;
+            br.origin = hitPos + N * 0.002f;
+            br.dir = nd;
+            br.thr = thr;
+            emit(br);
+        }
+    }
+    // ---- the sun shadow ray; it starts 0.001 off the voxel just hit: in the deepest cell of that walk's stack that holds its start voxel
     if (NdotL > 0.0f) {
         const F3 so = hitPos + N * 0.001f;
         HitRec sh;
         rays++;
-        if (!traverse<kStats>(W, stk, so.x, so.y, so.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps, true)) {
-            const F3 diffuse = m.albedo * (1.0f - m.metallic);
-            radiance = radiance + thr * diffuse * sunRad * NdotL * BLOKB_INV_PI;
-            if (m.roughness < 0.9f) {
-                const F3 Hh = normalize3(sunDir - rayDir);
-                const float NdotH = fmaxf(dot3(N, Hh), 0.0f), VdotH = fmaxf(dot3(-rayDir, Hh), 0.0f);
-                const float a = m.roughness * m.roughness, a2 = a * a;
-                const float denom = NdotH * NdotH * (a2 - 1.0f) + 1.0f;
-                const float D = a2 / (BLOKB_PI * denom * denom);
-                const F3 F0 = mix3(f3(0.04f), m.albedo, m.metallic);
-                const F3 F = fresnel(VdotH, F0);
-                radiance = radiance + thr * F * D * 0.25f * sunRad * NdotL;
-            }
+        if (!traverse<kStats>(W, stk, so.x, so.y, so.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps, true, &resume)) {
+            radiance = radiance + direct;
+            if (haveSpec) radiance = radiance + spec;
         }
     }
-    // no Russian roulette on iteration 0 (:329: bounce > 0)
-    const float ux = random_float(rng);
-    const float uy = random_float(rng);
-    const F3 F0 = mix3(f3(0.04f), m.albedo, m.metallic);
-    const F3 V = -rayDir;
-    const float NdotV = fmaxf(dot3(N, V), 0.001f);
-    const F3 F = fresnel(NdotV, F0);
-    float sw = (F.x + F.y + F.z) / 3.0f;
-    sw = sw * (1.0f - m.metallic) + 1.0f * m.metallic;
-    F3 nd;
-    if (random_float(rng) < sw) {
-        const F3 Hh = sample_ggx(ux, uy, N, fmaxf(m.roughness, 0.04f));
-        nd = reflect3(rayDir, Hh);
-        if (dot3(nd, N) <= 0.0f) return false;
-        const float HdotV = fmaxf(dot3(Hh, V), 0.0f);
-        const F3 Fh = fresnel(HdotV, F0);
-        thr = thr * (Fh / fmaxf(sw, 0.001f));
-    } else {
-        nd = sample_cosine(ux, uy, N);
-        const F3 diffuse = m.albedo * (1.0f - m.metallic);
-        thr = thr * (diffuse / fmaxf(1.0f - sw, 0.001f));
-    }
-    const float mt = max3(thr);
-    if (mt > 10.0f) thr = thr * (10.0f / mt);
-    br.origin = hitPos + N * 0.002f;
-    br.dir = nd;
-    br.thr = thr;
-    return true;
+    if (resumeOut) *resumeOut = resume;   // the fused form lets the bounce ray start from this thread's stack too
 }
 
 // Iteration bounce == 1: the term it adds to the sample's radiance (`add` = whether it adds one at all; adding is kept apart
 // from "adds zero" so that both forms perform exactly the shader's additions).
 template <bool kStats>
-BLOKB_HD F3 path_bounce(const DeviceWorld& W, const NodeStack& stk, const BounceRay& br, uint32_t& rays, uint32_t& steps, bool& add) {
+BLOKB_HD F3 path_bounce(const DeviceWorld& W, const NodeStack& stk, const BounceRay& br, uint32_t& rays, uint32_t& steps, bool& add,
+                        WalkResume* resume = nullptr) {
     HitRec h;
     rays++;
     // the bounce ray starts on geometry: start voxel located once (Walker::init, locate = true)
     const bool hit = traverse<kStats>(W, stk, br.origin.x, br.origin.y, br.origin.z, br.dir.x, br.dir.y, br.dir.z, 0.001f, 10000.0f, h, steps,
-                                      /*locate=*/true);
+                                      /*locate=*/true, resume);
     if (!hit) { add = true; return br.thr * sky_color(br.dir); }
     const Surface m = fetch_surface(W, h.material);
     add = is_emissive(m.emission);
@@ -255,9 +277,12 @@ BLOKB_HD F3 path_sample(const DeviceWorld& W, const NodeStack& stk, const FrameD
                         FirstHit* first, uint32_t& rays, uint32_t& steps) {
     F3 radiance;
     BounceRay br;
-    if (path_front<kStats>(W, stk, f, px, py, s, first, rays, steps, radiance, br)) {
+    bool alive = false;
+    WalkResume resume;
+    path_front<kStats>(W, stk, f, px, py, s, first, rays, steps, radiance, [&](const BounceRay& b) { br = b; alive = true; }, &resume);
+    if (alive) {
         bool add;
-        const F3 c = path_bounce<kStats>(W, stk, br, rays, steps, add);
+        const F3 c = path_bounce<kStats>(W, stk, br, rays, steps, add, &resume);
         if (add) radiance = radiance + c;
     }
     return radiance;

@@ -41,6 +41,26 @@ class Emu:
         steps = self.lib.emu_trace(self.h, rays.ctypes.data_as(_vp), len(rays), out.ctypes.data_as(_vp), threads, int(locate))
         return out, steps
 
+    def trace_chain(self, first, second, locate_first=False):
+        """second[i] traced right after first[i] on the same node stack (WalkResume). Returns (records of second, #resumed)."""
+        from blok_b200.api import HIT_DT
+        first, second = np.ascontiguousarray(first, np.float32), np.ascontiguousarray(second, np.float32)
+        assert first.shape == second.shape
+        out = np.empty(len(first), HIT_DT)
+        self.lib.emu_trace_chain.argtypes = [_vp, _vp, _vp, C.c_size_t, _vp, C.c_int]
+        self.lib.emu_trace_chain.restype = C.c_uint64
+        n = self.lib.emu_trace_chain(self.h, first.ctypes.data_as(_vp), second.ctypes.data_as(_vp), len(first), out.ctypes.data_as(_vp), int(locate_first))
+        return out, int(n)
+
+    def warp_vote(self, rays, num, den, locate=False):
+        """The vote-scheduled what-if loop (emu_warp_vote): 12 counters, [11] = iterations."""
+        rays = np.ascontiguousarray(rays, np.float32)
+        out = np.zeros(12, np.uint64)
+        self.lib.emu_warp_vote.argtypes = [_vp, _vp, C.c_size_t, C.c_int, C.c_int, C.c_int, _vp]
+        self.lib.emu_warp_vote.restype = None
+        self.lib.emu_warp_vote(self.h, rays.ctypes.data_as(_vp), len(rays) // 32, int(locate), int(num), int(den), out.ctypes.data_as(_vp))
+        return out
+
     def walk_profile(self, rays, locate=True):
         """Per child-cell size (row index = sh / 2: 0 voxels, 1 bricks, ...): descents, descents that needed plane tests,
         steps, climbs landing there. Returns (counts[4, kMaxLevels + 1], hits). Single-threaded."""

@@ -70,6 +70,25 @@ uint64_t emu_trace(void* p, const float* rays, size_t n, blokb_hit* out, int nTh
     });
     return total;
 }
+// Ray i of `second` traced right after ray i of `first` by the same "thread", starting from where the first walk left the node stack
+// (WalkResume) — the way the kernels trace a sun shadow / bounce ray after the camera ray. out = the second rays' records; they must
+// equal emu_trace(second) bit for bit. Returns how many second rays found a usable stack (started below the root).
+uint64_t emu_trace_chain(void* p, const float* first, const float* second, size_t n, blokb_hit* out, int locateFirst) {
+    Emu* e = (Emu*)p;
+    uint64_t resumed = 0;
+    for (size_t i = 0; i < n; i++) {
+        uint4 stackMem[kMaxLevels]; const NodeStack stk{stackMem, 1};
+        HitRec h; uint32_t steps = 0;
+        WalkResume rs;
+        const float* a = first + 8 * i; const float* b = second + 8 * i;
+        traverse<false>(e->dw, stk, a[0], a[1], a[2], a[3], a[4], a[5], a[6], a[7], h, steps, locateFirst != 0, &rs);
+        resumed += rs.level > 0;
+        const bool hit = traverse<false>(e->dw, stk, b[0], b[1], b[2], b[3], b[4], b[5], b[6], b[7], h, steps, true, &rs);
+        if (hit) out[i] = blokb_hit{h.node, h.material, h.t, h.facePrim};
+        else out[i] = blokb_hit{0xFFFFFFFFu, 0xFFFFFFFFu, -1.0f, 0xFFFFFFFFu};
+    }
+    return resumed;
+}
 // Where the walk spends its decisions (profiling aid, tools/walk_profile.py): the loop of traverse() restated around the
 // Walker's own methods, counting per child-cell size (index = sh / 2: 0 = voxels, 1 = 4^3 bricks, ...) the descents into a
 // cell of that child size, how many of them needed plane tests (select) rather than m's bits, the steps taken at that size

@@ -189,6 +189,52 @@ def test_walk_profile_counts_the_same_walk(emul, oracle):
         assert all(int(wp[2 * k]) <= int(wp[2 * k + 1]) <= 32 * int(wp[2 * k]) for k in range(5))
 
 
+def test_secondary_rays_started_from_the_previous_walks_stack(emul, oracle):
+    """WalkResume (traverse.cuh): a shadow / bounce ray traced right after the camera ray begins in the deepest cell of that walk's
+    node stack that holds its start voxel. Same records as a start at the root, bit for bit — for the rays the kernels cast (just off
+    the voxel that was hit) and for arbitrary second rays (far away, outside the grid, after a miss)."""
+    import bench
+    rng = np.random.default_rng(5)
+    xyz, m, mats = scenes.terrain(160)   # lit terrain: thousands of sun shadow rays, multi-chunk
+    terrain = (WorldSvoGpu.from_voxels(xyz, m, mats), blok_b200.Camera((80, 110, -40), 90.0, -25.0).frame(160, 96, 0, 1).to_numpy())
+    for path in (GOLD[1], GOLD[3], None):
+        if path is None:
+            w, ubo_s = terrain
+            z = {"ubo_s": ubo_s, "subs": w.globalSubChunks}
+        else:
+            z, w = _gold(path)
+        e = emul.world(w)
+        prim = oracle.primary_rays(z["ubo_s"])
+        h, t, _ = oracle.trace(to_scene(w), prim, threads=8)
+        srays, cast = bench.shadow_rays(prim, h, t)
+        # bounce-like rays off the same hits: random directions in the hemisphere of the face normal, origin 0.002 off the face
+        normals = np.array([[1, 0, 0], [-1, 0, 0], [0, 1, 0], [0, -1, 0], [0, 0, 1], [0, 0, -1]], np.float32)
+        hit = t >= 0
+        N = normals[np.where(hit, h[:, 3], 0)]
+        d = rng.normal(size=(len(prim), 3)).astype(np.float32)
+        d /= np.linalg.norm(d, axis=1, keepdims=True)
+        d = np.where(((d * N).sum(1) < 0)[:, None], -d, d).astype(np.float32)
+        o = (prim[:, 0:3] + prim[:, 3:6] * t[:, None] + N * np.float32(0.002)).astype(np.float32)
+        brays = np.concatenate([o, d, np.full((len(o), 1), 0.001, np.float32), np.full((len(o), 1), 10000, np.float32)], 1).astype(np.float32)
+        assert hit.sum() > 200 and (path is not None or cast.sum() > 2000)
+        for first, second in ((prim[cast], srays), (prim[hit], brays[hit])):
+            got, resumed = e.trace_chain(first, second)
+            want, _ = e.trace(second, locate=True)
+            assert got.tobytes() == want.tobytes()
+            assert resumed == len(first)
+        # arbitrary second rays (incl. after misses, from outside the grid, degenerate directions)
+        lo, hi = z["subs"]["worldMin"].min(0) - 20, z["subs"]["worldMax"].max(0) + 20
+        second = make_rays(rng, len(prim), lo, hi)
+        got, resumed = e.trace_chain(prim, second)
+        want, _ = e.trace(second, locate=True)
+        assert got.tobytes() == want.tobytes()
+        assert 0 < resumed < len(prim)
+        # and chains of secondary rays: the second walk's own end state feeds the next start
+        got, _ = e.trace_chain(second, second[::-1].copy(), locate_first=True)
+        want, _ = e.trace(second[::-1].copy(), locate=True)
+        assert got.tobytes() == want.tobytes()
+
+
 def test_dda_path_samples_match_oracle(emul, oracle):
     """path_sample (shade.cuh) compiled for the host uses the same libm as the oracle => radiance sums agree to fp32
     rounding of the sum; also: any split of the sample range reproduces the whole (sharding invariant)."""
