@@ -16,10 +16,13 @@ namespace blokb {
 // Register budgets of the traversal kernels of the path tracer (min resident blocks per SM -> registers per thread): measured on
 // the c4 frame with variant libraries, tools/wave_bench.py.
 #ifndef BLOKB_FRONT_MINBLOCKS
-#define BLOKB_FRONT_MINBLOCKS 1
+#define BLOKB_FRONT_MINBLOCKS 5
 #endif
 #ifndef BLOKB_PATH_MINBLOCKS
-#define BLOKB_PATH_MINBLOCKS 1
+#define BLOKB_PATH_MINBLOCKS 6
+#endif
+#ifndef BLOKB_PRIMARY_MINBLOCKS
+#define BLOKB_PRIMARY_MINBLOCKS 8
 #endif
 #ifndef BLOKB_BOUNCE_MINBLOCKS
 #define BLOKB_BOUNCE_MINBLOCKS 1
@@ -171,34 +174,39 @@ __global__ void __launch_bounds__(256) k_trace_rays_ordered(const __grid_constan
 
 // Sample-0 primary rays (raygen.rgen:193-229) -> hit records; optionally the sun shadow ray of :280-298.
 template <bool kShadow, bool kStats>
-__global__ void __launch_bounds__(kPixThreads) k_primary(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
+__global__ void __launch_bounds__(kPixThreads, BLOKB_PRIMARY_MINBLOCKS) k_primary(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
                                                  const __grid_constant__ PeerOut out, const __grid_constant__ PeerOut shadow,
                                                  unsigned long long* stats) {
     uint32_t px, py;
     if (!thread_pixel(F, px, py)) return;
     const F3 d = primary_dir(F, float(px) + 0.5f, float(py) + 0.5f);
-    HitRec h;
     uint32_t steps = 0;
     const NodeStack stk = thread_stack();
-    WalkResume resume;
-    const bool hit = traverse<kStats>(W, stk, F.camPos[0], F.camPos[1], F.camPos[2], d.x, d.y, d.z, 0.001f, 10000.0f, h, steps, /*locate=*/false,
-                                      kShadow ? &resume : nullptr);
     const size_t pi = size_t(py) * F.width + px;
-    store_hit_all(out, pi, hit, h);
-    if (kShadow) {
-        uint8_t sv = 0;  // 0 = no shadow ray cast, 1 = lit, 2 = shadowed
-        if (hit) {
-            F3 N = face_normal(h.facePrim & 7u);
-            if (dot3(N, d) > 0.0f) N = -N;
-            const F3 sunDir = sun_dir();
-            if (fmaxf(dot3(N, sunDir), 0.0f) > 0.0f) {
-                const F3 o = f3(F.camPos[0], F.camPos[1], F.camPos[2]) + d * h.t + N * 0.001f;
-                HitRec sh;
-                sv = traverse<kStats>(W, stk, o.x, o.y, o.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps, true, &resume) ? 2 : 1;
-            }
-        }
-        store8_all(shadow, pi, sv);
+    // camera ray, then (kShadow) the sun shadow ray of a lit hit: two passes around ONE inlined copy of the walk, so that the lanes
+    // re-converge between the rays (shade.cuh, path_rays); the shadow ray starts from the camera ray's node stack (WalkResume)
+    WalkResume resume;
+    F3 o = f3(F.camPos[0], F.camPos[1], F.camPos[2]), dir = d;
+    float tmax = 10000.0f;
+    uint8_t sv = 0;  // 0 = no shadow ray cast, 1 = lit, 2 = shadowed
+    int pass = 0;
+#pragma unroll 1
+    for (;;) {
+        HitRec h;
+        const bool hit = traverse<kStats>(W, stk, o.x, o.y, o.z, dir.x, dir.y, dir.z, 0.001f, tmax, h, steps, /*locate=*/pass > 0, kShadow ? &resume : nullptr);
+        if (pass == 1) { sv = hit ? 2 : 1; break; }
+        store_hit_all(out, pi, hit, h);
+        if (!kShadow || !hit) break;
+        F3 N = face_normal(h.facePrim & 7u);
+        if (dot3(N, d) > 0.0f) N = -N;
+        const F3 sunDir = sun_dir();
+        if (!(fmaxf(dot3(N, sunDir), 0.0f) > 0.0f)) break;
+        o = f3(F.camPos[0], F.camPos[1], F.camPos[2]) + d * h.t + N * 0.001f;
+        dir = sunDir;
+        tmax = 1000.0f;
+        pass = 1;
     }
+    if (kShadow) store8_all(shadow, pi, sv);
     if (kStats) atomicAdd(stats, (unsigned long long)steps);
 }
 
@@ -349,7 +357,7 @@ __global__ void __launch_bounds__(kPixThreads, BLOKB_FRONT_MINBLOCKS) k_path_fro
         uint32_t key = kDeadKey;
         B.order[slot] = uint32_t(slot);
         if (inFrame)
-            path_front<kStats>(W, stk, F, px, py, s0 + k, nullptr, rays, steps, rad, [&](const BounceRay& br) {
+            path_rays<kStats, false>(W, stk, F, px, py, s0 + k, nullptr, rays, steps, rad, [&](const BounceRay& br) {
                 // called before the sun shadow ray is traced: the bounce ray leaves the registers here
                 key = wave_key(W, K, br.origin, br.dir);
                 float4* r = B.rec + 3 * slot;
@@ -360,6 +368,7 @@ __global__ void __launch_bounds__(kPixThreads, BLOKB_FRONT_MINBLOCKS) k_path_fro
             });
         if (key == kDeadKey) B.keys[slot] = kDeadKey;
         B.front[slot] = make_float4(rad.x, rad.y, rad.z, key != kDeadKey ? 1.0f : 0.0f);
+
     }
     if (kStats) { atomicAdd(stats, (unsigned long long)steps); atomicAdd(stats + 1, (unsigned long long)rays); }
 }

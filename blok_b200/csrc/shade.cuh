@@ -135,25 +135,38 @@ BLOKB_HD Surface fetch_surface(const DeviceWorld& W, uint32_t materialId) {  // 
     return s;
 }
 
-// One sample of raygen.rgen's path loop (:188-380), cut where the wavefront formulation cuts it (kernels.cu, k_path_front /
-// k_bounce): path_front() is everything up to and including the choice of the bounce ray (loop iteration bounce == 0: camera
-// ray, shading, sun shadow ray, lobe sampling), path_bounce() is iteration bounce == 1, of which only two statements can
-// still change the radiance — the sky term of a miss (:231-235) and the emission of an emissive hit (:265-277); the
-// Russian roulette, lobe choice and next origin computed after them (:329-376) feed an iteration that never runs
-// (bounce < 2) and a generator that is re-seeded per sample (:92-99). path_sample() = front, then bounce: the fused form.
-// Every expression is the shader's, in the shader's order, so both forms add the same fp32 values in the same order.
+// One sample of raygen.rgen's path loop (:188-380) as a loop over the RAYS of the sample — camera ray, sun shadow ray, bounce ray —
+// around ONE inlined copy of the walk. The shape is deliberate: with a copy of traverse() per ray kind the compiler finds no
+// re-convergence point between them, lanes that skip a ray run ahead into the next copy, and the warp then executes every copy
+// once per group of lanes (measured on the c4 frame: 7.1 threads per instruction and 1.7x the time of this form).
+// Every expression is the shader's, in the shader's order, so every form adds the same fp32 values in the same order:
+//   * iteration bounce == 0: camera ray (:217-235), emission (:265-277), direct light (:280-326), lobe sampling (:337-376). The
+//     lobe sampling does not depend on the shadow verdict and draws from the generator after nothing the shadow ray touches, so it
+//     is evaluated BEFORE the shadow ray is traced and `emit(br)` hands the bounce ray out at that point (a record in k_path_front,
+//     the caller's variables in the fused form); the two direct-light terms are formed before that walk too and only ADDED after it;
+//   * iteration bounce == 1 (path_bounce / the inline third pass): only two statements can still change the radiance — the sky
+//     term of a miss (:231-235) and the emission of an emissive hit (:265-277); the Russian roulette, lobe choice and next origin
+//     after them (:329-376) feed an iteration that never runs (bounce < 2) and a generator that is re-seeded per sample (:92-99).
+// The shadow ray starts 0.001 and the bounce ray 0.002 off the voxel the camera ray hit: both begin in the deepest cell of that
+// walk's node stack that holds their start voxel (WalkResume, traverse.cuh).
 // When `first` is non-null and the primary ray hits, *first receives the G-buffer first-hit data (:253-263).
 struct FirstHit { F3 pos, N, albedo, emission; float roughness, metallic, depth; bool had, emissive; };
 struct BounceRay { F3 origin, dir, thr; };
 
-// `emit(br)` is called once, for a path that goes on, BEFORE the sun shadow ray is traced: the lobe sampling of :337-376 does not
-// depend on the shadow verdict and consumes the generator after nothing the shadow ray touches, so it is evaluated first (same
-// expressions, same values) and the bounce ray leaves the registers — into a record (k_path_front) or into the caller's variables —
-// before the second traversal begins; the two direct-light terms are formed before that traversal too and only ADDED after it,
-// in the shader's order. Radiance gathered by iteration 0 is returned in `radiance`.
-template <bool kStats, class Emit>
-BLOKB_HD void path_front(const DeviceWorld& W, const NodeStack& stk, const FrameDev& f, uint32_t px, uint32_t py, uint32_t s,
-                         FirstHit* first, uint32_t& rays, uint32_t& steps, F3& radiance, Emit&& emit, WalkResume* resumeOut = nullptr) {
+// Iteration bounce == 1 given its hit / miss: the term it adds to the radiance (`add` = whether it adds one at all; kept apart from
+// "adds zero" so that every form performs exactly the shader's additions).
+BLOKB_HD F3 bounce_term(const DeviceWorld& W, const BounceRay& br, bool hit, uint32_t material, bool& add) {
+    if (!hit) { add = true; return br.thr * sky_color(br.dir); }
+    const Surface m = fetch_surface(W, material);
+    add = is_emissive(m.emission);
+    return br.thr * m.emission;
+}
+
+// kInlineBounce = false: iteration 0 only; `emit(br)` is called once for a path that goes on (k_path_front).
+// kInlineBounce = true: the bounce ray is traced as a third pass of the same loop (the fused kernel, k_path); emit is not used.
+template <bool kStats, bool kInlineBounce, class Emit>
+BLOKB_HD void path_rays(const DeviceWorld& W, const NodeStack& stk, const FrameDev& f, uint32_t px, uint32_t py, uint32_t s,
+                        FirstHit* first, uint32_t& rays, uint32_t& steps, F3& radiance, Emit&& emit) {
     uint32_t rng = init_rng(px, py, f.width, f.frameCount, s);
     float pcx, pcy;
     if (s == 0u) { pcx = float(px) + 0.5f; pcy = float(py) + 0.5f; }
@@ -168,121 +181,135 @@ BLOKB_HD void path_front(const DeviceWorld& W, const NodeStack& stk, const Frame
     F3 thr = f3(1.f);
     const F3 sunDir = sun_dir();
     const F3 sunRad = f3(3.0f, 2.9f, 2.7f);
-    HitRec h;
-    rays++;
-    // the camera ray enters the grid from outside: start cell found level by level (Walker::init, locate = false)
     WalkResume resume;
-    const bool hit = traverse<kStats>(W, stk, rayOrigin.x, rayOrigin.y, rayOrigin.z, rayDir.x, rayDir.y, rayDir.z, 0.001f, 10000.0f, h, steps,
-                                      /*locate=*/false, &resume);
-    if (!hit) {
-        radiance = radiance + thr * sky_color(rayDir);
-        return;
-    }
-    const Surface m = fetch_surface(W, h.material);
-    F3 N = face_normal(h.facePrim & 7u);
-    const F3 hitPos = rayOrigin + rayDir * h.t;
-    if (dot3(N, rayDir) > 0.0f) N = -N;
-    if (first && s == 0u && !first->had) {
-        first->had = true; first->pos = hitPos; first->N = N; first->albedo = m.albedo; first->emission = m.emission;
-        first->roughness = m.roughness; first->metallic = m.metallic; first->depth = h.t; first->emissive = is_emissive(m.emission);
-    }
-    if (is_emissive(m.emission)) {
-        radiance = radiance + thr * m.emission;
-        if (luminance(m.emission) > 5.0f) return;
-    }
-    const float NdotL = fmaxf(dot3(N, sunDir), 0.0f);
-    // ---- direct light (:280-326), everything but the shadow verdict
+    F3 o = rayOrigin, d = rayDir;
+    float tmax = 10000.0f;
     F3 direct = f3(0.f), spec = f3(0.f);
-    bool haveSpec = false;
-    if (NdotL > 0.0f) {
-        const F3 diffuse = m.albedo * (1.0f - m.metallic);
-        direct = thr * diffuse * sunRad * NdotL * BLOKB_INV_PI;
-        if (m.roughness < 0.9f) {
-            const F3 Hh = normalize3(sunDir - rayDir);
-            const float NdotH = fmaxf(dot3(N, Hh), 0.0f), VdotH = fmaxf(dot3(-rayDir, Hh), 0.0f);
-            const float a = m.roughness * m.roughness, a2 = a * a;
-            const float denom = NdotH * NdotH * (a2 - 1.0f) + 1.0f;
-            const float D = a2 / (BLOKB_PI * denom * denom);
-            const F3 F0 = mix3(f3(0.04f), m.albedo, m.metallic);
-            const F3 F = fresnel(VdotH, F0);
-            spec = thr * F * D * 0.25f * sunRad * NdotL;
-            haveSpec = true;
-        }
-    }
-    // ---- the bounce ray (:329-376; no Russian roulette on iteration 0)
-    {
-        const float ux = random_float(rng);
-        const float uy = random_float(rng);
-        const F3 F0 = mix3(f3(0.04f), m.albedo, m.metallic);
-        const F3 V = -rayDir;
-        const float NdotV = fmaxf(dot3(N, V), 0.001f);
-        const F3 F = fresnel(NdotV, F0);
-        float sw = (F.x + F.y + F.z) / 3.0f;
-        sw = sw * (1.0f - m.metallic) + 1.0f * m.metallic;
-        F3 nd;
-        bool alive = true;
-        if (random_float(rng) < sw) {
-            const F3 Hh = sample_ggx(ux, uy, N, fmaxf(m.roughness, 0.04f));
-            nd = reflect3(rayDir, Hh);
-            alive = !(dot3(nd, N) <= 0.0f);
-            const float HdotV = fmaxf(dot3(Hh, V), 0.0f);
-            const F3 Fh = fresnel(HdotV, F0);
-            thr = thr * (Fh / fmaxf(sw, 0.001f));
-        } else {
-            nd = sample_cosine(ux, uy, N);
-            const F3 diffuse = m.albedo * (1.0f - m.metallic);
-            thr = thr * (diffuse / fmaxf(1.0f - sw, 0.001f));
-        }
-        if (alive) {
-            const float mt = max3(thr);
-            if (mt > 10.0f) thr = thr * (10.0f / mt);
-            BounceRay br;
-            br.origin = hitPos + N * 0.002f;
-            br.dir = nd;
-            br.thr = thr;
-            emit(br);
-        }
-    }
-    // ---- the sun shadow ray; it starts 0.001 off the voxel just hit: in the deepest cell of that walk's stack that holds its start voxel
-    if (NdotL > 0.0f) {
-        const F3 so = hitPos + N * 0.001f;
-        HitRec sh;
+    bool haveSpec = false, wantShadow = false, wantBounce = false;
+    BounceRay br;
+    int pass = 0;   // 0 camera ray, 1 sun shadow ray, 2 bounce ray
+#pragma unroll 1
+    for (;;) {
+        HitRec h;
         rays++;
-        if (!traverse<kStats>(W, stk, so.x, so.y, so.z, sunDir.x, sunDir.y, sunDir.z, 0.001f, 1000.0f, sh, steps, true, &resume)) {
-            radiance = radiance + direct;
-            if (haveSpec) radiance = radiance + spec;
+        const bool hit = traverse<kStats>(W, stk, o.x, o.y, o.z, d.x, d.y, d.z, 0.001f, tmax, h, steps, /*locate=*/pass > 0, &resume);
+        if (pass == 0) {
+            if (!hit) {
+                radiance = radiance + thr * sky_color(rayDir);
+                break;
+            }
+            const Surface m = fetch_surface(W, h.material);
+            F3 N = face_normal(h.facePrim & 7u);
+            const F3 hitPos = rayOrigin + rayDir * h.t;
+            if (dot3(N, rayDir) > 0.0f) N = -N;
+            if (first && s == 0u && !first->had) {
+                first->had = true; first->pos = hitPos; first->N = N; first->albedo = m.albedo; first->emission = m.emission;
+                first->roughness = m.roughness; first->metallic = m.metallic; first->depth = h.t; first->emissive = is_emissive(m.emission);
+            }
+            if (is_emissive(m.emission)) {
+                radiance = radiance + thr * m.emission;
+                if (luminance(m.emission) > 5.0f) break;
+            }
+            const float NdotL = fmaxf(dot3(N, sunDir), 0.0f);
+            wantShadow = NdotL > 0.0f;
+            if (wantShadow) {   // direct light (:280-326), everything but the shadow verdict
+                const F3 diffuse = m.albedo * (1.0f - m.metallic);
+                direct = thr * diffuse * sunRad * NdotL * BLOKB_INV_PI;
+                if (m.roughness < 0.9f) {
+                    const F3 Hh = normalize3(sunDir - rayDir);
+                    const float NdotH = fmaxf(dot3(N, Hh), 0.0f), VdotH = fmaxf(dot3(-rayDir, Hh), 0.0f);
+                    const float a = m.roughness * m.roughness, a2 = a * a;
+                    const float denom = NdotH * NdotH * (a2 - 1.0f) + 1.0f;
+                    const float D = a2 / (BLOKB_PI * denom * denom);
+                    const F3 F0 = mix3(f3(0.04f), m.albedo, m.metallic);
+                    const F3 F = fresnel(VdotH, F0);
+                    spec = thr * F * D * 0.25f * sunRad * NdotL;
+                    haveSpec = true;
+                }
+            }
+            {   // the bounce ray (:329-376; no Russian roulette on iteration 0)
+                const float ux = random_float(rng);
+                const float uy = random_float(rng);
+                const F3 F0 = mix3(f3(0.04f), m.albedo, m.metallic);
+                const F3 V = -rayDir;
+                const float NdotV = fmaxf(dot3(N, V), 0.001f);
+                const F3 F = fresnel(NdotV, F0);
+                float sw = (F.x + F.y + F.z) / 3.0f;
+                sw = sw * (1.0f - m.metallic) + 1.0f * m.metallic;
+                F3 nd;
+                bool alive = true;
+                if (random_float(rng) < sw) {
+                    const F3 Hh = sample_ggx(ux, uy, N, fmaxf(m.roughness, 0.04f));
+                    nd = reflect3(rayDir, Hh);
+                    alive = !(dot3(nd, N) <= 0.0f);
+                    const float HdotV = fmaxf(dot3(Hh, V), 0.0f);
+                    const F3 Fh = fresnel(HdotV, F0);
+                    thr = thr * (Fh / fmaxf(sw, 0.001f));
+                } else {
+                    nd = sample_cosine(ux, uy, N);
+                    const F3 diffuse = m.albedo * (1.0f - m.metallic);
+                    thr = thr * (diffuse / fmaxf(1.0f - sw, 0.001f));
+                }
+                if (alive) {
+                    const float mt = max3(thr);
+                    if (mt > 10.0f) thr = thr * (10.0f / mt);
+                    br.origin = hitPos + N * 0.002f;
+                    br.dir = nd;
+                    br.thr = thr;
+                    if (kInlineBounce) wantBounce = true;
+                    else emit(br);
+                }
+            }
+            if (wantShadow) {
+                o = hitPos + N * 0.001f;
+                d = sunDir;
+                tmax = 1000.0f;
+                pass = 1;
+                continue;
+            }
+        } else if (pass == 1) {
+            if (!hit) {
+                radiance = radiance + direct;
+                if (haveSpec) radiance = radiance + spec;
+            }
+        } else {
+            bool add;
+            const F3 c = bounce_term(W, br, hit, h.material, add);
+            if (add) radiance = radiance + c;
+            break;
         }
+        if (!(kInlineBounce && wantBounce)) break;
+        o = br.origin;
+        d = br.dir;
+        tmax = 10000.0f;
+        pass = 2;
     }
-    if (resumeOut) *resumeOut = resume;   // the fused form lets the bounce ray start from this thread's stack too
 }
 
-// Iteration bounce == 1: the term it adds to the sample's radiance (`add` = whether it adds one at all; adding is kept apart
-// from "adds zero" so that both forms perform exactly the shader's additions).
+// Iteration bounce == 1 of a ray that was handed out by path_rays<.., false> (k_bounce: one thread per sorted bounce ray).
 template <bool kStats>
-BLOKB_HD F3 path_bounce(const DeviceWorld& W, const NodeStack& stk, const BounceRay& br, uint32_t& rays, uint32_t& steps, bool& add,
-                        WalkResume* resume = nullptr) {
+BLOKB_HD F3 path_bounce(const DeviceWorld& W, const NodeStack& stk, const BounceRay& br, uint32_t& rays, uint32_t& steps, bool& add) {
     HitRec h;
     rays++;
     // the bounce ray starts on geometry: start voxel located once (Walker::init, locate = true)
     const bool hit = traverse<kStats>(W, stk, br.origin.x, br.origin.y, br.origin.z, br.dir.x, br.dir.y, br.dir.z, 0.001f, 10000.0f, h, steps,
-                                      /*locate=*/true, resume);
-    if (!hit) { add = true; return br.thr * sky_color(br.dir); }
-    const Surface m = fetch_surface(W, h.material);
-    add = is_emissive(m.emission);
-    return br.thr * m.emission;
+                                      /*locate=*/true);
+    return bounce_term(W, br, hit, h.material, add);
 }
 
+// The fused form: all of the sample's rays by this thread. The bounce ray gets its own copy of the walk after the two-pass loop:
+// measured on the c4 frame, 16 spp at 4K: 45.1 ms this way, 54.7 ms with the bounce ray as a third pass of the loop (80 registers and
+// spills under the same occupancy), 69 ms with a copy of the walk per ray kind; the wavefront schedule does the same samples in 37 ms.
 template <bool kStats>
 BLOKB_HD F3 path_sample(const DeviceWorld& W, const NodeStack& stk, const FrameDev& f, uint32_t px, uint32_t py, uint32_t s,
                         FirstHit* first, uint32_t& rays, uint32_t& steps) {
     F3 radiance;
     BounceRay br;
     bool alive = false;
-    WalkResume resume;
-    path_front<kStats>(W, stk, f, px, py, s, first, rays, steps, radiance, [&](const BounceRay& b) { br = b; alive = true; }, &resume);
+    path_rays<kStats, false>(W, stk, f, px, py, s, first, rays, steps, radiance, [&](const BounceRay& b) { br = b; alive = true; });
     if (alive) {
         bool add;
-        const F3 c = path_bounce<kStats>(W, stk, br, rays, steps, add, &resume);
+        const F3 c = path_bounce<kStats>(W, stk, br, rays, steps, add);
         if (add) radiance = radiance + c;
     }
     return radiance;

@@ -316,7 +316,11 @@ template <bool kStats>
 BLOKB_HD bool traverse(const DeviceWorld& W, const NodeStack& stk, float ox, float oy, float oz, float dx, float dy, float dz,
                        float tmin, float tmax, HitRec& out, uint32_t& steps, bool locate = true, WalkResume* resume = nullptr) {
     Walker wk;
+#if defined(BLOKB_NO_RESUME)
+    const bool inside = wk.init(W, ox, oy, oz, dx, dy, dz, tmin, tmax, locate);   // measurement variant: every walk starts at the root
+#else
     const bool inside = wk.init(W, ox, oy, oz, dx, dy, dz, tmin, tmax, locate, &stk, resume);
+#endif
     if (resume) resume->level = 0;
     if (!inside) return false;
     bool hit = false;

@@ -18,8 +18,11 @@ L = blok_b200.load_library()
 r = blok_b200.Renderer(W, H, 0)
 r.add_voxels(*workloads.voxels(name))
 r.set_frame(workloads.camera_for(name).frame(W, H, 0, spp))
-if mode and hasattr(L, "blokb_set_path_options"):
-    r.set_path_options(mode=blok_b200.PATH_FUSED if mode == "fused" else blok_b200.PATH_WAVEFRONT)
+if mode:
+    try:
+        r.set_path_options(mode=blok_b200.PATH_FUSED if mode == "fused" else blok_b200.PATH_WAVEFRONT)
+    except blok_b200.BlokbError:
+        pass   # a build from before blokb_set_path_options: it only has the fused kernel
 r.reset_accum(); r.trace_path(0, spp); r.sync()
 ts = []
 for _ in range(iters):
