@@ -235,8 +235,10 @@ def out_bytes_per_ray(kind, rays_per_pixel=1.0):
     return 32.0 / rays_per_pixel
 
 
-def roofline_for(name, kind, rays, ms, V, A, rays_per_pixel, va_src, clocks, sms):
-    """roofline block of one workload: algorithmic bytes / live kernel time against the measured HBM peak, plus the issue-slot bound."""
+def roofline_for(name, kind, rays, ms, V, A, rays_per_pixel, va_src, clocks, sms, share=1.0):
+    """roofline block of one workload: algorithmic bytes / live kernel time against the measured HBM peak, plus the issue-slot bound.
+    share = the fraction of the frame's launch this rank executes (1 / G when one frame is tiled or sample-sharded over G GPUs): the
+    committed warp-instruction count is that of the whole frame on one GPU."""
     peak, peak_src = measured_peaks()
     B = 16.0 * V + 48.0 * A + out_bytes_per_ray(kind, rays_per_pixel)
     achieved = rays * B / (ms * 1e-3) / 1e9
@@ -254,7 +256,7 @@ def roofline_for(name, kind, rays, ms, V, A, rays_per_pixel, va_src, clocks, sms
             roof["traffic"] = t.get("total")
             roof["traffic_detail"] = t
             if t.get("warp_instructions") and (clocks or {}).get("sm_mhz") and sms:
-                ach = t["warp_instructions"] / (ms * 1e-3) / 1e9
+                ach = t["warp_instructions"] * share / (ms * 1e-3) / 1e9
                 pk = sms * 4 * clocks["sm_mhz"] * 1e6 / 1e9
                 roof["issue"] = {"achieved": ach, "peak": pk, "unit": "G warp-instr/s", "frac": ach / pk,
                                  "threads_per_instruction": t.get("threads_per_instruction")}
@@ -674,7 +676,8 @@ def extra_workload(env, name, steps, warmup, do_cpu):
             V, A, src = (cc["V"], cc["A"], "blok_b200/workload_counts.json (CPU checker counts of the same sample, committed)") if cc else (None, None, None)
         if V is not None:
             rpp = rays_total / (W * H) / (1 if kind == "path" else G)
-            out["roofline"] = roofline_for(name, kind, m["rays_rank"], m["ms_rank"], V, A, rpp, src, m["clocks"], env.sms)
+            out["roofline"] = roofline_for(name, kind, m["rays_rank"], m["ms_rank"], V, A, rpp, src, m["clocks"], env.sms,
+                                           share=(1.0 / G if kind == "path" else 1.0))
         if res is not None:
             r.set_frame(ctx["ubo"])
             if kind == "path":
@@ -868,14 +871,16 @@ def main():
         par = (f"{G} GPU(s), scene replicated, the frame's {wl['spp']} spp sharded over the ranks, accumulation buffers reduced by "
                "blokb_reduce_accum (NCCL reduce-scatter + resolve + all-gather)")
     elif tiled:
-        m = measure_tiled(env, ctx, args.steps, args.warmup)
+        # the records that cross NVLink are the 8-byte packed ones (node | face << 29, bits of t: every hit ID and the distance; material and
+        # gl_PrimitiveID are functions of the node): an all-to-all of 16-byte records is bound by NVLink ingress at 7/8 of the image per GPU
+        m = measure_tiled(env, ctx, args.steps, args.warmup, packed=True)
         m["rays_rank"] = W * H / G
         rays_total, ms = W * H, m["ms"]
         scaling = "strong"
-        par = (f"ONE frame tiled over {G} GPUs in interleaved 8-row strips, scene replicated; exchange fused into the traversal kernel: {m['exchange']}; "
-               "frame fence = 4-byte all-reduce")
+        par = (f"ONE frame tiled over {G} GPUs in interleaved 8-row strips, scene replicated; exchange fused into the traversal kernel: {m['exchange']} "
+               "of 8-byte packed hit records (blokb_hit_packed), every rank ends with the whole image; frame fence = 4-byte all-reduce")
         extras["tiled"] = {"identical_on_every_rank": m["identical"], "trace_only_ms": m["trace_only_ms"], "exchange": m["exchange"],
-                           "nvlink_ingress_bytes_per_gpu": m["nvlink_ingress_bytes_per_gpu"], "record_bytes": 16}
+                           "nvlink_ingress_bytes_per_gpu": m["nvlink_ingress_bytes_per_gpu"], "record_bytes": m["record_bytes"]}
         from blok_b200 import sharding
         r.set_strips(*sharding.strip_set(rank, G))
         e2e = e2e_pipeline(env, ctx, args.steps)
@@ -911,7 +916,8 @@ def main():
         V, A, va_src = (cc["V"], cc["A"], "blok_b200/workload_counts.json (CPU checker counts of the same sample, committed)") if cc else (None, None, None)
     if V is not None:
         rpp = rays_total / (W * H) / (G if (kind != "path" and not tiled) else 1)
-        roof = roofline_for(name, kind, m["rays_rank"], m["ms_rank"], V, A, rpp, va_src, m["clocks"], env.sms)
+        roof = roofline_for(name, kind, m["rays_rank"], m["ms_rank"], V, A, rpp, va_src, m["clocks"], env.sms,
+                            share=(1.0 / G if (tiled or kind == "path") else 1.0))
 
     line = None
     if rank == 0:
@@ -932,6 +938,12 @@ def main():
                 except Exception as ex:  # an extra must never cost the headline line
                     extras[key] = {"error": repr(ex)}
             if kind == "primary":
+                try:   # the kernel the N > 1 headline runs on each rank (8-byte packed records), whole frame on one GPU
+                    _, pk_ms, _ = env.timed(lambda: r.trace_primary(packed=True, stream=env.sp), max(10, args.steps // 2), 3)
+                    extras["packed_records"] = {"ms_per_step": pk_ms, "value": W * H / pk_ms / 1e3, "unit": "Mrays/s",
+                                                "what": "k_primary_packed: same traversal, 8-byte records (node | face << 29, t) — the form a tiled frame exchanges at N > 1"}
+                except Exception as ex:
+                    extras["packed_records"] = {"error": repr(ex)}
                 try:
                     extras["e2e_packed"] = e2e_pipeline(env, ctx, args.steps, packed=True)
                     extras["e2e_packed"]["what"] += ("; 8-B records (node | face << 29, t): material and gl_PrimitiveID are looked up on the host from "
@@ -939,12 +951,12 @@ def main():
                 except Exception as ex:
                     extras["e2e_packed"] = {"error": repr(ex)}
         if tiled:
-            def packed_leg():
-                mp = measure_tiled(env, ctx, max(10, args.steps // 2), 3, packed=True)
-                return {"what": "the same tiled frame with 8-byte packed records (node | face << 29, t) through the exchange: half the NVLink bytes",
+            def full_leg():
+                mp = measure_tiled(env, ctx, max(10, args.steps // 2), 3, packed=False)
+                return {"what": "the same tiled frame with the full 16-byte records (node, material, t, face | prim << 3) through the exchange: twice the NVLink bytes",
                         "ms_per_frame": mp["ms"], "value": W * H / mp["ms"] / 1e3, "unit": "Mrays/s", "identical_on_every_rank": mp["identical"],
                         "trace_only_ms": mp["trace_only_ms"], "exchange": mp["exchange"], "nvlink_ingress_bytes_per_gpu": mp["nvlink_ingress_bytes_per_gpu"]}
-            guarded(env, line, extras, "tiled_packed", packed_leg)
+            guarded(env, line, extras, "tiled_full_records", full_leg)
 
             def replicas_leg():
                 mr = measure_single(env, ctx, 20, 3, cam_rank=rank)
