@@ -22,7 +22,13 @@ namespace blokb {
 #define BLOKB_PATH_MINBLOCKS 6
 #endif
 #ifndef BLOKB_PRIMARY_MINBLOCKS
-#define BLOKB_PRIMARY_MINBLOCKS 8
+#define BLOKB_PRIMARY_MINBLOCKS 1    // k_primary<false>: left alone ptxas stays at 45 registers = 11 blocks per SM; any bound rounds to 40 (spills) or 48 (10 blocks)
+#endif
+#ifndef BLOKB_SHADOW_MINBLOCKS
+#define BLOKB_SHADOW_MINBLOCKS 8     // k_primary<true>
+#endif
+#ifndef BLOKB_PRIMARY_LOCATE
+#define BLOKB_PRIMARY_LOCATE 0   // measurement variant: camera rays find their start voxel like secondary rays (Walker::init, locate)
 #endif
 #ifndef BLOKB_BOUNCE_MINBLOCKS
 #define BLOKB_BOUNCE_MINBLOCKS 1
@@ -174,7 +180,7 @@ __global__ void __launch_bounds__(256) k_trace_rays_ordered(const __grid_constan
 
 // Sample-0 primary rays (raygen.rgen:193-229) -> hit records; optionally the sun shadow ray of :280-298.
 template <bool kShadow, bool kStats>
-__global__ void __launch_bounds__(kPixThreads, BLOKB_PRIMARY_MINBLOCKS) k_primary(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
+__global__ void __launch_bounds__(kPixThreads, kShadow ? BLOKB_SHADOW_MINBLOCKS : BLOKB_PRIMARY_MINBLOCKS) k_primary(const __grid_constant__ DeviceWorld W, const __grid_constant__ FrameDev F,
                                                  const __grid_constant__ PeerOut out, const __grid_constant__ PeerOut shadow,
                                                  unsigned long long* stats) {
     uint32_t px, py;
@@ -193,7 +199,7 @@ __global__ void __launch_bounds__(kPixThreads, BLOKB_PRIMARY_MINBLOCKS) k_primar
 #pragma unroll 1
     for (;;) {
         HitRec h;
-        const bool hit = traverse<kStats>(W, stk, o.x, o.y, o.z, dir.x, dir.y, dir.z, 0.001f, tmax, h, steps, /*locate=*/pass > 0, kShadow ? &resume : nullptr);
+        const bool hit = traverse<kStats>(W, stk, o.x, o.y, o.z, dir.x, dir.y, dir.z, 0.001f, tmax, h, steps, /*locate=*/BLOKB_PRIMARY_LOCATE || pass > 0, kShadow ? &resume : nullptr);
         if (pass == 1) { sv = hit ? 2 : 1; break; }
         store_hit_all(out, pi, hit, h);
         if (!kShadow || !hit) break;

@@ -19,6 +19,13 @@
 #include "hd.h"
 #include "scene.h"
 
+#ifndef BLOKB_SELECT_V2
+#define BLOKB_SELECT_V2 1
+#endif
+#ifndef BLOKB_OCC_V2
+#define BLOKB_OCC_V2 1
+#endif
+
 namespace blokb {
 
 struct HitRec {
@@ -68,8 +75,16 @@ BLOKB_HD void select_child(uint32_t& m, float& w, uint32_t& bit, int axisShift, 
     const float p1 = __fmaf_rn(sgn, fs, w1);
     const bool lo = t >= (p1 - o) * inv;
     w = lo ? p1 : w1;
+#if BLOKB_SELECT_V2
+    // child index first, then one multiply-add each for the corner and the 6-bit index (IMAD runs on the FMA pipe; the ALU pipe —
+    // compares, selects, logic — is the one this kernel saturates)
+    const uint32_t c = (hi ? 2u : 0u) + (lo ? 1u : 0u);
+    m = c * s + m;
+    bit = c * (1u << axisShift) + bit;
+#else
     if (hi) { m += 2u * s; bit += 2u << axisShift; }
     if (lo) { m += s; bit += 1u << axisShift; }
+#endif
 }
 
 // Mirrored voxel coordinate m (and float(P(m)) of its near plane) of the voxel holding parameter t on one axis:
@@ -229,11 +244,19 @@ struct Walker {
     BLOKB_HD uint32_t abit() const { return bit ^ flip; }  // actual-orientation child index: x + 4y + 16z
     BLOKB_HD bool occupied() const {
         const uint32_t ab = abit();
+#if BLOKB_OCC_V2
+        return int32_t(((ab & 32u) ? mhi : mlo) << (~ab & 31u)) < 0;   // the child's bit moved into the sign position
+#else
         return (((ab & 32u) ? mhi : mlo) >> (ab & 31u)) & 1u;
+#endif
     }
     // number of occupied children before child `ab` = its index among the node's children
     BLOKB_HD uint32_t child_rank(uint32_t ab) const {
+#if BLOKB_OCC_V2
+        const uint32_t below = 0x7FFFFFFFu >> (~ab & 31u);   // (1 << n) - 1 from the shift amount occupied() already formed
+#else
         const uint32_t below = (1u << (ab & 31u)) - 1u;
+#endif
         return (ab & 32u) ? __popc(mlo) + __popc(mhi & below) : __popc(mlo & below);
     }
 
