@@ -97,7 +97,7 @@ struct blokb_ctx {
     size_t reorderCap = 0;
     unsigned long long* dStats = nullptr;  // 2 counters when stats enabled
     // wavefront path tracing (blokb_set_path_options): slot arrays of one batch, grow-only
-    blokb_path_options pathOpt{BLOKB_PATH_WAVEFRONT, 8, 8, 6, 5};
+    blokb_path_options pathOpt{BLOKB_PATH_WAVEFRONT, 8, 8, 6, 2};
     void* dWave = nullptr;
     size_t waveCap = 0;
     uint32_t waveBatch = 0;   // batch the current scratch was sized for (<= pathOpt.batchSamples)
@@ -296,7 +296,7 @@ int blokb_upload_world(blokb_ctx* c, const blokb_svo_node* nodes, size_t nNodes,
     s.levels = hw.levels;
     s.buildMs = std::chrono::duration<float, std::milli>(t1 - t0).count();
     s.uploadMs = std::chrono::duration<float, std::milli>(t2 - t1).count();
-    c->nNodesCompact = hw.nodes.size(); c->nBlocks = hw.blockFirstLeaf.size(); c->nVoxels = hw.voxels;
+    c->nNodesCompact = hw.nodes.size(); d.nNodes = uint32_t(hw.nodes.size()); c->nBlocks = hw.blockFirstLeaf.size(); c->nVoxels = hw.voxels;
     c->haveWorld = true;
     return 0;
 }
@@ -400,7 +400,7 @@ static int finish_device_build(blokb_ctx* c, build::DeviceBuild& B, const blokb_
         CK(cudaMemcpyAsync(dn, hw.nodes.data(), hw.nodes.size() * sizeof(Node), cudaMemcpyHostToDevice, c->stream));
         if (B.nBricks) CK(cudaMemcpyAsync(static_cast<Node*>(dn) + brickStart, dBricks, B.nBricks * sizeof(Node), cudaMemcpyDeviceToDevice, c->stream));
         d.nodes = reinterpret_cast<const uint4*>(dn);
-        c->nNodesCompact = total;
+        c->nNodesCompact = total; d.nNodes = uint32_t(total);
     }
     {
         std::vector<blokb_material> m(materials, materials + nMaterials);
@@ -611,7 +611,7 @@ int blokb_world_load(blokb_ctx* c, const char* path) {
     d.levels = h.levels; d.matWide = h.matWide;
     d.nodes = static_cast<const uint4*>(dst[0]); d.blockFirstLeaf = static_cast<const uint32_t*>(dst[1]); d.voxelMat = dst[2];
     d.materials = static_cast<const float4*>(dst[3]); d.nMaterials = uint32_t(h.nMaterials);
-    c->nNodesCompact = h.nNodes; c->nBlocks = h.nBlocks; c->nVoxels = h.nVoxels;
+    c->nNodesCompact = h.nNodes; d.nNodes = uint32_t(h.nNodes); c->nBlocks = h.nBlocks; c->nVoxels = h.nVoxels;
     c->dSubs = static_cast<const blokb_subchunk*>(dst[4]); c->nSubsDev = h.nSubs;
     c->stats = h.stats;
     const auto t2 = std::chrono::steady_clock::now();
@@ -820,7 +820,7 @@ int blokb_trace_path(blokb_ctx* c, uint32_t sampleBegin, uint32_t sampleEnd, voi
     return dispatched(c, pick(c, stream));
 }
 void blokb_path_options_default(blokb_path_options* o) {
-    if (o) *o = blokb_path_options{BLOKB_PATH_WAVEFRONT, 8, 8, 6, 5};
+    if (o) *o = blokb_path_options{BLOKB_PATH_WAVEFRONT, 8, 8, 6, 2};
 }
 int blokb_set_path_options(blokb_ctx* c, const blokb_path_options* o) {
     if (!c || !o) return fail(BLOKB_E_ARG, "null argument");

@@ -51,6 +51,7 @@ struct DeviceWorld {
     const void* voxelMat;
     const float4* materials;  // 2 x float4 per MaterialGpu
     uint32_t nMaterials;
+    uint32_t nNodes;  // records in nodes[]
 };
 
 }  // namespace blokb

@@ -91,4 +91,4 @@ def test_path_options_validation(renderer_factory):
     with pytest.raises(blok_b200.BlokbError):
         r.set_path_options(dir_cells=17)
     o = r.set_path_options(mode=PATH_WAVEFRONT, batch_samples=0, dir_cells=0, origin_cell_shift=0, morton_bits_per_axis=0)
-    assert (o["batchSamples"], o["dirCells"], o["originCellShift"], o["mortonBitsPerAxis"]) == (8, 8, 6, 5)
+    assert (o["batchSamples"], o["dirCells"], o["originCellShift"], o["mortonBitsPerAxis"]) == (8, 8, 6, 2)
