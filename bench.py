@@ -503,11 +503,15 @@ def measure_tiled(env, ctx, steps, warmup, packed=False):
         sharding.connect_peers(r, (img,))
     r.set_strips(*sharding.strip_set(rank, G))
     token = torch.zeros(1, device=env.dev)
+    fence_keep = sharding.connect_fence(r) if keep is not None else None   # the library's own fence over a multicast word, else NCCL
 
     def step():
         r.trace_primary(packed=packed, stream=env.sp)
-        with torch.cuda.stream(env.stream):
-            sharding.frame_barrier(token)
+        if fence_keep is not None:
+            r.frame_fence(stream=env.sp)
+        else:
+            with torch.cuda.stream(env.stream):
+                sharding.frame_barrier(token)
 
     l0 = r.launch_count()
     ms, ms_max, clocks = env.timed(step, steps, warmup)
@@ -520,6 +524,11 @@ def measure_tiled(env, ctx, steps, warmup, packed=False):
     step()
     env.barrier()
     same = env.min(int(r.readback(img).tobytes() == full.tobytes()))
+    fence_name = "4-byte NCCL all-reduce"
+    if fence_keep is not None:
+        r.fence_status()
+        sharding.disconnect_fence(r, fence_keep)
+        fence_name = "blokb_frame_fence (multimem.red on a multicast counter + acquire spin, one thread)"
     if keep is None:
         sharding.disconnect_peers(r, (img,))
     else:
@@ -528,6 +537,7 @@ def measure_tiled(env, ctx, steps, warmup, packed=False):
     recb = 8 if packed else 16
     return dict(ms=ms_max, ms_rank=ms, launches=launches, clocks=clocks, ms_warm_l2=warm, identical=bool(same), trace_only_ms=trace_ms,
                 exchange="NVLink multicast (multimem.st into symmetric memory)" if keep is not None else "P2P stores into IPC-mapped peer images",
+                fence=fence_name,
                 nvlink_ingress_bytes_per_gpu=int(W * H * recb * (G - 1) / G), record_bytes=recb)
 
 
@@ -730,10 +740,15 @@ def extra_c5(env):
         out["exchange"] = "NVLink multicast (multimem.st)" if keep is not None else "P2P stores into IPC-mapped peer images"
     r.set_strips(*sharding.strip_set(rank, G))
     token = torch.zeros(1, device=env.dev)
+    fence_keep = sharding.connect_fence(r) if keep is not None else None
+    out["fence"] = "blokb_frame_fence" if fence_keep is not None else "4-byte NCCL all-reduce"
 
     def fence():
-        with torch.cuda.stream(env.stream):
-            sharding.frame_barrier(token)
+        if fence_keep is not None:
+            r.frame_fence(stream=env.sp)
+        else:
+            with torch.cuda.stream(env.stream):
+                sharding.frame_barrier(token)
 
     def p_primary():
         r.trace_primary(stream=env.sp)
@@ -806,6 +821,8 @@ def extra_c5(env):
         except Exception as ex:
             out["heightfield_properties"] = {"error": repr(ex)}
     env.barrier()
+    if fence_keep is not None:
+        sharding.disconnect_fence(r, fence_keep)
     if G > 1:
         if keep is None:
             sharding.disconnect_peers(r, images)
@@ -886,8 +903,8 @@ def main():
         rays_total, ms = W * H, m["ms"]
         scaling = "strong"
         par = (f"ONE frame tiled over {G} GPUs in interleaved 8-row strips, scene replicated; exchange fused into the traversal kernel: {m['exchange']} "
-               "of 8-byte packed hit records (blokb_hit_packed), every rank ends with the whole image; frame fence = 4-byte all-reduce")
-        extras["tiled"] = {"identical_on_every_rank": m["identical"], "trace_only_ms": m["trace_only_ms"], "exchange": m["exchange"],
+               f"of 8-byte packed hit records (blokb_hit_packed), every rank ends with the whole image; frame fence = {m['fence']}")
+        extras["tiled"] = {"identical_on_every_rank": m["identical"], "trace_only_ms": m["trace_only_ms"], "exchange": m["exchange"], "fence": m["fence"],
                            "nvlink_ingress_bytes_per_gpu": m["nvlink_ingress_bytes_per_gpu"], "record_bytes": m["record_bytes"]}
         from blok_b200 import sharding
         r.set_strips(*sharding.strip_set(rank, G))

@@ -138,7 +138,8 @@ EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_wo
            "blokb_pipeline_create_packed", "blokb_pipeline_submit_packed", "blokb_node_prims", "blokb_unpack_hits",
            "blokb_path_options_default", "blokb_set_path_options", "blokb_get_path_options", "blokb_trace_primary_packed",
            "blokb_comm_unique_id", "blokb_comm_init", "blokb_set_comm", "blokb_comm_rank", "blokb_reduce_accum", "blokb_reduce_slice",
-           "blokb_readback_slice", "blokb_readback_strips"]
+           "blokb_readback_slice", "blokb_readback_strips", "blokb_bind_fence", "blokb_frame_fence", "blokb_fence_status",
+           "blokb_bind_accum_for_reduce"]
 
 _lib = None
 _host = None
@@ -243,6 +244,10 @@ def load_library():
     L.blokb_reduce_slice.argtypes = [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.blokb_readback_slice.argtypes = [_vp, C.c_int, _vp, C.c_size_t]
     L.blokb_readback_strips.argtypes = [_vp, C.c_int, _vp, C.c_size_t]
+    L.blokb_bind_fence.argtypes = [_vp, _vp, _vp, C.c_uint32]
+    L.blokb_bind_accum_for_reduce.argtypes = [_vp, _vp, _vp]
+    L.blokb_frame_fence.argtypes = [_vp, _vp]
+    L.blokb_fence_status.argtypes = [_vp]
     for f in ("blokb_trace_primary", "blokb_trace_primary_shadow", "blokb_trace_primary_packed", "blokb_render", "blokb_resolve", "blokb_reset_accum"):
         getattr(L, f).argtypes = [_vp, _vp]
     L.blokb_trace_path.argtypes = [_vp, C.c_uint32, C.c_uint32, _vp]
@@ -514,10 +519,16 @@ class Renderer:
         share of ONE frame, sharding.strip_set); (0, 1) = the whole frame."""
         _ck(self.L.blokb_set_strips(self._ctx, first, stride))
 
-    def bind_image(self, image: int, local_ptr=None, multicast_ptr=None):
+    def bind_image(self, image: int, local_ptr=None, multicast_ptr=None, reduce_only=False):
         """Place IMG_HIT / IMG_SHADOW / IMG_ACCUM in caller-owned (symmetric) memory; with multicast_ptr the kernels store each
-        record once to the NVLink multicast address (sharding.connect_multicast). bind_image(image) restores the own buffer."""
-        _ck(self.L.blokb_bind_image(self._ctx, image, local_ptr or None, multicast_ptr or None))
+        record once to the NVLink multicast address (sharding.connect_multicast). bind_image(image) restores the own buffer.
+        reduce_only (IMG_ACCUM of sample-sharded frames): dispatches keep storing locally, the multicast address only serves
+        reduce_accum's in-switch sum (blokb_bind_accum_for_reduce)."""
+        if reduce_only:
+            assert image == IMG_ACCUM
+            _ck(self.L.blokb_bind_accum_for_reduce(self._ctx, local_ptr or None, multicast_ptr or None))
+        else:
+            _ck(self.L.blokb_bind_image(self._ctx, image, local_ptr or None, multicast_ptr or None))
 
     def ipc_export(self, image: int) -> bytes:
         """64-byte CUDA IPC handle of one of this context's exchangeable images (IMG_HIT, IMG_SHADOW, IMG_ACCUM)."""
@@ -583,6 +594,17 @@ class Renderer:
 
     def readback_slice_into(self, image: int, host_ptr: int, nbytes: int):
         _ck(self.L.blokb_readback_slice(self._ctx, image, host_ptr, nbytes))
+
+    def bind_fence(self, local_ptr=None, multicast_ptr=None, nranks=0):
+        """Frame fence over a multicast word pair in symmetric memory (sharding.connect_fence); nranks = 0 unbinds."""
+        _ck(self.L.blokb_bind_fence(self._ctx, local_ptr or None, multicast_ptr or None, nranks))
+
+    def frame_fence(self, stream=None):
+        """Enqueue the cross-GPU fence: completes when every rank's earlier work on its fence stream has been performed."""
+        _ck(self.L.blokb_frame_fence(self._ctx, stream))
+
+    def fence_status(self):
+        _ck(self.L.blokb_fence_status(self._ctx))
 
     def readback_strips_into(self, image: int, host_ptr: int, nbytes: int):
         """Only this context's strips (set_strips) of an image, copied to their full-frame positions in a whole-image host buffer."""

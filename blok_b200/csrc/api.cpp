@@ -77,6 +77,7 @@ struct blokb_ctx {
         void* own = nullptr;
         void* mc = nullptr;
         bool on = false;
+        bool readOnlyMc = false;   // blokb_bind_accum_for_reduce: dispatches store into the local copy only; mc serves multimem.ld_reduce
     } bound[kSlots];
     // cross-GPU reduction (blokb_set_comm / blokb_comm_init / blokb_reduce_accum)
     NcclComm comm = nullptr;
@@ -85,6 +86,10 @@ struct blokb_ctx {
     float* dSlice = nullptr;      // reduce-scatter destination: this rank's slice of the summed accumulation image
     size_t sliceCap = 0;          // pixels
     float* dFence = nullptr;      // 4-byte all-reduce operand (fence around the multimem reduction)
+    // blokb_bind_fence: counter word pair in symmetric memory, ranks of the frame, fences enqueued so far
+    uint32_t* fenceLocal = nullptr;
+    void* fenceMc = nullptr;
+    uint32_t fenceRanks = 0, fenceEpoch = 0;
     // editable worlds (blokb_upload_dense keeps the voxel list on the device; blokb_update_dense replaces dirty chunks in it)
     build::VoxelList edit;
     std::vector<blokb_material> editMaterials;
@@ -161,7 +166,7 @@ static PeerOut out_for(blokb_ctx* c, int slot, void* own) {
     PeerOut o;
     o.dst[0] = own;
     o.n = 1;
-    if (c->bound[slot].on && c->bound[slot].mc) {
+    if (c->bound[slot].on && c->bound[slot].mc && !c->bound[slot].readOnlyMc) {
         o.mc = c->bound[slot].mc;
         return o;
     }
@@ -745,6 +750,42 @@ int blokb_bind_image(blokb_ctx* c, int image, void* local, void* multicast) {
     *image_slot_ptr(c, slot) = local;
     return 0;
 }
+int blokb_bind_fence(blokb_ctx* c, void* local, void* multicast, uint32_t nranks) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    CK(cudaSetDevice(c->device));
+    if (int rc = idle(c)) return rc;
+    c->fenceLocal = nullptr; c->fenceMc = nullptr; c->fenceRanks = 0; c->fenceEpoch = 0;
+    if (nranks == 0) return 0;
+    if (!local || !multicast) return fail(BLOKB_E_ARG, "the fence needs the local and the multicast address of the same symmetric word pair");
+    if ((reinterpret_cast<uintptr_t>(local) | reinterpret_cast<uintptr_t>(multicast)) & 15u) return fail(BLOKB_E_ARG, "addresses must be 16-byte aligned");
+    c->fenceLocal = static_cast<uint32_t*>(local); c->fenceMc = multicast; c->fenceRanks = nranks;
+    return 0;
+}
+int blokb_fence_status(blokb_ctx* c) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    if (!c->fenceRanks) return fail(BLOKB_E_STATE, "no fence bound (blokb_bind_fence)");
+    CK(cudaSetDevice(c->device));
+    if (int rc = join_dispatches(c)) return rc;
+    uint32_t w[2] = {0, 0};
+    CK(cudaMemcpyAsync(w, c->fenceLocal, sizeof w, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    if (w[1]) return fail(BLOKB_E_STATE, "a frame fence timed out: not every rank arrived (counter " + std::to_string(w[0]) + ")");
+    return 0;
+}
+int blokb_frame_fence(blokb_ctx* c, void* stream) {
+    if (!c) return fail(BLOKB_E_ARG, "ctx is null");
+    if (!c->fenceRanks) return fail(BLOKB_E_STATE, "no fence bound (blokb_bind_fence)");
+    CK(cudaSetDevice(c->device));
+    c->fenceEpoch++;
+    CK(launch_fence(c->fenceLocal, c->fenceMc, c->fenceRanks * c->fenceEpoch, pick(c, stream)));
+    c->launches++;
+    return dispatched(c, pick(c, stream));
+}
+int blokb_bind_accum_for_reduce(blokb_ctx* c, void* local, void* multicast) {
+    if (int rc = blokb_bind_image(c, BLOKB_IMG_ACCUM, local, multicast)) return rc;
+    if (local) c->bound[2].readOnlyMc = true;
+    return 0;
+}
 int blokb_trace_primary(blokb_ctx* c, void* stream) {
     if (int rc = ready(c, true)) return rc;
     CK(launch_primary(c->dw, c->frame, false, out_for(c, 0, c->buf.hit), own_only(c->buf.shadow), st(c), pick(c, stream)));
@@ -1256,6 +1297,7 @@ int blokb_write_image(blokb_ctx* c, int image, const void* host, size_t bytes) {
         case BLOKB_IMG_ACCUM: dst = c->buf.accum; sz = n * 16; break;
         case BLOKB_IMG_HIT: dst = c->buf.hit; sz = n * sizeof(blokb_hit); break;
         case BLOKB_IMG_SHADOW: dst = c->buf.shadow; sz = n; break;
+        case BLOKB_IMG_HIT_PACKED: dst = c->buf.hitPacked; sz = n * sizeof(blokb_hit_packed); break;
         default: return fail(BLOKB_E_ARG, "image is not writable");
     }
     if (bytes != sz) return fail(BLOKB_E_ARG, "host buffer size mismatch: expected " + std::to_string(sz));

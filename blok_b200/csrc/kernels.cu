@@ -479,6 +479,20 @@ __global__ void __launch_bounds__(256) k_reduce_resolve_mc(const float4* __restr
     }
 }
 
+// Cross-GPU frame fence (blokb_frame_fence): one multimem.red adds this rank's arrival to the counter on every GPU at once; the
+// release makes everything this GPU did before (earlier kernels of the stream: their multicast stores) visible first; the acquire
+// loop on the LOCAL copy ends when all ranks of this round have arrived. Bounded: ~2 s of polling, then the error word is set.
+__global__ void k_fence(uint32_t* local, void* mc, uint32_t target) {
+    asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" ::"l"(mc), "r"(1u) : "memory");
+    uint32_t v = 0;
+    for (uint32_t spin = 0; spin < 20000000u; spin++) {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(local) : "memory");
+        if (int32_t(v - target) >= 0) return;
+        __nanosleep(64);
+    }
+    local[1] = 1u;
+}
+
 // ---- launchers ------------------------------------------------------------------------------------
 static inline dim3 pixel_grid(const FrameDev& F) {
     const uint32_t strips = (F.height + 7) / 8;
@@ -641,6 +655,10 @@ cudaError_t launch_reduce_resolve_mc(const void* accumMc, float* color, void* co
     if (n == 0) return cudaSuccess;
     k_reduce_resolve_mc<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(static_cast<const float4*>(accumMc), reinterpret_cast<float4*>(color),
                                                                     static_cast<float4*>(colorMc), first, n);
+    return cudaGetLastError();
+}
+cudaError_t launch_fence(uint32_t* local, void* multicast, uint32_t target, cudaStream_t st) {
+    k_fence<<<1, 1, 0, st>>>(local, multicast, target);
     return cudaGetLastError();
 }
 cudaError_t launch_resolve(const float* accum, float* color, size_t n, cudaStream_t st) {

@@ -90,11 +90,12 @@ def connect_peers(renderer, images, group=None):
     dist.barrier(group=group)
 
 
-def connect_multicast(renderer, images, group=None):
+def connect_multicast(renderer, images, group=None, reduce_only=()):
     """The fused exchange through NVLink multicast: each of `images` is re-homed in torch symmetric memory bound to a
     multicast object (Renderer.bind_image); kernels then store every record once and the NVSwitch replicates it into all
     ranks' copies. Returns the keep-alive list [(image, tensor, handle)] (pass it to disconnect_multicast), or None when
-    the platform has no multicast support — callers fall back to connect_peers."""
+    the platform has no multicast support — callers fall back to connect_peers. Images listed in reduce_only (IMG_ACCUM of a
+    sample-sharded frame) keep their dispatch stores local: the multicast address only feeds Renderer.reduce_accum."""
     import torch
     import torch.distributed as dist
     import torch.distributed._symmetric_memory as symm_mem
@@ -122,7 +123,7 @@ def connect_multicast(renderer, images, group=None):
     torch.cuda.synchronize()
     dist.barrier(group=group)
     for img, t, h in keep:
-        renderer.bind_image(img, t.data_ptr(), int(h.multicast_ptr))
+        renderer.bind_image(img, t.data_ptr(), int(h.multicast_ptr), reduce_only=img in reduce_only)
     dist.barrier(group=group)
     return keep
 
@@ -138,6 +139,40 @@ def connect_comm(renderer, group=None):
     box = [renderer.comm_unique_id() if rank == 0 else None]
     dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
     renderer.comm_init(box[0], rank, size)
+
+
+def connect_fence(renderer, group=None):
+    """The library's own frame fence (Renderer.frame_fence) instead of a collective call: a zero-filled 16-byte word pair in
+    symmetric memory bound to a multicast object, shared by the ranks of `group`. Returns the keep-alive (tensor, handle), or None
+    when the platform has no multicast support (callers keep using frame_barrier)."""
+    import torch
+    import torch.distributed as dist
+    import torch.distributed._symmetric_memory as symm_mem
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return None
+    pg = group if group is not None else dist.group.WORLD
+    name = pg.group_name if hasattr(pg, "group_name") else pg
+    t = symm_mem.empty(16, dtype=torch.uint8, device=torch.device("cuda", torch.cuda.current_device()))
+    h = symm_mem.rendezvous(t, name)
+    if not int(h.multicast_ptr):
+        return None
+    t.zero_()
+    torch.cuda.synchronize()
+    dist.barrier(group=group)
+    renderer.bind_fence(t.data_ptr(), int(h.multicast_ptr), dist.get_world_size(group))
+    dist.barrier(group=group)
+    return (t, h)
+
+
+def disconnect_fence(renderer, keep, group=None):
+    import torch
+    import torch.distributed as dist
+    torch.cuda.synchronize()
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.barrier(group=group)
+    renderer.bind_fence()
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.barrier(group=group)
 
 
 def disconnect_multicast(renderer, keep, group=None):

@@ -279,7 +279,21 @@ int blokb_set_strips(blokb_ctx* ctx, uint32_t first, uint32_t stride);
 /* Exchangeable images: BLOKB_IMG_HIT, _SHADOW, _ACCUM, _HIT_PACKED (stores of the dispatches) and _COLOR (the resolved slices of
  * blokb_reduce_accum). */
 int blokb_bind_image(blokb_ctx* ctx, int image, void* local, void* multicast);
+/* The accumulation image in symmetric memory for SAMPLE-sharded frames: every rank accumulates all pixels, so dispatches keep storing
+ * into the LOCAL copy only, and the multicast address serves blokb_reduce_accum's multimem.ld_reduce (with blokb_bind_image the stores
+ * of a dispatch would be replicated into every rank's copy — right for a tiled frame whose pixels have one owner, wrong here). */
+int blokb_bind_accum_for_reduce(blokb_ctx* ctx, void* local, void* multicast);
 int blokb_ipc_export(blokb_ctx* ctx, int image, void* handle64);
+/* Frame fence of a tiled frame without a collective library: `local` / `multicast` name a 16-byte, zero-filled word pair in symmetric
+ * memory bound to an NVLink multicast object (like the images above), shared by the `nranks` contexts of the frame. blokb_frame_fence
+ * enqueues a one-thread kernel that adds 1 to the word on EVERY GPU with one multimem.red.release and then waits (ld.acquire, bounded)
+ * until its own copy has counted all ranks of this round: when it completes on a rank, every rank's earlier work on its fence stream
+ * — the multicast stores of its traversal kernel — has been performed. Every rank must enqueue the same number of fences. A fence that
+ * times out (a rank missing for ~2 s) sets the second word to 1 and the next blokb_frame_fence / blokb_fence_status returns
+ * BLOKB_E_STATE. nranks == 0 unbinds. */
+int blokb_bind_fence(blokb_ctx* ctx, void* local, void* multicast, uint32_t nranks);
+int blokb_frame_fence(blokb_ctx* ctx, void* stream);
+int blokb_fence_status(blokb_ctx* ctx);
 int blokb_set_peers(blokb_ctx* ctx, int image, const void* handles, uint32_t n, uint32_t self);
 
 /* Cross-GPU reduction of the per-GPU accumulation buffers — the one exchange step of sample-sharded path tracing (SURVEY.md

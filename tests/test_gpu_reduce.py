@@ -94,7 +94,7 @@ def _worker(rank, world, port, out_dir):
     # accum still holds the LOCAL sums: a later trace_path keeps accumulating
     status.append(bool(np.all(r.readback(IMG_ACCUM)[..., 3] == float(s1 - s0))))
     # in-switch reduction over symmetric memory (NVLink multicast), colour broadcast by multicast stores
-    keep = sharding.connect_multicast(r, (IMG_ACCUM, IMG_COLOR))
+    keep = sharding.connect_multicast(r, (IMG_ACCUM, IMG_COLOR), reduce_only=(IMG_ACCUM,))
     mc = keep is not None
     if mc:
         shard_frame(); r.reduce_accum(REDUCE_ALL)
@@ -114,6 +114,21 @@ def _worker(rank, world, port, out_dir):
     r.trace_primary(packed=True)
     r.sync(); dist.barrier()
     status.append(r.readback(IMG_HIT_PACKED).tobytes() == full_pk.tobytes())
+    # the library's own frame fence (multimem.red counter + acquire spin) in place of the barrier: after it, every rank's strips are here
+    fk = sharding.connect_fence(r) if keep is not None else None
+    if fk is not None:
+        import time
+        for frame in range(5):
+            r.write_image(IMG_HIT_PACKED, np.zeros((H, W), blok_b200.PACKED_DT))   # own copy cleared ...
+            r.frame_fence()                                                        # ... on every rank before anyone stores into it
+            if rank == frame % world:
+                time.sleep(0.05)                                                   # ranks out of step: the fence has to wait for the late one
+            r.trace_primary(packed=True)
+            r.frame_fence()
+            status.append(r.readback(IMG_HIT_PACKED).tobytes() == full_pk.tobytes())
+            r.frame_fence()      # nobody clears the image before everyone has read it
+        r.fence_status()
+        sharding.disconnect_fence(r, fk)
     if keep is None:
         sharding.disconnect_peers(r, (IMG_HIT_PACKED,))
     else:
