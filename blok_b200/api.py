@@ -94,7 +94,7 @@ PATH_WAVEFRONT, PATH_FUSED = 0, 1
 class PathOptions(C.Structure):
     """blokb_path_options: how render / trace_path schedule a sample's rays (wavefront with sorted bounce rays, or fused)."""
     _fields_ = [("mode", C.c_int32), ("batchSamples", C.c_uint32), ("dirCells", C.c_uint32), ("originCellShift", C.c_int32),
-                ("mortonBitsPerAxis", C.c_uint32)]
+                ("mortonBitsPerAxis", C.c_uint32), ("refillBelow", C.c_uint32)]
 
 
 class DenseChunkC(C.Structure):
@@ -610,12 +610,13 @@ class Renderer:
         """Only this context's strips (set_strips) of an image, copied to their full-frame positions in a whole-image host buffer."""
         _ck(self.L.blokb_readback_strips(self._ctx, image, host_ptr, nbytes))
 
-    def set_path_options(self, mode=None, batch_samples=None, dir_cells=None, origin_cell_shift=None, morton_bits_per_axis=None):
+    def set_path_options(self, mode=None, batch_samples=None, dir_cells=None, origin_cell_shift=None, morton_bits_per_axis=None,
+                         refill_below=None):
         """blokb_set_path_options; arguments left None keep their current value. Returns the options now in force."""
         o = PathOptions()
         _ck(self.L.blokb_get_path_options(self._ctx, C.byref(o)))
         for name, v in (("mode", mode), ("batchSamples", batch_samples), ("dirCells", dir_cells), ("originCellShift", origin_cell_shift),
-                        ("mortonBitsPerAxis", morton_bits_per_axis)):
+                        ("mortonBitsPerAxis", morton_bits_per_axis), ("refillBelow", refill_below)):
             if v is not None:
                 setattr(o, name, int(v))
         _ck(self.L.blokb_set_path_options(self._ctx, C.byref(o)))

@@ -29,6 +29,7 @@ static int fail(int code, const std::string& msg) { g_err = msg; return code; }
     } while (0)
 
 constexpr int kSlots = 5;
+constexpr uint32_t kRefillDefault = 0;  // bounce pass: lanes refilled below this many walking lanes (0 = off); measured: DESIGN.md 5
 constexpr size_t kSlicePad = 64;  // >= the largest communicator size blokb_reduce_accum slices for
 struct blokb_ctx {
     int device = 0;
@@ -102,7 +103,7 @@ struct blokb_ctx {
     size_t reorderCap = 0;
     unsigned long long* dStats = nullptr;  // 2 counters when stats enabled
     // wavefront path tracing (blokb_set_path_options): slot arrays of one batch, grow-only
-    blokb_path_options pathOpt{BLOKB_PATH_WAVEFRONT, 8, 8, 6, 2};
+    blokb_path_options pathOpt{BLOKB_PATH_WAVEFRONT, 8, 8, 6, 2, kRefillDefault};
     void* dWave = nullptr;
     size_t waveCap = 0;
     uint32_t waveBatch = 0;   // batch the current scratch was sized for (<= pathOpt.batchSamples)
@@ -841,7 +842,7 @@ int blokb_render(blokb_ctx* c, void* stream) {
     CK(launch_gbuffer(c->dw, c->frame, c->buf.worldPos, c->buf.normalRough, c->buf.albedoMetal, c->buf.motion, pick(c, stream)));
     c->launches++;
     const WaveKey K = make_wave_key(c->dw, c->pathOpt.dirCells, c->pathOpt.originCellShift, c->pathOpt.mortonBitsPerAxis);
-    CK(launch_path_wavefront(c->dw, c->frame, 0u, c->frame.sampleCount, true, own_only(c->buf.color), c->dWave, batch, K, st(c), &c->launches, pick(c, stream)));
+    CK(launch_path_wavefront(c->dw, c->frame, 0u, c->frame.sampleCount, true, own_only(c->buf.color), c->dWave, batch, K, c->pathOpt.refillBelow, st(c), &c->launches, pick(c, stream)));
     return dispatched(c, pick(c, stream));
 }
 int blokb_trace_path(blokb_ctx* c, uint32_t sampleBegin, uint32_t sampleEnd, void* stream) {
@@ -856,12 +857,12 @@ int blokb_trace_path(blokb_ctx* c, uint32_t sampleBegin, uint32_t sampleEnd, voi
     uint32_t batch = 0;
     if (int rc = wave_ready(c, sampleEnd - sampleBegin, &batch)) return rc;
     const WaveKey K = make_wave_key(c->dw, c->pathOpt.dirCells, c->pathOpt.originCellShift, c->pathOpt.mortonBitsPerAxis);
-    CK(launch_path_wavefront(c->dw, c->frame, sampleBegin, sampleEnd, false, out_for(c, 2, c->buf.accum), c->dWave, batch, K, st(c), &c->launches,
+    CK(launch_path_wavefront(c->dw, c->frame, sampleBegin, sampleEnd, false, out_for(c, 2, c->buf.accum), c->dWave, batch, K, c->pathOpt.refillBelow, st(c), &c->launches,
                              pick(c, stream)));
     return dispatched(c, pick(c, stream));
 }
 void blokb_path_options_default(blokb_path_options* o) {
-    if (o) *o = blokb_path_options{BLOKB_PATH_WAVEFRONT, 8, 8, 6, 2};
+    if (o) *o = blokb_path_options{BLOKB_PATH_WAVEFRONT, 8, 8, 6, 2, kRefillDefault};
 }
 int blokb_set_path_options(blokb_ctx* c, const blokb_path_options* o) {
     if (!c || !o) return fail(BLOKB_E_ARG, "null argument");
@@ -874,6 +875,10 @@ int blokb_set_path_options(blokb_ctx* c, const blokb_path_options* o) {
     c->pathOpt.dirCells = o->dirCells ? o->dirCells : d.dirCells;
     c->pathOpt.originCellShift = o->originCellShift ? o->originCellShift : d.originCellShift;
     c->pathOpt.mortonBitsPerAxis = o->mortonBitsPerAxis ? o->mortonBitsPerAxis : d.mortonBitsPerAxis;
+    if (o->refillBelow != BLOKB_REFILL_KEEP) {
+        if (o->refillBelow > 32) return fail(BLOKB_E_ARG, "refillBelow must be 0..32");
+        c->pathOpt.refillBelow = o->refillBelow;
+    }
     return 0;
 }
 int blokb_get_path_options(blokb_ctx* c, blokb_path_options* o) {

@@ -39,14 +39,18 @@ namespace blokb {
 #ifndef BLOKB_BLOCK_ROWS
 #define BLOKB_BLOCK_ROWS 4  // pixel kernels: block = 32 x BLOKB_BLOCK_ROWS pixels (4 or 8 rows of an 8-row strip; 4 measured 0.6-0.9 % faster: DESIGN.md 5)
 #endif
-constexpr uint32_t kBlocksPerStrip = 8u / BLOKB_BLOCK_ROWS, kPixThreads = 32u * BLOKB_BLOCK_ROWS;
+#ifndef BLOKB_BLOCK_W
+#define BLOKB_BLOCK_W 32   // pixel kernels: block width in pixels (32 = four 8x4 warp tiles side by side; 16 = two, measured: DESIGN.md 5)
+#endif
+constexpr uint32_t kBlockW = BLOKB_BLOCK_W;
+constexpr uint32_t kBlocksPerStrip = 8u / BLOKB_BLOCK_ROWS, kPixThreads = kBlockW * BLOKB_BLOCK_ROWS;
 __device__ __forceinline__ bool thread_pixel(const FrameDev& F, uint32_t& px, uint32_t& py) {
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
 #ifndef BLOKB_TILE_W_LOG2
 #define BLOKB_TILE_W_LOG2 3  // warp tile = 8 x 4 pixels (measured against 4x8, 16x2 and 32x1: DESIGN.md 5)
 #endif
-    constexpr uint32_t TW = 1u << BLOKB_TILE_W_LOG2, TH = 32u / TW, tilesX = 32u / TW;
-    px = blockIdx.x * 32u + (warp % tilesX) * TW + (lane & (TW - 1u));
+    constexpr uint32_t TW = 1u << BLOKB_TILE_W_LOG2, TH = 32u / TW, tilesX = kBlockW / TW;
+    px = blockIdx.x * kBlockW + (warp % tilesX) * TW + (lane & (TW - 1u));
     py = (F.stripFirst + (blockIdx.y / kBlocksPerStrip) * F.stripStride) * 8u + (blockIdx.y % kBlocksPerStrip) * BLOKB_BLOCK_ROWS +
          (warp / tilesX) * TH + (lane >> BLOKB_TILE_W_LOG2);
     return px < F.width && py < F.height;
@@ -419,6 +423,82 @@ __global__ void __launch_bounds__(256, BLOKB_BOUNCE_MINBLOCKS) k_bounce(const __
     if (kStats) { atomicAdd(stats, (unsigned long long)steps); atomicAdd(stats + 1, (unsigned long long)rays); }
 }
 
+// k_bounce with idle lanes refilled. Sorted or not, the bounce rays of a warp end at very different times (10.1 of 32 lanes per issued
+// instruction in k_bounce: the warp lasts as long as its longest ray). Here a warp is persistent: lanes whose ray has ended wait, and
+// as soon as fewer than `refillBelow` lanes are still walking, ALL idle lanes fetch the next rays of the sorted list together (one
+// atomicAdd per warp), set up their walks together, and the warp goes on — the walk's loop is the product's while-while loop, run to
+// the next refill point instead of to the end of the longest ray. Which thread walks a ray does not change its result: same records.
+template <bool kStats>
+__global__ void __launch_bounds__(256, BLOKB_BOUNCE_MINBLOCKS) k_bounce_refill(const __grid_constant__ DeviceWorld W, const uint32_t* __restrict__ keys,
+                                                                               const uint32_t* __restrict__ order, uint32_t n, const float4* __restrict__ rec,
+                                                                               float4* __restrict__ front, unsigned* counter, uint32_t refillBelow,
+                                                                               unsigned long long* stats) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const NodeStack stk = thread_stack();
+    Walker wk;
+    BounceRay br;
+    uint32_t slot = 0, steps = 0, rays = 0;
+    bool have = false;   // this lane is in the middle of a walk
+    bool more = true;    // (warp-uniform) the list may still hold rays
+    auto settle = [&](bool hit) {   // iteration 1's term into the ray's slot (shade.cuh, bounce_term)
+        bool add;
+        const F3 t = bounce_term(W, br, hit, hit ? wk.hit_material(W) : 0u, add);
+        if (add) {
+            float4 f = front[slot];
+            f.x += t.x; f.y += t.y; f.z += t.z;
+            front[slot] = f;
+        }
+    };
+    for (;;) {
+        if (more) {
+            const unsigned idle = __ballot_sync(0xFFFFFFFFu, !have);
+            uint32_t start = 0;
+            if (lane == 0) start = atomicAdd(counter, (unsigned)__popc(idle));
+            start = __shfl_sync(0xFFFFFFFFu, start, 0);
+            const uint32_t i = start + __popc(idle & ((1u << lane) - 1u));
+            bool dry = false;
+            if (!have) {
+                if (i < n && __ldg(keys + i) != kDeadKey) {
+                    slot = __ldg(order + i);
+                    const float4 a = __ldg(rec + 3 * size_t(slot)), b = __ldg(rec + 3 * size_t(slot) + 1), c = __ldg(rec + 3 * size_t(slot) + 2);
+                    br.origin = f3(a.x, a.y, a.z); br.dir = f3(a.w, b.x, b.y); br.thr = f3(b.z, b.w, c.x);
+                    rays++;
+                    if (wk.init(W, br.origin.x, br.origin.y, br.origin.z, br.dir.x, br.dir.y, br.dir.z, 0.001f, 10000.0f, /*locate=*/true)) have = true;
+                    else settle(false);   // the ray never enters the grid
+                } else {
+                    dry = true;           // past the last ray (slots without one sort behind every ray)
+                }
+            }
+            more = !__any_sync(0xFFFFFFFFu, dry);
+        }
+        if (!__any_sync(0xFFFFFFFFu, have)) {
+            if (!more) break;
+            continue;
+        }
+        bool fin = false, hit = false;
+        for (;;) {
+            if (have && !fin) {
+                while (wk.occupied()) {
+                    if (wk.sh == 0) { hit = true; break; }
+                    wk.descend(W, stk);
+                }
+                if (hit) fin = true;
+                else {
+                    if (kStats) steps++;
+                    if (!wk.step(W, stk)) fin = true;
+                }
+            }
+            const unsigned walking = __ballot_sync(0xFFFFFFFFu, have && !fin);
+            if (walking == 0u || (more && uint32_t(__popc(walking)) < refillBelow)) break;
+        }
+        if (have && fin) {
+            settle(hit);
+            have = false;
+        }
+    }
+    if (kStats) { atomicAdd(stats, (unsigned long long)steps); atomicAdd(stats + 1, (unsigned long long)rays); }
+}
+
 // firstBatch / lastBatch: position of this batch inside one blokb_trace_path / blokb_render call (sTotal samples in all).
 template <bool kColor>
 __global__ void __launch_bounds__(kPixThreads) k_path_gather(const __grid_constant__ FrameDev F, uint32_t nS, bool firstBatch, bool lastBatch, uint32_t sTotal,
@@ -497,7 +577,7 @@ __global__ void k_fence(uint32_t* local, void* mc, uint32_t target) {
 static inline dim3 pixel_grid(const FrameDev& F) {
     const uint32_t strips = (F.height + 7) / 8;
     const uint32_t mine = F.stripFirst < strips ? (strips - F.stripFirst + F.stripStride - 1) / F.stripStride : 0;
-    return dim3((F.width + 31) / 32, mine * kBlocksPerStrip);
+    return dim3((F.width + kBlockW - 1) / kBlockW, mine * kBlocksPerStrip);
 }
 static inline size_t pix_stack_bytes(const DeviceWorld& W) { return size_t(W.levels) * kPixThreads * sizeof(uint4) + size_t(BLOKB_STAGE_TOP) * sizeof(uint4); }
 static inline size_t stack_bytes(const DeviceWorld& W) { return size_t(W.levels) * 256 * sizeof(uint4); }  // <= 48 KB (kMaxLevels = 12)
@@ -602,10 +682,11 @@ size_t wave_scratch_bytes(size_t nT, uint32_t batch) {
     size_t tb = 0;
     cub::DoubleBuffer<uint32_t> dk(nullptr, nullptr), dv(nullptr, nullptr);
     cub::DeviceRadixSort::SortPairs(nullptr, tb, dk, dv, (int64_t)n, 0, 32);
-    return al256(n * 16) + al256(n * 48) + 4 * al256(n * 4) + al256(nT * 16) + al256(tb);
+    return al256(n * 16) + al256(n * 48) + 4 * al256(n * 4) + al256(nT * 16) + 256 + al256(tb);
 }
 cudaError_t launch_path_wavefront(const DeviceWorld& W, const FrameDev& F, uint32_t sBegin, uint32_t sEnd, bool toColor, const PeerOut& accum,
-                                  void* scratch, uint32_t batch, const WaveKey& K, unsigned long long* stats, uint64_t* launches, cudaStream_t st) {
+                                  void* scratch, uint32_t batch, const WaveKey& K, uint32_t refillBelow, unsigned long long* stats, uint64_t* launches,
+                                  cudaStream_t st) {
     const dim3 g = pixel_grid(F);
     if (g.y == 0 || sEnd <= sBegin) return cudaSuccess;
     const size_t nT = size_t(g.x) * g.y * kPixThreads;
@@ -621,6 +702,7 @@ cudaError_t launch_path_wavefront(const DeviceWorld& W, const FrameDev& F, uint3
     uint32_t* i0 = reinterpret_cast<uint32_t*>(p); p += al256(cap * 4);
     uint32_t* i1 = reinterpret_cast<uint32_t*>(p); p += al256(cap * 4);
     B.partial = reinterpret_cast<float4*>(p); p += al256(nT * 16);
+    unsigned* counter = reinterpret_cast<unsigned*>(p); p += 256;
     void* tmp = p;
     B.keys = k0; B.order = i0;
     const uint32_t sTotal = sEnd - sBegin;
@@ -635,7 +717,25 @@ cudaError_t launch_path_wavefront(const DeviceWorld& W, const FrameDev& F, uint3
         cudaError_t e = cub::DeviceRadixSort::SortPairs(tmp, tb, dk, dv, (int64_t)n, 0, int(K.bits), st);
         if (e != cudaSuccess) return e;
         const unsigned blocks = (unsigned)((n + 255) / 256);
-        if (stats) k_bounce<true><<<blocks, 256, stack_bytes(W), st>>>(W, dk.Current(), dv.Current(), n, B.rec, B.front, stats);
+        if (refillBelow > 0) {
+            // persistent warps: as many blocks as stay resident, each warp pulls rays off the sorted list until it is empty
+            static int perSM[2] = {0, 0}, sms = 0;
+            if (!sms) {
+                int dev = 0;
+                cudaGetDevice(&dev);
+                cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            }
+            int& occ = perSM[stats ? 1 : 0];
+            if (!occ) {
+                if (stats) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_bounce_refill<true>, 256, stack_bytes(W));
+                else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_bounce_refill<false>, 256, stack_bytes(W));
+                if (occ < 1) occ = 1;
+            }
+            const unsigned pblocks = std::min<unsigned>(blocks, unsigned(sms * occ));
+            cudaMemsetAsync(counter, 0, sizeof(unsigned), st);
+            if (stats) k_bounce_refill<true><<<pblocks, 256, stack_bytes(W), st>>>(W, dk.Current(), dv.Current(), uint32_t(n), B.rec, B.front, counter, refillBelow, stats);
+            else k_bounce_refill<false><<<pblocks, 256, stack_bytes(W), st>>>(W, dk.Current(), dv.Current(), uint32_t(n), B.rec, B.front, counter, refillBelow, nullptr);
+        } else if (stats) k_bounce<true><<<blocks, 256, stack_bytes(W), st>>>(W, dk.Current(), dv.Current(), n, B.rec, B.front, stats);
         else k_bounce<false><<<blocks, 256, stack_bytes(W), st>>>(W, dk.Current(), dv.Current(), n, B.rec, B.front, nullptr);
         const bool first = s0 == sBegin, last = s0 + nS == sEnd;
         if (toColor) k_path_gather<true><<<g, kPixThreads, 0, st>>>(F, nS, first, last, sTotal, B, accum);

@@ -63,7 +63,8 @@ size_t wave_threads(const FrameDev& F);
 size_t wave_scratch_bytes(size_t nT, uint32_t batch);
 // samples [sBegin, sEnd) in batches of `batch`; toColor: colour = mean + firefly clamp into accum.dst[0] (blokb_render) instead of accumulating
 cudaError_t launch_path_wavefront(const DeviceWorld& W, const FrameDev& F, uint32_t sBegin, uint32_t sEnd, bool toColor, const PeerOut& accum,
-                                  void* scratch, uint32_t batch, const WaveKey& K, unsigned long long* stats, uint64_t* launches, cudaStream_t st);
+                                  void* scratch, uint32_t batch, const WaveKey& K, uint32_t refillBelow, unsigned long long* stats, uint64_t* launches,
+                                  cudaStream_t st);
 cudaError_t launch_gbuffer(const DeviceWorld& W, const FrameDev& F, float* worldPos, uint16_t* normalRough, uint8_t* albedoMetal, uint16_t* motion,
                            cudaStream_t st);
 cudaError_t launch_resolve(const float* accum, float* color, size_t n, cudaStream_t st);

@@ -347,6 +347,13 @@ struct Walker {
         return true;
     }
 
+    // Material id of the filled voxel the walk stands on (sh == 0, occupied()): all a bounce ray needs of its hit.
+    BLOKB_HD uint32_t hit_material(const DeviceWorld& W) const {
+        const uint32_t mi = base + child_rank(abit());
+        return W.matWide ? __ldg(reinterpret_cast<const uint32_t*>(W.voxelMat) + mi)
+                         : (uint32_t)__ldg(reinterpret_cast<const uint16_t*>(W.voxelMat) + mi);
+    }
+
     // The child holding the ray is a filled voxel (sh == 0, occupied(); then rs == 0 too): t is its slab entry (or
     // tmin / grid entry for the first cell). (dx, dy, dz) is the ray's direction as given (intersect.rint:138).
     BLOKB_HD void finish_hit(const DeviceWorld& W, const NodeStack& stk, float dx, float dy, float dz, HitRec& out) const {

@@ -355,7 +355,10 @@ typedef struct blokb_path_options {
     uint32_t dirCells;          /* 1..16, default 8 */
     int32_t originCellShift;    /* default 6 (64-voxel cells); raised as needed to cover the grid */
     uint32_t mortonBitsPerAxis; /* 1..6, default 2: 9 + 6 = 15 key bits = two radix passes (finer origin cells measured no faster) */
+    uint32_t refillBelow;       /* bounce pass: 0 = one sorted ray per thread; k in 1..32 = persistent warps whose idle lanes fetch the next
+                                   rays of the sorted list whenever fewer than k lanes are still walking. Default: BLOKB_REFILL_DEFAULT */
 } blokb_path_options;
+#define BLOKB_REFILL_KEEP 0xFFFFFFFFu /* in blokb_set_path_options: leave refillBelow as it is (0 is a value here, not "default") */
 void blokb_path_options_default(blokb_path_options* out);
 int blokb_set_path_options(blokb_ctx* ctx, const blokb_path_options* opt);
 int blokb_get_path_options(blokb_ctx* ctx, blokb_path_options* out);

@@ -47,6 +47,21 @@ def test_wavefront_accum_and_colour_equal_fused_bitwise(renderer_factory, name):
     for dc, sh, mb in ((1, 6, 1), (4, 4, 6), (16, 5, 5), (8, 6, 5)):
         r.set_path_options(mode=PATH_WAVEFRONT, batch_samples=4, dir_cells=dc, origin_cell_shift=sh, morton_bits_per_axis=mb)
         assert _accum(r, 0, 6).tobytes() == want_acc.tobytes(), f"accum differs with key ({dc}, {sh}, {mb})"
+    # persistent bounce warps whose idle lanes are refilled from the sorted list: which thread walks a ray does not change its result
+    for rb in (1, 7, 16, 32):
+        o = r.set_path_options(mode=PATH_WAVEFRONT, batch_samples=4, refill_below=rb)
+        assert o["refillBelow"] == rb
+        assert _accum(r, 0, 6).tobytes() == want_acc.tobytes(), f"accum differs with lanes refilled below {rb}"
+    r.stats_enable(True)
+    r.reset_accum(); r.trace_path(0, 6); r.sync()
+    refill_counts = r.stats_read()
+    r.set_path_options(refill_below=0)
+    r.stats_enable(True)   # zeroes the counters
+    r.reset_accum(); r.trace_path(0, 6); r.sync()
+    assert r.stats_read() == refill_counts   # same rays, same DDA steps
+    r.stats_enable(False)
+    with pytest.raises(blok_b200.BlokbError):
+        r.set_path_options(refill_below=33)
     # a sample range that does not start at 0, accumulated on top of an earlier call
     r.set_path_options(mode=PATH_FUSED)
     r.reset_accum(); r.trace_path(0, 2); r.trace_path(2, 5)

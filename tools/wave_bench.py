@@ -41,7 +41,7 @@ base["rays"] = rays
 rows.append(base)
 print(f"{name} {W}x{H} {spp} spp: {rays} rays ({rays / (W * H * spp):.3f} per sample)", flush=True)
 print(f"{base['label']:44s} {base['ms_min']:9.3f} ms  {rays / base['ms_min'] / 1e6:7.3f} Grays/s", flush=True)
-variants = [(b, 8, 6, 5) for b in ((8,) if quick else (2, 4, 8, 16))]
+variants = [(b, 8, 6, 2) for b in ((8,) if quick else (2, 4, 8, 16))]
 if not quick:
     variants += [(8, dc, sh, mb) for dc, sh, mb in ((4, 6, 5), (16, 6, 5), (8, 5, 5), (8, 4, 6), (8, 5, 6), (16, 5, 6), (8, 7, 4), (1, 6, 5), (8, 6, 1))]
     variants += [(16, dc, sh, mb) for dc, sh, mb in ((8, 5, 6), (16, 5, 6))]
@@ -49,10 +49,18 @@ for b, dc, sh, mb in variants:
     if b > spp:
         continue
     row, acc = timed(f"wavefront batch {b} key dir {dc}^3 cell 2^{sh} morton 3x{mb}", mode=PATH_WAVEFRONT, batch_samples=b, dir_cells=dc,
-                     origin_cell_shift=sh, morton_bits_per_axis=mb)
+                     origin_cell_shift=sh, morton_bits_per_axis=mb, refill_below=0)
     row["identical_to_fused"] = acc == want
     rows.append(row)
     print(f"{row['label']:44s} {row['ms_min']:9.3f} ms  {rays / row['ms_min'] / 1e6:7.3f} Grays/s  identical={row['identical_to_fused']}", flush=True)
+refills = (8, 16, 24) if quick else (4, 8, 12, 16, 20, 24, 28, 32)
+for rb in refills:
+    row, acc = timed(f"wavefront batch 8, bounce lanes refilled below {rb}", mode=PATH_WAVEFRONT, batch_samples=8, dir_cells=8,
+                     origin_cell_shift=6, morton_bits_per_axis=2, refill_below=rb)
+    row["identical_to_fused"] = acc == want
+    rows.append(row)
+    print(f"{row['label']:44s} {row['ms_min']:9.3f} ms  {rays / row['ms_min'] / 1e6:7.3f} Grays/s  identical={row['identical_to_fused']}", flush=True)
+r.set_path_options(refill_below=0)
 for a in sys.argv:
     if a.startswith("--json"):
         path = sys.argv[sys.argv.index(a) + 1]
