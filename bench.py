@@ -783,6 +783,15 @@ def extra_c5(env):
     out["path_1spp"] = {"ms_per_frame": ms, "rays": rays_path, "value": rays_path / ms / 1e3, "unit": "Mrays/s", "path_options": r.set_path_options(),
                         "what": "primary + sun shadow + one incoherent bounce ray per pixel; bounce rays sorted by direction cell + origin Morton code "
                                 "before they are traced (wavefront), accum strips exchanged by the kernel's stores, resolve"}
+    try:   # the same frame with the fused kernel (no reordering): its accum stores leave DURING the traversal instead of after it
+        from blok_b200 import PATH_FUSED, PATH_WAVEFRONT
+        r.set_path_options(mode=PATH_FUSED)
+        _, msf, _ = env.timed(p_path, 5, 2)
+        out["path_1spp_fused"] = {"ms_per_frame": msf, "rays": rays_path, "value": rays_path / msf / 1e3, "unit": "Mrays/s",
+                                  "what": "BLOKB_PATH_FUSED: one thread walks camera, shadow and bounce ray back to back, bounce rays in pixel order"}
+        r.set_path_options(mode=PATH_WAVEFRONT)
+    except Exception as ex:
+        out["path_1spp_fused"] = {"error": repr(ex)}
     # ---- parity at full size (rank 0 holds the whole hit image after the fenced dispatch)
     p_primary()
     env.barrier()
