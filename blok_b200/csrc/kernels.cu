@@ -561,11 +561,11 @@ __global__ void __launch_bounds__(256) k_reduce_resolve_mc(const float4* __restr
 
 // Cross-GPU frame fence (blokb_frame_fence): one multimem.red adds this rank's arrival to the counter on every GPU at once; the
 // release makes everything this GPU did before (earlier kernels of the stream: their multicast stores) visible first; the acquire
-// loop on the LOCAL copy ends when all ranks of this round have arrived. Bounded: ~2 s of polling, then the error word is set.
+// loop on the LOCAL copy ends when all ranks of this round have arrived. Bounded: ~1 s of polling, then the error word is set.
 __global__ void k_fence(uint32_t* local, void* mc, uint32_t target) {
     asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" ::"l"(mc), "r"(1u) : "memory");
     uint32_t v = 0;
-    for (uint32_t spin = 0; spin < 20000000u; spin++) {
+    for (uint32_t spin = 0; spin < 8000000u; spin++) {   // ~1 s: a poll is a system-scope load plus a 64 ns sleep
         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(local) : "memory");
         if (int32_t(v - target) >= 0) return;
         __nanosleep(64);

@@ -161,6 +161,21 @@ def connect_fence(renderer, group=None):
     dist.barrier(group=group)
     renderer.bind_fence(t.data_ptr(), int(h.multicast_ptr), dist.get_world_size(group))
     dist.barrier(group=group)
+    # prove it on this box before anyone relies on it: three rounds, then the error word; all ranks agree on the verdict
+    ok = 1
+    try:
+        for _ in range(3):
+            renderer.frame_fence()
+        renderer.fence_status()
+    except Exception:
+        ok = 0
+    flag = torch.tensor([ok], device=t.device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+    if int(flag.item()) == 0:
+        torch.cuda.synchronize()
+        renderer.bind_fence()
+        dist.barrier(group=group)
+        return None
     return (t, h)
 
 

@@ -289,7 +289,7 @@ int blokb_ipc_export(blokb_ctx* ctx, int image, void* handle64);
  * enqueues a one-thread kernel that adds 1 to the word on EVERY GPU with one multimem.red.release and then waits (ld.acquire, bounded)
  * until its own copy has counted all ranks of this round: when it completes on a rank, every rank's earlier work on its fence stream
  * — the multicast stores of its traversal kernel — has been performed. Every rank must enqueue the same number of fences. A fence that
- * times out (a rank missing for ~2 s) sets the second word to 1 and the next blokb_frame_fence / blokb_fence_status returns
+ * times out (a rank missing for ~1 s) sets the second word to 1 and the next blokb_frame_fence / blokb_fence_status returns
  * BLOKB_E_STATE. nranks == 0 unbinds. */
 int blokb_bind_fence(blokb_ctx* ctx, void* local, void* multicast, uint32_t nranks);
 int blokb_frame_fence(blokb_ctx* ctx, void* stream);
