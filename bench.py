@@ -7,9 +7,10 @@ A step = one frame of the workload (default c3: 2048^3 SVO terrain, 3840x2160 pr
   N = 1     value: rays/s with the scene and frame constants resident in HBM; CUDA events on the launching stream around every
             step, L2 flushed (256 MiB memset) between steps outside the event pairs.
   N > 1     ONE frame tiled over the N GPUs (strong scaling): rank g traces the 8-row strips g, g + N, ... and its kernel stores
-            every hit record into all ranks' images through an NVLink multicast address (P2P stores where the box has no
-            multicast); a 4-byte all-reduce on the dispatch stream is the frame fence. value = the frame's rays / max over ranks
-            of the device time. The old headline — every rank its own frame, no exchange — is extras.replicas.
+            every hit record (8-byte packed form) into all ranks' images through an NVLink multicast address (P2P stores where the
+            box has no multicast); the frame fence is the library's own (blokb_frame_fence: multimem.red counter + acquire spin), a
+            4-byte all-reduce where multicast is missing. value = the frame's rays / max over ranks of the device time. The same
+            exchange with 16-byte records is extras.tiled_full_records; every rank its own frame, no exchange, is extras.replicas.
   e2e       the same frames through the public API with HOST buffers, two frames in flight (blokb_pipeline_*): per step the
             host builds a FrameUBO, submits it, and the hit records arrive in pinned host memory (at N > 1 each rank delivers
             the strips it traced: the host receives the frame once).
