@@ -134,7 +134,7 @@ EXPORTS = ["blokb_last_error", "blokb_create", "blokb_destroy", "blokb_upload_wo
            "blokb_pipeline_destroy", "blokb_host_alloc", "blokb_host_free", "blokb_post_settings_default", "blokb_denoise",
            "blokb_postprocess", "blokb_end_frame", "blokb_reset_history", "blokb_write_image", "blokb_upload_voxels", "blokb_upload_dense", "blokb_world_export", "blokb_vox_load", "blokb_vox_parse",
            "blokb_vox_counts", "blokb_vox_xyz", "blokb_vox_material_ids", "blokb_vox_materials", "blokb_vox_free", "blokb_vox_last_error", "blokb_upload_vox", "blokb_set_strips", "blokb_ipc_export", "blokb_set_peers", "blokb_bind_image",
-           "blokb_world_save", "blokb_world_load", "blokb_update_dense", "blokb_trace_rays_reordered",
+           "blokb_world_save", "blokb_world_load", "blokb_update_dense", "blokb_trace_rays_reordered", "blokb_trace_rays_reordered_static",
            "blokb_pipeline_create_packed", "blokb_pipeline_submit_packed", "blokb_node_prims", "blokb_unpack_hits",
            "blokb_path_options_default", "blokb_set_path_options", "blokb_get_path_options", "blokb_trace_primary_packed",
            "blokb_comm_unique_id", "blokb_comm_init", "blokb_set_comm", "blokb_comm_rank", "blokb_reduce_accum", "blokb_reduce_slice",
@@ -264,6 +264,7 @@ def load_library():
     L.blokb_set_peers.argtypes = [_vp, C.c_int, _vp, C.c_uint32, C.c_uint32]
     L.blokb_trace_rays.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp, _vp]
     L.blokb_trace_rays_reordered.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp, _vp]
+    L.blokb_trace_rays_reordered_static.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp, _vp]
     L.blokb_trace_rays_host.argtypes = [_vp, _vp, C.c_size_t, C.c_int, _vp]
     L.blokb_get_buffers.argtypes = [_vp, C.POINTER(Buffers)]
     L.blokb_readback.argtypes = [_vp, C.c_int, _vp, C.c_size_t]

@@ -924,6 +924,20 @@ int blokb_trace_rays_reordered(blokb_ctx* c, const float* dRays, size_t n, int /
     c->launches += 3;  // keys, radix sort (counted as one), ordered trace
     return dispatched(c, pick(c, stream));
 }
+// blokb_trace_rays_reordered for hosts that cannot allocate (include/blokb200.h): scratch lives in a file-scope __device__ array of
+// kernels.cu, nothing is allocated or freed here — not even the per-stream event `dispatched` would create for a caller stream.
+int blokb_trace_rays_reordered_static(blokb_ctx* c, const float* dRays, size_t n, int /*anyHit*/, blokb_hit* dOut, void* stream) {
+    if (int rc = ready(c, false)) return rc;
+    if (n && (!dRays || !dOut)) return fail(BLOKB_E_ARG, "null ray / output pointer");
+    if (n == 0) return 0;
+    if (n > size_t(BLOKB_STATIC_MAX_RAYS))
+        return fail(BLOKB_E_ARG, "ray list of " + std::to_string(n) + " exceeds BLOKB_STATIC_MAX_RAYS (" + std::to_string(BLOKB_STATIC_MAX_RAYS) +
+                                     "): the static scratch holds no more; split the list or use blokb_trace_rays_reordered");
+    const cudaError_t e = launch_trace_rays_reordered_static(c->dw, dRays, n, dOut, c->device, st(c), pick(c, stream));
+    if (e != cudaSuccess) return fail(BLOKB_E_CUDA, std::string("static-scratch reordered trace: ") + cudaGetErrorString(e));
+    c->launches += 4;  // keys + histogram, scan, scatter, ordered trace
+    return 0;
+}
 int blokb_trace_rays_host(blokb_ctx* c, const float* rays, size_t n, int anyHit, blokb_hit* out) {
     if (int rc = ready(c, false)) return rc;
     if (n == 0) return 0;

@@ -7,6 +7,7 @@
 #include <cub/cub.cuh>
 
 #include <algorithm>
+#include <mutex>
 
 #include "kernels.h"
 #include "shade.cuh"
@@ -631,6 +632,108 @@ cudaError_t launch_trace_rays_reordered(const DeviceWorld& W, const float* rays,
     if (e != cudaSuccess) return e;
     if (stats) k_trace_rays_ordered<true><<<blocks, 256, stack_bytes(W), st>>>(W, reinterpret_cast<const float4*>(rays), i1, n, out, stats);
     else k_trace_rays_ordered<false><<<blocks, 256, stack_bytes(W), st>>>(W, reinterpret_cast<const float4*>(rays), i1, n, out, nullptr);
+    return cudaGetLastError();
+}
+// ---- reordered ray lists for callers that cannot allocate (blokb_trace_rays_reordered_static) --------------------------------------
+// Same contract as launch_trace_rays_reordered — every record lands in its ray's own slot, so the output bytes do not depend on the
+// order — but the scratch (bin counters, keys, order) is the file-scope array below instead of memory the context allocates, and the
+// ordering is a counting sort written here (15-bit key, 32768 bins) instead of cub's radix sort: no library call on this path at all.
+// The array exists once per GPU that loads this library and is shared by every context and every call on that GPU: calls that
+// overlap on the device race on it. It keeps the last call's contents, so the bin counters are zeroed at the start of every call.
+constexpr size_t kStaticMaxRays = size_t(BLOKB_STATIC_MAX_RAYS);
+constexpr uint32_t kStaticBins = 1u << 15;   // 8^3 direction cells x 4^3 origin cells
+constexpr size_t kStaticBinBytes = size_t(kStaticBins) * 4;
+constexpr size_t kStaticBytes = kStaticBinBytes + 2 * kStaticMaxRays * 4;   // 128 KiB + 16 MiB
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
+
+__global__ void __launch_bounds__(256) k_static_keys(const __grid_constant__ DeviceWorld W, const float4* __restrict__ rays, uint32_t n, int cellShift,
+                                                     uint32_t* __restrict__ bins, uint32_t* __restrict__ keys) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 a = __ldg(&rays[2 * size_t(i)]), b = __ldg(&rays[2 * size_t(i) + 1]);
+    const float dx = a.w, dy = b.x, dz = b.y;
+    const float inv = rsqrtf(fmaxf(dx * dx + dy * dy + dz * dz, 1e-30f));
+    auto dcell = [inv](float d) { const int q = int((d * inv + 1.0f) * 4.0f); return uint32_t(q < 0 ? 0 : (q > 7 ? 7 : q)); };
+    auto ocell = [cellShift](float o, int g, int dim) {
+        float r = o - float(g);
+        r = r < 0.0f ? 0.0f : (r > float(dim - 1) ? float(dim - 1) : r);
+        const uint32_t q = uint32_t(int(r) >> cellShift);
+        return q > 3u ? 3u : q;
+    };
+    const uint32_t key = (dcell(dx) | (dcell(dy) << 3) | (dcell(dz) << 6)) << 6 |
+                         (ocell(a.x, W.origin[0], W.dim[0]) | (ocell(a.y, W.origin[1], W.dim[1]) << 2) | (ocell(a.z, W.origin[2], W.dim[2]) << 4));
+    keys[i] = key;
+    atomicAdd(bins + key, 1u);
+}
+// counts -> exclusive prefix sums, in place; one block of 1024 threads, 32 consecutive bins each
+__global__ void __launch_bounds__(1024) k_static_scan(uint32_t* __restrict__ bins) {
+    __shared__ uint32_t warpSum[32];
+    const uint32_t t = threadIdx.x, lane = t & 31u, w = t >> 5;
+    uint32_t sum = 0;
+    for (int k = 0; k < 32; k++) sum += bins[t * 32 + k];
+    uint32_t incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= uint32_t(d)) incl += o; }
+    if (lane == 31) warpSum[w] = incl;
+    __syncthreads();
+    if (w == 0) {
+        uint32_t x = warpSum[lane];
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, x, d); if (lane >= uint32_t(d)) x += o; }
+        warpSum[lane] = x;
+    }
+    __syncthreads();
+    uint32_t run = incl - sum + (w ? warpSum[w - 1] : 0u);
+    for (int k = 0; k < 32; k++) { const uint32_t v = bins[t * 32 + k]; bins[t * 32 + k] = run; run += v; }
+}
+// order[slot of ray i inside its bin] = i. Rays of one bin land in whatever order the atomics resolve: harmless, each record goes to out[i].
+__global__ void __launch_bounds__(256) k_static_scatter(const uint32_t* __restrict__ keys, uint32_t n, uint32_t* __restrict__ bins, uint32_t* __restrict__ order) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    order[atomicAdd(bins + keys[i], 1u)] = i;
+}
+// Device address of g_static_scratch on the CURRENT device (which must be `device`). In host code the array's name is only a handle
+// for the runtime, not an address a kernel can use: the address is asked for once per device and remembered.
+static cudaError_t static_scratch_address(int device, unsigned char** out) {
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static unsigned char* known[kMaxDevices] = {};
+    if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!known[device]) {
+        int cur = -1;
+        cudaError_t e = cudaGetDevice(&cur);
+        if (e != cudaSuccess) return e;
+        if (cur != device) return cudaErrorInvalidDevice;
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        known[device] = static_cast<unsigned char*>(p);
+    }
+    *out = known[device];
+    return cudaSuccess;
+}
+cudaError_t launch_trace_rays_reordered_static(const DeviceWorld& W, const float* rays, size_t n, blokb_hit* out, int device, unsigned long long* stats,
+                                               cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    if (n > kStaticMaxRays) return cudaErrorInvalidValue;
+    unsigned char* p = nullptr;
+    cudaError_t e = static_scratch_address(device, &p);
+    if (e != cudaSuccess) return e;
+    uint32_t* bins = reinterpret_cast<uint32_t*>(p);
+    uint32_t* keys = reinterpret_cast<uint32_t*>(p + kStaticBinBytes);
+    uint32_t* order = keys + kStaticMaxRays;
+    int shift = 0;   // four origin cells per axis must cover the grid
+    while ((std::max(W.dim[0], std::max(W.dim[1], W.dim[2])) >> shift) > 4) shift++;
+    const unsigned blocks = (unsigned)((n + 255) / 256);
+    e = cudaMemsetAsync(bins, 0, kStaticBinBytes, st);   // the previous call left its running offsets here
+    if (e != cudaSuccess) return e;
+    k_static_keys<<<blocks, 256, 0, st>>>(W, reinterpret_cast<const float4*>(rays), uint32_t(n), shift, bins, keys);
+    k_static_scan<<<1, 1024, 0, st>>>(bins);
+    k_static_scatter<<<blocks, 256, 0, st>>>(keys, uint32_t(n), bins, order);
+    if (stats) k_trace_rays_ordered<true><<<blocks, 256, stack_bytes(W), st>>>(W, reinterpret_cast<const float4*>(rays), order, n, out, stats);
+    else k_trace_rays_ordered<false><<<blocks, 256, stack_bytes(W), st>>>(W, reinterpret_cast<const float4*>(rays), order, n, out, nullptr);
     return cudaGetLastError();
 }
 cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow, const PeerOut& out, const PeerOut& shadowOut,

@@ -34,6 +34,10 @@ cudaError_t launch_trace_rays(const DeviceWorld& W, const float* rays, size_t n,
 size_t reorder_scratch_bytes(size_t n, size_t* cubBytes);
 cudaError_t launch_trace_rays_reordered(const DeviceWorld& W, const float* rays, size_t n, blokb_hit* out, void* scratch, unsigned long long* stats,
                                         cudaStream_t st);
+// The same without any allocation: scratch is a file-scope __device__ array in kernels.cu (one per GPU, shared by all callers), the
+// ordering a counting sort of its own. n <= BLOKB_STATIC_MAX_RAYS; `device` must be the current device.
+cudaError_t launch_trace_rays_reordered_static(const DeviceWorld& W, const float* rays, size_t n, blokb_hit* out, int device, unsigned long long* stats,
+                                               cudaStream_t st);
 cudaError_t launch_primary(const DeviceWorld& W, const FrameDev& F, bool shadow, const PeerOut& out, const PeerOut& shadowOut, unsigned long long* stats,
                            cudaStream_t st);
 cudaError_t launch_primary_packed(const DeviceWorld& W, const FrameDev& F, const PeerOut& out, cudaStream_t st);

@@ -386,6 +386,26 @@ int blokb_trace_rays(blokb_ctx* ctx, const float* dRays, size_t n, int anyHit, b
  * is written to its ray's own slot — dOut is byte-identical to blokb_trace_rays'. Costs one key pass + one radix sort;
  * pays off when neighbouring list entries point different ways. One list per context at a time. */
 int blokb_trace_rays_reordered(blokb_ctx* ctx, const float* dRays, size_t n, int anyHit, blokb_hit* dOut, void* stream);
+/* No counterpart in the reference (it never allocates on its traversal path: the driver's ray-tracing pipeline owns all scratch).
+ * blokb_trace_rays_reordered once more, for hosts that must not allocate device memory when they call it. Two kinds of host are meant:
+ * an engine that sizes its device memory once at start-up and hands the rest of the GPU to its own pool, so that a cudaMalloc
+ * arriving later from inside this library either fails or breaks the engine's budget; and a frame loop with a latency bound, because
+ * blokb_trace_rays_reordered grows its scratch with cudaDeviceSynchronize + cudaFree + cudaMalloc whenever a list is longer than any
+ * before it, and those calls stall every stream of the process, not only this context's.
+ * This entry point calls no cudaMalloc / cudaFree and no library routine that could (the ordering is a counting sort of the library's
+ * own, not cub's radix sort; on a caller stream it does not register the stream with the context either, so blokb_sync does not wait
+ * for it — order later work on that stream yourself). Its scratch — bin counters, keys and the traversal order, 16 MiB + 128 KiB — is a
+ * fixed array inside the library's device image: every GPU that loads the library carries it from then until the process exits,
+ * whether or not this function is ever called. Hence the limit: n <= BLOKB_STATIC_MAX_RAYS, more is BLOKB_E_ARG (split the list;
+ * records are per ray, so the pieces can go one after another). dOut is byte-identical to blokb_trace_rays' and
+ * blokb_trace_rays_reordered's; only the order in which rays are walked differs (15-bit key: 8^3 direction cells above 4^3 origin cells).
+ * The array is ONE per GPU, shared by all contexts and all calls: two calls that overlap on the device (different streams, or different
+ * contexts on the same GPU) race on it and return garbage — keep them on one stream or order them with events. Nothing needs clearing
+ * by the caller: the function zeroes the counters it needs at the start of every call.
+ * The first call on each GPU looks up the array's device address (cudaGetSymbolAddress, with that GPU current; it is remembered); a
+ * failure there is BLOKB_E_CUDA. Make that first call during set-up, before any stream capture is begun. */
+#define BLOKB_STATIC_MAX_RAYS (1u << 21)
+int blokb_trace_rays_reordered_static(blokb_ctx* ctx, const float* dRays, size_t n, int anyHit, blokb_hit* dOut, void* stream);
 /* Same with HOST buffers: copies in, traces, copies out, synchronises. */
 int blokb_trace_rays_host(blokb_ctx* ctx, const float* rays, size_t n, int anyHit, blokb_hit* out);
 
