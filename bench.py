@@ -261,6 +261,12 @@ def roofline_for(name, kind, rays, ms, V, A, rays_per_pixel, va_src, clocks, sms
                 pk = sms * 4 * clocks["sm_mhz"] * 1e6 / 1e9
                 roof["issue"] = {"achieved": ach, "peak": pk, "unit": "G warp-instr/s", "frac": ach / pk,
                                  "threads_per_instruction": t.get("threads_per_instruction")}
+                if ach / pk > roof["frac"]:
+                    # the roof that actually binds: warp-instruction issue (HBM is a few % busy, profiles/). achieved / peak / frac above stay
+                    # the SURVEY 8(d) HBM-algorithmic figure the contract asks for
+                    roof["bound"] = "issue"
+                    roof["bound_note"] = ("binding roof = warp-instruction issue slots (roofline.issue); achieved / peak / frac are the HBM-algorithmic "
+                                          "figure of SURVEY.md 8(d), kept for comparison")
     return roof
 
 
@@ -524,7 +530,10 @@ def measure_tiled(env, ctx, steps, warmup, packed=False):
     _, trace_ms, _ = env.timed(trace_only, max(5, steps // 4), 2, flush=False)
     step()
     env.barrier()
-    same = env.min(int(r.readback(img).tobytes() == full.tobytes()))
+    got_img = r.readback(img)
+    same = env.min(int(got_img.tobytes() == full.tobytes()))
+    assembled = got_img.reshape(-1)[::CPU_SAMPLE_STRIDE].copy() if rank == 0 else None   # checked against the CPU checker by the caller
+    del got_img
     fence_name = "4-byte NCCL all-reduce"
     if fence_keep is not None:
         r.fence_status()
@@ -538,7 +547,7 @@ def measure_tiled(env, ctx, steps, warmup, packed=False):
     recb = 8 if packed else 16
     return dict(ms=ms_max, ms_rank=ms, launches=launches, clocks=clocks, ms_warm_l2=warm, identical=bool(same), trace_only_ms=trace_ms,
                 exchange="NVLink multicast (multimem.st into symmetric memory)" if keep is not None else "P2P stores into IPC-mapped peer images",
-                fence=fence_name,
+                fence=fence_name, assembled_sample=assembled,
                 nvlink_ingress_bytes_per_gpu=int(W * H * recb * (G - 1) / G), record_bytes=recb)
 
 
@@ -587,7 +596,34 @@ def measure_path(env, ctx, steps, warmup, e2e_steps=2):
                    "slice, blokb_readback_slice of the RGBA32F colour slice into pinned host memory"}
     step(REDUCE_ALL)
     env.barrier()
-    return dict(rays_rank=rays, rays_total=total, ms=ms_max, ms_rank=ms, launches=launches, clocks=clocks, e2e=e2e, samples=(s0, s1))
+    mc = None
+    if G > 1:
+        # the same frame with accum in symmetric memory: the sum over the GPUs happens in the NVSwitch (multimem.ld_reduce inside
+        # k_reduce_resolve_mc) and the resolved texels are broadcast by multicast stores — timed, and left in the colour image for the parity check
+        nccl_color = r.readback(IMG_COLOR).reshape(-1, 4)[::PATH_SAMPLE_STRIDE, :3].copy() if rank == 0 else None
+        try:
+            from blok_b200 import IMG_ACCUM
+            keep = sharding.connect_multicast(r, (IMG_ACCUM, IMG_COLOR), reduce_only=(IMG_ACCUM,))
+            if keep is None:
+                mc = {"unavailable": "no NVLink multicast on this box"}
+            else:
+                _, mc_ms, _ = env.timed(step, steps, warmup)
+                step(REDUCE_ALL)
+                r.sync(); env.barrier()
+                mc = {"ms_per_step": mc_ms, "value": total / (mc_ms * 1e-3) / 1e6, "unit": "Mrays/s",
+                      "what": "blokb_bind_accum_for_reduce + colour bound to a multicast address: blokb_reduce_accum = two 4-byte all-reduces around ONE "
+                              "kernel (k_reduce_resolve_mc: multimem.ld_reduce of the G accum copies, resolve, multimem.st of the colour texel)"}
+                if rank == 0:
+                    got = r.readback(IMG_COLOR).reshape(-1, 4)[::PATH_SAMPLE_STRIDE, :3].copy()
+                    mc["color_sample"] = got
+                    mc["max_abs_diff_vs_nccl_path"] = float(np.abs(got - nccl_color).max())
+                env.barrier()
+                sharding.disconnect_multicast(r, keep)
+                step(REDUCE_ALL)      # leave the NCCL-path result in the (context-owned) colour image again
+                env.barrier()
+        except Exception as ex:
+            mc = {"error": repr(ex)}
+    return dict(rays_rank=rays, rays_total=total, ms=ms_max, ms_rank=ms, launches=launches, clocks=clocks, e2e=e2e, samples=(s0, s1), mc=mc)
 
 
 def extra_device_build(env, ctx):
@@ -653,7 +689,45 @@ def extra_full_frame(env, ctx):
     return out
 
 
-def extra_workload(env, name, steps, warmup, do_cpu):
+def c2_lit_side(env, ctx):
+    """c2 once more from the sunny side. From the SURVEY 8(d) pose almost every visible face looks away from the sun, so only ~2 % of the
+    hits cast a shadow ray; this camera sits 40 degrees off the sun direction (0.5, 0.8, 0.3), where most hits do: the shadow-ray half of
+    k_primary<true> measured and checked (flags vs the checker's any-hit trace) at bench size."""
+    from blok_b200 import IMG_HIT, IMG_SHADOW, workloads
+    r, wl = ctx["renderer"], ctx["wl"]
+    W, H, N = wl["width"], wl["height"], wl["N"]
+    cam = workloads._look_at((1.59 * N, 1.105 * N, 0.258 * N), (0.5 * N, 0.5 * N, 0.5 * N), 40.0)
+    ubo = cam.frame(W, H, 0, 1)
+    r.set_frame(ubo)
+    try:
+        m = measure_single(env, dict(ctx, cam=cam, ubo=ubo), 10, 3)
+        res = run_cpu(ctx["world"], wl, cam)
+        r.trace_primary(shadow=True)
+        got = r.readback(IMG_HIT).reshape(-1)[::CPU_SAMPLE_STRIDE]
+        sh = r.readback(IMG_SHADOW).reshape(-1)[::CPU_SAMPLE_STRIDE]
+        par = hit_parity(got, res, sh)
+        hits = int(np.count_nonzero(got["node"] != 0xFFFFFFFF))
+        return {"camera": "(1.59N, 1.105N, 0.258N) -> centre, fov 40: 40 degrees off the sun direction", "ms_per_step": m["ms"],
+                "rays_per_step": m["rays_rank"], "value": m["rays_rank"] / (m["ms"] * 1e-3) / 1e6, "unit": "Mrays/s",
+                "shadow_rays_per_step": m["rays_rank"] - W * H, "hit_fraction": res["hit_fraction"],
+                "shadow_rays_per_hit_in_sample": (par.get("shadow_checked", 0) / hits) if hits else None, "parity": par}
+    finally:
+        r.set_frame(ctx["ubo"])
+
+
+def mc_block(m, res):
+    """extras block of measure_path's multicast-reduction leg; its colour sample is compared with the CPU checker when one ran."""
+    mc = m.get("mc")
+    if not mc:
+        return None
+    mc = dict(mc)
+    got = mc.pop("color_sample", None)
+    if got is not None and res is not None:
+        mc["parity"] = radiance_parity(got, res)
+    return mc
+
+
+def extra_workload(env, name, steps, warmup, do_cpu, do_check=None):
     """A secondary workload measured like the headline: value, roofline (V, A from the CPU checker on this run's sample at N = 1,
     else the committed counts) and a parity block against the checker at bench size."""
     from blok_b200 import IMG_COLOR, IMG_HIT, IMG_SHADOW
@@ -678,8 +752,11 @@ def extra_workload(env, name, steps, warmup, do_cpu):
                    "value_warm_l2": rays_total / (m["ms_warm_l2"] * 1e-3) / 1e6, "scaling": "weak (every rank renders the frame)" if G > 1 else "one GPU",
                    "gpu_launches": m["launches"], "clocks": m["clocks"]}
         res = None
-        if do_cpu:
+        if do_check is None:
+            do_check = do_cpu
+        if do_cpu or do_check:   # at N > 1 rank 0 still runs the checker — as the parity check of the exchanged / reduced result, not as a baseline
             res = run_cpu(ctx["world"], wl, ctx["cam"])
+        if do_cpu:
             V, A, src = res["V"], res["A"], f"counted by the CPU checker ({res['kind']}) on this run's sample: {res['sample']}"
             out["cpu_baseline"] = {"value": res["value"], "unit": "Mrays/s", "cores": res["cores"], "kind": res["kind"], "sample": res["sample"]}
         else:
@@ -694,29 +771,46 @@ def extra_workload(env, name, steps, warmup, do_cpu):
             if kind == "path":
                 got = r.readback(IMG_COLOR).reshape(-1, 4)[::res["stride"], :3]
                 out["parity"] = radiance_parity(got, res)
+                if G > 1:
+                    out["parity"]["what"] = f"the REDUCED image of the {G} ranks' sample shards (blokb_reduce_accum over NCCL): " + out["parity"]["what"]
             else:
                 r.trace_primary(shadow=(kind == "primary_shadow"))
                 got = r.readback(IMG_HIT).reshape(-1)[::CPU_SAMPLE_STRIDE]
                 sh = r.readback(IMG_SHADOW).reshape(-1)[::CPU_SAMPLE_STRIDE] if kind == "primary_shadow" else None
                 out["parity"] = hit_parity(got, res, sh)
                 out["hit_fraction"] = res["hit_fraction"]
+        if kind == "path" and m.get("mc"):
+            out["multicast_reduce"] = mc_block(m, res)
+        if name == "c2" and do_cpu:
+            try:
+                out["lit_side"] = c2_lit_side(env, ctx)
+            except Exception as ex:
+                out["lit_side"] = {"error": repr(ex)}
         return out
     finally:
         r.close()
 
 
-def extra_c5(env):
+def extra_c5(env, check=True):
     """BASELINE configs[4] under the bench: 8192^3 terrain (201 M voxels, built by the device builder from the voxel list), one
     7680x4320 frame tiled over the ranks with the multicast exchange — primary rays, and a 1-spp path-traced frame whose incoherent
     bounce rays go through the wavefront reordering. Parity at full size: (a) rank 0 packs the same voxel list into the reference's
     arrays (host) and the CPU checker traces every 251st pixel: hit records bit-exact; (b) the size-independent heightfield properties
     (tests/heightfield.py) on 20 000 random pixels."""
     import blok_b200
-    from blok_b200 import IMG_ACCUM, IMG_HIT, IMG_HIT_PACKED, sharding, workloads
+    from blok_b200 import IMG_ACCUM, IMG_COLOR, IMG_HIT, IMG_HIT_PACKED, sharding, workloads
     from blok_b200.api import WorldSvoGpu
     torch = env.torch
     G, rank = env.world_size, env.rank
     wl = workloads.WORKLOADS["c5"]
+
+    def colour_sample():
+        """One more fenced 1-spp frame; rank 0 keeps every 251st pixel of the resolved colour for the check against the CPU raygen."""
+        p_path()
+        fence()
+        torch.cuda.synchronize()
+        env.barrier()
+        return r.readback(IMG_COLOR).reshape(-1, 4)[::251, :3].copy() if rank == 0 else None
     W, H, N = wl["width"], wl["height"], wl["N"]
     t0 = time.perf_counter()
     xyz, mid, mats = workloads.voxels("c5")
@@ -784,12 +878,14 @@ def extra_c5(env):
     out["path_1spp"] = {"ms_per_frame": ms, "rays": rays_path, "value": rays_path / ms / 1e3, "unit": "Mrays/s", "path_options": r.set_path_options(),
                         "what": "primary + sun shadow + one incoherent bounce ray per pixel; bounce rays sorted by direction cell + origin Morton code "
                                 "before they are traced (wavefront), accum strips exchanged by the kernel's stores, resolve"}
+    path_cols = {"path_1spp": colour_sample()}
     try:   # the same frame with the fused kernel (no reordering): its accum stores leave DURING the traversal instead of after it
         from blok_b200 import PATH_FUSED, PATH_WAVEFRONT
         r.set_path_options(mode=PATH_FUSED)
         _, msf, _ = env.timed(p_path, 5, 2)
         out["path_1spp_fused"] = {"ms_per_frame": msf, "rays": rays_path, "value": rays_path / msf / 1e3, "unit": "Mrays/s",
                                   "what": "BLOKB_PATH_FUSED: one thread walks camera, shadow and bounce ray back to back, bounce rays in pixel order"}
+        path_cols["path_1spp_fused"] = colour_sample()
         r.set_path_options(mode=PATH_WAVEFRONT)
     except Exception as ex:
         out["path_1spp_fused"] = {"error": repr(ex)}
@@ -799,6 +895,8 @@ def extra_c5(env):
     if rank == 0:
         full = r.readback(IMG_HIT)
         try:
+            if not check:
+                raise InterruptedError
             from oracle import pyoracle
             lib, kind = cpu_checker()
             t0 = time.perf_counter()
@@ -811,7 +909,18 @@ def extra_c5(env):
             par = hit_parity(full.reshape(-1)[::251], res)
             par["what"] = par["what"].replace("on the cpu_baseline sample", f"on every 251st pixel of the 8K frame (reference-format arrays packed on the host in {t_pack:.0f} s)")
             out["parity"] = par
+            # the path-traced frames (three fences, the accum exchange and the resolve sit between the kernels and these pixels)
+            img = lib.render(sc, ubo.to_numpy(), 0, W * H, 251, threads=os.cpu_count() or 1, want=("color",))
+            pres = dict(color=img["color"].reshape(-1, 4)[::251, :3].copy(), cap_hits=int(img["counters"][2]), kind=kind,
+                        sample=f"every 251st pixel of the {W}x{H} frame, 1 spp full raygen")
+            del img
+            for key, col in path_cols.items():
+                if col is not None and isinstance(out.get(key), dict) and "error" not in out[key]:
+                    out[key]["parity"] = radiance_parity(col, pres)
             del world, sc
+        except InterruptedError:
+            out["parity"] = {"skipped": "packing the 8192^3 scene into the reference's arrays takes ~55 s of host time: the CPU checker runs at N = 8 only; "
+                                        "the heightfield properties below are checked at every N"}
         except Exception as ex:
             out["parity"] = {"error": repr(ex)}
         try:
@@ -845,6 +954,37 @@ def extra_c5(env):
 _REAL_STDOUT = None
 
 
+def parity_summary(extras):
+    """Every parity block of the line in ~300 bytes: {where: mismatches (hit records, exact) | passed (radiance, tolerance 2e-3)}."""
+    out = {}
+
+    def walk(prefix, d):
+        if not isinstance(d, dict):
+            return
+        p = d.get("parity")
+        if isinstance(p, dict):
+            if "error" in p:
+                out[prefix] = "error"
+            elif "skipped" in p:
+                out[prefix] = "skipped"
+            elif "mismatches" in p:
+                out[prefix] = {"mismatches": p["mismatches"], "checked": p.get("checked_rays")}
+            elif "passed" in p:
+                out[prefix] = {"passed": p["passed"], "checked": p.get("checked_pixels")}
+        for k in ("identical_on_every_rank",):
+            if k in d:
+                out[prefix + "." + k] = d[k]
+        hp = d.get("heightfield_properties")
+        if isinstance(hp, dict) and "passed" in hp:
+            out[prefix + ".heightfield"] = hp["passed"]
+        for k, v in d.items():
+            if k not in ("parity", "roofline", "e2e", "clocks", "world") and isinstance(v, dict):
+                walk(f"{prefix}.{k}" if prefix else k, v)
+    walk("headline", {"parity": extras.get("parity")})
+    walk("", {k: v for k, v in extras.items() if k != "parity"})
+    return out
+
+
 def emit(line: dict):
     """The one JSON line goes to the real stdout; everything else printed during the run (NCCL's version banner, library
     chatter) was redirected to stderr by main()."""
@@ -858,6 +998,7 @@ def guarded(env, line, extras, key, fn, seconds=240.0):
     def bail():
         if env.rank == 0:
             extras[key] = {"error": f"watchdog: no result within {seconds:.0f} s"}
+            line["parity_summary"] = parity_summary(extras)
             emit(line)
         os._exit(0)
     wd = threading.Timer(seconds, bail)
@@ -889,12 +1030,13 @@ def main():
             pr = res.get("primary", {})
             emit({"metric": "Mrays/s", "value": pr.get("value"), "unit": "Mrays/s", "n_gpus": G, "steps": 10, "warmup": 3, "ms_per_step": pr.get("ms_per_frame"),
                   "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                  "config": {"workload": "c5: " + res["workload"]}, "extras": {"c5": res}})
+                  "config": {"workload": "c5: " + res["workload"]}, "extras": {"c5": res}, "parity_summary": parity_summary({"c5": res})})
         return
     ctx = open_workload(env, name)
     wl, r = ctx["wl"], ctx["renderer"]
     W, H, kind = wl["width"], wl["height"], wl["kind"]
     do_cpu = rank == 0 and G == 1 and not args.no_cpu
+    do_check = rank == 0 and not args.no_cpu    # the CPU checker as the parity check: every N (cpu_baseline itself stays an N = 1 figure)
     extras = {"world": {k: ctx["stats"][k] for k in ("nodes", "subChunks", "voxels", "bricks", "compactBytes", "levels", "buildMs", "uploadMs")},
               "scene_gen_s": ctx["gen_s"]}
     tiled = G > 1 and kind == "primary"
@@ -908,12 +1050,16 @@ def main():
     elif tiled:
         # the records that cross NVLink are the 8-byte packed ones (node | face << 29, bits of t: every hit ID and the distance; material and
         # gl_PrimitiveID are functions of the node): an all-to-all of 16-byte records is bound by NVLink ingress at 7/8 of the image per GPU
-        m = measure_tiled(env, ctx, args.steps, args.warmup, packed=True)
+        # Same records at every N: the headline exchanges the full 16-byte blokb_hit records the N = 1 headline, the e2e figure and the CPU
+        # arm produce; the 8-byte packed exchange (half the NVLink bytes) is extras.tiled_packed_records, to be set against
+        # extras.packed_records of the N = 1 line.
+        m = measure_tiled(env, ctx, args.steps, args.warmup, packed=False)
         m["rays_rank"] = W * H / G
         rays_total, ms = W * H, m["ms"]
         scaling = "strong"
         par = (f"ONE frame tiled over {G} GPUs in interleaved 8-row strips, scene replicated; exchange fused into the traversal kernel: {m['exchange']} "
-               f"of 8-byte packed hit records (blokb_hit_packed), every rank ends with the whole image; frame fence = {m['fence']}")
+               f"of the full 16-byte hit records (blokb_hit, as at N = 1), every rank ends with the whole image; frame fence = {m['fence']}")
+        tiled_sample = m.pop("assembled_sample")
         extras["tiled"] = {"identical_on_every_rank": m["identical"], "trace_only_ms": m["trace_only_ms"], "exchange": m["exchange"], "fence": m["fence"],
                            "nvlink_ingress_bytes_per_gpu": m["nvlink_ingress_bytes_per_gpu"], "record_bytes": m["record_bytes"]}
         from blok_b200 import sharding
@@ -934,6 +1080,20 @@ def main():
 
     # ---- CPU leg (rank 0, N = 1): the checker timed on a strided sample of the same frame; doubles as the parity check
     cpu, roof = None, None
+    res = None
+    if do_check and not do_cpu:
+        # N > 1: rank 0 checks what the exchange / the reduction delivered against the CPU checker (same strided sample as at N = 1)
+        from blok_b200 import IMG_COLOR
+        res = run_cpu(ctx["world"], wl, ctx["cam"])
+        if tiled:
+            extras["tiled"]["parity"] = hit_parity(tiled_sample, res)
+            extras["tiled"]["parity"]["what"] = "the ASSEMBLED image on rank 0 (own strips + the peers' strips that arrived over NVLink): " + extras["tiled"]["parity"]["what"]
+            extras["parity"] = extras["tiled"]["parity"]
+        elif kind == "path":
+            extras["parity"] = radiance_parity(r.readback(IMG_COLOR).reshape(-1, 4)[::res["stride"], :3], res)
+            extras["parity"]["what"] = f"the REDUCED image of the {G} ranks' sample shards (blokb_reduce_accum over NCCL): " + extras["parity"]["what"]
+    if kind == "path" and m.get("mc"):
+        extras["multicast_reduce"] = mc_block(m, res if not do_cpu else None)
     if do_cpu:
         from blok_b200 import IMG_COLOR, IMG_HIT, IMG_SHADOW
         res = run_cpu(ctx["world"], wl, ctx["cam"])
@@ -986,12 +1146,16 @@ def main():
                 except Exception as ex:
                     extras["e2e_packed"] = {"error": repr(ex)}
         if tiled:
-            def full_leg():
-                mp = measure_tiled(env, ctx, max(10, args.steps // 2), 3, packed=False)
-                return {"what": "the same tiled frame with the full 16-byte records (node, material, t, face | prim << 3) through the exchange: twice the NVLink bytes",
-                        "ms_per_frame": mp["ms"], "value": W * H / mp["ms"] / 1e3, "unit": "Mrays/s", "identical_on_every_rank": mp["identical"],
-                        "trace_only_ms": mp["trace_only_ms"], "exchange": mp["exchange"], "nvlink_ingress_bytes_per_gpu": mp["nvlink_ingress_bytes_per_gpu"]}
-            guarded(env, line, extras, "tiled_full_records", full_leg)
+            def packed_leg():
+                mp = measure_tiled(env, ctx, max(10, args.steps // 2), 3, packed=True)
+                out = {"what": "the same tiled frame with 8-byte packed records (node | face << 29, t; material and gl_PrimitiveID re-derived on the host by "
+                               "blokb_unpack_hits) through the exchange: half the NVLink bytes. N = 1 denominator: extras.packed_records of the N = 1 line",
+                       "ms_per_frame": mp["ms"], "value": W * H / mp["ms"] / 1e3, "unit": "Mrays/s", "identical_on_every_rank": mp["identical"],
+                       "trace_only_ms": mp["trace_only_ms"], "exchange": mp["exchange"], "nvlink_ingress_bytes_per_gpu": mp["nvlink_ingress_bytes_per_gpu"]}
+                if rank == 0 and res is not None:
+                    out["parity"] = hit_parity(ctx["world"].unpack_hits(mp["assembled_sample"]), res)
+                return out
+            guarded(env, line, extras, "tiled_packed_records", packed_leg)
 
             def replicas_leg():
                 mr = measure_single(env, ctx, 20, 3, cam_rank=rank)
@@ -1004,12 +1168,13 @@ def main():
         for other, st, wu in (("c2", 20, 3), ("c4", 2, 1)):
             if other == name:
                 continue
-            guarded(env, line, extras, other, lambda o=other, s=st, w=wu: extra_workload(env, o, s, w, do_cpu), seconds=420.0)
-        if G == 8:
-            guarded(env, line, extras, "c5", lambda: extra_c5(env), seconds=420.0)
+            guarded(env, line, extras, other, lambda o=other, s=st, w=wu: extra_workload(env, o, s, w, do_cpu, do_check), seconds=420.0)
+        # the 8K frame at every N (a 1 -> 8 curve on a frame big enough to scale); the CPU-checker leg only at N = 8
+        guarded(env, line, extras, "c5", lambda: extra_c5(env, check=(G == 8)), seconds=420.0)
     elif ctx is not None:
         r.close()
     if rank == 0:
+        line["parity_summary"] = parity_summary(extras)   # LAST key: the driver's record keeps the tail of the line
         emit(line)
     if G > 1:
         env.dist.barrier()

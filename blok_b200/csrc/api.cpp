@@ -91,6 +91,11 @@ struct blokb_ctx {
     uint32_t* fenceLocal = nullptr;
     void* fenceMc = nullptr;
     uint32_t fenceRanks = 0, fenceEpoch = 0;
+    // dWave / dReorder are one scratch per context: a dispatch that uses one on another stream than the previous user first waits for that
+    // user's event, so path dispatches of one context on different streams serialise on the scratch instead of racing on it
+    struct ScratchGuard { cudaStream_t last = nullptr; cudaEvent_t ev = nullptr; bool used = false; } waveGuard, reorderGuard;
+    uint32_t* fenceFlagHost = nullptr;   // mapped page-locked word: set by a fence kernel that timed out, read before the next fence is enqueued
+    uint32_t* fenceFlagDev = nullptr;
     // editable worlds (blokb_upload_dense keeps the voxel list on the device; blokb_update_dense replaces dirty chunks in it)
     build::VoxelList edit;
     std::vector<blokb_material> editMaterials;
@@ -242,6 +247,8 @@ void blokb_destroy(blokb_ctx* c) {
     cudaSetDevice(c->device);
     idle(c);
     for (auto& f : c->foreign) cudaEventDestroy(f.ev);
+    if (c->waveGuard.ev) cudaEventDestroy(c->waveGuard.ev);
+    if (c->reorderGuard.ev) cudaEventDestroy(c->reorderGuard.ev);
     free_world(c);
     free_images(c);
     if (c->dRays) cudaFree(c->dRays);
@@ -251,6 +258,7 @@ void blokb_destroy(blokb_ctx* c) {
     if (c->dWave) cudaFree(c->dWave);
     if (c->dSlice) cudaFree(c->dSlice);
     if (c->dFence) cudaFree(c->dFence);
+    if (c->fenceFlagHost) cudaFreeHost(c->fenceFlagHost);
     if (c->comm && c->commOwned) { std::string err; if (const NcclApi* N = nccl_api(err)) N->CommDestroy(c->comm); }
     cudaStreamDestroy(c->stream);
     delete c;
@@ -755,10 +763,16 @@ int blokb_bind_fence(blokb_ctx* c, void* local, void* multicast, uint32_t nranks
     if (!c) return fail(BLOKB_E_ARG, "ctx is null");
     CK(cudaSetDevice(c->device));
     if (int rc = idle(c)) return rc;
-    c->fenceLocal = nullptr; c->fenceMc = nullptr; c->fenceRanks = 0; c->fenceEpoch = 0;
+    c->fenceLocal = nullptr; c->fenceMc = nullptr; c->fenceRanks = 0; c->fenceEpoch = 0;   // a new binding starts a new count (the words arrive zero-filled)
+    if (c->fenceFlagHost) *reinterpret_cast<volatile uint32_t*>(c->fenceFlagHost) = 0;
     if (nranks == 0) return 0;
     if (!local || !multicast) return fail(BLOKB_E_ARG, "the fence needs the local and the multicast address of the same symmetric word pair");
     if ((reinterpret_cast<uintptr_t>(local) | reinterpret_cast<uintptr_t>(multicast)) & 15u) return fail(BLOKB_E_ARG, "addresses must be 16-byte aligned");
+    if (!c->fenceFlagHost) {
+        CK(cudaHostAlloc((void**)&c->fenceFlagHost, 64, cudaHostAllocMapped));
+        *c->fenceFlagHost = 0;
+        CK(cudaHostGetDevicePointer((void**)&c->fenceFlagDev, c->fenceFlagHost, 0));
+    }
     c->fenceLocal = static_cast<uint32_t*>(local); c->fenceMc = multicast; c->fenceRanks = nranks;
     return 0;
 }
@@ -777,8 +791,11 @@ int blokb_frame_fence(blokb_ctx* c, void* stream) {
     if (!c) return fail(BLOKB_E_ARG, "ctx is null");
     if (!c->fenceRanks) return fail(BLOKB_E_STATE, "no fence bound (blokb_bind_fence)");
     CK(cudaSetDevice(c->device));
+    // sticky: a fence that timed out (its kernel has finished by now) has left the counters short; further fences cannot be trusted
+    if (*reinterpret_cast<volatile uint32_t*>(c->fenceFlagHost))
+        return fail(BLOKB_E_STATE, "an earlier frame fence timed out (a rank was missing); rebind the fence on every rank (blokb_bind_fence) to resynchronise");
     c->fenceEpoch++;
-    CK(launch_fence(c->fenceLocal, c->fenceMc, c->fenceRanks * c->fenceEpoch, pick(c, stream)));
+    CK(launch_fence(c->fenceLocal, c->fenceMc, c->fenceRanks * c->fenceEpoch, c->fenceFlagDev, pick(c, stream)));
     c->launches++;
     return dispatched(c, pick(c, stream));
 }
@@ -805,6 +822,16 @@ int blokb_trace_primary_packed(blokb_ctx* c, void* stream) {
     CK(launch_primary_packed(c->dw, c->frame, out_for(c, 3, c->buf.hitPacked), pick(c, stream)));
     c->launches++;
     return dispatched(c, pick(c, stream));
+}
+static int scratch_enter(blokb_ctx::ScratchGuard& g, cudaStream_t q) {
+    if (g.used && g.last != q) CK(cudaStreamWaitEvent(q, g.ev, 0));
+    return 0;
+}
+static int scratch_leave(blokb_ctx::ScratchGuard& g, cudaStream_t q) {
+    if (!g.ev) CK(cudaEventCreateWithFlags(&g.ev, cudaEventDisableTiming));
+    CK(cudaEventRecord(g.ev, q));
+    g.last = q; g.used = true;
+    return 0;
 }
 // Scratch of the wavefront schedule for the current launch size (frame size / strip set): grow-only, sized for the configured
 // batch; when the device cannot hold that, the batch is halved until it fits and the smaller batch is remembered.
@@ -842,7 +869,9 @@ int blokb_render(blokb_ctx* c, void* stream) {
     CK(launch_gbuffer(c->dw, c->frame, c->buf.worldPos, c->buf.normalRough, c->buf.albedoMetal, c->buf.motion, pick(c, stream)));
     c->launches++;
     const WaveKey K = make_wave_key(c->dw, c->pathOpt.dirCells, c->pathOpt.originCellShift, c->pathOpt.mortonBitsPerAxis);
+    if (int rc = scratch_enter(c->waveGuard, pick(c, stream))) return rc;
     CK(launch_path_wavefront(c->dw, c->frame, 0u, c->frame.sampleCount, true, own_only(c->buf.color), c->dWave, batch, K, c->pathOpt.refillBelow, st(c), &c->launches, pick(c, stream)));
+    if (int rc = scratch_leave(c->waveGuard, pick(c, stream))) return rc;
     return dispatched(c, pick(c, stream));
 }
 int blokb_trace_path(blokb_ctx* c, uint32_t sampleBegin, uint32_t sampleEnd, void* stream) {
@@ -857,8 +886,10 @@ int blokb_trace_path(blokb_ctx* c, uint32_t sampleBegin, uint32_t sampleEnd, voi
     uint32_t batch = 0;
     if (int rc = wave_ready(c, sampleEnd - sampleBegin, &batch)) return rc;
     const WaveKey K = make_wave_key(c->dw, c->pathOpt.dirCells, c->pathOpt.originCellShift, c->pathOpt.mortonBitsPerAxis);
+    if (int rc = scratch_enter(c->waveGuard, pick(c, stream))) return rc;
     CK(launch_path_wavefront(c->dw, c->frame, sampleBegin, sampleEnd, false, out_for(c, 2, c->buf.accum), c->dWave, batch, K, c->pathOpt.refillBelow, st(c), &c->launches,
                              pick(c, stream)));
+    if (int rc = scratch_leave(c->waveGuard, pick(c, stream))) return rc;
     return dispatched(c, pick(c, stream));
 }
 void blokb_path_options_default(blokb_path_options* o) {
@@ -920,7 +951,9 @@ int blokb_trace_rays_reordered(blokb_ctx* c, const float* dRays, size_t n, int /
         CK(cudaMalloc(&c->dReorder, need));
         c->reorderCap = need;
     }
+    if (int rc = scratch_enter(c->reorderGuard, pick(c, stream))) return rc;
     CK(launch_trace_rays_reordered(c->dw, dRays, n, dOut, c->dReorder, st(c), pick(c, stream)));
+    if (int rc = scratch_leave(c->reorderGuard, pick(c, stream))) return rc;
     c->launches += 3;  // keys, radix sort (counted as one), ordered trace
     return dispatched(c, pick(c, stream));
 }
@@ -1237,14 +1270,17 @@ int blokb_reduce_accum(blokb_ctx* c, int mode, void* stream) {
     if (accumMc) {
         // in-switch sum + resolve in one kernel over peer memory, fenced by two tiny all-reduces: every rank's samples are in
         // its accum before anyone reads through the multicast address, and nobody resets accum while a peer may still read it
+        // refused before anything is enqueued: a rank that bailed out between the collectives would leave its peers waiting in NCCL
+        if (mode == BLOKB_REDUCE_ALL && !colorMc && c->bound[4].on && n % size_t(c->commSize) != 0)
+            return fail(BLOKB_E_UNSUPPORTED, "colour image in caller-owned memory without a multicast address and w*h not divisible by the ranks: bind it with one, or use BLOKB_REDUCE_SLICE");
         if (!c->dFence) { CK(cudaMalloc((void**)&c->dFence, 16)); CK(cudaMemsetAsync(c->dFence, 0, 16, q)); }
         NK(N->AllReduce(c->dFence, c->dFence, 1, kNcclFloat32, kNcclSum, c->comm, q));
         CK(launch_reduce_resolve_mc(c->bound[2].mc, c->buf.color, (mode == BLOKB_REDUCE_ALL && colorMc) ? c->bound[4].mc : nullptr, first, count, q));
         c->launches++;
         if (mode == BLOKB_REDUCE_ALL && !colorMc) {
-            if (c->bound[4].on && n % size_t(c->commSize) != 0)
-                return fail(BLOKB_E_UNSUPPORTED, "colour image in caller-owned memory without a multicast address and w*h not divisible by the ranks: bind it with one, or use BLOKB_REDUCE_SLICE");
-            NK(N->AllGather(c->buf.color + 4 * first, c->buf.color, per * 4, kNcclFloat32, c->comm, q));
+            // in-place all-gather: the send pointer is recvbuf + rank * per even where `first` was clamped to n (tiny frames with many
+            // ranks) — the context's own colour image carries the slack, and a caller-owned one got here only with n % G == 0
+            NK(N->AllGather(c->buf.color + 4 * size_t(c->commRank) * per, c->buf.color, per * 4, kNcclFloat32, c->comm, q));
         }
         NK(N->AllReduce(c->dFence, c->dFence, 1, kNcclFloat32, kNcclSum, c->comm, q));
         return dispatched(c, q);

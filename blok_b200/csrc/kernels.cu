@@ -578,8 +578,12 @@ __global__ void __launch_bounds__(256) k_reduce_resolve_mc(const float4* __restr
 // Cross-GPU frame fence (blokb_frame_fence): one multimem.red adds this rank's arrival to the counter on every GPU at once; the
 // release makes everything this GPU did before (earlier kernels of the stream: their multicast stores) visible first; the acquire
 // loop on the LOCAL copy ends when all ranks of this round have arrived. Bounded: ~1 s of polling, then the error word is set.
-__global__ void k_fence(uint32_t* local, void* mc, uint32_t target) {
+// A fence that timed out leaves the counters short for good, so later fences on this rank could only time out again: once the error
+// word is set they still add their arrival (peers keep counting this rank) but return without polling. `hostFlag` is a word of mapped
+// page-locked host memory the C-ABI layer reads before it enqueues the next fence (may be null).
+__global__ void k_fence(uint32_t* local, void* mc, uint32_t target, uint32_t* hostFlag) {
     asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" ::"l"(mc), "r"(1u) : "memory");
+    if (*reinterpret_cast<volatile uint32_t*>(local + 1)) return;
     uint32_t v = 0;
     for (uint32_t spin = 0; spin < 8000000u; spin++) {   // ~1 s: a poll is a system-scope load plus a 64 ns sleep
         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(local) : "memory");
@@ -587,6 +591,7 @@ __global__ void k_fence(uint32_t* local, void* mc, uint32_t target) {
         __nanosleep(64);
     }
     local[1] = 1u;
+    if (hostFlag) { *reinterpret_cast<volatile uint32_t*>(hostFlag) = 1u; __threadfence_system(); }
 }
 
 // ---- launchers ------------------------------------------------------------------------------------
@@ -831,8 +836,12 @@ cudaError_t launch_path_wavefront(const DeviceWorld& W, const FrameDev& F, uint3
         else k_path_front<false><<<g, kPixThreads, pix_stack_bytes(W), st>>>(W, F, s0, nS, B, K, nullptr);
         size_t tb = 0;
         cub::DoubleBuffer<uint32_t> dk(k0, k1), dv(i0, i1);
-        cub::DeviceRadixSort::SortPairs(nullptr, tb, dk, dv, (int64_t)n, 0, int(K.bits));
-        cudaError_t e = cub::DeviceRadixSort::SortPairs(tmp, tb, dk, dv, (int64_t)n, 0, int(K.bits), st);
+        // one bit more than the key uses: live keys are < 2^K.bits, the dead key is 0xFFFFFFFF, so bit K.bits puts every dead slot strictly
+        // behind every live one. With K.bits alone a live key whose bits are all ones (reachable with 1, 2 or 4 direction cells per axis)
+        // ties with the dead key and the stable sort interleaves them — the refill variant stops at the first dead key it meets.
+        const int sortBits = int(std::min(K.bits + 1u, 32u));
+        cub::DeviceRadixSort::SortPairs(nullptr, tb, dk, dv, (int64_t)n, 0, sortBits);
+        cudaError_t e = cub::DeviceRadixSort::SortPairs(tmp, tb, dk, dv, (int64_t)n, 0, sortBits, st);
         if (e != cudaSuccess) return e;
         const unsigned blocks = (unsigned)((n + 255) / 256);
         if (refillBelow > 0) {
@@ -875,8 +884,8 @@ cudaError_t launch_reduce_resolve_mc(const void* accumMc, float* color, void* co
                                                                     static_cast<float4*>(colorMc), first, n);
     return cudaGetLastError();
 }
-cudaError_t launch_fence(uint32_t* local, void* multicast, uint32_t target, cudaStream_t st) {
-    k_fence<<<1, 1, 0, st>>>(local, multicast, target);
+cudaError_t launch_fence(uint32_t* local, void* multicast, uint32_t target, uint32_t* hostFlag, cudaStream_t st) {
+    k_fence<<<1, 1, 0, st>>>(local, multicast, target, hostFlag);
     return cudaGetLastError();
 }
 cudaError_t launch_resolve(const float* accum, float* color, size_t n, cudaStream_t st) {

@@ -72,8 +72,9 @@ cudaError_t launch_path_wavefront(const DeviceWorld& W, const FrameDev& F, uint3
 cudaError_t launch_gbuffer(const DeviceWorld& W, const FrameDev& F, float* worldPos, uint16_t* normalRough, uint8_t* albedoMetal, uint16_t* motion,
                            cudaStream_t st);
 cudaError_t launch_resolve(const float* accum, float* color, size_t n, cudaStream_t st);
-// one-thread cross-GPU barrier over a multicast word (blokb_frame_fence): word[0] counts arrivals, word[1] = 1 after a timeout
-cudaError_t launch_fence(uint32_t* local, void* multicast, uint32_t target, cudaStream_t st);
+// one-thread cross-GPU barrier over a multicast word (blokb_frame_fence): word[0] counts arrivals, word[1] = 1 after a timeout, which
+// is also written to *hostFlag (device address of a mapped page-locked host word; may be null)
+cudaError_t launch_fence(uint32_t* local, void* multicast, uint32_t target, uint32_t* hostFlag, cudaStream_t st);
 // colour[first, first + n) = resolve(sum over GPUs of accum) through an NVLink multicast address of the accumulation images
 cudaError_t launch_reduce_resolve_mc(const void* accumMc, float* color, void* colorMc, size_t first, size_t n, cudaStream_t st);
 }  // namespace blokb

@@ -22,6 +22,9 @@
  * for every dispatch this context enqueued on any caller stream; so "dispatch on my stream, then blokb_readback" returns that
  * dispatch's output without a synchronisation by the caller, and blokb_sync waits for caller-stream dispatches too. The
  * reverse direction needs nothing: those calls have completed when they return.
+ * Dispatches that share a context's scratch — blokb_render / blokb_trace_path in wavefront mode (one slot-array scratch per context) and
+ * blokb_trace_rays_reordered (one sort scratch) — are serialised by the library when they arrive on different streams: the later one
+ * waits (cudaStreamWaitEvent) for the earlier one's last kernel. They never run concurrently; use two contexts for that.
  * There is no CPU fallback: without a CUDA device every compute entry point fails with BLOKB_E_CUDA.
  */
 #ifndef BLOKB200_H
@@ -289,8 +292,10 @@ int blokb_ipc_export(blokb_ctx* ctx, int image, void* handle64);
  * enqueues a one-thread kernel that adds 1 to the word on EVERY GPU with one multimem.red.release and then waits (ld.acquire, bounded)
  * until its own copy has counted all ranks of this round: when it completes on a rank, every rank's earlier work on its fence stream
  * — the multicast stores of its traversal kernel — has been performed. Every rank must enqueue the same number of fences. A fence that
- * times out (a rank missing for ~1 s) sets the second word to 1 and the next blokb_frame_fence / blokb_fence_status returns
- * BLOKB_E_STATE. nranks == 0 unbinds. */
+ * times out (a rank missing for ~1 s) sets the second word to 1; from then on blokb_fence_status returns BLOKB_E_STATE, fence kernels
+ * already enqueued pass without waiting, and every blokb_frame_fence called after the timed-out kernel has finished returns
+ * BLOKB_E_STATE without enqueuing anything — until the fence is bound again (all ranks, fresh zero-filled words), which restarts the
+ * count. nranks == 0 unbinds. */
 int blokb_bind_fence(blokb_ctx* ctx, void* local, void* multicast, uint32_t nranks);
 int blokb_frame_fence(blokb_ctx* ctx, void* stream);
 int blokb_fence_status(blokb_ctx* ctx);

@@ -128,6 +128,20 @@ def _worker(rank, world, port, out_dir):
             status.append(r.readback(IMG_HIT_PACKED).tobytes() == full_pk.tobytes())
             r.frame_fence()      # nobody clears the image before everyone has read it
         r.fence_status()
+        # a rank that fences alone times out after ~1 s; from then on its fences are refused (not silently passed) until the fence is
+        # bound again on every rank, which restarts the count
+        if rank == 0:
+            r.frame_fence(); r.sync()
+            for call in (r.frame_fence, r.fence_status):
+                try:
+                    call(); status.append(False)
+                except blok_b200.BlokbError:
+                    status.append(True)
+        dist.barrier()
+        sharding.disconnect_fence(r, fk)
+        fk = sharding.connect_fence(r)          # fresh words, epoch 0: its own three proving rounds must pass again
+        status.append(fk is not None)
+        r.frame_fence(); r.fence_status()
         sharding.disconnect_fence(r, fk)
     if keep is None:
         sharding.disconnect_peers(r, (IMG_HIT_PACKED,))

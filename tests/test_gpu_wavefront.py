@@ -52,6 +52,13 @@ def test_wavefront_accum_and_colour_equal_fused_bitwise(renderer_factory, name):
         o = r.set_path_options(mode=PATH_WAVEFRONT, batch_samples=4, refill_below=rb)
         assert o["refillBelow"] == rb
         assert _accum(r, 0, 6).tobytes() == want_acc.tobytes(), f"accum differs with lanes refilled below {rb}"
+    # ... also when a live ray's key is all ones (few direction cells, origin in the top Morton cell): dead slots must still sort last,
+    # or the refilling warps, which stop at the first dead key, leave live rays untraced
+    for dc, sh, mb in ((1, 6, 1), (2, 5, 2), (4, 4, 3), (2, 6, 1), (4, 6, 1)):
+        for rb in (1, 32):
+            r.set_path_options(mode=PATH_WAVEFRONT, batch_samples=4, dir_cells=dc, origin_cell_shift=sh, morton_bits_per_axis=mb, refill_below=rb)
+            assert _accum(r, 0, 6).tobytes() == want_acc.tobytes(), f"accum differs with key ({dc}, {sh}, {mb}), lanes refilled below {rb}"
+    r.set_path_options(mode=PATH_WAVEFRONT, batch_samples=4, dir_cells=8, origin_cell_shift=6, morton_bits_per_axis=2, refill_below=32)
     r.stats_enable(True)
     r.reset_accum(); r.trace_path(0, 6); r.sync()
     refill_counts = r.stats_read()
