@@ -505,6 +505,11 @@ def measure_tiled(env, ctx, steps, warmup, packed=False):
     r.set_frame(ctx["ubo"])
     r.trace_primary(packed=packed)
     full = r.readback(img).copy()
+    # this rank's share of the frame with NO exchange bound (stores stay local): what the traversal of 1/G of the strips costs by itself —
+    # launch + wave tail; trace_only_ms below minus this is what the peer stores add, ms minus trace_only_ms what the fence adds
+    r.set_strips(*sharding.strip_set(rank, G))
+    _, share_ms, _ = env.timed(lambda: r.trace_primary(packed=packed, stream=env.sp), max(5, steps // 4), 2, flush=False)
+    r.set_strips(0, 1)
     keep = sharding.connect_multicast(r, (img,))
     if keep is None:
         sharding.connect_peers(r, (img,))
@@ -547,7 +552,7 @@ def measure_tiled(env, ctx, steps, warmup, packed=False):
     recb = 8 if packed else 16
     return dict(ms=ms_max, ms_rank=ms, launches=launches, clocks=clocks, ms_warm_l2=warm, identical=bool(same), trace_only_ms=trace_ms,
                 exchange="NVLink multicast (multimem.st into symmetric memory)" if keep is not None else "P2P stores into IPC-mapped peer images",
-                fence=fence_name, assembled_sample=assembled,
+                fence=fence_name, assembled_sample=assembled, share_only_ms=share_ms,
                 nvlink_ingress_bytes_per_gpu=int(W * H * recb * (G - 1) / G), record_bytes=recb)
 
 
@@ -1060,7 +1065,10 @@ def main():
         par = (f"ONE frame tiled over {G} GPUs in interleaved 8-row strips, scene replicated; exchange fused into the traversal kernel: {m['exchange']} "
                f"of the full 16-byte hit records (blokb_hit, as at N = 1), every rank ends with the whole image; frame fence = {m['fence']}")
         tiled_sample = m.pop("assembled_sample")
-        extras["tiled"] = {"identical_on_every_rank": m["identical"], "trace_only_ms": m["trace_only_ms"], "exchange": m["exchange"], "fence": m["fence"],
+        extras["tiled"] = {"identical_on_every_rank": m["identical"], "share_only_ms": m["share_only_ms"], "trace_only_ms": m["trace_only_ms"],
+                           "split": "share_only_ms = this rank's strips, stores local (launch + wave tail of 1/G of the frame); trace_only_ms = the same with the "
+                                    "peer / multicast stores; ms_per_step = that plus the frame fence. All max over ranks, warm L2",
+                           "exchange": m["exchange"], "fence": m["fence"],
                            "nvlink_ingress_bytes_per_gpu": m["nvlink_ingress_bytes_per_gpu"], "record_bytes": m["record_bytes"]}
         from blok_b200 import sharding
         r.set_strips(*sharding.strip_set(rank, G))
@@ -1151,7 +1159,8 @@ def main():
                 out = {"what": "the same tiled frame with 8-byte packed records (node | face << 29, t; material and gl_PrimitiveID re-derived on the host by "
                                "blokb_unpack_hits) through the exchange: half the NVLink bytes. N = 1 denominator: extras.packed_records of the N = 1 line",
                        "ms_per_frame": mp["ms"], "value": W * H / mp["ms"] / 1e3, "unit": "Mrays/s", "identical_on_every_rank": mp["identical"],
-                       "trace_only_ms": mp["trace_only_ms"], "exchange": mp["exchange"], "nvlink_ingress_bytes_per_gpu": mp["nvlink_ingress_bytes_per_gpu"]}
+                       "share_only_ms": mp["share_only_ms"], "trace_only_ms": mp["trace_only_ms"], "exchange": mp["exchange"],
+                       "nvlink_ingress_bytes_per_gpu": mp["nvlink_ingress_bytes_per_gpu"]}
                 if rank == 0 and res is not None:
                     out["parity"] = hit_parity(ctx["world"].unpack_hits(mp["assembled_sample"]), res)
                 return out

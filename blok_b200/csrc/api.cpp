@@ -94,6 +94,8 @@ struct blokb_ctx {
     // dWave / dReorder are one scratch per context: a dispatch that uses one on another stream than the previous user first waits for that
     // user's event, so path dispatches of one context on different streams serialise on the scratch instead of racing on it
     struct ScratchGuard { cudaStream_t last = nullptr; cudaEvent_t ev = nullptr; bool used = false; } waveGuard, reorderGuard;
+    // Persisting-L2 window over nodes[]: set-aside bytes granted by the device, 0 = off
+    size_t l2SetAside = 0, l2MaxWindow = 0;
     uint32_t* fenceFlagHost = nullptr;   // mapped page-locked word: set by a fence kernel that timed out, read before the next fence is enqueued
     uint32_t* fenceFlagDev = nullptr;
     // editable worlds (blokb_upload_dense keeps the voxel list on the device; blokb_update_dense replaces dirty chunks in it)
@@ -123,6 +125,7 @@ struct blokb_ctx {
     std::vector<Foreign> foreign;
 };
 
+static void l2_window(blokb_ctx* c, cudaStream_t q);
 // After a dispatch on stream q: remember it if q is not the context's own stream.
 static int dispatched(blokb_ctx* c, cudaStream_t q) {
     if (q == c->stream) return 0;
@@ -132,7 +135,26 @@ static int dispatched(blokb_ctx* c, cudaStream_t q) {
     CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     c->foreign.push_back({q, ev, true});
     CK(cudaEventRecord(ev, q));
+    l2_window(c, q);   // from this stream's next dispatch on
     return 0;
+}
+// Access-policy window of a stream: loads from the node pool are marked persisting in L2 (up to the set-aside the device granted),
+// so the gigabytes of slot arrays a wavefront batch streams past do not evict the tree the walks descend through. Best effort.
+static void l2_window(blokb_ctx* c, cudaStream_t q) {
+    if (!c->l2SetAside || !c->haveWorld || !c->dw.nodes) return;
+    cudaStreamAttrValue v{};
+    const size_t bytes = std::min(size_t(c->dw.nNodes) * sizeof(Node), c->l2MaxWindow);
+    v.accessPolicyWindow.base_ptr = const_cast<uint4*>(c->dw.nodes);
+    v.accessPolicyWindow.num_bytes = bytes;
+    v.accessPolicyWindow.hitRatio = bytes ? std::min(1.0f, float(double(c->l2SetAside) / double(bytes))) : 0.0f;
+    v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    cudaStreamSetAttribute(q, cudaStreamAttributeAccessPolicyWindow, &v);
+    cudaGetLastError();
+}
+static void world_windows(blokb_ctx* c) {   // a new world: the windows of every stream this context knows move to the new node pool
+    l2_window(c, c->stream);
+    for (auto& f : c->foreign) l2_window(c, f.s);
 }
 // Before work on the context's own stream that reads or replaces what dispatches wrote.
 static int join_dispatches(blokb_ctx* c) {
@@ -238,6 +260,19 @@ int blokb_create(int device, blokb_ctx** out) {
     e = cudaMalloc(&c->dStats, 4 * sizeof(unsigned long long));
     if (e != cudaSuccess) { cudaStreamDestroy(c->stream); delete c; return fail(BLOKB_E_CUDA, cudaGetErrorString(e)); }
     cudaMemset(c->dStats, 0, 4 * sizeof(unsigned long long));
+    // BLOKB_L2_PERSIST_MB=<n>: ask the device to set n MB of L2 aside for persisting lines (device-wide limit; clamped to what it allows)
+    // and mark the node pool persisting on every stream this context dispatches on. Off unless set: measured, DESIGN.md 5.
+    if (const char* env = std::getenv("BLOKB_L2_PERSIST_MB")) {
+        const long mb = std::strtol(env, nullptr, 10);
+        int maxPersist = 0, maxWindow = 0;
+        cudaDeviceGetAttribute(&maxPersist, cudaDevAttrMaxPersistingL2CacheSize, device);
+        cudaDeviceGetAttribute(&maxWindow, cudaDevAttrMaxAccessPolicyWindowSize, device);
+        if (mb > 0 && maxPersist > 0 && maxWindow > 0) {
+            const size_t want = std::min(size_t(mb) << 20, size_t(maxPersist));
+            if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) { c->l2SetAside = want; c->l2MaxWindow = size_t(maxWindow); }
+            cudaGetLastError();
+        }
+    }
     *out = c;
     return 0;
 }
@@ -312,6 +347,7 @@ int blokb_upload_world(blokb_ctx* c, const blokb_svo_node* nodes, size_t nNodes,
     s.uploadMs = std::chrono::duration<float, std::milli>(t2 - t1).count();
     c->nNodesCompact = hw.nodes.size(); d.nNodes = uint32_t(hw.nodes.size()); c->nBlocks = hw.blockFirstLeaf.size(); c->nVoxels = hw.voxels;
     c->haveWorld = true;
+    world_windows(c);
     return 0;
 }
 
@@ -437,6 +473,7 @@ static int finish_device_build(blokb_ctx* c, build::DeviceBuild& B, const blokb_
     s.uploadMs = std::chrono::duration<float, std::milli>(t2 - t1).count();
     c->nBlocks = B.nBlocks; c->nVoxels = B.nVox;
     c->haveWorld = true;
+    world_windows(c);
     return 0;
 }
 
@@ -632,6 +669,7 @@ int blokb_world_load(blokb_ctx* c, const char* path) {
     c->stats.buildMs = std::chrono::duration<float, std::milli>(t1 - t0).count();   // file read + checksum
     c->stats.uploadMs = std::chrono::duration<float, std::milli>(t2 - t1).count();
     c->haveWorld = true;
+    world_windows(c);
     return 0;
 }
 
