@@ -43,9 +43,6 @@ namespace blokb {
 #ifndef BLOKB_SHADOW_MINBLOCKS
 #define BLOKB_SHADOW_MINBLOCKS 8     // k_primary<true>
 #endif
-#ifndef BLOKB_PRIMARY_LOCATE
-#define BLOKB_PRIMARY_LOCATE 0   // measurement variant: camera rays find their start voxel like secondary rays (Walker::init, locate)
-#endif
 #ifndef BLOKB_BOUNCE_MINBLOCKS
 #define BLOKB_BOUNCE_MINBLOCKS 1
 #endif
@@ -204,26 +201,14 @@ __global__ void __launch_bounds__(kPixThreads, kShadow ? BLOKB_SHADOW_MINBLOCKS 
                                                  const __grid_constant__ PeerOut out, const __grid_constant__ PeerOut shadow,
                                                  unsigned long long* stats) {
     uint32_t px, py;
-#if BLOKB_STAGE_TOP
-    // measurement variant: the first BLOKB_STAGE_TOP nodes (root + the levels under it, breadth first) staged behind the stacks
-    uint4* topNodes = g_stackMem + W.levels * kPixThreads;
-    const uint32_t nTop = min(uint32_t(BLOKB_STAGE_TOP), W.nNodes);
-    for (uint32_t i = threadIdx.x; i < nTop; i += kPixThreads) topNodes[i] = __ldg(W.nodes + i);
-    __syncthreads();
-#endif
     if (!thread_pixel(F, px, py)) return;
     const F3 d = primary_dir(F, float(px) + 0.5f, float(py) + 0.5f);
     uint32_t steps = 0;
     NodeStack stk = thread_stack();
-#if BLOKB_STAGE_TOP
-    stk.top = uint32_t(__cvta_generic_to_shared(topNodes));
-    stk.nTop = nTop;
-#endif
     const size_t pi = size_t(py) * F.width + px;
     if constexpr (!kShadow) {   // the camera ray alone: no loop state to carry (45 registers = 11 blocks per SM)
         HitRec h;
-        const bool hit = traverse<kStats>(W, stk, F.camPos[0], F.camPos[1], F.camPos[2], d.x, d.y, d.z, 0.001f, 10000.0f, h, steps,
-                                          /*locate=*/BLOKB_PRIMARY_LOCATE != 0);
+        const bool hit = traverse<kStats>(W, stk, F.camPos[0], F.camPos[1], F.camPos[2], d.x, d.y, d.z, 0.001f, 10000.0f, h, steps, /*locate=*/false);
         store_hit_all(out, pi, hit, h);
         if (kStats) atomicAdd(stats, (unsigned long long)steps);
         return;
@@ -238,7 +223,7 @@ __global__ void __launch_bounds__(kPixThreads, kShadow ? BLOKB_SHADOW_MINBLOCKS 
 #pragma unroll 1
     for (;;) {
         HitRec h;
-        const bool hit = traverse<kStats>(W, stk, o.x, o.y, o.z, dir.x, dir.y, dir.z, 0.001f, tmax, h, steps, /*locate=*/BLOKB_PRIMARY_LOCATE || pass > 0, kShadow ? &resume : nullptr);
+        const bool hit = traverse<kStats>(W, stk, o.x, o.y, o.z, dir.x, dir.y, dir.z, 0.001f, tmax, h, steps, /*locate=*/pass > 0, kShadow ? &resume : nullptr);
         if (pass == 1) { sv = hit ? 2 : 1; break; }
         store_hit_all(out, pi, hit, h);
         if (!kShadow || !hit) break;
@@ -600,7 +585,7 @@ static inline dim3 pixel_grid(const FrameDev& F) {
     const uint32_t mine = F.stripFirst < strips ? (strips - F.stripFirst + F.stripStride - 1) / F.stripStride : 0;
     return dim3((F.width + kBlockW - 1) / kBlockW, mine * kBlocksPerStrip);
 }
-static inline size_t pix_stack_bytes(const DeviceWorld& W) { return size_t(W.levels) * kPixThreads * sizeof(uint4) + size_t(BLOKB_STAGE_TOP) * sizeof(uint4); }
+static inline size_t pix_stack_bytes(const DeviceWorld& W) { return size_t(W.levels) * kPixThreads * sizeof(uint4); }
 static inline size_t stack_bytes(const DeviceWorld& W) { return size_t(W.levels) * 256 * sizeof(uint4); }  // <= 48 KB (kMaxLevels = 12)
 
 cudaError_t launch_trace_rays(const DeviceWorld& W, const float* rays, size_t n, blokb_hit* out, unsigned long long* stats, cudaStream_t st) {

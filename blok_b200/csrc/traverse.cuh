@@ -22,17 +22,8 @@
 #ifndef BLOKB_SELECT_V2
 #define BLOKB_SELECT_V2 1
 #endif
-// Measurement variants of the two north-star items that did NOT pay on this kernel (DESIGN.md 5 has the numbers):
-//   BLOKB_STAGE_TOP = K   the first K nodes of the breadth-first array (root and the levels under it) are copied to shared memory
-//                         once per block and descents into them read LDS instead of LDG;
-//   BLOKB_WARP_SHARE = 1  a descent in which every active lane of the warp wants the same child is served by ONE load of the
-//                         leader lane and four shuffles (ballot / shuffle node sharing).
-#ifndef BLOKB_STAGE_TOP
-#define BLOKB_STAGE_TOP 0
-#endif
-#ifndef BLOKB_WARP_SHARE
-#define BLOKB_WARP_SHARE 0
-#endif
+// Two north-star items were built as variants of descend(), measured slower on c3 and removed in round 3 (numbers and the code's
+// shape are in DESIGN.md 5; the code is in history at 312663e): top levels staged in shared memory, ballot / shuffle node sharing.
 #ifndef BLOKB_OCC_V2
 #define BLOKB_OCC_V2 1
 #endif
@@ -122,12 +113,6 @@ struct NodeStack {
 #if defined(__CUDACC__)
     uint32_t base;    // shared-window byte address of this thread's level-1 entry
     uint32_t stride;  // bytes between consecutive levels
-    uint32_t top = 0, nTop = 0;  // BLOKB_STAGE_TOP: shared-window address / count of the staged first nodes (0 = none staged)
-    BLOKB_HD uint4 staged(uint32_t idx) const {
-        uint4 v;
-        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(top + idx * 16u) : "memory");
-        return v;
-    }
     BLOKB_HD void put(int level, uint32_t mlo, uint32_t mhi, uint32_t b, uint32_t aux) const {
         asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(base + uint32_t(level - 1) * stride), "r"(mlo), "r"(mhi), "r"(b), "r"(aux) : "memory");
     }
@@ -139,8 +124,6 @@ struct NodeStack {
 #else
     uint4* base;
     uint32_t stride;  // entries between consecutive levels
-    uint32_t top = 0, nTop = 0;
-    BLOKB_HD uint4 staged(uint32_t) const { return make_uint4(0, 0, 0, 0); }
     BLOKB_HD void put(int level, uint32_t mlo, uint32_t mhi, uint32_t b, uint32_t aux) const { base[(level - 1) * stride] = make_uint4(mlo, mhi, b, aux); }
     BLOKB_HD uint4 get(int level) const { return base[(level - 1) * stride]; }
 #endif
@@ -283,26 +266,7 @@ struct Walker {
     BLOKB_HD void descend(const DeviceWorld& W, const NodeStack& stk) {
         stk.put((sh >> 1) + 1, mlo, mhi, base, aux);
         const uint32_t idx = base + child_rank(abit());
-        uint4 c;
-#if BLOKB_WARP_SHARE && defined(__CUDA_ARCH__)
-        {
-            const unsigned act = __activemask();
-            const int leader = __ffs(act) - 1;
-            const uint32_t lidx = __shfl_sync(act, idx, leader);
-            if (__all_sync(act, idx == lidx)) {
-                if (int(threadIdx.x & 31u) == leader) c = __ldg(W.nodes + idx);
-                c.x = __shfl_sync(act, c.x, leader); c.y = __shfl_sync(act, c.y, leader);
-                c.z = __shfl_sync(act, c.z, leader); c.w = __shfl_sync(act, c.w, leader);
-            } else {
-                c = __ldg(W.nodes + idx);
-            }
-        }
-#elif BLOKB_STAGE_TOP && defined(__CUDA_ARCH__)
-        if (idx < stk.nTop) c = stk.staged(idx);
-        else c = __ldg(W.nodes + idx);
-#else
-        c = __ldg(W.nodes + idx);
-#endif
+        const uint4 c = __ldg(W.nodes + idx);
         mlo = c.x; mhi = c.y; base = c.z; aux = c.w;
         sh -= 2;
         fs *= 0.25f;
