@@ -64,13 +64,7 @@ __device__ __forceinline__ bool thread_pixel(const FrameDev& F, uint32_t& px, ui
 #endif
     constexpr uint32_t TW = 1u << BLOKB_TILE_W_LOG2, TH = 32u / TW, tilesX = kBlockW / TW;
     px = blockIdx.x * kBlockW + (warp % tilesX) * TW + (lane & (TW - 1u));
-    // BLOKB_STRIP_ORDER (measurement knob): 0 = strips in image order, top rows first; 1 = bottom rows first (the blocks dispatched last
-    // then are the sky rows, which finish quickly: a shorter tail when the costly rows are in the lower half of the frame)
-#ifndef BLOKB_STRIP_ORDER
-#define BLOKB_STRIP_ORDER 0
-#endif
-    const uint32_t by = BLOKB_STRIP_ORDER ? gridDim.y - 1u - blockIdx.y : blockIdx.y;
-    py = (F.stripFirst + (by / kBlocksPerStrip) * F.stripStride) * 8u + (by % kBlocksPerStrip) * BLOKB_BLOCK_ROWS +
+    py = (F.stripFirst + (blockIdx.y / kBlocksPerStrip) * F.stripStride) * 8u + (blockIdx.y % kBlocksPerStrip) * BLOKB_BLOCK_ROWS +
          (warp / tilesX) * TH + (lane >> BLOKB_TILE_W_LOG2);
     return px < F.width && py < F.height;
 }
